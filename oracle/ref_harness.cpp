@@ -1,0 +1,463 @@
+// ref_harness.cpp — TEST INFRASTRUCTURE: headless driver around the UNMODIFIED reference
+// (ciechowoj/master @ /root/reference).  Built only by oracle/build_ref.sh into
+// oracle/_ref/ref_harness; never linked into the product library.
+//
+// It links the reference's own translation units (Technique, PT, BPT, UPG, Scene, BSDF,
+// AreaLights, Cameras, loader, ... — see build_ref.sh) against the vendored Embree 2.12 and
+// Assimp fork, compiled with -fno-access-control so the harness can own the pixel loop and
+// read private state, and with -include rng_shim.h so every (pixel, sample) has its own
+// random stream.  All light transport, intersection and sampling code executed below is the
+// reference's.
+//
+// Sub-commands:
+//   dump   <scene.blend> <out.b2s> [--light px py pz  dx dy dz  ux uy uz  er eg eb  sx sy]
+//   rays   <scene> <mode 0|1|2> <rays.bin> <hits.bin>       (B2ptRay in, B2ptHit out)
+//   render <scene> key=value ...   per-(pixel,sample) streams, 1 thread, golden outputs
+//   time   <scene> key=value ...   the reference's own Technique::render loop, N threads
+// <scene> is a .blend (needs the reference's models/) or a .b2s written by `dump`.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <map>
+#include <string>
+#include <thread>
+
+#include <xmmintrin.h>
+#include <pmmintrin.h>
+
+#include <BPT.hpp>
+#include <PT.hpp>
+#include <UPG.hpp>
+#include <Scene.hpp>
+#include <loader.hpp>
+
+#include "../include/b2pt.h"
+
+using namespace haste;
+using std::string;
+
+// ---------------------------------------------------------------- .b2s format
+// magic "B2SCENE1"; u32 counts[8] = {cameras, meshes, vertices, indices, materials, lights, 0, 0};
+// cameras * CameraRec; u32 mesh_material_id[M]; u32 vertex_offset[M+1]; u32 index_offset[M+1];
+// f32 vertices[3V]; f32 tangents[9V]; i32 indices[I]; B2ptMaterial[materials]; B2ptLight[lights].
+struct CameraRec {
+  float position[3], direction[3], up[3];
+  float fovx, near, far, focal;
+  float world_to_view[9], view_to_world[9];
+};
+
+static void put(std::ofstream& f, const void* p, size_t n) { f.write((const char*)p, n); }
+static void get(std::ifstream& f, void* p, size_t n) {
+  f.read((char*)p, n);
+  if (!f) throw std::runtime_error("short read in .b2s");
+}
+
+static B2ptMaterial flatten_bsdf(const BSDF* bsdf) {
+  B2ptMaterial m;
+  std::memset(&m, 0, sizeof m);
+  m.light_id = UINT32_MAX;
+  if (auto b = dynamic_cast<const DiffuseBSDF*>(bsdf)) {
+    m.type = B2PT_BSDF_DIFFUSE;
+    std::memcpy(m.diffuse, &b->_diffuse, 12);
+  } else if (auto b = dynamic_cast<const PhongBSDF*>(bsdf)) {
+    m.type = B2PT_BSDF_PHONG;
+    std::memcpy(m.diffuse, &b->_diffuse, 12);
+    std::memcpy(m.specular, &b->_specular, 12);
+    m.power = b->_power;
+    m.diffuse_probability = b->_diffuse_probability;
+  } else if (dynamic_cast<const ReflectionBSDF*>(bsdf)) {
+    m.type = B2PT_BSDF_REFLECTION;
+  } else if (auto b = dynamic_cast<const TransmissionBSDF*>(bsdf)) {
+    m.type = B2PT_BSDF_TRANSMISSION;
+    m.ext_over_int_ior = b->externalOverInternalIOR;
+    m.internal_ior = b->internalIOR;
+  } else if (auto b = dynamic_cast<const LightBSDF*>(bsdf)) {
+    m.type = B2PT_BSDF_LIGHT;
+    m.light_id = b->_light_id;
+    std::memcpy(m.sphere, &b->_sphere, 16);
+  } else if (auto b = dynamic_cast<const sun_light_bsdf*>(bsdf)) {
+    m.type = B2PT_BSDF_SUN;
+    m.light_id = b->_light_id;
+    std::memcpy(m.sphere, &b->_sphere, 16);
+  } else if (dynamic_cast<const CameraBSDF*>(bsdf)) {
+    m.type = B2PT_BSDF_CAMERA;
+  } else {
+    throw std::runtime_error("unknown BSDF class");
+  }
+  return m;
+}
+
+static void write_b2s(const Scene& scene, const string& path) {
+  std::ofstream f(path, std::ios::binary);
+  uint32_t nv = 0, ni = 0;
+  for (auto& m : scene.meshes) { nv += m.vertices.size(); ni += m.indices.size(); }
+  const Cameras& cams = scene.cameras();
+  uint32_t counts[8] = {uint32_t(cams.numCameras()), uint32_t(scene.meshes.size()), nv, ni,
+                        uint32_t(scene.materials.bsdfs.size()), uint32_t(scene.lights.num_lights()), 0, 0};
+  put(f, "B2SCENE1", 8);
+  put(f, counts, sizeof counts);
+  for (size_t i = 0; i < cams.numCameras(); ++i) {
+    CameraRec c;
+    std::memcpy(c.position, &cams._descs[i].position, 12);
+    std::memcpy(c.direction, &cams._descs[i].direction, 12);
+    std::memcpy(c.up, &cams._descs[i].up, 12);
+    c.fovx = cams._descs[i].fovx; c.near = cams._descs[i].near; c.far = cams._descs[i].far;
+    c.focal = cams._focals[i];
+    mat3 w2v = cams.world_to_view_mat3(i), v2w = cams.view_to_world_mat3(i);
+    std::memcpy(c.world_to_view, &w2v, 36);
+    std::memcpy(c.view_to_world, &v2w, 36);
+    put(f, &c, sizeof c);
+  }
+  std::vector<uint32_t> mat, voff(1, 0), ioff(1, 0);
+  for (auto& m : scene.meshes) {
+    mat.push_back(m.material_id);
+    voff.push_back(voff.back() + m.vertices.size());
+    ioff.push_back(ioff.back() + m.indices.size());
+  }
+  put(f, mat.data(), mat.size() * 4);
+  put(f, voff.data(), voff.size() * 4);
+  put(f, ioff.data(), ioff.size() * 4);
+  for (auto& m : scene.meshes) put(f, m.vertices.data(), m.vertices.size() * 12);
+  for (auto& m : scene.meshes) put(f, m.tangents.data(), m.tangents.size() * 36);
+  for (auto& m : scene.meshes) put(f, m.indices.data(), m.indices.size() * 4);
+  for (auto& b : scene.materials.bsdfs) { B2ptMaterial m = flatten_bsdf(b.get()); put(f, &m, sizeof m); }
+  for (size_t i = 0; i < scene.lights.num_lights(); ++i) {
+    const AreaLight& l = scene.lights.light(i);
+    B2ptLight r;
+    std::memcpy(r.position, &l.position, 12);
+    std::memcpy(r.tangent, &l.tangent, 36);
+    std::memcpy(r.size, &l.size, 8);
+    std::memcpy(r.exitance, &l.exitance, 12);
+    r.diffuse = l.diffuse; r.material_id = l.material_id; r.weight = scene.lights._weights[i];
+    put(f, &r, sizeof r);
+  }
+}
+
+// Rebuilds a haste::Scene from a .b2s through the reference's own constructors
+// (Cameras::addCameraFovX, AreaLights::addLight, the BSDF classes, Scene::Scene).
+static shared<Scene> read_b2s(const string& path) {
+  std::ifstream f(path, std::ios::binary);
+  if (!f) throw std::runtime_error("cannot open " + path);
+  char magic[8]; get(f, magic, 8);
+  if (std::memcmp(magic, "B2SCENE1", 8)) throw std::runtime_error("not a .b2s file");
+  uint32_t counts[8]; get(f, counts, sizeof counts);
+  uint32_t nc = counts[0], nm = counts[1], nv = counts[2], ni = counts[3], nmat = counts[4], nl = counts[5];
+  Cameras cameras;
+  for (uint32_t i = 0; i < nc; ++i) {
+    CameraRec c; get(f, &c, sizeof c);
+    cameras.addCameraFovX("camera" + std::to_string(i), *(vec3*)c.position, *(vec3*)c.direction,
+                          *(vec3*)c.up, c.fovx, c.near, c.far);
+  }
+  std::vector<uint32_t> mat(nm), voff(nm + 1), ioff(nm + 1);
+  get(f, mat.data(), nm * 4); get(f, voff.data(), (nm + 1) * 4); get(f, ioff.data(), (nm + 1) * 4);
+  std::vector<vec3> verts(nv); std::vector<mat3> tans(nv); std::vector<int> idx(ni);
+  get(f, verts.data(), size_t(nv) * 12); get(f, tans.data(), size_t(nv) * 36); get(f, idx.data(), size_t(ni) * 4);
+  std::vector<B2ptMaterial> mats(nmat); get(f, mats.data(), nmat * sizeof(B2ptMaterial));
+  std::vector<B2ptLight> lights(nl); get(f, lights.data(), nl * sizeof(B2ptLight));
+
+  vector<Mesh> meshes(nm);
+  for (uint32_t m = 0; m < nm; ++m) {
+    meshes[m].name = "mesh" + std::to_string(m);
+    meshes[m].material_id = mat[m];
+    meshes[m].vertices.assign(verts.begin() + voff[m], verts.begin() + voff[m + 1]);
+    meshes[m].tangents.assign(tans.begin() + voff[m], tans.begin() + voff[m + 1]);
+    meshes[m].indices.assign(idx.begin() + ioff[m], idx.begin() + ioff[m + 1]);
+  }
+  AreaLights area;
+  for (uint32_t i = 0; i < nl; ++i) {
+    const B2ptLight& l = lights[i];
+    const mat3& t = *(const mat3*)l.tangent;
+    area.addLight("light" + std::to_string(i), l.material_id >> 2, *(const vec3*)l.position, t[1], t[2],
+                  *(const vec3*)l.exitance, *(const vec2*)l.size, l.diffuse != 0.0f);
+    // addLight recomputes tangent[0] = normalize(cross(up, direction)); keep the stored frame bit-exact
+    area._lights[i].tangent = t;
+  }
+  Materials materials;
+  for (uint32_t i = 0; i < nmat; ++i) {
+    const B2ptMaterial& m = mats[i];
+    materials.names.push_back("material" + std::to_string(i));
+    bounding_sphere_t sphere = {vec3(m.sphere[0], m.sphere[1], m.sphere[2]), m.sphere[3]};
+    switch (m.type) {
+      case B2PT_BSDF_CAMERA: materials.bsdfs.push_back(unique<BSDF>(new CameraBSDF())); break;
+      case B2PT_BSDF_DIFFUSE: materials.bsdfs.push_back(unique<BSDF>(new DiffuseBSDF(*(const vec3*)m.diffuse))); break;
+      case B2PT_BSDF_PHONG:
+        materials.bsdfs.push_back(unique<BSDF>(new PhongBSDF(*(const vec3*)m.diffuse, *(const vec3*)m.specular, m.power)));
+        break;
+      case B2PT_BSDF_REFLECTION: materials.bsdfs.push_back(unique<BSDF>(new ReflectionBSDF())); break;
+      case B2PT_BSDF_TRANSMISSION: {
+        auto t = new TransmissionBSDF(m.internal_ior, 1.0f);
+        t->externalOverInternalIOR = m.ext_over_int_ior;
+        materials.bsdfs.push_back(unique<BSDF>(t));
+        break;
+      }
+      case B2PT_BSDF_LIGHT: materials.bsdfs.push_back(unique<BSDF>(new LightBSDF(sphere, m.light_id))); break;
+      case B2PT_BSDF_SUN: materials.bsdfs.push_back(unique<BSDF>(new sun_light_bsdf(sphere, m.light_id))); break;
+      default: throw std::runtime_error("bad material type in .b2s");
+    }
+  }
+  return make_shared<Scene>(std::move(cameras), std::move(materials), std::move(meshes), std::move(area));
+}
+
+static bool ends_with(const string& s, const string& e) {
+  return s.size() >= e.size() && s.compare(s.size() - e.size(), e.size(), e) == 0;
+}
+
+static shared<Scene> open_scene(const string& path) {
+  shared<Scene> scene = ends_with(path, ".b2s") ? read_b2s(path) : loadScene(path);
+  static RTCDevice device = rtcNewDevice(NULL);
+  scene->buildAccelStructs(device);
+  return scene;
+}
+
+// Adds one area light the way loader.cpp:434-456 does (for scenes that ship without one).
+static shared<Scene> with_extra_light(const string& path, const float* a) {
+  // load_lights needs mutable pieces, so redo loadScene's steps around the extra light
+  shared<Scene> base = loadScene(path);
+  Cameras cameras = base->_cameras;
+  vector<Mesh> meshes = base->meshes;
+  Materials materials;
+  for (size_t i = 0; i < base->materials.bsdfs.size(); ++i) materials.names.push_back(base->materials.names[i]);
+  // BSDFs are move-only; steal them from the (about to be dropped) base scene
+  Materials& src = const_cast<Materials&>(base->materials);
+  for (auto& b : src.bsdfs) materials.bsdfs.push_back(std::move(b));
+  AreaLights lights = base->lights;
+  bounding_sphere_t sphere = {vec3(0.0f), 0.0f};
+  {  // compute_bounding_sphere (loader.cpp:408-432) over the meshes present before the light
+    size_t n = 0;
+    for (auto& m : meshes) { for (auto& v : m.vertices) sphere.center += v; n += m.vertices.size(); }
+    sphere.center /= float(n);
+    for (auto& m : meshes) for (auto& v : m.vertices) sphere.radius = glm::max(sphere.radius, glm::distance2(sphere.center, v));
+    sphere.radius = glm::sqrt(sphere.radius);
+  }
+  size_t i = lights.num_lights();
+  lights.addLight("extra_light", materials.names.size(), vec3(a[0], a[1], a[2]), normalize(vec3(a[3], a[4], a[5])),
+                  normalize(vec3(a[6], a[7], a[8])), vec3(a[9], a[10], a[11]), vec2(a[12], a[13]), true);
+  meshes.push_back(lights.light(i).create_mesh(materials.names.size(), "extra_light"));
+  materials.names.push_back("extra_light");
+  materials.bsdfs.push_back(lights.light(i).create_bsdf(sphere, i, true));
+  return make_shared<Scene>(std::move(cameras), std::move(materials), std::move(meshes), std::move(lights));
+}
+
+// ---------------------------------------------------------------- helpers
+typedef std::map<string, string> Args;
+static Args parse_kv(int argc, char** argv, int first) {
+  Args a;
+  for (int i = first; i < argc; ++i) {
+    string s = argv[i];
+    size_t e = s.find('=');
+    if (e == string::npos) throw std::runtime_error("expected key=value, got " + s);
+    a[s.substr(0, e)] = s.substr(e + 1);
+  }
+  return a;
+}
+static string arg(const Args& a, const string& k, const string& d) { auto i = a.find(k); return i == a.end() ? d : i->second; }
+static double argd(const Args& a, const string& k, double d) { auto i = a.find(k); return i == a.end() ? d : atof(i->second.c_str()); }
+
+static shared<Technique> make(const shared<Scene>& scene, const Args& a, size_t threads) {
+  string t = arg(a, "technique", "PT");
+  float lights = argd(a, "lights", 1.0), roulette = argd(a, "roulette", 0.9), beta = argd(a, "beta", t == "PT" ? 1.0 : 2.0);
+  size_t W = argd(a, "width", 512), H = argd(a, "height", 512);
+  if (t == "PT") {
+    size_t max_path = argd(a, "max_path", 0);
+    return make_shared<PathTracing>(scene, lights, roulette, beta, max_path ? max_path : size_t(PTRDIFF_MAX), threads);
+  }
+  if (t == "BPT") {
+    if (beta == 0.0f) return make_shared<BPT0>(scene, lights, roulette, beta, threads);
+    if (beta == 1.0f) return make_shared<BPT1>(scene, lights, roulette, beta, threads);
+    if (beta == 2.0f) return make_shared<BPT2>(scene, lights, roulette, beta, threads);
+    return make_shared<BPTb>(scene, lights, roulette, beta, threads);
+  }
+  if (t == "VCM" || t == "UPG") {
+    bool unbiased = t == "UPG";
+    bool vc = argd(a, "enable_vc", 1) != 0, vm = argd(a, "enable_vm", 1) != 0, from_light = argd(a, "from_light", 1) != 0;
+    size_t photons = argd(a, "num_photons", 0);
+    if (!photons) photons = W * H;  // Options.cpp:914-916
+    float radius = argd(a, "radius", 0.01), alpha = argd(a, "alpha", 0.75);
+    if (beta == 0.0f) return make_shared<UPG0>(scene, unbiased, vc, vm, from_light, lights, roulette, photons, radius, alpha, beta, threads);
+    if (beta == 1.0f) return make_shared<UPG1>(scene, unbiased, vc, vm, from_light, lights, roulette, photons, radius, alpha, beta, threads);
+    if (beta == 2.0f) return make_shared<UPG2>(scene, unbiased, vc, vm, from_light, lights, roulette, photons, radius, alpha, beta, threads);
+    return make_shared<UPGb>(scene, unbiased, vc, vm, from_light, lights, roulette, photons, radius, alpha, beta, threads);
+  }
+  throw std::runtime_error("unknown technique " + t);
+}
+
+static render_context_t make_context(const Scene& scene, size_t cameraId, size_t W, size_t H, random_generator_t& gen) {
+  // Technique::render, Technique.cpp:37-45
+  auto& cameras = scene.cameras();
+  render_context_t context;
+  context.view_to_world_mat3 = cameras.view_to_world_mat3(cameraId);
+  context.world_to_view_mat3 = cameras.world_to_view_mat3(cameraId);
+  context.camera_position = cameras.position(cameraId);
+  context.resolution = vec2(W, H);
+  context.resolution_y_inv = 1.0f / context.resolution.y;
+  context.focal_length_y = cameras.focal_length_y(cameraId, context.resolution.x / context.resolution.y);
+  context.focal_factor_y = context.focal_length_y * context.focal_length_y * 0.25f;
+  context.generator = &gen;
+  context.camera_id = int32_t(cameraId);
+  return context;
+}
+
+template <class T> static void write_vec(const string& path, const std::vector<T>& v) {
+  std::ofstream f(path, std::ios::binary);
+  f.write((const char*)v.data(), v.size() * sizeof(T));
+}
+
+// ---------------------------------------------------------------- sub-commands
+static int cmd_dump(int argc, char** argv) {
+  if (argc < 4) return 2;
+  shared<Scene> scene;
+  if (argc >= 5 && string(argv[4]) == "--light") {
+    if (argc < 19) throw std::runtime_error("--light needs 14 numbers");
+    float a[14];
+    for (int i = 0; i < 14; ++i) a[i] = atof(argv[5 + i]);
+    scene = with_extra_light(argv[2], a);
+  } else {
+    scene = ends_with(argv[2], ".b2s") ? read_b2s(argv[2]) : loadScene(argv[2]);
+  }
+  write_b2s(*scene, argv[3]);
+  size_t tris = 0;
+  for (auto& m : scene->meshes) tris += m.indices.size() / 3;
+  printf("{\"meshes\": %zu, \"triangles\": %zu, \"materials\": %zu, \"lights\": %zu, \"cameras\": %zu}\n",
+         scene->meshes.size(), tris, scene->materials.bsdfs.size(), scene->lights.num_lights(), scene->cameras().numCameras());
+  return 0;
+}
+
+static int cmd_rays(int argc, char** argv) {
+  if (argc < 6) return 2;
+  shared<Scene> scene = open_scene(argv[2]);
+  int mode = atoi(argv[3]);
+  std::ifstream f(argv[4], std::ios::binary | std::ios::ate);
+  size_t n = size_t(f.tellg()) / sizeof(B2ptRay);
+  f.seekg(0);
+  std::vector<B2ptRay> rays(n);
+  f.read((char*)rays.data(), n * sizeof(B2ptRay));
+  std::vector<B2ptHit> hits(n);
+  auto t0 = std::chrono::steady_clock::now();
+  for (size_t i = 0; i < n; ++i) {
+    // the RTCRay set-up of Scene.cpp:162-171 / 186-196 / 209-219
+    RTCRay r;
+    std::memcpy(r.org, rays[i].org, 12);
+    std::memcpy(r.dir, rays[i].dir, 12);
+    r.tnear = rays[i].tnear; r.tfar = rays[i].tfar;
+    r.geomID = r.primID = r.instID = RTC_INVALID_GEOMETRY_ID;
+    r.mask = mode == B2PT_TRACE_CLOSEST_ALL ? 0xFFFFFFFFu : 1u << uint32_t(entity_type::mesh);
+    r.time = 0.f;
+    if (mode == B2PT_TRACE_OCCLUDED_MESH) rtcOccluded(scene->rtcScene, r); else rtcIntersect(scene->rtcScene, r);
+    hits[i].t = r.tfar; hits[i].u = r.u; hits[i].v = r.v; hits[i].geom = r.geomID; hits[i].prim = r.primID;
+  }
+  double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  write_vec(argv[5], hits);
+  printf("{\"rays\": %zu, \"seconds\": %.6f, \"mrays_per_s\": %.4f}\n", n, s, n / s * 1e-6);
+  return 0;
+}
+
+// Per-(pixel, sample) streams.  The harness owns only the pixel loop and the seeding; the jitter
+// draws, _traceEye, the splats and the commit are the reference's (Technique.cpp:194-352).
+static int cmd_render(int argc, char** argv) {
+  if (argc < 3) return 2;
+  Args a = parse_kv(argc, argv, 3);
+  shared<Scene> scene = open_scene(argv[2]);
+  size_t W = argd(a, "width", 512), H = argd(a, "height", 512), cam = argd(a, "camera", 0);
+  uint32_t seed = argd(a, "seed", 1234), first = argd(a, "first_sample", 0), stride = argd(a, "sample_stride", 1);
+  size_t spp = argd(a, "num_samples", 1);
+  bool per_path = argd(a, "per_path", 1) != 0;
+  string out = arg(a, "out", "/tmp/ref_render");
+  shared<Technique> tech = make(scene, a, 1);
+  Technique& T = *tech;
+
+  std::vector<dvec4> accum(W * H, dvec4(0.0));
+  subimage_view_t view(accum.data(), W, H);
+  random_generator_t gen(size_t(0));
+  render_context_t context = make_context(*scene, cam, W, H, gen);
+  std::vector<float> path_radiance;  // [spp][H][W][3], eye image only
+  std::vector<double> light_image(W * H * 3, 0.0);  // sum over passes of the light-tracing splats
+  size_t rays0 = scene->numNormalRays(), shadow0 = scene->numShadowRays();
+  auto t0 = std::chrono::steady_clock::now();
+  for (size_t s = 0; s < spp; ++s) {
+    uint32_t sample = first + uint32_t(s) * stride;
+    T._adjust_helper_image(view);
+    // domain 1 = whole-pass preprocessing (UPG/VCM photon scatter, UPG.cpp:177-186)
+    gen.seed(std::b2pt_counter_engine::stream_key(seed, 1, 0, sample));
+    T._preprocess(gen, double(T._statistics.num_samples));
+    for (size_t y = 0; y < H; ++y) {
+      for (size_t x = 0; x < W; ++x) {
+        gen.seed(std::b2pt_counter_engine::stream_key(seed, 0, uint32_t(y * W + x), sample));
+        subimage_view_t px = view;
+        px._xOffset = x; px._xWindow = 1; px._yOffset = y; px._yWindow = 1;
+        T._for_each_ray(px, context);
+        if (per_path) {
+          const dvec3& e = T._eye_image[y * W + x];
+          path_radiance.push_back(float(e.x)); path_radiance.push_back(float(e.y)); path_radiance.push_back(float(e.z));
+        }
+      }
+    }
+    for (size_t i = 0; i < W * H; ++i) {
+      light_image[i * 3 + 0] += T._light_image[i].x; light_image[i * 3 + 1] += T._light_image[i].y; light_image[i * 3 + 2] += T._light_image[i].z;
+    }
+    T._commit_images(view);
+    ++T._statistics.num_samples;
+  }
+  double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  write_vec(out + ".accum.f64", accum);
+  write_vec(out + ".light.f64", light_image);
+  if (per_path) write_vec(out + ".paths.f32", path_radiance);
+  size_t nb = scene->numNormalRays() - rays0, ns = scene->numShadowRays() - shadow0;
+  printf("{\"width\": %zu, \"height\": %zu, \"num_samples\": %zu, \"seconds\": %.6f, \"basic_rays\": %zu, \"shadow_rays\": %zu, "
+         "\"focal_length_y\": %.9g, \"msamples_per_s\": %.6f, \"mrays_per_s\": %.6f}\n",
+         W, H, spp, sec, nb, ns, context.focal_length_y, W * H * spp / sec * 1e-6, (nb + ns) / sec * 1e-6);
+  return 0;
+}
+
+// The reference's own pass loop (Application::render -> Technique::render), as it ships:
+// num_threads pool threads, 32x32 tiles, per-tile std::random_device seeding when threads > 1.
+static int cmd_time(int argc, char** argv) {
+  if (argc < 3) return 2;
+  Args a = parse_kv(argc, argv, 3);
+  shared<Scene> scene = open_scene(argv[2]);
+  size_t W = argd(a, "width", 512), H = argd(a, "height", 512), cam = argd(a, "camera", 0);
+  size_t threads = argd(a, "threads", 0);
+  if (!threads) threads = std::thread::hardware_concurrency();
+  size_t spp = argd(a, "num_samples", 1), warm = argd(a, "warmup", 0);
+  double budget = argd(a, "seconds", 0.0);  // stop after this much time (0 = run all num_samples)
+  shared<Technique> tech = make(scene, a, threads);
+  std::vector<dvec4> accum(W * H, dvec4(0.0));
+  subimage_view_t view(accum.data(), W, H);
+  random_generator_t gen(size_t(argd(a, "seed", 1234)));
+  for (size_t s = 0; s < warm; ++s) tech->render(view, gen, cam, {}, {});
+  size_t rays0 = scene->numNormalRays(), shadow0 = scene->numShadowRays();
+  auto t0 = std::chrono::steady_clock::now();
+  size_t done = 0;
+  double sec = 0;
+  for (size_t s = 0; s < spp; ++s) {
+    tech->render(view, gen, cam, {}, {});
+    ++done;
+    sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (budget > 0 && sec >= budget) break;
+  }
+  size_t nb = scene->numNormalRays() - rays0, ns = scene->numShadowRays() - shadow0;
+  string out = arg(a, "out", "");
+  if (!out.empty()) write_vec(out + ".accum.f64", accum);
+  printf("{\"width\": %zu, \"height\": %zu, \"num_samples\": %zu, \"threads\": %zu, \"seconds\": %.6f, \"basic_rays\": %zu, "
+         "\"shadow_rays\": %zu, \"msamples_per_s\": %.6f, \"mrays_per_s\": %.6f}\n",
+         W, H, done, threads, sec, nb, ns, W * H * done / sec * 1e-6, (nb + ns) / sec * 1e-6);
+  return 0;
+}
+
+int main(int argc, char** argv) {
+  _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);          // main.cpp:70-71
+  _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
+  try {
+    string c = argc > 1 ? argv[1] : "";
+    if (c == "dump") return cmd_dump(argc, argv);
+    if (c == "rays") return cmd_rays(argc, argv);
+    if (c == "render") return cmd_render(argc, argv);
+    if (c == "time") return cmd_time(argc, argv);
+    fprintf(stderr, "usage: ref_harness dump|rays|render|time ...\n");
+    return 2;
+  } catch (const std::exception& e) {
+    fprintf(stderr, "ref_harness: %s\n", e.what());
+    return 1;
+  }
+}
