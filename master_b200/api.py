@@ -1,0 +1,227 @@
+"""ctypes binding of include/b2pt.h (master_b200/libb2pt.so).
+
+Thin by design: structures mirror the header field for field, functions raise B2ptError carrying
+b2pt_last_error() the way the reference throws std::runtime_error / std::logic_error
+(runtime_assert.cpp:7-11).  There is no CPU fallback: if the library is missing or no CUDA device
+is visible, the compute calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .scene import FlatScene, LIGHT_DTYPE, MATERIAL_DTYPE
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb2pt.so")
+
+TRACE_CLOSEST_ALL, TRACE_CLOSEST_MESH, TRACE_OCCLUDED_MESH = 0, 1, 2
+TECHNIQUE_PT, TECHNIQUE_BPT, TECHNIQUE_VCM, TECHNIQUE_UPG = 0, 1, 2, 3
+TECHNIQUES = {"PT": TECHNIQUE_PT, "BPT": TECHNIQUE_BPT, "VCM": TECHNIQUE_VCM, "UPG": TECHNIQUE_UPG}
+
+RAY_DTYPE = np.dtype([("org", "<f4", 3), ("tnear", "<f4"), ("dir", "<f4", 3), ("tfar", "<f4")])
+HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("geom", "<u4"), ("prim", "<u4")])
+assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 20
+
+
+class B2ptError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("b2pt error %d: %s" % (code, message))
+        self.code = code
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [
+        ("num_meshes", C.c_uint32),
+        ("mesh_material_id", C.c_void_p),
+        ("mesh_vertex_offset", C.c_void_p),
+        ("mesh_index_offset", C.c_void_p),
+        ("vertices", C.c_void_p),
+        ("tangents", C.c_void_p),
+        ("indices", C.c_void_p),
+        ("num_materials", C.c_uint32),
+        ("materials", C.c_void_p),
+        ("num_lights", C.c_uint32),
+        ("lights", C.c_void_p),
+    ]
+
+
+class Camera(C.Structure):
+    _fields_ = [
+        ("view_to_world", C.c_float * 9),
+        ("world_to_view", C.c_float * 9),
+        ("position", C.c_float * 3),
+        ("focal_length_y", C.c_float),
+    ]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [
+        ("technique", C.c_uint32),
+        ("beta", C.c_float),
+        ("roulette", C.c_float),
+        ("lights", C.c_float),
+        ("max_path", C.c_uint32),
+        ("radius", C.c_float),
+        ("alpha", C.c_float),
+        ("num_photons", C.c_uint32),
+        ("unbiased", C.c_uint32),
+        ("enable_vc", C.c_uint32),
+        ("enable_vm", C.c_uint32),
+        ("from_light", C.c_uint32),
+        ("width", C.c_uint32),
+        ("height", C.c_uint32),
+        ("camera", Camera),
+        ("seed", C.c_uint32),
+        ("first_sample", C.c_uint32),
+        ("sample_stride", C.c_uint32),
+        ("num_samples", C.c_uint32),
+        ("sky_horizon", C.c_float * 3),
+        ("sky_zenith", C.c_float * 3),
+        ("max_subpath", C.c_uint32),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("num_samples", C.c_uint64),
+        ("num_basic_rays", C.c_uint64),
+        ("num_shadow_rays", C.c_uint64),
+        ("num_paths", C.c_uint64),
+        ("numeric_errors", C.c_uint64),
+        ("capacity_events", C.c_uint64),
+        ("kernel_launches", C.c_uint64),
+        ("device_ms", C.c_float),
+        ("trace_ms", C.c_float),
+    ]
+
+    def as_dict(self):
+        return {name: getattr(self, name) for name, _ in self._fields_}
+
+
+# every symbol include/b2pt.h declares; tests/test_abi.py checks the list against the header
+EXPORTS = [
+    "b2pt_last_error", "b2pt_abi_version", "b2pt_device_count", "b2pt_scene_create", "b2pt_scene_destroy",
+    "b2pt_scene_info", "b2pt_trace", "b2pt_trace_device", "b2pt_render", "b2pt_render_host", "b2pt_grid_build",
+    "b2pt_grid_destroy", "b2pt_grid_query",
+]
+
+_lib = None
+
+
+def load_library():
+    """dlopen libb2pt.so; raises if it has not been built (python -m master_b200.build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B2ptError(-1, "%s not found: build it with `python -m master_b200.build` "
+                            "(there is no CPU fallback)" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    lib.b2pt_last_error.restype = C.c_char_p
+    lib.b2pt_abi_version.restype = C.c_int
+    lib.b2pt_device_count.restype = C.c_int
+    lib.b2pt_scene_create.argtypes = [C.POINTER(SceneDesc), C.POINTER(C.c_void_p)]
+    lib.b2pt_scene_destroy.argtypes = [C.c_void_p]
+    lib.b2pt_scene_destroy.restype = None
+    lib.b2pt_scene_info.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                    C.POINTER(C.c_float)]
+    lib.b2pt_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint, C.c_void_p]
+    lib.b2pt_trace_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint, C.c_void_p, C.c_void_p]
+    lib.b2pt_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(Stats)]
+    lib.b2pt_render_host.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.POINTER(Stats)]
+    lib.b2pt_grid_build.argtypes = [C.c_void_p, C.c_size_t, C.c_float, C.POINTER(C.c_void_p)]
+    lib.b2pt_grid_destroy.argtypes = [C.c_void_p]
+    lib.b2pt_grid_destroy.restype = None
+    lib.b2pt_grid_query.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p, C.c_void_p]
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        raise B2ptError(rc, load_library().b2pt_last_error().decode("utf-8", "replace"))
+
+
+def device_count():
+    return load_library().b2pt_device_count()
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class DeviceSceneHandle:
+    """Owns a b2pt_scene_t: the scene uploaded to HBM with its BVH built there."""
+
+    def __init__(self, flat: FlatScene):
+        lib = load_library()
+        self.flat = flat
+        d = SceneDesc()
+        d.num_meshes = flat.num_meshes
+        d.mesh_material_id = _ptr(flat.mesh_material_id)
+        d.mesh_vertex_offset = _ptr(flat.mesh_vertex_offset)
+        d.mesh_index_offset = _ptr(flat.mesh_index_offset)
+        d.vertices = _ptr(flat.vertices)
+        d.tangents = _ptr(flat.tangents)
+        d.indices = _ptr(flat.indices)
+        d.num_materials = len(flat.materials)
+        d.materials = _ptr(flat.materials)
+        d.num_lights = len(flat.lights)
+        d.lights = _ptr(flat.lights) if len(flat.lights) else None
+        assert flat.materials.dtype == MATERIAL_DTYPE and flat.lights.dtype == LIGHT_DTYPE
+        h = C.c_void_p()
+        check(lib.b2pt_scene_create(C.byref(d), C.byref(h)))
+        self.handle = h
+
+    def info(self):
+        nt, nn, nb, ms = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_float()
+        check(load_library().b2pt_scene_info(self.handle, C.byref(nt), C.byref(nn), C.byref(nb), C.byref(ms)))
+        return {"triangles": nt.value, "nodes": nn.value, "bvh_bytes": nb.value, "build_ms": ms.value}
+
+    def trace(self, rays, mode):
+        """rays: RAY_DTYPE array in host memory -> HIT_DTYPE array (copies both ways)."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.empty(len(rays), dtype=HIT_DTYPE)
+        check(load_library().b2pt_trace(self.handle, _ptr(rays), len(rays), mode, _ptr(hits)))
+        return hits
+
+    def trace_device(self, rays_ptr, n, mode, hits_ptr, stream=0):
+        check(load_library().b2pt_trace_device(self.handle, C.c_void_p(rays_ptr), n, mode, C.c_void_p(hits_ptr),
+                                               C.c_void_p(stream)))
+
+    def close(self):
+        if getattr(self, "handle", None):
+            load_library().b2pt_scene_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def make_params(flat, technique="PT", width=512, height=512, camera=0, beta=None, roulette=0.9, lights=1.0, max_path=0,
+                radius=0.01, alpha=0.75, num_photons=0, enable_vc=True, enable_vm=True, from_light=True, seed=1234,
+                first_sample=0, sample_stride=1, num_samples=1, sky_horizon=(0, 0, 0), sky_zenith=(0, 0, 0),
+                max_subpath=0, focal_length_y=None):
+    """Options (Options.hpp:19-71) + render_context_t (Technique.hpp:14-27) -> B2ptRenderParams."""
+    p = RenderParams()
+    p.technique = TECHNIQUES[technique]
+    p.beta = (1.0 if technique == "PT" else 2.0) if beta is None else beta
+    p.roulette, p.lights, p.max_path = roulette, lights, max_path
+    p.radius, p.alpha, p.num_photons = radius, alpha, num_photons
+    p.unbiased = 1 if technique == "UPG" else 0
+    p.enable_vc, p.enable_vm, p.from_light = int(enable_vc), int(enable_vm), int(from_light)
+    p.width, p.height = width, height
+    ctx = flat.camera_context(camera, width, height)
+    p.camera.view_to_world[:] = ctx["view_to_world"].tolist()
+    p.camera.world_to_view[:] = ctx["world_to_view"].tolist()
+    p.camera.position[:] = ctx["position"].tolist()
+    p.camera.focal_length_y = float(ctx["focal_length_y"] if focal_length_y is None else focal_length_y)
+    p.seed, p.first_sample, p.sample_stride, p.num_samples = seed, first_sample, sample_stride, num_samples
+    p.sky_horizon[:] = list(sky_horizon)
+    p.sky_zenith[:] = list(sky_zenith)
+    p.max_subpath = max_subpath
+    return p

@@ -1,0 +1,99 @@
+// common.cuh — small float3/mat3 algebra, error handling and launch helpers shared by the kernels.
+//
+// The library is compiled with --fmad=false -ftz=true: the reference runs on x86-64 SSE without
+// FMA contraction and with FTZ/DAZ on (main.cpp:70-71), and the per-path 1e-4 parity level of
+// north_star is easiest to hold when a*b+c rounds twice here as it does there.  Where fusing is
+// wanted for speed and does not touch parity (BVH slab tests) the code calls __fmaf_rn itself.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+#include "../../include/b2pt.h"
+
+namespace b2pt {
+
+// ---------------------------------------------------------------- errors
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define B2_CUDA(call)                                                        \
+  do {                                                                       \
+    cudaError_t e__ = (call);                                                \
+    if (e__ != cudaSuccess) return b2pt::cuda_fail(e__, #call, __FILE__, __LINE__); \
+  } while (0)
+
+#define B2_CHECK(cond, code, msg)                  \
+  do {                                             \
+    if (!(cond)) { b2pt::set_error(msg); return (code); } \
+  } while (0)
+
+constexpr int kNumSMs = 148;  // B200; grids are sized in multiples of this
+
+// ---------------------------------------------------------------- float3 algebra (glm semantics)
+struct mat3 { float3 c0, c1, c2; };  // column-major like glm::mat3
+
+#define B2_HD __host__ __device__ __forceinline__
+
+B2_HD float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
+B2_HD float3 f3(float s) { return make_float3(s, s, s); }
+B2_HD float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+B2_HD float3 operator-(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+B2_HD float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
+B2_HD float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
+B2_HD float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
+B2_HD float3 operator*(float s, float3 a) { return f3(s * a.x, s * a.y, s * a.z); }
+B2_HD float3 operator/(float3 a, float s) { return f3(a.x / s, a.y / s, a.z / s); }
+B2_HD float3 operator/(float3 a, float3 b) { return f3(a.x / b.x, a.y / b.y, a.z / b.z); }
+B2_HD float3& operator+=(float3& a, float3 b) { a = a + b; return a; }
+B2_HD float3& operator*=(float3& a, float s) { a = a * s; return a; }
+B2_HD float3& operator/=(float3& a, float s) { a = a / s; return a; }
+// glm::dot for vec3 (compute_dot<vec3>): tmp = a*b; tmp.x + tmp.y + tmp.z
+B2_HD float dot(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+B2_HD float3 cross(float3 a, float3 b) {
+  return f3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
+}
+B2_HD float l1norm(float3 a) { return fabsf(a.x) + fabsf(a.y) + fabsf(a.z); }
+B2_HD float length2(float3 a) { return dot(a, a); }
+B2_HD float distance2(float3 a, float3 b) { return length2(b - a); }
+
+// glm::inversesqrt is 1/sqrt(x); glm::normalize is v * inversesqrt(dot(v, v))
+__device__ __forceinline__ float3 normalize(float3 a) { return a * (1.0f / sqrtf(dot(a, a))); }
+__device__ __forceinline__ float length(float3 a) { return sqrtf(dot(a, a)); }
+
+// glm mat3 * vec3 :  m[0]*v.x + m[1]*v.y + m[2]*v.z  (component-wise, left to right)
+B2_HD float3 mul(const mat3& m, float3 v) {
+  return f3(m.c0.x * v.x + m.c1.x * v.y + m.c2.x * v.z,
+            m.c0.y * v.x + m.c1.y * v.y + m.c2.y * v.z,
+            m.c0.z * v.x + m.c1.z * v.y + m.c2.z * v.z);
+}
+// glm vec3 * mat3 :  (dot(v, m[0]), dot(v, m[1]), dot(v, m[2]))
+B2_HD float3 mul(float3 v, const mat3& m) { return f3(dot(v, m.c0), dot(v, m.c1), dot(v, m.c2)); }
+
+B2_HD float sign_glm(float x) { return float((0.0f < x) - (x < 0.0f)); }  // glm::sign
+B2_HD float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+constexpr float kPi = 3.14159265358979323846264338327950288f;
+constexpr float kOneOverPi = 0.318309886183790671537767526745028724f;
+constexpr float kHalfPi = 1.57079632679489661923132169163975144f;
+constexpr float kTwoPi = 6.28318530717958647692528676655900576f;
+constexpr float kFltEpsilon = 1.192092896e-07f;
+constexpr float kFltMin = 1.175494351e-38f;
+
+// ---------------------------------------------------------------- warp-aggregated queue append
+// One atomic per warp: ballot the lanes that append, lane 0 of the group reserves, everyone
+// computes its slot from the prefix popcount.  Returns the slot (valid only where `want`).
+__device__ __forceinline__ unsigned warp_append(unsigned* counter, bool want) {
+  unsigned active = __activemask();
+  unsigned mask = __ballot_sync(active, want);
+  if (!want) return 0xFFFFFFFFu;
+  unsigned lane = threadIdx.x & 31u;
+  int leader = __ffs(mask) - 1;
+  unsigned base = 0;
+  if (lane == unsigned(leader)) base = atomicAdd(counter, unsigned(__popc(mask)));
+  base = __shfl_sync(mask, base, leader);
+  return base + __popc(mask & ((1u << lane) - 1u));
+}
+
+}  // namespace b2pt

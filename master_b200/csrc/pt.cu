@@ -1,0 +1,347 @@
+// pt.cu — wavefront path tracer: PathTracing::_traceEye / _connect (PT.cpp:15-120) re-thought as
+// three persistent-style stages over a pool of path slots in HBM.
+//
+// The reference runs one pixel-sample to completion on one thread.  Here the unit of work is one
+// STAGE over every path in flight:
+//
+//   logic   (pt_logic_kernel)   per slot: consume the closest hit found by the previous trace —
+//                               light hit: MIS-weighted emission, continue through the light;
+//                               surface hit: throughput update, Russian roulette, next-event
+//                               estimation set-up (shadow ray + unoccluded contribution into the
+//                               shadow queue), BSDF sample (extension ray into the trace queue);
+//                               finished paths commit to the film and the slot immediately
+//                               REGENERATES a new (pixel, sample) so the pool stays full.
+//   trace   (pt_trace_kernel)   closest hit for every slot in the trace queue (mask: meshes + lights)
+//   shadow  (pt_shadow_kernel)  any-hit for every entry of the shadow queue (mask: meshes only);
+//                               visible -> add the contribution to the path's radiance.
+//
+// Queues hold slot indices, compacted with one warp-aggregated atomic per warp.  Path state is SoA
+// float4 streams so each stage moves 128-bit words.  Every path owns a counter-based RNG stream
+// (rng.cuh), so the draw order inside a path is the reference's whatever the stage interleaving.
+#include "render_common.cuh"
+
+namespace b2pt {
+
+enum { kFree = 0, kPrimary = 1, kBounce = 2, kAwaitShadow = 3 };
+enum { kQueueTrace = 0, kQueueShadow = 1 };
+enum { kShadowCommit = 1u };
+
+struct PtPool {
+  uint32_t* state;
+  float4* ray_o;    // extension ray origin (already offset), w unused
+  float4* ray_d;    // extension ray direction, w unused
+  float4* hit;      // t, u, v, bits(triangle)
+  float4* prev;     // previous vertex position xyz, w = bsdf.density of the sampled direction
+  float4* thr;      // throughput of the NEXT vertex (already * f * cos / pdf), w = bits(finite | path_size << 1)
+  float4* rad;      // radiance gathered so far
+  uint2* rng;       // key, counter
+  unsigned long long* work;
+  uint32_t* trace_q;
+  float4* shadow_q; // 3 float4 per entry: (org, bits slot) (dir, bits flags) (contribution, 0)
+};
+
+__device__ __forceinline__ unsigned long long warp_grab_work(unsigned long long* counter, bool want) {
+  const unsigned active = __activemask();
+  const unsigned mask = __ballot_sync(active, want);
+  if (!want) return ~0ull;
+  const unsigned lane = threadIdx.x & 31u;
+  const int leader = __ffs(mask) - 1;
+  unsigned long long base = 0;
+  if (lane == unsigned(leader)) base = atomicAdd(counter, (unsigned long long)__popc(mask));
+  base = __shfl_sync(mask, base, leader);
+  return base + __popc(mask & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool pool, int parity) {
+  const DeviceScene& sc = cfg.scene;
+  RenderCounters* cnt = cfg.counters;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    cnt->queue_count[parity ^ 1][kQueueTrace] = 0;
+    cnt->queue_count[parity ^ 1][kQueueShadow] = 0;
+  }
+  const float beta = cfg.params.beta;
+  const uint32_t max_path = cfg.params.max_path ? cfg.params.max_path : 0xFFFFFFFFu;
+  // pool_size is a multiple of the block size, so every lane of a warp runs the same trip count
+  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < cfg.pool_size; slot += gridDim.x * blockDim.x) {
+    uint32_t st = pool.state[slot];
+    bool want_trace = false, want_shadow = false;
+    float3 sh_o = f3(0.f), sh_d = f3(0.f), sh_c = f3(0.f);
+    uint32_t sh_flags = 0;
+    float3 O = f3(0.f), D = f3(0.f), rad = f3(0.f);
+    Rng rng; rng.key = 0; rng.ctr = 0;
+    unsigned long long work = 0;
+
+    if (st == kPrimary || st == kBounce) {
+      const float4 ro = pool.ray_o[slot], rd = pool.ray_d[slot], hv = pool.hit[slot], rv = pool.rad[slot];
+      const uint2 rs = pool.rng[slot];
+      O = f3(ro.x, ro.y, ro.z); D = f3(rd.x, rd.y, rd.z); rad = f3(rv.x, rv.y, rv.z);
+      rng.key = rs.x; rng.ctr = rs.y;
+      work = pool.work[slot];
+      const uint32_t tri = __float_as_uint(hv.w);
+      bool terminated = false, proceed = false;
+      float3 thr = f3(1.0f);
+      uint32_t path_size = 2;
+      Surface s;
+      if (tri == kInvalid) {
+        terminated = true;  // PT.cpp:49-51 / :28-30: the ray left the scene
+      } else {
+        s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, D);
+        const float3 omega = -D;
+        if (st == kPrimary) {
+          if (s.is_light() && max_path > 0) {  // PT.cpp:23-26: lights seen directly, then look through them
+            float3 lr; float ld;
+            query_lsdf(sc, s, omega, lr, ld);
+            rad += cfg.params.lights * lr;
+            O = offset_origin(s.pos, s.gnormal, D);
+            want_trace = true;
+          } else if (max_path < 2) {
+            terminated = true;
+          } else {
+            proceed = true;  // first surface vertex: throughput 1, path_size 2 (PT.cpp:32-38)
+          }
+        } else {
+          const float4 pv = pool.prev[slot], tv = pool.thr[slot];
+          const float bsdf_density = pv.w;
+          const uint32_t packed = __float_as_uint(tv.w);
+          const uint32_t finite = packed & 1u;
+          path_size = packed >> 1;
+          thr = f3(tv.x, tv.y, tv.z);
+          // Edge(eye[prv].surface, eye[itr].surface, eye[itr].omega) (PT.cpp:56): only fGeometry is still needed
+          const float dist_sq_inv = 1.0f / distance2(f3(pv.x, pv.y, pv.z), s.pos);
+          const float f_geometry = dist_sq_inv * fabsf(dot(omega, s.normal()));
+          if (s.is_light()) {  // PT.cpp:69-80: emission with the power heuristic, then through the light
+            float3 lr; float ld;
+            query_lsdf(sc, s, omega, lr, ld);
+            float weight_inv = pow_beta(ld, beta) / pow_beta(f_geometry * bsdf_density, beta) + 1.0f;
+            if (finite == 0) weight_inv = 1.0f;
+            rad += lr * thr / weight_inv;
+            O = offset_origin(s.pos, s.gnormal, D);
+            want_trace = true;
+          } else {  // PT.cpp:84-94: Russian roulette once the path has 3 vertices
+            const float roulette = path_size < 3 ? 1.0f : cfg.params.roulette;
+            const float uniform = rng.sample();
+            if (roulette < uniform) {
+              terminated = true;
+            } else {
+              thr /= roulette;
+              ++path_size;
+              if (path_size > max_path) terminated = true; else proceed = true;
+            }
+          }
+        }
+      }
+
+      if (proceed) {
+        const float3 eye_omega = -D;
+        // ---- PathTracing::_connect (PT.cpp:100-120): next-event estimation
+        const LightSample light = sample_light(sc, rng);
+        const float3 omega = normalize(s.pos - light.surface.pos);
+        const BsdfQuery lb = bsdf_query(sc, light.surface, light.surface.normal(), omega);
+        if (!(l1norm(lb.throughput) < kFltEpsilon)) {
+          const BsdfQuery eb = bsdf_query(sc, s, -omega, eye_omega);
+          const Edge edge(light.surface.pos, light.surface.normal(), s.pos, s.normal(), omega);
+          const float weight_inv = pow_beta(eb.density_rev * edge.b_geometry, beta) / pow_beta(light.combined_density(), beta) + 1.0f;
+          sh_c = light.radiance / light.combined_density() * thr * eb.throughput * edge.b_cos * edge.f_geometry / weight_inv;
+          // Scene::occluded(eye.surface, light.surface) (Scene.cpp:151-171)
+          const float3 direction = normalize(light.surface.pos - s.pos);
+          const float3 a = s.pos + (dot(s.gnormal, direction) > 0.0f ? 1.0f : -1.0f) * s.gnormal * 0.0001f;
+          const float3 b = light.surface.pos + (dot(light.surface.gnormal, direction) < 0.0f ? 1.0f : -1.0f) * light.surface.gnormal * 0.0001f;
+          sh_o = a; sh_d = b - a;
+          want_shadow = !(l1norm(sh_c) == 0.0f);  // a zero contribution needs no visibility test
+        }
+        // ---- Scene::sampleBSDF + the throughput the next vertex will carry (PT.cpp:43-66)
+        const BsdfSample bs = bsdf_sample(sc, rng, s, eye_omega);
+        const float b_cos = fabsf(dot(-bs.omega, s.normal()));
+        float3 thr_next = thr * bs.throughput * b_cos;
+        if (l1norm(thr_next) < kFltEpsilon) {
+          terminated = true;  // PT.cpp:61-63 (taken whether or not the extension ray would have hit)
+        } else {
+          thr_next /= bs.density;
+          D = bs.omega;
+          O = offset_origin(s.pos, s.gnormal, D);
+          pool.prev[slot] = make_float4(s.pos.x, s.pos.y, s.pos.z, bs.density);
+          pool.thr[slot] = make_float4(thr_next.x, thr_next.y, thr_next.z, __uint_as_float((bs.finite & 1u) | (path_size << 1)));
+          pool.ray_d[slot] = make_float4(D.x, D.y, D.z, 0.f);
+          st = kBounce;
+          want_trace = true;
+        }
+      }
+
+      if (terminated) {
+        if (want_shadow) {
+          sh_flags = kShadowCommit;  // the shadow stage adds the last contribution, then commits
+          st = kAwaitShadow;
+          pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+        } else {
+          commit_sample(cfg, work, rad);
+          st = kFree;
+        }
+      } else {
+        pool.ray_o[slot] = make_float4(O.x, O.y, O.z, 0.f);
+        pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+        pool.rng[slot] = make_uint2(rng.key, rng.ctr);
+      }
+    }
+
+    // ---- regeneration: a free slot takes the next (sample, pixel) (Technique::_for_each_ray, Technique.cpp:307-352)
+    {
+      const bool was_free = st == kFree;
+      const unsigned long long w = warp_grab_work(&cnt->next_work, was_free);
+      if (was_free && w < cfg.total_work) {
+        const uint32_t pixel = uint32_t(w % cfg.pixels);
+        const uint32_t pass = uint32_t(w / cfg.pixels);
+        const uint32_t sample = cfg.params.first_sample + pass * (cfg.params.sample_stride ? cfg.params.sample_stride : 1u);
+        Rng g; g.key = stream_key(cfg.params.seed, kDomainPixel, pixel, sample); g.ctr = 0;
+        const float3 dir = shoot_primary(cfg, g, pixel);
+        const float3 org = offset_origin(cfg.camera.pos, cfg.camera.gnormal, dir);
+        pool.ray_o[slot] = make_float4(org.x, org.y, org.z, 0.f);
+        pool.ray_d[slot] = make_float4(dir.x, dir.y, dir.z, 0.f);
+        pool.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+        pool.rng[slot] = make_uint2(g.key, g.ctr);
+        pool.work[slot] = w;
+        st = kPrimary;
+        want_trace = true;
+      }
+    }
+    pool.state[slot] = st;
+
+    const unsigned tq = warp_append(&cnt->queue_count[parity][kQueueTrace], want_trace);
+    if (want_trace) pool.trace_q[tq] = slot;
+    const unsigned sq = warp_append(&cnt->queue_count[parity][kQueueShadow], want_shadow);
+    if (want_shadow) {
+      float4* e = pool.shadow_q + size_t(sq) * 3;
+      e[0] = make_float4(sh_o.x, sh_o.y, sh_o.z, __uint_as_float(slot));
+      e[1] = make_float4(sh_d.x, sh_d.y, sh_d.z, __uint_as_float(sh_flags));
+      e[2] = make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) pt_trace_kernel(RenderConfig cfg, PtPool pool, int parity) {
+  const uint32_t n = cfg.counters->queue_count[parity][kQueueTrace];
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cfg.counters->basic_rays, (unsigned long long)n);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t slot = pool.trace_q[i];
+    const float4 o = pool.ray_o[slot], d = pool.ray_d[slot];
+    // Scene::intersect: tnear 0, tfar inf, mask 0xFFFFFFFF (Scene.cpp:190-197)
+    const Hit h = trace_ray<false, false>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY);
+    pool.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+  }
+}
+
+__global__ void __launch_bounds__(256) pt_shadow_kernel(RenderConfig cfg, PtPool pool, int parity) {
+  const uint32_t n = cfg.counters->queue_count[parity][kQueueShadow];
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cfg.counters->shadow_rays, (unsigned long long)n);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4* e = pool.shadow_q + size_t(i) * 3;
+    const float4 o = e[0], d = e[1], c = e[2];
+    const uint32_t slot = __float_as_uint(o.w), flags = __float_as_uint(d.w);
+    // Scene::occluded: t in (0, 1) along the unnormalised segment, meshes only (Scene.cpp:162-176)
+    const Hit h = trace_ray<true, true>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, 1.0f);
+    float4 r = pool.rad[slot];
+    if (h.tri == kInvalid) {
+      r.x += c.x; r.y += c.y; r.z += c.z;
+      if (!(flags & kShadowCommit)) pool.rad[slot] = r;
+    }
+    if (flags & kShadowCommit) {
+      commit_sample(cfg, pool.work[slot], f3(r.x, r.y, r.z));
+      pool.state[slot] = kFree;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- host driver
+struct PtWorkspace {
+  PtPool pool{};
+  uint32_t pool_size = 0;
+  RenderCounters* counters = nullptr;
+  RenderCounters* host_counters = nullptr;  // pinned
+  void* blocks[16] = {nullptr};
+  int num_blocks = 0;
+};
+
+static void pt_workspace_free(void* p) {
+  PtWorkspace* w = (PtWorkspace*)p;
+  for (int i = 0; i < w->num_blocks; ++i) cudaFree(w->blocks[i]);
+  if (w->host_counters) cudaFreeHost(w->host_counters);
+  delete w;
+}
+
+template <class T>
+static int ws_alloc(PtWorkspace* w, T** p, size_t count) {
+  void* q = nullptr;
+  B2_CUDA(cudaMalloc(&q, count * sizeof(T)));
+  w->blocks[w->num_blocks++] = q;
+  *p = (T*)q;
+  return B2PT_OK;
+}
+
+static int pt_workspace(b2pt_scene_s* scene, uint32_t pool_size, PtWorkspace** out) {
+  PtWorkspace* w = (PtWorkspace*)scene->workspace;
+  if (w && scene->workspace_free == pt_workspace_free && w->pool_size == pool_size) { *out = w; return B2PT_OK; }
+  if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
+  scene->workspace = nullptr;
+  w = new PtWorkspace();
+  scene->workspace = w; scene->workspace_free = pt_workspace_free;
+  w->pool_size = pool_size;
+  int rc;
+  if ((rc = ws_alloc(w, &w->pool.state, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.ray_o, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.ray_d, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.hit, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.prev, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.thr, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.rad, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.rng, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.work, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.trace_q, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.shadow_q, size_t(pool_size) * 3))) return rc;
+  if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
+  B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(RenderCounters)));
+  *out = w;
+  return B2PT_OK;
+}
+
+int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
+  const int block = 256;
+  // pool: enough slots to fill the machine several times over, never more than the work, multiple of the block
+  unsigned long long want = base.total_work < (1ull << 21) ? base.total_work : (1ull << 21);
+  uint32_t pool_size = uint32_t((want + block - 1) / block * block);
+  PtWorkspace* w = nullptr;
+  if (int rc = pt_workspace(scene, pool_size, &w)) return rc;
+  RenderConfig cfg = base;
+  cfg.pool_size = pool_size;
+  cfg.counters = w->counters;
+  B2_CUDA(cudaMemsetAsync(w->counters, 0, sizeof(RenderCounters), stream));
+  B2_CUDA(cudaMemsetAsync(w->pool.state, 0, size_t(pool_size) * 4, stream));
+  const int grid = grid_for(pool_size, block);
+  uint64_t launches = 0;
+  const int kBatch = 8;  // stage iterations between two looks at the device counters
+  for (int it = 0;; ) {
+    for (int k = 0; k < kBatch; ++k, ++it) {
+      const int parity = it & 1;
+      pt_logic_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity);
+      pt_trace_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity);
+      pt_shadow_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity);
+      launches += 3;
+    }
+    B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(RenderCounters), cudaMemcpyDeviceToHost, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));
+    const RenderCounters& c = *w->host_counters;
+    const int last = (it - 1) & 1;
+    if (c.next_work >= cfg.total_work && c.queue_count[last][kQueueTrace] == 0 && c.queue_count[last][kQueueShadow] == 0) break;
+    if (it > (1 << 22)) { set_error("render_pt: path pool did not drain"); return B2PT_ERR_CUDA; }
+  }
+  B2_CUDA(cudaGetLastError());
+  if (stats) {
+    const RenderCounters& c = *w->host_counters;
+    stats->num_basic_rays = c.basic_rays;
+    stats->num_shadow_rays = c.shadow_rays;
+    stats->numeric_errors = c.numeric_errors;
+    stats->capacity_events = c.capacity_events;
+    stats->kernel_launches = launches;
+  }
+  return B2PT_OK;
+}
+
+}  // namespace b2pt

@@ -1,0 +1,104 @@
+// render.cu — b2pt_render / b2pt_render_host: the Technique::render boundary (Technique.cpp:15-77).
+//
+// Builds the render_context_t equivalent (Technique.cpp:37-45), dispatches to the wavefront
+// integrator the Options select (make_technique.cpp:112-170) and fills the statistics_t fields a
+// device technique can know (Technique.cpp:52-76).
+#include "render_common.cuh"
+
+namespace b2pt {
+
+int render_pt(b2pt_scene_s* scene, const RenderConfig& cfg, cudaStream_t stream, B2ptStats* stats);
+int render_bpt(b2pt_scene_s* scene, const RenderConfig& cfg, cudaStream_t stream, B2ptStats* stats);
+int render_vcm(b2pt_scene_s* scene, const RenderConfig& cfg, cudaStream_t stream, B2ptStats* stats);
+
+static int make_config(b2pt_scene_s* scene, const B2ptRenderParams* p, double* accum, float* path_radiance, RenderConfig* cfg) {
+  B2_CHECK(p->width > 0 && p->height > 0, B2PT_ERR_INVALID, "b2pt_render: empty window");
+  B2_CHECK(p->technique <= B2PT_TECHNIQUE_UPG, B2PT_ERR_INVALID, "b2pt_render: unknown technique");
+  B2_CHECK(p->roulette > 0.0f && p->roulette <= 1.0f, B2PT_ERR_INVALID, "b2pt_render: roulette must be in (0, 1]");
+  // AreaLights::_sampleLight: runtime_assert(num_lights() != 0) (AreaLights.cpp:217)
+  B2_CHECK(scene->dev.num_lights > 0, B2PT_ERR_INVALID, "b2pt_render: the scene has no lights (AreaLights.cpp:217)");
+  cfg->scene = scene->dev;
+  cfg->params = *p;
+  cfg->camera = Surface();
+  // host copy of camera_surface(): same arithmetic as the device function (negations only)
+  const float* v = p->camera.view_to_world;
+  cfg->camera.pos = f3(p->camera.position[0], p->camera.position[1], p->camera.position[2]);
+  cfg->camera.tan.c0 = f3(v[3], v[4], v[5]);
+  cfg->camera.tan.c1 = f3(-v[6], -v[7], -v[8]);
+  cfg->camera.tan.c2 = f3(v[0], v[1], v[2]);
+  cfg->camera.gnormal = f3(-v[6], -v[7], -v[8]);
+  cfg->camera.material_id = 0u << 2 | B2PT_ENTITY_CAMERA;
+  cfg->width_f = float(p->width);
+  cfg->height_f = float(p->height);
+  cfg->res_y_inv = 1.0f / float(p->height);
+  cfg->focal_factor_y = p->camera.focal_length_y * p->camera.focal_length_y * 0.25f;
+  cfg->pixels = p->width * p->height;
+  cfg->total_work = (unsigned long long)cfg->pixels * p->num_samples;
+  cfg->pool_size = 0;
+  cfg->accum = accum;
+  cfg->path_radiance = path_radiance;
+  cfg->counters = nullptr;
+  return B2PT_OK;
+}
+
+}  // namespace b2pt
+
+extern "C" {
+
+int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accum_dev, float* path_radiance_dev, void* stream_,
+                B2ptStats* stats) {
+  using namespace b2pt;
+  B2_CHECK(scene && params && accum_dev, B2PT_ERR_INVALID, "b2pt_render: null argument");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  RenderConfig cfg;
+  if (int rc = make_config(scene, params, accum_dev, path_radiance_dev, &cfg)) return rc;
+  B2ptStats local{};
+  if (params->num_samples == 0) { if (stats) *stats = local; return B2PT_OK; }
+  cudaEvent_t e0, e1;
+  B2_CUDA(cudaEventCreate(&e0)); B2_CUDA(cudaEventCreate(&e1));
+  B2_CUDA(cudaEventRecord(e0, stream));
+  int rc;
+  switch (params->technique) {
+    case B2PT_TECHNIQUE_PT: rc = render_pt(scene, cfg, stream, &local); break;
+    case B2PT_TECHNIQUE_BPT: rc = render_bpt(scene, cfg, stream, &local); break;
+    default: rc = render_vcm(scene, cfg, stream, &local); break;
+  }
+  if (rc == B2PT_OK) {
+    cudaError_t e = cudaEventRecord(e1, stream);
+    if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&local.device_ms, e0, e1);
+    if (e != cudaSuccess) rc = cuda_fail(e, "b2pt_render timing", __FILE__, __LINE__);
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (rc != B2PT_OK) return rc;
+  uint32_t flags = 0;
+  B2_CUDA(cudaMemcpy(&flags, scene->dev.error_flags, 4, cudaMemcpyDeviceToHost));
+  B2_CHECK((flags & 1u) == 0, B2PT_ERR_CAPACITY, "BVH traversal stack overflow");
+  local.num_samples = params->num_samples;
+  local.num_paths = cfg.total_work;
+  if (stats) *stats = local;
+  return B2PT_OK;
+}
+
+int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* params, double* view_host, B2ptStats* stats) {
+  using namespace b2pt;
+  B2_CHECK(scene && params && view_host, B2PT_ERR_INVALID, "b2pt_render_host: null argument");
+  const size_t n = size_t(params->width) * params->height * 4;
+  double* d = nullptr;
+  B2_CUDA(cudaMalloc(&d, n * sizeof(double)));
+  cudaError_t e = cudaMemset(d, 0, n * sizeof(double));
+  int rc = e == cudaSuccess ? b2pt_render(scene, params, d, nullptr, nullptr, stats) : cuda_fail(e, "cudaMemset", __FILE__, __LINE__);
+  if (rc == B2PT_OK) {
+    // view += pass sums (Technique::_commit_images adds into the caller's dvec4 buffer)
+    double* h = nullptr;
+    e = cudaMallocHost((void**)&h, n * sizeof(double));
+    if (e == cudaSuccess) e = cudaMemcpy(h, d, n * sizeof(double), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) for (size_t i = 0; i < n; ++i) view_host[i] += h[i];
+    if (h) cudaFreeHost(h);
+    if (e != cudaSuccess) rc = cuda_fail(e, "b2pt_render_host copy", __FILE__, __LINE__);
+  }
+  cudaFree(d);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,500 @@
+// scene.cu — b2pt_scene_create: upload + GPU BVH build.
+//
+// Replaces Scene::buildAccelStructs / updateRTCScene / makeRTCMesh (Scene.cpp:20-73), i.e. Embree's
+// rtcNewTriangleMesh + rtcCommit (SAH builder with spatial splits, kernels/common/scene.cpp:100-124),
+// with a build that runs entirely on the device:
+//   1. per-triangle bounds + centroid, scene bounds by float atomics              (bounds_kernel)
+//   2. 30-bit Morton code of the centroid, made unique with the triangle index    (morton_kernel)
+//   3. 64-bit radix sort of the keys                                              (cub::DeviceRadixSort)
+//   4. binary radix tree over the sorted keys, Karras 2012                        (radix_tree_kernel)
+//   5. bottom-up box fitting with one atomic counter per inner node               (fit_kernel)
+//   6. top-down collapse of the binary tree into 4-wide nodes, opening the child
+//      with the largest surface area first; subtrees of <= 4 triangles become leaves (collapse_kernel, per level)
+//   7. triangle + shading records written in leaf order                           (pack_kernel)
+// The result is a different tree from Embree's; parity is defined on what the tree returns
+// (closest triangle id, t, u, v), not on the tree.
+#include <cub/cub.cuh>
+#include <float.h>
+#include <math.h>
+#include <vector>
+
+#include "scene.cuh"
+
+namespace b2pt {
+
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+const char* get_error() { return g_error.c_str(); }
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  char buf[512];
+  snprintf(buf, sizeof buf, "%s failed: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
+  g_error = buf;
+  return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? B2PT_ERR_NO_DEVICE : B2PT_ERR_CUDA;
+}
+
+// ---------------------------------------------------------------- build kernels
+struct BuildInput {
+  uint32_t num_meshes, num_tris;
+  const uint32_t* mesh_material_id;
+  const uint32_t* mesh_vertex_offset;
+  const uint32_t* mesh_index_offset;
+  const float* vertices;
+  const float* tangents;
+  const int32_t* indices;
+};
+
+__device__ __forceinline__ uint32_t find_mesh(const BuildInput& in, uint32_t tri) {
+  // last mesh m with index_offset[m] <= 3*tri
+  uint32_t lo = 0, hi = in.num_meshes;
+  uint32_t key = tri * 3u;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (in.mesh_index_offset[mid] <= key) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ float3 load_vertex(const BuildInput& in, uint32_t mesh, uint32_t corner_index) {
+  uint32_t v = in.mesh_vertex_offset[mesh] + uint32_t(in.indices[corner_index]);
+  return f3(in.vertices[v * 3 + 0], in.vertices[v * 3 + 1], in.vertices[v * 3 + 2]);
+}
+
+// monotone float <-> uint mapping so that atomicMin/atomicMax order floats
+__device__ __forceinline__ uint32_t float_to_ordered(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ordered_to_float(uint32_t u) {
+  u = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(u);
+#else
+  float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+
+__global__ void bounds_kernel(BuildInput in, float4* tri_lo, float4* tri_hi, uint32_t* scene_bounds) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  float3 lo = f3(FLT_MAX), hi = f3(-FLT_MAX);
+  if (t < in.num_tris) {
+    uint32_t m = find_mesh(in, t);
+    float3 a = load_vertex(in, m, t * 3 + 0), b = load_vertex(in, m, t * 3 + 1), c = load_vertex(in, m, t * 3 + 2);
+    lo = f3(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)));
+    hi = f3(fmaxf(a.x, fmaxf(b.x, c.x)), fmaxf(a.y, fmaxf(b.y, c.y)), fmaxf(a.z, fmaxf(b.z, c.z)));
+    tri_lo[t] = make_float4(lo.x, lo.y, lo.z, __uint_as_float(m));
+    tri_hi[t] = make_float4(hi.x, hi.y, hi.z, 0.f);
+  }
+  // warp reduce, then one atomic per warp and component
+  for (int o = 16; o > 0; o >>= 1) {
+    lo.x = fminf(lo.x, __shfl_xor_sync(0xFFFFFFFFu, lo.x, o));
+    lo.y = fminf(lo.y, __shfl_xor_sync(0xFFFFFFFFu, lo.y, o));
+    lo.z = fminf(lo.z, __shfl_xor_sync(0xFFFFFFFFu, lo.z, o));
+    hi.x = fmaxf(hi.x, __shfl_xor_sync(0xFFFFFFFFu, hi.x, o));
+    hi.y = fmaxf(hi.y, __shfl_xor_sync(0xFFFFFFFFu, hi.y, o));
+    hi.z = fmaxf(hi.z, __shfl_xor_sync(0xFFFFFFFFu, hi.z, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(&scene_bounds[0], float_to_ordered(lo.x));
+    atomicMin(&scene_bounds[1], float_to_ordered(lo.y));
+    atomicMin(&scene_bounds[2], float_to_ordered(lo.z));
+    atomicMax(&scene_bounds[3], float_to_ordered(hi.x));
+    atomicMax(&scene_bounds[4], float_to_ordered(hi.y));
+    atomicMax(&scene_bounds[5], float_to_ordered(hi.z));
+  }
+}
+
+__device__ __forceinline__ uint32_t expand_bits10(uint32_t v) {
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+
+__global__ void morton_kernel(uint32_t n, const float4* tri_lo, const float4* tri_hi, const uint32_t* scene_bounds,
+                              uint64_t* keys) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  float3 slo = f3(ordered_to_float(scene_bounds[0]), ordered_to_float(scene_bounds[1]), ordered_to_float(scene_bounds[2]));
+  float3 shi = f3(ordered_to_float(scene_bounds[3]), ordered_to_float(scene_bounds[4]), ordered_to_float(scene_bounds[5]));
+  float4 lo = tri_lo[t], hi = tri_hi[t];
+  float3 c = f3(0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z));
+  float3 ext = f3(fmaxf(shi.x - slo.x, 1e-30f), fmaxf(shi.y - slo.y, 1e-30f), fmaxf(shi.z - slo.z, 1e-30f));
+  uint32_t x = uint32_t(fminf(fmaxf((c.x - slo.x) / ext.x * 1024.f, 0.f), 1023.f));
+  uint32_t y = uint32_t(fminf(fmaxf((c.y - slo.y) / ext.y * 1024.f, 0.f), 1023.f));
+  uint32_t z = uint32_t(fminf(fmaxf((c.z - slo.z) / ext.z * 1024.f, 0.f), 1023.f));
+  uint32_t code = (expand_bits10(x) << 2) | (expand_bits10(y) << 1) | expand_bits10(z);
+  keys[t] = (uint64_t(code) << 32) | t;
+}
+
+// binary radix tree node ids: inner nodes 0..n-2, leaves encoded as (i | 0x80000000)
+struct BinNode {
+  uint32_t left, right;   // child ids (bit 31 = leaf = sorted triangle position)
+  uint32_t first, last;   // range of sorted triangle positions covered
+};
+
+__device__ __forceinline__ int delta(const uint64_t* keys, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  return __clzll(keys[i] ^ keys[j]);
+}
+
+__global__ void radix_tree_kernel(int n, const uint64_t* keys, BinNode* nodes, uint32_t* parent_inner, uint32_t* parent_leaf) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+  int dmin = delta(keys, n, i, i - d);
+  int lmax = 2;
+  while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+  int l = 0;
+  for (int t = lmax >> 1; t >= 1; t >>= 1)
+    if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+  int j = i + l * d;
+  int dnode = delta(keys, n, i, j);
+  int s = 0;
+  int t = l;
+  do {
+    t = (t + 1) >> 1;
+    if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+  } while (t > 1);
+  int gamma = i + s * d + min(d, 0);
+  int first = min(i, j), last = max(i, j);
+  BinNode nd;
+  nd.first = first; nd.last = last;
+  if (first == gamma) { nd.left = uint32_t(gamma) | 0x80000000u; parent_leaf[gamma] = i; }
+  else { nd.left = gamma; parent_inner[gamma] = i; }
+  if (last == gamma + 1) { nd.right = uint32_t(gamma + 1) | 0x80000000u; parent_leaf[gamma + 1] = i; }
+  else { nd.right = gamma + 1; parent_inner[gamma + 1] = i; }
+  nodes[i] = nd;
+  if (i == 0) parent_inner[0] = kInvalid;
+}
+
+__global__ void fit_kernel(int n, const uint64_t* keys, const float4* tri_lo, const float4* tri_hi, const BinNode* nodes,
+                           const uint32_t* parent_inner, const uint32_t* parent_leaf, float4* box_lo, float4* box_hi,
+                           uint32_t* visit) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t p = parent_leaf[i];
+  while (p != kInvalid) {
+    __threadfence();
+    if (atomicAdd(&visit[p], 1u) == 0u) return;  // first arrival waits for the sibling
+    BinNode nd = nodes[p];
+    float4 llo, lhi, rlo, rhi;
+    if (nd.left & 0x80000000u) { uint32_t t = uint32_t(keys[nd.left & 0x7FFFFFFFu]); llo = tri_lo[t]; lhi = tri_hi[t]; }
+    else { llo = __ldcg(&box_lo[nd.left]); lhi = __ldcg(&box_hi[nd.left]); }  // L2: written by another SM
+    if (nd.right & 0x80000000u) { uint32_t t = uint32_t(keys[nd.right & 0x7FFFFFFFu]); rlo = tri_lo[t]; rhi = tri_hi[t]; }
+    else { rlo = __ldcg(&box_lo[nd.right]); rhi = __ldcg(&box_hi[nd.right]); }
+    box_lo[p] = make_float4(fminf(llo.x, rlo.x), fminf(llo.y, rlo.y), fminf(llo.z, rlo.z), 0.f);
+    box_hi[p] = make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), 0.f);
+    p = parent_inner[p];
+  }
+}
+
+struct CollapseItem { uint32_t wide, bin; };
+
+__device__ __forceinline__ float half_area(float4 lo, float4 hi) {
+  float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+  return dx * dy + dy * dz + dz * dx;
+}
+
+// One thread per wide node of the current level.
+__global__ void collapse_kernel(uint32_t count, const CollapseItem* items, const uint64_t* keys, const float4* tri_lo,
+                                const float4* tri_hi, const BinNode* bin, const float4* box_lo, const float4* box_hi,
+                                float4* nodes, uint32_t* num_wide, CollapseItem* next_items, uint32_t* next_count,
+                                float pad) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  CollapseItem it = items[i];
+  uint32_t ch[4];
+  int nch = 2;
+  ch[0] = bin[it.bin].left; ch[1] = bin[it.bin].right;
+  auto is_final = [&](uint32_t c) {  // a child that will not be opened further
+    if (c & 0x80000000u) return true;
+    return bin[c].last - bin[c].first + 1u <= uint32_t(kMaxLeafTris);
+  };
+  while (nch < 4) {
+    int best = -1; float best_area = -1.f;
+    for (int k = 0; k < nch; ++k) {
+      if (is_final(ch[k])) continue;
+      float a = half_area(box_lo[ch[k]], box_hi[ch[k]]);
+      if (a > best_area) { best_area = a; best = k; }
+    }
+    if (best < 0) break;
+    uint32_t c = ch[best];
+    ch[best] = bin[c].left;
+    ch[nch++] = bin[c].right;
+  }
+  float lo[3][4], hi[3][4];
+  uint32_t link[4];
+  for (int k = 0; k < 4; ++k) {
+    if (k >= nch) {
+      for (int a = 0; a < 3; ++a) { lo[a][k] = INFINITY; hi[a][k] = -INFINITY; }
+      link[k] = kInvalid;
+      continue;
+    }
+    uint32_t c = ch[k];
+    float4 blo, bhi;
+    if (c & 0x80000000u) {
+      uint32_t pos = c & 0x7FFFFFFFu;
+      uint32_t t = uint32_t(keys[pos]);
+      blo = tri_lo[t]; bhi = tri_hi[t];
+      link[k] = make_leaf(pos, 1);
+    } else {
+      blo = box_lo[c]; bhi = box_hi[c];
+      uint32_t cnt = bin[c].last - bin[c].first + 1u;
+      if (cnt <= uint32_t(kMaxLeafTris)) {
+        link[k] = make_leaf(bin[c].first, cnt);
+      } else {
+        uint32_t w = atomicAdd(num_wide, 1u);
+        uint32_t q = atomicAdd(next_count, 1u);
+        next_items[q] = CollapseItem{w, c};
+        link[k] = w;
+      }
+    }
+    lo[0][k] = blo.x - pad; lo[1][k] = blo.y - pad; lo[2][k] = blo.z - pad;
+    hi[0][k] = bhi.x + pad; hi[1][k] = bhi.y + pad; hi[2][k] = bhi.z + pad;
+  }
+  float4* out = nodes + size_t(it.wide) * kNodeFloat4s;
+  for (int a = 0; a < 3; ++a) {
+    out[a] = make_float4(lo[a][0], lo[a][1], lo[a][2], lo[a][3]);
+    out[3 + a] = make_float4(hi[a][0], hi[a][1], hi[a][2], hi[a][3]);
+  }
+  out[6] = make_float4(__uint_as_float(link[0]), __uint_as_float(link[1]), __uint_as_float(link[2]), __uint_as_float(link[3]));
+  out[7] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// Triangle + shading records in leaf (sorted) order.
+__global__ void pack_kernel(BuildInput in, const uint64_t* keys, const float4* tri_lo, float4* v0o, float4* e1o, float4* e2o,
+                            float4* frames) {
+  uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= in.num_tris) return;
+  uint32_t t = uint32_t(keys[pos]);
+  uint32_t m = __float_as_uint(tri_lo[t].w);
+  uint32_t prim = t - in.mesh_index_offset[m] / 3u;
+  float3 a = load_vertex(in, m, t * 3 + 0), b = load_vertex(in, m, t * 3 + 1), c = load_vertex(in, m, t * 3 + 2);
+  float3 e1 = a - b, e2 = c - a;  // Embree: e1 = v0 - v1, e2 = v2 - v0
+  uint32_t material = in.mesh_material_id[m];
+  uint32_t mask = 1u << (material & 3u);  // rtcSetMask, Scene.cpp:47
+  v0o[pos] = make_float4(a.x, a.y, a.z, __uint_as_float(m));
+  e1o[pos] = make_float4(e1.x, e1.y, e1.z, __uint_as_float(prim));
+  e2o[pos] = make_float4(e2.x, e2.y, e2.z, __uint_as_float(mask));
+  float fr[28];
+  for (int k = 0; k < 3; ++k) {
+    uint32_t v = in.mesh_vertex_offset[m] + uint32_t(in.indices[t * 3 + k]);
+    for (int j = 0; j < 9; ++j) fr[k * 9 + j] = in.tangents[size_t(v) * 9 + j];
+  }
+  fr[27] = __uint_as_float(material);
+  float4* out = frames + size_t(pos) * kFrameFloat4s;
+  for (int k = 0; k < kFrameFloat4s; ++k) out[k] = make_float4(fr[k * 4], fr[k * 4 + 1], fr[k * 4 + 2], fr[k * 4 + 3]);
+}
+
+// ---------------------------------------------------------------- host side
+template <class T>
+static int dev_alloc(b2pt_scene_s* s, T** p, size_t count, bool keep) {
+  void* q = nullptr;
+  B2_CUDA(cudaMalloc(&q, count * sizeof(T) + 16));
+  *p = (T*)q;
+  if (keep) s->allocations[s->num_allocations++] = q;
+  return B2PT_OK;
+}
+
+static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
+  const uint32_t M = d->num_meshes;
+  const uint32_t nv = d->mesh_vertex_offset[M], ni = d->mesh_index_offset[M];
+  const uint32_t n = ni / 3;
+  B2_CHECK(n >= 1, B2PT_ERR_INVALID, "scene has no triangles");
+  B2_CHECK(n < (1u << 28), B2PT_ERR_CAPACITY, "more than 2^28 triangles");
+  for (uint32_t m = 0; m < M; ++m)
+    B2_CHECK(d->mesh_index_offset[m] % 3 == 0, B2PT_ERR_INVALID, "mesh index count not a multiple of 3");
+
+  std::vector<void*> temps;
+  auto tmp = [&](size_t bytes) -> void* { void* q = nullptr; if (cudaMalloc(&q, bytes + 16) != cudaSuccess) return nullptr; temps.push_back(q); return q; };
+  struct Cleanup { std::vector<void*>& t; ~Cleanup() { for (void* q : t) cudaFree(q); } } cleanup{temps};
+
+  cudaEvent_t ev0, ev1;
+  B2_CUDA(cudaEventCreate(&ev0)); B2_CUDA(cudaEventCreate(&ev1));
+
+  // ---- upload (inputs are temporaries except the small tables)
+  BuildInput in;
+  in.num_meshes = M; in.num_tris = n;
+  uint32_t* d_mat = (uint32_t*)tmp(M * 4); uint32_t* d_voff = (uint32_t*)tmp((M + 1) * 4); uint32_t* d_ioff = (uint32_t*)tmp((M + 1) * 4);
+  float* d_vert = (float*)tmp(size_t(nv) * 12); float* d_tan = (float*)tmp(size_t(nv) * 36); int32_t* d_idx = (int32_t*)tmp(size_t(ni) * 4);
+  B2_CHECK(d_mat && d_voff && d_ioff && d_vert && d_tan && d_idx, B2PT_ERR_CUDA, "cudaMalloc failed for scene upload");
+  B2_CUDA(cudaMemcpy(d_mat, d->mesh_material_id, M * 4, cudaMemcpyHostToDevice));
+  B2_CUDA(cudaMemcpy(d_voff, d->mesh_vertex_offset, (M + 1) * 4, cudaMemcpyHostToDevice));
+  B2_CUDA(cudaMemcpy(d_ioff, d->mesh_index_offset, (M + 1) * 4, cudaMemcpyHostToDevice));
+  B2_CUDA(cudaMemcpy(d_vert, d->vertices, size_t(nv) * 12, cudaMemcpyHostToDevice));
+  B2_CUDA(cudaMemcpy(d_tan, d->tangents, size_t(nv) * 36, cudaMemcpyHostToDevice));
+  B2_CUDA(cudaMemcpy(d_idx, d->indices, size_t(ni) * 4, cudaMemcpyHostToDevice));
+  in.mesh_material_id = d_mat; in.mesh_vertex_offset = d_voff; in.mesh_index_offset = d_ioff;
+  in.vertices = d_vert; in.tangents = d_tan; in.indices = d_idx;
+
+  B2_CUDA(cudaEventRecord(ev0));
+  const int B = 256;
+  const uint32_t G = (n + B - 1) / B;
+  float4* tri_lo = (float4*)tmp(size_t(n) * 16); float4* tri_hi = (float4*)tmp(size_t(n) * 16);
+  uint32_t* bounds = (uint32_t*)tmp(6 * 4);
+  uint64_t* keys_in = (uint64_t*)tmp(size_t(n) * 8); uint64_t* keys = (uint64_t*)tmp(size_t(n) * 8);
+  B2_CHECK(tri_lo && tri_hi && bounds && keys_in && keys, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
+  uint32_t init_bounds[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
+  B2_CUDA(cudaMemcpy(bounds, init_bounds, sizeof init_bounds, cudaMemcpyHostToDevice));
+  bounds_kernel<<<G, B>>>(in, tri_lo, tri_hi, bounds);
+  morton_kernel<<<G, B>>>(n, tri_lo, tri_hi, bounds, keys_in);
+  size_t sort_bytes = 0;
+  B2_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, keys_in, keys, int(n)));
+  void* sort_tmp = tmp(sort_bytes);
+  B2_CHECK(sort_tmp, B2PT_ERR_CUDA, "cudaMalloc failed for sort");
+  B2_CUDA(cub::DeviceRadixSort::SortKeys(sort_tmp, sort_bytes, keys_in, keys, int(n)));
+
+  float4* nodes = nullptr;
+  uint32_t num_wide = 1;
+  uint32_t h_bounds[6];
+  B2_CUDA(cudaMemcpy(h_bounds, bounds, sizeof h_bounds, cudaMemcpyDeviceToHost));
+  float ext = 0.f;
+  for (int a = 0; a < 3; ++a) ext = fmaxf(ext, ordered_to_float(h_bounds[3 + a]) - ordered_to_float(h_bounds[a]));
+  const float pad = ext * 1e-6f;  // conservative slack on every child box (see trace.cuh)
+
+  if (n == 1) {
+    // a single leaf under the root
+    if (int rc = dev_alloc(s, &nodes, kNodeFloat4s, true)) return rc;
+    float4 lo, hi;
+    B2_CUDA(cudaMemcpy(&lo, tri_lo, 16, cudaMemcpyDeviceToHost));
+    B2_CUDA(cudaMemcpy(&hi, tri_hi, 16, cudaMemcpyDeviceToHost));
+    float4 h[kNodeFloat4s];
+    const float inf = INFINITY;
+    h[0] = make_float4(lo.x - pad, inf, inf, inf); h[1] = make_float4(lo.y - pad, inf, inf, inf); h[2] = make_float4(lo.z - pad, inf, inf, inf);
+    h[3] = make_float4(hi.x + pad, -inf, -inf, -inf); h[4] = make_float4(hi.y + pad, -inf, -inf, -inf); h[5] = make_float4(hi.z + pad, -inf, -inf, -inf);
+    uint32_t l0 = make_leaf(0, 1), inv = kInvalid;
+    float f0, fi; memcpy(&f0, &l0, 4); memcpy(&fi, &inv, 4);
+    h[6] = make_float4(f0, fi, fi, fi); h[7] = make_float4(0, 0, 0, 0);
+    B2_CUDA(cudaMemcpy(nodes, h, sizeof h, cudaMemcpyHostToDevice));
+  } else {
+    BinNode* bin = (BinNode*)tmp(size_t(n - 1) * sizeof(BinNode));
+    uint32_t* parent_inner = (uint32_t*)tmp(size_t(n) * 4); uint32_t* parent_leaf = (uint32_t*)tmp(size_t(n) * 4);
+    float4* box_lo = (float4*)tmp(size_t(n) * 16); float4* box_hi = (float4*)tmp(size_t(n) * 16);
+    uint32_t* visit = (uint32_t*)tmp(size_t(n) * 4);
+    CollapseItem* items_a = (CollapseItem*)tmp(size_t(n) * sizeof(CollapseItem));
+    CollapseItem* items_b = (CollapseItem*)tmp(size_t(n) * sizeof(CollapseItem));
+    uint32_t* counters = (uint32_t*)tmp(16);  // [0] num_wide, [1] next_count
+    B2_CHECK(bin && parent_inner && parent_leaf && box_lo && box_hi && visit && items_a && items_b && counters, B2PT_ERR_CUDA,
+             "cudaMalloc failed for BVH build");
+    B2_CUDA(cudaMemset(visit, 0, size_t(n) * 4));
+    radix_tree_kernel<<<G, B>>>(int(n), keys, bin, parent_inner, parent_leaf);
+    fit_kernel<<<G, B>>>(int(n), keys, tri_lo, tri_hi, bin, parent_inner, parent_leaf, box_lo, box_hi, visit);
+    // worst case one wide node per binary inner node
+    if (int rc = dev_alloc(s, &nodes, size_t(n) * kNodeFloat4s, true)) return rc;
+    CollapseItem root{0u, 0u};
+    B2_CUDA(cudaMemcpy(items_a, &root, sizeof root, cudaMemcpyHostToDevice));
+    uint32_t h_counters[2] = {1u, 0u};
+    B2_CUDA(cudaMemcpy(counters, h_counters, 8, cudaMemcpyHostToDevice));
+    uint32_t count = 1;
+    while (count > 0) {
+      collapse_kernel<<<(count + B - 1) / B, B>>>(count, items_a, keys, tri_lo, tri_hi, bin, box_lo, box_hi, nodes, &counters[0],
+                                                 items_b, &counters[1], pad);
+      B2_CUDA(cudaMemcpy(h_counters, counters, 8, cudaMemcpyDeviceToHost));
+      count = h_counters[1];
+      num_wide = h_counters[0];
+      B2_CUDA(cudaMemset(&counters[1], 0, 4));
+      std::swap(items_a, items_b);
+    }
+  }
+
+  float4 *v0o, *e1o, *e2o, *frames;
+  if (int rc = dev_alloc(s, &v0o, n, true)) return rc;
+  if (int rc = dev_alloc(s, &e1o, n, true)) return rc;
+  if (int rc = dev_alloc(s, &e2o, n, true)) return rc;
+  if (int rc = dev_alloc(s, &frames, size_t(n) * kFrameFloat4s, true)) return rc;
+  pack_kernel<<<G, B>>>(in, keys, tri_lo, v0o, e1o, e2o, frames);
+  B2_CUDA(cudaEventRecord(ev1));
+  B2_CUDA(cudaEventSynchronize(ev1));
+  B2_CUDA(cudaGetLastError());
+  B2_CUDA(cudaEventElapsedTime(&s->build_ms, ev0, ev1));
+  cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+
+  // ---- small tables
+  B2ptMaterial* d_materials; B2ptLight* d_lights = nullptr;
+  if (int rc = dev_alloc(s, &d_materials, d->num_materials ? d->num_materials : 1, true)) return rc;
+  B2_CUDA(cudaMemcpy(d_materials, d->materials, d->num_materials * sizeof(B2ptMaterial), cudaMemcpyHostToDevice));
+  const uint32_t L = d->num_lights;
+  double *d_cp = nullptr, *d_den = nullptr; float* d_int = nullptr;
+  if (L) {
+    if (int rc = dev_alloc(s, &d_lights, L, true)) return rc;
+    B2_CUDA(cudaMemcpy(d_lights, d->lights, L * sizeof(B2ptLight), cudaMemcpyHostToDevice));
+    // std::piecewise_constant_distribution<float>(L, 0, 1, weights) as libstdc++ initialises it
+    // (Sample.inl:235-247; bits/random.tcc param_type(nw, xmin, xmax, fw) + _M_initialize)
+    std::vector<float> ints(L + 1);
+    std::vector<double> den(L), cp(L);
+    const float delta = (1.0f - 0.0f) / float(L);
+    for (uint32_t k = 0; k <= L; ++k) ints[k] = 0.0f + float(k) * delta;
+    for (uint32_t k = 0; k < L; ++k) den[k] = double(d->lights[k].weight);
+    double sum = 0.0;
+    for (uint32_t k = 0; k < L; ++k) sum += den[k];
+    for (uint32_t k = 0; k < L; ++k) den[k] /= sum;
+    double acc = 0.0;
+    for (uint32_t k = 0; k < L; ++k) { acc += den[k]; cp[k] = acc; }
+    cp[L - 1] = 1.0;
+    for (uint32_t k = 0; k < L; ++k) den[k] /= double(ints[k + 1] - ints[k]);
+    if (int rc = dev_alloc(s, &d_cp, L, true)) return rc;
+    if (int rc = dev_alloc(s, &d_den, L, true)) return rc;
+    if (int rc = dev_alloc(s, &d_int, L + 1, true)) return rc;
+    B2_CUDA(cudaMemcpy(d_cp, cp.data(), L * 8, cudaMemcpyHostToDevice));
+    B2_CUDA(cudaMemcpy(d_den, den.data(), L * 8, cudaMemcpyHostToDevice));
+    B2_CUDA(cudaMemcpy(d_int, ints.data(), (L + 1) * 4, cudaMemcpyHostToDevice));
+  }
+  uint32_t* d_flags;
+  if (int rc = dev_alloc(s, &d_flags, 4, true)) return rc;
+  B2_CUDA(cudaMemset(d_flags, 0, 16));
+
+  DeviceScene& ds = s->dev;
+  ds.num_tris = n; ds.num_nodes = num_wide; ds.num_materials = d->num_materials; ds.num_lights = L;
+  ds.tri_v0 = v0o; ds.tri_e1 = e1o; ds.tri_e2 = e2o; ds.tri_frames = frames; ds.nodes = nodes;
+  ds.materials = d_materials; ds.lights = d_lights; ds.light_cp = d_cp; ds.light_den = d_den; ds.light_int = d_int;
+  ds.error_flags = d_flags;
+  s->bvh_bytes = uint64_t(num_wide) * kNodeFloat4s * 16 + uint64_t(n) * 48;
+  return B2PT_OK;
+}
+
+}  // namespace b2pt
+
+extern "C" {
+
+const char* b2pt_last_error(void) { return b2pt::get_error(); }
+int b2pt_abi_version(void) { return B2PT_ABI_VERSION; }
+
+int b2pt_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int b2pt_scene_create(const B2ptSceneDesc* desc, b2pt_scene_t* out) {
+  B2_CHECK(desc && out, B2PT_ERR_INVALID, "b2pt_scene_create: null argument");
+  B2_CHECK(desc->num_meshes > 0 && desc->mesh_material_id && desc->mesh_vertex_offset && desc->mesh_index_offset && desc->vertices &&
+               desc->tangents && desc->indices && desc->materials,
+           B2PT_ERR_INVALID, "b2pt_scene_create: incomplete scene description");
+  B2_CHECK(b2pt_device_count() > 0, B2PT_ERR_NO_DEVICE, "no CUDA device: the B200 path has no CPU fallback");
+  for (uint32_t m = 0; m < desc->num_meshes; ++m)
+    B2_CHECK((desc->mesh_material_id[m] >> 2) < desc->num_materials, B2PT_ERR_INVALID, "mesh material index out of range");
+  b2pt_scene_s* s = new b2pt_scene_s();
+  int rc = b2pt::build_scene(desc, s);
+  if (rc != B2PT_OK) { b2pt_scene_destroy(s); return rc; }
+  *out = s;
+  return B2PT_OK;
+}
+
+void b2pt_scene_destroy(b2pt_scene_t s) {
+  if (!s) return;
+  if (s->workspace && s->workspace_free) s->workspace_free(s->workspace);
+  for (int i = 0; i < s->num_allocations; ++i) cudaFree(s->allocations[i]);
+  delete s;
+}
+
+int b2pt_scene_info(b2pt_scene_t s, uint64_t* num_triangles, uint64_t* num_nodes, uint64_t* bvh_bytes, float* build_ms) {
+  B2_CHECK(s, B2PT_ERR_INVALID, "b2pt_scene_info: null scene");
+  if (num_triangles) *num_triangles = s->dev.num_tris;
+  if (num_nodes) *num_nodes = s->dev.num_nodes;
+  if (bvh_bytes) *bvh_bytes = s->bvh_bytes;
+  if (build_ms) *build_ms = s->build_ms;
+  return B2PT_OK;
+}
+
+}  // extern "C"

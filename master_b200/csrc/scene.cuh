@@ -1,0 +1,66 @@
+// scene.cuh — the scene as it lives in HBM.
+//
+// Replaces what haste::Scene + Embree hold on the host (Scene.hpp:28-76, Scene.cpp:20-73):
+//   * triangles in BVH-leaf order as three float4 streams (128-bit loads):
+//       tri_v0 = (v0.xyz, bits geomID)   tri_e1 = (v0-v1, bits primID)   tri_e2 = (v2-v0, bits mask)
+//     — Embree's Triangle4 convention e1 = v0-v1, e2 = v2-v0 (kernels/geometry/triangle.h:54), so the
+//     Möller–Trumbore arithmetic can follow triangle_intersector_moeller.h:78-111 operation by operation;
+//   * the per-triangle shading record in the same order: the three vertex tangent frames
+//     (Mesh::tangents, AreaLights.hpp:14-20) + material id, 7 float4 = 112 B, so querySurface
+//     (Scene.cpp:80-126) is one contiguous read instead of index + 3 gathers;
+//   * a 4-wide BVH, 128 B per node (8 float4), child boxes SoA so one node test is 6 float4 loads
+//     + 1 for the child links;
+//   * small tables: materials (64 B), lights (80 B), the light-pick CDF in double.
+#pragma once
+#include "common.cuh"
+
+namespace b2pt {
+
+constexpr uint32_t kInvalid = 0xFFFFFFFFu;
+constexpr int kNodeFloat4s = 8;    // 128-byte BVH4 node
+constexpr int kFrameFloat4s = 7;   // 112-byte shading record per triangle
+constexpr int kMaxLeafTris = 4;
+
+// Child link encoding in node float4 #6:
+//   0xFFFFFFFF                      empty slot (box is +inf/-inf, never hit)
+//   bit 31 set                      leaf: bits 0..27 first triangle (leaf order), bits 28..30 count-1
+//   otherwise                       index of an inner node
+__host__ __device__ __forceinline__ bool child_is_leaf(uint32_t c) { return (c & 0x80000000u) != 0; }
+__host__ __device__ __forceinline__ uint32_t leaf_first(uint32_t c) { return c & 0x0FFFFFFFu; }
+__host__ __device__ __forceinline__ uint32_t leaf_count(uint32_t c) { return ((c >> 28) & 7u) + 1u; }
+__host__ __device__ __forceinline__ uint32_t make_leaf(uint32_t first, uint32_t count) {
+  return 0x80000000u | ((count - 1u) << 28) | first;
+}
+
+struct DeviceScene {
+  uint32_t num_tris = 0;
+  uint32_t num_nodes = 0;
+  uint32_t num_materials = 0;
+  uint32_t num_lights = 0;
+  const float4* tri_v0 = nullptr;
+  const float4* tri_e1 = nullptr;
+  const float4* tri_e2 = nullptr;
+  const float4* tri_frames = nullptr;  // [num_tris * kFrameFloat4s]
+  const float4* nodes = nullptr;       // [num_nodes * kNodeFloat4s], root = node 0
+  const B2ptMaterial* materials = nullptr;
+  const B2ptLight* lights = nullptr;
+  // std::piecewise_constant_distribution<float> state (Sample.inl:233-247), in double as libstdc++ keeps it
+  const double* light_cp = nullptr;    // cumulative probabilities [num_lights] (empty semantics when num_lights == 1)
+  const double* light_den = nullptr;   // densities [num_lights]
+  const float* light_int = nullptr;    // interval boundaries [num_lights + 1]
+  uint32_t* error_flags = nullptr;     // bit 0: traversal stack overflow
+};
+
+}  // namespace b2pt
+
+// host-side owner of the device arrays; defined in scene.cu
+struct b2pt_scene_s {
+  b2pt::DeviceScene dev;
+  uint64_t bvh_bytes = 0;
+  float build_ms = 0.f;
+  void* allocations[24] = {nullptr};
+  int num_allocations = 0;
+  // per-scene render workspace (path pool, queues), created lazily by render.cu
+  void* workspace = nullptr;
+  void (*workspace_free)(void*) = nullptr;
+};

@@ -1,0 +1,143 @@
+// trace.cuh — closest-hit and any-hit ray queries against the device BVH.
+//
+// Replaces rtcIntersect / rtcOccluded as the reference calls them (Scene.cpp:151-226,
+// Intersector.cpp:17-46).  One ray per thread; a short traversal stack in registers/local memory;
+// every node is fetched with seven 128-bit loads, every triangle with three.
+//
+// The leaf test follows Embree's MoellerTrumboreIntersector1
+// (submodules/embree/kernels/geometry/triangle_intersector_moeller.h:78-111 and the hit
+// finalisation :40-50) operation by operation, with Embree's dot/cross association
+// (common/math/vec3.h:188,193: dot = a.x*b.x + (a.y*b.y + a.z*b.z)) and unfused multiplies
+// (the oracle build caps Embree at the AVX ISA, which has no FMA), so den, U, V, T — and with
+// them the accept/reject decision for a given triangle — are bit-identical to the reference's.
+// t = T * rcp(|den|) differs from Embree's Newton-refined _mm_rcp_ps by <= 1 ulp.
+//
+// Box tests are NOT part of the parity contract (the tree is a different tree); they use fused
+// multiply-adds and are made conservative: child boxes carry a small absolute pad (scene.cu) and
+// the exit distance is stretched by 2 ulp, so a triangle the leaf test would accept is never culled.
+#pragma once
+#include "scene.cuh"
+
+namespace b2pt {
+
+constexpr int kStackSize = 64;
+
+struct Hit {
+  float t, u, v;
+  uint32_t tri;  // triangle position in leaf order, kInvalid on a miss
+};
+
+__device__ __forceinline__ float xor_sign(float x, uint32_t sgn) { return __uint_as_float(__float_as_uint(x) ^ sgn); }
+
+// Embree dot: madd(a.x, b.x, madd(a.y, b.y, a.z*b.z)) without FMA
+__device__ __forceinline__ float dot_embree(float3 a, float3 b) {
+  return __fadd_rn(__fmul_rn(a.x, b.x), __fadd_rn(__fmul_rn(a.y, b.y), __fmul_rn(a.z, b.z)));
+}
+// Embree cross: (msub(a.y,b.z,a.z*b.y), msub(a.z,b.x,a.x*b.z), msub(a.x,b.y,a.y*b.x)) without FMA
+__device__ __forceinline__ float3 cross_embree(float3 a, float3 b) {
+  return f3(__fsub_rn(__fmul_rn(a.y, b.z), __fmul_rn(a.z, b.y)),
+            __fsub_rn(__fmul_rn(a.z, b.x), __fmul_rn(a.x, b.z)),
+            __fsub_rn(__fmul_rn(a.x, b.y), __fmul_rn(a.y, b.x)));
+}
+
+// Returns true and updates (tfar, u, v) when triangle `pos` is hit inside (tnear, tfar).
+template <bool kMeshOnly>
+__device__ __forceinline__ bool intersect_triangle(const DeviceScene& sc, uint32_t pos, float3 O, float3 D, float tnear,
+                                                   float& tfar, float& u, float& v) {
+  const float4 q0 = __ldg(&sc.tri_v0[pos]);
+  const float4 q1 = __ldg(&sc.tri_e1[pos]);
+  const float4 q2 = __ldg(&sc.tri_e2[pos]);
+  if (kMeshOnly) {
+    // ray.mask = 1 << entity_type::mesh (Scene.cpp:169); geometry mask = 1 << (material_id & 3) (Scene.cpp:47)
+    if ((__float_as_uint(q2.w) & (1u << B2PT_ENTITY_MESH)) == 0u) return false;
+  }
+  const float3 v0 = f3(q0.x, q0.y, q0.z), e1 = f3(q1.x, q1.y, q1.z), e2 = f3(q2.x, q2.y, q2.z);
+  const float3 Ng = cross_embree(e1, e2);  // Triangle4 stores Ng = cross(e1, e2)
+  const float3 C = f3(__fsub_rn(v0.x, O.x), __fsub_rn(v0.y, O.y), __fsub_rn(v0.z, O.z));
+  const float3 R = cross_embree(D, C);
+  const float den = dot_embree(Ng, D);
+  const float absDen = fabsf(den);
+  const uint32_t sgnDen = __float_as_uint(den) & 0x80000000u;
+  const float U = xor_sign(dot_embree(R, e2), sgnDen);
+  const float V = xor_sign(dot_embree(R, e1), sgnDen);
+  if (!((den != 0.0f) & (U >= 0.0f) & (V >= 0.0f) & (__fadd_rn(U, V) <= absDen))) return false;
+  const float T = xor_sign(dot_embree(Ng, C), sgnDen);
+  if (!((T > __fmul_rn(absDen, tnear)) & (T < __fmul_rn(absDen, tfar)))) return false;
+  const float rcpAbsDen = __frcp_rn(absDen);
+  tfar = __fmul_rn(T, rcpAbsDen);
+  u = __fmul_rn(U, rcpAbsDen);
+  v = __fmul_rn(V, rcpAbsDen);
+  return true;
+}
+
+__device__ __forceinline__ void cswap(float& ta, uint32_t& ca, float& tb, uint32_t& cb) {
+  if (tb < ta) { float t = ta; ta = tb; tb = t; uint32_t c = ca; ca = cb; cb = c; }
+}
+
+// kAnyHit: stop at the first accepted triangle (rtcOccluded).  kMeshOnly: ray mask = meshes only.
+template <bool kAnyHit, bool kMeshOnly>
+__device__ __forceinline__ Hit trace_ray(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar) {
+  Hit hit; hit.t = tfar; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
+  // safe reciprocal direction: a zero component becomes +-huge instead of inf so 0*inf never appears
+  const float kHuge = 1e30f;
+  const float3 idir = f3(fabsf(D.x) > 1e-30f ? 1.0f / D.x : copysignf(kHuge, D.x),
+                         fabsf(D.y) > 1e-30f ? 1.0f / D.y : copysignf(kHuge, D.y),
+                         fabsf(D.z) > 1e-30f ? 1.0f / D.z : copysignf(kHuge, D.z));
+  const float3 ood = f3(O.x * idir.x, O.y * idir.y, O.z * idir.z);
+  uint32_t stack[kStackSize];
+  int sp = 0;
+  uint32_t cur = 0;  // root is always an inner node
+  while (true) {
+    if (!child_is_leaf(cur)) {
+      const float4* n = sc.nodes + size_t(cur) * kNodeFloat4s;
+      const float4 lox = __ldg(n + 0), loy = __ldg(n + 1), loz = __ldg(n + 2);
+      const float4 hix = __ldg(n + 3), hiy = __ldg(n + 4), hiz = __ldg(n + 5);
+      const float4 lk = __ldg(n + 6);
+      float tn[4];
+      uint32_t ch[4] = {__float_as_uint(lk.x), __float_as_uint(lk.y), __float_as_uint(lk.z), __float_as_uint(lk.w)};
+      const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
+      const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float x0 = __fmaf_rn(lx[k], idir.x, -ood.x), x1 = __fmaf_rn(hx[k], idir.x, -ood.x);
+        const float y0 = __fmaf_rn(ly[k], idir.y, -ood.y), y1 = __fmaf_rn(hy[k], idir.y, -ood.y);
+        const float z0 = __fmaf_rn(lz[k], idir.z, -ood.z), z1 = __fmaf_rn(hz[k], idir.z, -ood.z);
+        const float t0 = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tnear));
+        const float t1 = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), hit.t)) * 1.0000003f;
+        const bool ok = (t0 <= t1) & (ch[k] != kInvalid);
+        tn[k] = ok ? t0 : INFINITY;
+      }
+      // sort the (up to four) children by entry distance: 5 compare-exchanges
+      cswap(tn[0], ch[0], tn[1], ch[1]); cswap(tn[2], ch[2], tn[3], ch[3]);
+      cswap(tn[0], ch[0], tn[2], ch[2]); cswap(tn[1], ch[1], tn[3], ch[3]);
+      cswap(tn[1], ch[1], tn[2], ch[2]);
+      if (tn[0] == INFINITY) {
+        if (sp == 0) break;
+        cur = stack[--sp];
+        continue;
+      }
+      // far children first onto the stack, nearest is visited next
+      if (tn[3] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[3]; else atomicOr(sc.error_flags, 1u); }
+      if (tn[2] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[2]; else atomicOr(sc.error_flags, 1u); }
+      if (tn[1] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[1]; else atomicOr(sc.error_flags, 1u); }
+      cur = ch[0];
+    } else {
+      const uint32_t first = leaf_first(cur), count = leaf_count(cur);
+      for (uint32_t k = 0; k < count; ++k) {
+        if (intersect_triangle<kMeshOnly>(sc, first + k, O, D, tnear, hit.t, hit.u, hit.v)) {
+          hit.tri = first + k;
+          if (kAnyHit) return hit;
+        }
+      }
+      if (sp == 0) break;
+      cur = stack[--sp];
+    }
+  }
+  return hit;
+}
+
+// geomID / primID of a triangle in leaf order
+__device__ __forceinline__ uint32_t tri_geom(const DeviceScene& sc, uint32_t pos) { return __float_as_uint(__ldg(&sc.tri_v0[pos]).w); }
+__device__ __forceinline__ uint32_t tri_prim(const DeviceScene& sc, uint32_t pos) { return __float_as_uint(__ldg(&sc.tri_e1[pos]).w); }
+
+}  // namespace b2pt

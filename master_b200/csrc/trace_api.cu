@@ -1,0 +1,72 @@
+// trace_api.cu — b2pt_trace / b2pt_trace_device: batches of explicit rays.
+//
+// The ray-level boundary: what Scene::intersect / intersectMesh / occluded hand to Embree
+// (an RTCRay with org, dir, tnear, tfar and a mask, Scene.cpp:162-171,186-196,209-219) and what
+// they read back (tfar, u, v, geomID, primID).  Used by the ray-level parity tests and the
+// Mrays/s micro-benchmark; the renderers call trace_ray() from their own stages.
+#include "trace.cuh"
+
+namespace b2pt {
+
+template <bool kAnyHit, bool kMeshOnly>
+__global__ void __launch_bounds__(256) trace_rays_kernel(DeviceScene sc, const float4* __restrict__ rays, size_t n,
+                                                         B2ptHit* __restrict__ hits) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const float4 a = __ldg(&rays[i * 2 + 0]);  // org.xyz, tnear
+    const float4 b = __ldg(&rays[i * 2 + 1]);  // dir.xyz, tfar
+    Hit h = trace_ray<kAnyHit, kMeshOnly>(sc, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), a.w, b.w);
+    B2ptHit o;
+    o.t = h.t; o.u = h.u; o.v = h.v;
+    if (h.tri == kInvalid) { o.geom = kInvalid; o.prim = kInvalid; }
+    else if (kAnyHit) { o.geom = 0u; o.prim = kInvalid; }  // rtcOccluded reports geomID = 0 (Scene.cpp:179)
+    else { o.geom = tri_geom(sc, h.tri); o.prim = tri_prim(sc, h.tri); }
+    hits[i] = o;
+  }
+}
+
+int launch_trace(const DeviceScene& sc, const B2ptRay* rays, size_t n, unsigned mode, B2ptHit* hits, cudaStream_t stream) {
+  if (n == 0) return B2PT_OK;
+  const int block = 256;
+  size_t want = (n + block - 1) / block;
+  // persistent-style grid: a multiple of the SM count, each thread strides over the rays
+  size_t cap = size_t(kNumSMs) * 8 * 4;
+  int grid = int(want < cap ? want : cap);
+  const float4* r = reinterpret_cast<const float4*>(rays);
+  switch (mode) {
+    case B2PT_TRACE_CLOSEST_ALL: trace_rays_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, n, hits); break;
+    case B2PT_TRACE_CLOSEST_MESH: trace_rays_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, n, hits); break;
+    case B2PT_TRACE_OCCLUDED_MESH: trace_rays_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, n, hits); break;
+    default: set_error("b2pt_trace: unknown mode"); return B2PT_ERR_INVALID;
+  }
+  B2_CUDA(cudaGetLastError());
+  return B2PT_OK;
+}
+
+}  // namespace b2pt
+
+extern "C" {
+
+int b2pt_trace_device(b2pt_scene_t scene, const B2ptRay* rays_dev, size_t n, unsigned mode, B2ptHit* hits_dev, void* stream) {
+  B2_CHECK(scene && (n == 0 || (rays_dev && hits_dev)), B2PT_ERR_INVALID, "b2pt_trace_device: null argument");
+  return b2pt::launch_trace(scene->dev, rays_dev, n, mode, hits_dev, (cudaStream_t)stream);
+}
+
+int b2pt_trace(b2pt_scene_t scene, const B2ptRay* rays, size_t n, unsigned mode, B2ptHit* hits) {
+  B2_CHECK(scene && (n == 0 || (rays && hits)), B2PT_ERR_INVALID, "b2pt_trace: null argument");
+  if (n == 0) return B2PT_OK;
+  B2ptRay* d_rays = nullptr; B2ptHit* d_hits = nullptr;
+  B2_CUDA(cudaMalloc(&d_rays, n * sizeof(B2ptRay)));
+  cudaError_t e = cudaMalloc(&d_hits, n * sizeof(B2ptHit));
+  if (e != cudaSuccess) { cudaFree(d_rays); return b2pt::cuda_fail(e, "cudaMalloc", __FILE__, __LINE__); }
+  int rc = B2PT_OK;
+  e = cudaMemcpy(d_rays, rays, n * sizeof(B2ptRay), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    rc = b2pt::launch_trace(scene->dev, d_rays, n, mode, d_hits, 0);
+    if (rc == B2PT_OK) e = cudaMemcpy(hits, d_hits, n * sizeof(B2ptHit), cudaMemcpyDeviceToHost);
+  }
+  cudaFree(d_rays); cudaFree(d_hits);
+  if (e != cudaSuccess) return b2pt::cuda_fail(e, "b2pt_trace copy", __FILE__, __LINE__);
+  return rc;
+}
+
+}  // extern "C"

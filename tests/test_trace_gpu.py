@@ -1,0 +1,84 @@
+"""Ray-level parity (north_star level 1): closest-hit triangle ids agree with Embree on >= 99.99 % of
+rays, hit distance within 1e-5 relative; occlusion answers agree.  Through the C ABI (b2pt_trace)."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import REF_HARNESS, golden_path
+
+pytestmark = pytest.mark.gpu
+
+SCENES = ["CornellBoxDiffuse", "CornellBoxSpecular", "TestCaseFurnace", "TestCase9", "MetalRings"]
+MISS = 0xFFFFFFFF
+
+
+def compare_closest(ours, ref, what, min_agree=0.9999):
+    same = (ours["geom"] == ref["geom"]) & (ours["prim"] == ref["prim"])
+    agree = same.mean()
+    hit = same & (ref["geom"] != MISS)
+    rel = np.abs(ours["t"][hit] - ref["t"][hit]) / np.maximum(np.abs(ref["t"][hit]), 1e-30)
+    # a mismatching id is only acceptable as a tie: same distance on a shared edge / coplanar pair
+    bad = ~same
+    both = bad & (ours["geom"] != MISS) & (ref["geom"] != MISS)
+    tie_rel = np.abs(ours["t"][both] - ref["t"][both]) / np.maximum(np.abs(ref["t"][both]), 1e-30)
+    info = dict(what=what, rays=len(ref), agree=float(agree), max_rel_t=float(rel.max() if rel.size else 0),
+                mismatches=int(bad.sum()), mismatch_max_rel_dt=float(tie_rel.max() if tie_rel.size else 0))
+    print(json.dumps(info))
+    assert agree >= min_agree, info
+    assert rel.size == 0 or rel.max() <= 1e-5, info
+    if hit.any():
+        assert np.abs(ours["u"][hit] - ref["u"][hit]).max() <= 1e-5, info
+        assert np.abs(ours["v"][hit] - ref["v"][hit]).max() <= 1e-5, info
+    return info
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_golden_ray_parity(name, device_scenes):
+    from master_b200 import api
+    g = np.load(golden_path("rays_%s.npz" % name))
+    scene = device_scenes(name)
+    compare_closest(scene.trace(g["camera_rays"], api.TRACE_CLOSEST_ALL), g["camera_hits"], name + " camera")
+    compare_closest(scene.trace(g["bounce_rays"], api.TRACE_CLOSEST_ALL), g["bounce_hits"], name + " bounce/all")
+    compare_closest(scene.trace(g["bounce_rays"], api.TRACE_CLOSEST_MESH), g["bounce_mesh_hits"], name + " bounce/mesh")
+    occ = scene.trace(g["shadow_rays"], api.TRACE_OCCLUDED_MESH)
+    agree = (occ["geom"] == g["shadow_hits"]["geom"]).mean()
+    print(json.dumps(dict(what=name + " shadow", rays=len(occ), agree=float(agree))))
+    assert agree >= 0.9999
+
+
+def test_empty_and_degenerate_batches(device_scenes):
+    from master_b200 import api
+    scene = device_scenes("CornellBoxDiffuse")
+    assert len(scene.trace(np.zeros(0, dtype=api.RAY_DTYPE), api.TRACE_CLOSEST_ALL)) == 0
+    rays = np.zeros(3, dtype=api.RAY_DTYPE)
+    rays["org"] = [[0, 0, 100], [0, 0, 100], [0, 0, 0]]
+    rays["dir"] = [[0, 0, 1], [0, 0, -1], [0, 1, 0]]   # away from the box, towards it, axis-parallel inside
+    rays["tfar"] = [np.inf, 1e-3, np.inf]              # second: tfar too short to reach anything
+    h = scene.trace(rays, api.TRACE_CLOSEST_ALL)
+    assert h["geom"][0] == MISS and h["geom"][1] == MISS
+    with pytest.raises(api.B2ptError):
+        scene.trace(rays, 17)
+
+
+@pytest.mark.skipif(not os.path.exists(REF_HARNESS), reason="oracle/_ref/ref_harness not built")
+@pytest.mark.parametrize("name", ["CornellBoxSpecular", "MetalRings"])
+def test_live_embree_parity_1m(name, device_scenes, flat_scenes, tmp_path):
+    """>= 1 M rays per class against Embree itself, run on this host by oracle/_ref/ref_harness."""
+    import sys
+    sys.path.insert(0, golden_path())
+    import make_golden as mg
+    from master_b200 import api
+    mg.TMP = str(tmp_path)
+    flat = flat_scenes(name)
+    path = golden_path("scenes", name + ".b2s")
+    sets = mg.make_ray_sets(flat, path, 1024, 1024, seed=7)
+    scene = device_scenes(name)
+    compare_closest(scene.trace(sets["camera_rays"], api.TRACE_CLOSEST_ALL), sets["camera_hits"], name + " 1M camera")
+    compare_closest(scene.trace(sets["bounce_rays"], api.TRACE_CLOSEST_ALL), sets["bounce_hits"], name + " 1M bounce")
+    occ = scene.trace(sets["shadow_rays"], api.TRACE_OCCLUDED_MESH)
+    agree = (occ["geom"] == sets["shadow_hits"]["geom"]).mean()
+    print(json.dumps(dict(what=name + " 1M shadow", rays=len(occ), agree=float(agree))))
+    assert agree >= 0.9999
