@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define B2PT_ABI_VERSION 1
+#define B2PT_ABI_VERSION 2
 
 enum {
   B2PT_OK = 0,
@@ -153,8 +153,14 @@ typedef struct {
   uint64_t capacity_events;  /* light subpaths truncated at max_subpath */
   uint64_t kernel_launches;  /* CUDA kernels launched by the call */
   float device_ms;           /* CUDA-event time of the call on its stream */
-  float trace_ms;            /* of which: closest-hit + occlusion traversal kernels
-                                (only when B2PT_PROFILE_STAGES is set; else 0) */
+  /* Per-stage device time, CUDA events around every launch of the stage on the call's stream.
+     Filled only when the environment variable B2PT_PROFILE_STAGES=1 is set (the extra events
+     cost a little); 0 otherwise. */
+  float trace_ms;            /* closest-hit traversal kernels (Scene::intersect / intersectMesh) */
+  float shadow_ms;           /* occlusion traversal kernels (Scene::occluded) */
+  float shade_ms;            /* everything else: raygen, shading, connection, splat, grid stages */
+  uint64_t trace_launches;   /* launches behind trace_ms */
+  uint64_t shadow_launches;  /* launches behind shadow_ms */
 } B2ptStats;
 
 typedef struct b2pt_scene_s* b2pt_scene_t;

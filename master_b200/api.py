@@ -93,6 +93,10 @@ class Stats(C.Structure):
         ("kernel_launches", C.c_uint64),
         ("device_ms", C.c_float),
         ("trace_ms", C.c_float),
+        ("shadow_ms", C.c_float),
+        ("shade_ms", C.c_float),
+        ("trace_launches", C.c_uint64),
+        ("shadow_launches", C.c_uint64),
     ]
 
     def as_dict(self):

@@ -315,18 +315,18 @@ int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream
   B2_CUDA(cudaMemsetAsync(w->counters, 0, sizeof(RenderCounters), stream));
   B2_CUDA(cudaMemsetAsync(w->pool.state, 0, size_t(pool_size) * 4, stream));
   const int grid = grid_for(pool_size, block);
-  uint64_t launches = 0;
+  StageTimer timer(stream);
   const int kBatch = 8;  // stage iterations between two looks at the device counters
   for (int it = 0;; ) {
     for (int k = 0; k < kBatch; ++k, ++it) {
       const int parity = it & 1;
-      pt_logic_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity);
-      pt_trace_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity);
-      pt_shadow_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity);
-      launches += 3;
+      timer.begin(kStageShade); pt_logic_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity); timer.end();
+      timer.begin(kStageTrace); pt_trace_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity); timer.end();
+      timer.begin(kStageShadow); pt_shadow_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity); timer.end();
     }
     B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(RenderCounters), cudaMemcpyDeviceToHost, stream));
     B2_CUDA(cudaStreamSynchronize(stream));
+    timer.resolve();
     const RenderCounters& c = *w->host_counters;
     const int last = (it - 1) & 1;
     if (c.next_work >= cfg.total_work && c.queue_count[last][kQueueTrace] == 0 && c.queue_count[last][kQueueShadow] == 0) break;
@@ -339,7 +339,7 @@ int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream
     stats->num_shadow_rays = c.shadow_rays;
     stats->numeric_errors = c.numeric_errors;
     stats->capacity_events = c.capacity_events;
-    stats->kernel_launches = launches;
+    timer.fill(stats);
   }
   return B2PT_OK;
 }

@@ -1,5 +1,8 @@
 // render_common.cuh — pieces shared by the wavefront integrators (pt.cu, bpt.cu, vcm.cu).
 #pragma once
+#include <stdlib.h>
+#include <vector>
+
 #include "shading.cuh"
 #include "trace.cuh"
 
@@ -60,6 +63,62 @@ __device__ __forceinline__ float3 shoot_primary(const RenderConfig& cfg, Rng& rn
   const float jx = rng.sample();
   return camera_ray_direction(cfg.params.camera, float(px) + jx, float(py) + jy, cfg.width_f, cfg.res_y_inv);
 }
+
+// Per-stage device time (B2ptStats::trace_ms / shadow_ms / shade_ms): a CUDA-event pair around every
+// launch of a stage, on the stream the kernels are launched on.  Counts launches always; records
+// events only when B2PT_PROFILE_STAGES=1, because the pairs serialise nothing but do cost host time.
+enum { kStageTrace = 0, kStageShadow = 1, kStageShade = 2, kNumStages = 3 };
+struct StageTimer {
+  bool enabled = false;
+  cudaStream_t stream = nullptr;
+  float ms[kNumStages] = {0.f, 0.f, 0.f};
+  uint64_t launches[kNumStages] = {0, 0, 0};
+  struct Pending { cudaEvent_t a, b; int stage; };
+  std::vector<Pending> pending;
+  std::vector<cudaEvent_t> spare;
+  int open_stage = -1;
+  cudaEvent_t open_a = nullptr;
+
+  explicit StageTimer(cudaStream_t s) : stream(s) {
+    const char* e = getenv("B2PT_PROFILE_STAGES");
+    enabled = e && e[0] == '1';
+  }
+  ~StageTimer() {
+    for (auto& p : pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto e : spare) cudaEventDestroy(e);
+  }
+  cudaEvent_t take() {
+    if (!spare.empty()) { cudaEvent_t e = spare.back(); spare.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+  }
+  void begin(int stage) {
+    ++launches[stage];
+    if (!enabled) return;
+    open_stage = stage; open_a = take();
+    cudaEventRecord(open_a, stream);
+  }
+  void end() {
+    if (!enabled) return;
+    cudaEvent_t b = take();
+    cudaEventRecord(b, stream);
+    pending.push_back(Pending{open_a, b, open_stage});
+  }
+  // call after the stream has been synchronised
+  void resolve() {
+    for (auto& p : pending) {
+      float t = 0.f;
+      if (cudaEventElapsedTime(&t, p.a, p.b) == cudaSuccess) ms[p.stage] += t;
+      spare.push_back(p.a); spare.push_back(p.b);
+    }
+    pending.clear();
+  }
+  uint64_t total_launches() const { return launches[0] + launches[1] + launches[2]; }
+  void fill(B2ptStats* st) const {
+    st->trace_ms = ms[kStageTrace]; st->shadow_ms = ms[kStageShadow]; st->shade_ms = ms[kStageShade];
+    st->trace_launches = launches[kStageTrace]; st->shadow_launches = launches[kStageShadow];
+    st->kernel_launches = total_launches();
+  }
+};
 
 inline int grid_for(size_t n, int block) {
   size_t want = (n + block - 1) / block;

@@ -112,8 +112,14 @@ class FlatScene:
 
 
 def load_b2s(path):
-    with open(path, "rb") as f:
-        buf = f.read()
+    """Reads a .b2s scene; a .b2s.xz (the large stand-in scene, tests/golden/make_large_scene.py) is unpacked in memory."""
+    if path.endswith(".xz"):
+        import lzma
+        with lzma.open(path, "rb") as f:
+            buf = f.read()
+    else:
+        with open(path, "rb") as f:
+            buf = f.read()
     if buf[:8] != b"B2SCENE1":
         raise ValueError("%s is not a .b2s scene" % path)
     nc, nm, nv, ni, nmat, nl, _, _ = np.frombuffer(buf, "<u4", 8, 8)
