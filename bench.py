@@ -124,7 +124,7 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--technique", default=os.environ.get("B2PT_BENCH_TECHNIQUE", "PT"), choices=["PT", "BPT", "VCM", "UPG"])
+    ap.add_argument("--technique", default=os.environ.get("B2PT_BENCH_TECHNIQUE", "BPT"), choices=["PT", "BPT", "VCM", "UPG"])
     ap.add_argument("--width", type=int, default=1024)
     ap.add_argument("--height", type=int, default=1024)
     ap.add_argument("--spp", type=int, default=4, help="passes (samples per pixel) per step")

@@ -1,5 +1,715 @@
-// bpt.cu — placeholder until the wavefront BPT lands (next milestone).
+// bpt.cu — wavefront bidirectional path tracer: BPTBase<Beta>::_traceEye / _traceLight / _connect* (BPT.cpp:14-324).
+//
+// The reference traces, per pixel-sample and on one thread, a light subpath into a 1024-slot stack array
+// (BPT.hpp:29-30), then walks the eye subpath and connects every eye vertex to every stored light vertex.
+// Here a BATCH of pixel-samples (whole passes, <= 2^21 paths) moves through four stages per iteration:
+//
+//   logic    (bpt_logic_kernel)    per path: a state machine over the reference's control flow.  Light phase:
+//                                  sample the emitter, roulette, BSDF sample, consume the closest mesh hit, push /
+//                                  overwrite / pop light vertices (BPT.cpp:122-192).  Eye phase: camera vertex,
+//                                  consume the closest hit, MIS partial sums c / C, emission through lights
+//                                  (_connect_light), roulette, next-event sample, BSDF sample (BPT.cpp:14-101).
+//                                  Every new eye vertex EXPANDS into (eye vertex, light vertex) pair descriptors.
+//   connect  (bpt_connect_kernel)  one thread per pair: two BSDF queries, the edge, the MIS weight Ap + Cp + 1
+//                                  (BPT.cpp:194-223); camera pairs also project to the pixel and apply the camera
+//                                  coefficient (BPT.cpp:294-319, Technique.cpp:246-305).  Non-zero contributions
+//                                  become shadow-queue entries.
+//   trace    (bpt_trace_kernel)    closest hit for every extension ray (mask: meshes only for light subpaths,
+//                                  meshes + lights for eye subpaths).
+//   shadow   (bpt_shadow_kernel)   any-hit for every queued connection; visible -> add to the path's radiance
+//                                  (float atomics) or splat into the pass's light image (double atomics).
+//
+// Light vertices live in ONE pool in HBM (112 B records, bump-allocated with a warp-aggregated atomic, chained
+// per path through a link array) instead of a 100 KB array per thread, so the stated cap is on the pool, not
+// on the path: 12 vertices per path on average (the expectation with roulette 0.9 is <= 8.1) and
+// B2ptRenderParams::max_subpath (default 1024, the reference's cap) per path.
+// Every path owns one counter-based RNG stream; light phase and eye phase consume it in the reference's order.
 #include "render_common.cuh"
+
 namespace b2pt {
-int render_bpt(b2pt_scene_s*, const RenderConfig&, cudaStream_t, B2ptStats*) { set_error("BPT: not built yet"); return B2PT_ERR_INVALID; }
+
+namespace {
+
+enum : uint32_t { kNew = 0, kLightWait = 1, kLightLoop = 2, kLightFinal = 3, kEyeStart = 4, kEyeWait = 5, kDone = 6 };
+constexpr uint32_t kPairCamera = 0x80000000u;  // descriptor.x bit 31: the eye vertex is the camera (light-image splat)
+constexpr uint32_t kNeeVertex = 0xFFFFFFFFu;   // descriptor.y: the freshly sampled emitter point instead of a stored vertex
+constexpr uint32_t kShadowSplat = 1u;
+constexpr int kVertexFloat4s = 7;
+
+struct BptCounters {
+  unsigned long long basic_rays, shadow_rays, numeric_errors, capacity_events;
+  unsigned int done;
+  unsigned int lv_count;
+  unsigned int trace_count[2], pair_count[2], shadow_count[2];
+};
+
+// LightVertex / EyeVertex (BPT.hpp:13-27): w0 = a or c, w1 = A or C
+struct Vertex {
+  Surface s;
+  float3 omega, thr;
+  float w0, w1;
+  uint32_t finite;
+};
+
+struct BptPool {
+  uint32_t size;         // slots in the batch (paths rounded up to the block size; the padding is born dead)
+  uint32_t valid;        // paths in the batch = passes * pixels
+  uint32_t lv_capacity;  // light vertex pool
+  uint32_t q_capacity;   // pair / shadow queues
+  uint32_t* state;
+  uint2* rng;
+  float4* cv;        // current vertex, SoA: cv[k * size + slot], k < 7
+  float4* bs_omega;  // pending BSDF sample: omega.xyz, density
+  float4* bs_thr;    //                      throughput.xyz, density_rev
+  float4* ray_o;     // extension ray origin, w = bits(bsdf.finite | ray mask selector << 1)
+  float4* hit;       // t, u, v, bits(triangle)
+  float4* rad;       // eye-path radiance (float atomics from the shadow stage)
+  float4* nee;       // next-event sample: position, bits(light id)
+  double* splat;     // light image of the pass the path belongs to: 3 doubles per slot (= per pixel of that pass)
+  uint32_t* lp_head;
+  uint32_t* lp_count;
+  float4* lv;        // light vertex pool, AoS: 7 float4 per vertex
+  uint32_t* lv_link; // previous vertex of the same path
+  uint32_t* trace_q;
+  uint2* pair_q;
+  float4* shadow_q;  // 3 float4 per entry
+};
+
+__device__ __forceinline__ void pack_vertex(const Vertex& v, float4* q) {
+  q[0] = make_float4(v.s.pos.x, v.s.pos.y, v.s.pos.z, __uint_as_float(v.s.material_id));
+  q[1] = make_float4(v.s.gnormal.x, v.s.gnormal.y, v.s.gnormal.z, __uint_as_float(v.finite));
+  q[2] = make_float4(v.s.tan.c0.x, v.s.tan.c0.y, v.s.tan.c0.z, v.w0);
+  q[3] = make_float4(v.s.tan.c1.x, v.s.tan.c1.y, v.s.tan.c1.z, v.w1);
+  q[4] = make_float4(v.s.tan.c2.x, v.s.tan.c2.y, v.s.tan.c2.z, 0.f);
+  q[5] = make_float4(v.omega.x, v.omega.y, v.omega.z, 0.f);
+  q[6] = make_float4(v.thr.x, v.thr.y, v.thr.z, 0.f);
 }
+__device__ __forceinline__ Vertex unpack_vertex(const float4* q) {
+  Vertex v;
+  v.s.pos = f3(q[0].x, q[0].y, q[0].z); v.s.material_id = __float_as_uint(q[0].w);
+  v.s.gnormal = f3(q[1].x, q[1].y, q[1].z); v.finite = __float_as_uint(q[1].w);
+  v.s.tan.c0 = f3(q[2].x, q[2].y, q[2].z); v.w0 = q[2].w;
+  v.s.tan.c1 = f3(q[3].x, q[3].y, q[3].z); v.w1 = q[3].w;
+  v.s.tan.c2 = f3(q[4].x, q[4].y, q[4].z);
+  v.omega = f3(q[5].x, q[5].y, q[5].z);
+  v.thr = f3(q[6].x, q[6].y, q[6].z);
+  return v;
+}
+__device__ __forceinline__ void store_slot_vertex(const BptPool& p, uint32_t slot, const Vertex& v) {
+  float4 q[kVertexFloat4s];
+  pack_vertex(v, q);
+#pragma unroll
+  for (int k = 0; k < kVertexFloat4s; ++k) p.cv[size_t(k) * p.size + slot] = q[k];
+}
+__device__ __forceinline__ Vertex load_slot_vertex(const BptPool& p, uint32_t slot) {
+  float4 q[kVertexFloat4s];
+#pragma unroll
+  for (int k = 0; k < kVertexFloat4s; ++k) q[k] = p.cv[size_t(k) * p.size + slot];
+  return unpack_vertex(q);
+}
+__device__ __forceinline__ void store_pool_vertex(const BptPool& p, uint32_t idx, const Vertex& v) {
+  float4 q[kVertexFloat4s];
+  pack_vertex(v, q);
+  float4* o = p.lv + size_t(idx) * kVertexFloat4s;
+#pragma unroll
+  for (int k = 0; k < kVertexFloat4s; ++k) o[k] = q[k];
+}
+__device__ __forceinline__ Vertex load_pool_vertex(const BptPool& p, uint32_t idx) {
+  float4 q[kVertexFloat4s];
+  const float4* o = p.lv + size_t(idx) * kVertexFloat4s;
+#pragma unroll
+  for (int k = 0; k < kVertexFloat4s; ++k) q[k] = o[k];
+  return unpack_vertex(q);
+}
+
+// BPTBase::_sample_to_vertex (BPT.cpp:103-114)
+__device__ __forceinline__ Vertex sample_to_vertex(const LightSample& sample, float roulette_inv, float beta) {
+  Vertex v;
+  v.s = sample.surface;
+  v.omega = v.s.normal();
+  v.thr = sample.radiance / sample.combined_density() * roulette_inv;
+  v.w0 = sample.directional ? 0.0f : 1.0f / beta_fn(sample.combined_density(), beta);
+  v.w1 = 0.0f;
+  v.finite = 1;
+  return v;
+}
+
+// the LightSample AreaLights::sample would return for light `id` at position `pos` (AreaLights.cpp:121-140)
+__device__ __forceinline__ LightSample light_sample_at(const DeviceScene& sc, uint32_t id, float3 pos) {
+  const B2ptLight& l = sc.lights[id];
+  LightSample r;
+  r.surface.pos = pos;
+  r.surface.tan.c0 = f3(l.tangent[0], l.tangent[1], l.tangent[2]);
+  r.surface.tan.c1 = f3(l.tangent[3], l.tangent[4], l.tangent[5]);
+  r.surface.tan.c2 = f3(l.tangent[6], l.tangent[7], l.tangent[8]);
+  r.surface.gnormal = r.surface.tan.c1;
+  r.surface.material_id = l.material_id;
+  r.radiance = f3(l.exitance[0], l.exitance[1], l.exitance[2]) * kOneOverPi;
+  r.area_density = 1.0f / (l.size[0] * l.size[1]);
+  r.light_density = l.weight;
+  r.directional = l.diffuse == 0.0f;
+  return r;
+}
+
+// BPTBase::_connect(light, eye) without the visibility factor (BPT.cpp:194-223)
+__device__ __forceinline__ float3 connect_vertices(const DeviceScene& sc, const Vertex& light, const Vertex& eye, float beta) {
+  const float3 omega = normalize(eye.s.pos - light.s.pos);
+  const BsdfQuery lb = bsdf_query(sc, light.s, light.omega, omega);
+  const BsdfQuery eb = bsdf_query(sc, eye.s, -omega, eye.omega);
+  const Edge edge(light.s.pos, light.s.normal(), eye.s.pos, eye.s.normal(), omega);
+  const float Ap = (light.w1 * beta_fn(lb.density_rev, beta) + light.w0 * float(light.finite)) * beta_fn(edge.b_geometry * eb.density_rev, beta);
+  const float Cp = (eye.w1 * beta_fn(eb.density, beta) + eye.w0 * float(eye.finite)) * beta_fn(edge.f_geometry * lb.density, beta);
+  const float weight_inv = Ap + Cp + 1.0f;
+  const float3 result = light.thr * lb.throughput * eye.thr * eb.throughput * edge.b_cos * edge.f_geometry;
+  return l1norm(result) < kFltEpsilon ? f3(0.0f) : result / weight_inv;
+}
+
+// BPTBase::_connect_light (BPT.cpp:225-243)
+__device__ __forceinline__ float3 connect_light(const DeviceScene& sc, const Vertex& eye, float beta) {
+  const BsdfQuery b = bsdf_query(sc, eye.s, f3(0.0f), eye.omega);
+  if (l1norm(b.throughput) < kFltMin) return f3(0.0f);
+  float3 lr; float ld;
+  query_lsdf(sc, eye.s, eye.omega, lr, ld);
+  const float Cp = (eye.w1 * beta_fn(b.density, beta) + eye.w0 * float(eye.finite)) * beta_fn(ld, beta);
+  return lr * eye.thr / (Cp + 1.0f);
+}
+
+// Technique::_camera_coefficient (Technique.cpp:246-274)
+__device__ __forceinline__ float camera_coefficient(float3 light_omega, float3 light_gnormal, float3 light_normal, float3 eye_omega,
+                                                    float3 eye_normal) {
+  const float normal_c = fabsf(dot(eye_omega, light_gnormal) * dot(light_omega, light_normal) /
+                               (dot(eye_omega, light_normal) * dot(light_omega, light_gnormal)));
+  const float c = fabsf(dot(eye_normal, eye_omega));
+  return normal_c * (1.0f / powf(c, 3.0f));
+}
+
+// warp-aggregated reservation of `n` consecutive queue entries per lane (one atomic per warp)
+__device__ __forceinline__ unsigned warp_reserve(unsigned* counter, unsigned n) {
+  const unsigned lane = threadIdx.x & 31u;
+  unsigned incl = n;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= unsigned(o)) incl += t;
+  }
+  const unsigned total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+  unsigned base = 0;
+  if (lane == 31 && total > 0) base = atomicAdd(counter, total);
+  base = __shfl_sync(0xFFFFFFFFu, base, 31);
+  return base + incl - n;
+}
+
+__global__ void __launch_bounds__(256) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0) {
+  const DeviceScene& sc = cfg.scene;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    cnt->trace_count[parity ^ 1] = 0;
+    cnt->pair_count[parity ^ 1] = 0;
+    cnt->shadow_count[parity ^ 1] = 0;
+  }
+  const float beta = cfg.params.beta;
+  const float roulette = cfg.params.roulette;
+  const float roulette_inv = 1.0f / roulette;
+  const uint32_t max_subpath = cfg.params.max_subpath ? cfg.params.max_subpath : 1024u;
+  // pool.size is a multiple of the block size: all lanes of a warp run the same trip count (warp_* helpers below)
+  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < pool.size; slot += gridDim.x * blockDim.x) {
+    const uint32_t st0 = pool.state[slot];
+    uint32_t st = st0;
+    bool want_trace = false, finished = false;
+    uint32_t emit_n = 0, emit_flags = 0;  // pair descriptors to write after the branches
+    bool emit_nee = false, emit_skip_first = false;
+    uint32_t head = kInvalid, count = 0;
+    uint32_t ray_mesh_only = 0;
+    float3 O = f3(0.f), rad = f3(0.f);
+    Rng rng; rng.key = 0; rng.ctr = 0;
+    Vertex cur;
+    BsdfSample bs;
+    bs.omega = f3(0.f); bs.throughput = f3(0.f); bs.density = 0.f; bs.density_rev = 0.f; bs.finite = 1;
+    bool cur_dirty = false;
+
+    if (st != kDone) {
+      if (st == kNew && slot >= pool.valid) {
+        finished = true;  // padding slot
+      } else if (st == kNew) {
+        // Technique::_for_each_ray (Technique.cpp:321-331): jitter, primary direction
+        const uint32_t pixel = slot % cfg.pixels;
+        const uint32_t pass = batch_pass0 + slot / cfg.pixels;
+        const uint32_t sample = cfg.params.first_sample + pass * (cfg.params.sample_stride ? cfg.params.sample_stride : 1u);
+        rng.key = stream_key(cfg.params.seed, kDomainPixel, pixel, sample);
+        const float3 dir = shoot_primary(cfg, rng, pixel);
+        (void)dir;  // recomputed from the stream at kEyeStart; the light phase comes first (BPT.cpp:23)
+        pool.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (roulette < rng.sample()) {  // BPT.cpp:19-21
+          finished = true;
+        } else if (roulette < rng.sample()) {  // _traceLight, BPT.cpp:126-128: empty light path
+          head = kInvalid; count = 0;
+          st = kEyeStart;
+        } else {
+          const LightSample ls = sample_light(sc, rng);
+          cur = sample_to_vertex(ls, roulette_inv, beta);
+          const unsigned idx = warp_append(&cnt->lv_count, true);
+          if (idx >= pool.lv_capacity) {
+            atomicAdd(&cnt->capacity_events, 1ull);
+            head = kInvalid; count = 0;
+            st = kEyeStart;
+          } else {
+            store_pool_vertex(pool, idx, cur);
+            pool.lv_link[idx] = kInvalid;
+            head = idx; count = 1;
+            cur_dirty = true;
+            st = kLightLoop;
+          }
+        }
+      } else {
+        const uint2 rs = pool.rng[slot];
+        rng.key = rs.x; rng.ctr = rs.y;
+        head = pool.lp_head[slot]; count = pool.lp_count[slot];
+        const float4 rv = pool.rad[slot];
+        rad = f3(rv.x, rv.y, rv.z);
+        cur = load_slot_vertex(pool, slot);
+        const float4 bo = pool.bs_omega[slot], bt = pool.bs_thr[slot], ro = pool.ray_o[slot];
+        bs.omega = f3(bo.x, bo.y, bo.z); bs.density = bo.w;
+        bs.throughput = f3(bt.x, bt.y, bt.z); bs.density_rev = bt.w;
+        bs.finite = __float_as_uint(ro.w) & 1u;
+        O = f3(ro.x, ro.y, ro.z);
+      }
+
+      if (st == kLightWait) {
+        // ---- _traceLight loop body after intersectMesh (BPT.cpp:139-176)
+        const float4 hv = pool.hit[slot];
+        const uint32_t tri = __float_as_uint(hv.w);
+        if (tri == kInvalid) {
+          st = kLightFinal;
+        } else {
+          Vertex nv;
+          nv.s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, bs.omega);
+          nv.omega = -bs.omega;
+          const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
+          nv.thr = cur.thr * bs.throughput * edge.b_cos * roulette_inv;
+          if (l1norm(nv.thr) < kFltEpsilon) {
+            st = kLightFinal;  // path.pop_back(); break;  — prv is untouched
+          } else {
+            nv.thr /= bs.density;
+            cur.finite = min(cur.finite, bs.finite);
+            nv.finite = bs.finite;
+            nv.w0 = 1.0f / beta_fn(edge.f_geometry * bs.density, beta);
+            nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + cur.w0 * float(cur.finite)) * beta_fn(edge.b_geometry, beta) * nv.w0;
+            if (bs.finite == 0) {
+              store_pool_vertex(pool, head, nv);  // path[prv] = path[itr]; path.pop_back();
+              cur = nv; cur_dirty = true;
+              st = kLightLoop;
+            } else {
+              // path[prv].finite was updated in place
+              pool.lv[size_t(head) * kVertexFloat4s + 1].w = __uint_as_float(cur.finite);
+              unsigned idx = kInvalid;
+              if (count < max_subpath) idx = atomicAdd(&cnt->lv_count, 1u);
+              if (idx >= pool.lv_capacity) {
+                atomicAdd(&cnt->capacity_events, 1ull);  // truncated here: the stored prefix stays valid
+                cur_dirty = true;
+                st = kLightFinal;
+              } else {
+                store_pool_vertex(pool, idx, nv);
+                pool.lv_link[idx] = head;
+                head = idx; ++count;
+                cur = nv; cur_dirty = true;
+                st = kLightLoop;
+              }
+            }
+          }
+        }
+      }
+
+      if (st == kLightLoop) {
+        if (roulette < rng.sample()) {  // while (!_russian_roulette(generator))
+          st = kLightFinal;
+        } else {
+          bs = bsdf_sample(sc, rng, cur.s, cur.omega);
+          O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);  // Scene::intersectMesh (Scene.cpp:204-208)
+          ray_mesh_only = 1;
+          want_trace = true;
+          st = kLightWait;
+        }
+      }
+
+      if (st == kLightFinal) {
+        // BPT.cpp:184-191: one more BSDF sample at the last vertex; a delta vertex cannot be connected
+        const BsdfSample last = bsdf_sample(sc, rng, cur.s, cur.omega);
+        if (last.finite == 0) {
+          head = pool.lv_link[head];
+          --count;
+        }
+        st = kEyeStart;
+      }
+
+      if (st == kEyeStart) {
+        // ---- BPT.cpp:26-34: the camera vertex
+        Rng first; first.key = rng.key; first.ctr = 0;  // the two jitter draws open the stream (Technique.cpp:322)
+        const float3 dir = shoot_primary(cfg, first, slot % cfg.pixels);
+        cur.s = cfg.camera;
+        cur.omega = -dir;
+        cur.thr = f3(1.0f) * roulette_inv;
+        cur.finite = 1; cur.w0 = 0.0f; cur.w1 = 0.0f;
+        cur_dirty = true;
+        emit_n = count; emit_flags = kPairCamera;  // _connect_eye: every light vertex, no next-event sample
+        bs = bsdf_sample(sc, rng, cur.s, cur.omega);  // CameraBSDF::sample: no draws
+        O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);
+        ray_mesh_only = 0;
+        want_trace = true;
+        st = kEyeWait;
+      } else if (st0 == kEyeWait) {
+        // ---- BPT.cpp:45-97: consume the closest hit of the extension ray
+        const float4 hv = pool.hit[slot];
+        const uint32_t tri = __float_as_uint(hv.w);
+        if (tri == kInvalid) {
+          if (cur.s.is_camera()) {  // sky_gradient(bsdf.omega) *= _roulette_inv  (Technique.cpp:87-89)
+            const float3 h = f3(cfg.params.sky_horizon[0], cfg.params.sky_horizon[1], cfg.params.sky_horizon[2]);
+            const float3 z = f3(cfg.params.sky_zenith[0], cfg.params.sky_zenith[1], cfg.params.sky_zenith[2]);
+            rad = (h * (1 - bs.omega.z) + z * bs.omega.z) * roulette_inv;
+          }
+          finished = true;
+        } else {
+          Vertex nv;
+          nv.s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, bs.omega);
+          nv.omega = -bs.omega;
+          const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
+          nv.thr = cur.thr * bs.throughput * edge.b_cos;
+          if (l1norm(nv.thr) < kFltEpsilon) {
+            finished = true;
+          } else {
+            nv.thr /= bs.density;
+            cur.finite = min(cur.finite, bs.finite);
+            nv.finite = bs.finite;
+            nv.w0 = 1.0f / beta_fn(edge.f_geometry * bs.density, beta);
+            nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + cur.w0 * float(cur.finite)) * beta_fn(edge.b_geometry, beta) * nv.w0;
+            if (nv.s.is_light()) {
+              rad += connect_light(sc, nv, beta);
+              // surface = _scene->intersect(surface, bsdf.omega): on through the light, eye[prv] stays
+              O = offset_origin(nv.s.pos, nv.s.gnormal, bs.omega);
+              cur_dirty = true;  // eye[prv].finite
+              ray_mesh_only = 0;
+              want_trace = true;
+            } else {
+              cur = nv; cur_dirty = true;  // std::swap(itr, prv)
+              if (roulette < rng.sample()) {
+                finished = true;
+              } else {
+                cur.thr = cur.thr * roulette_inv;
+                // ---- _connect(context, eye, path) (BPT.cpp:272-291)
+                if (!(roulette < rng.sample())) {
+                  const LightSample ls = sample_light(sc, rng);
+                  if (!ls.directional) {
+                    emit_nee = true;
+                    const uint32_t light_id = sc.materials[ls.surface.material_index()].light_id;
+                    pool.nee[slot] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
+                  } else {
+                    atomicAdd(&cnt->capacity_events, 1ull);  // _connect_directional: sun lights are not wired into the GPU BPT yet
+                  }
+                }
+                emit_n = (count > 0 ? count - 1u : 0u) + (emit_nee ? 1u : 0u);  // light vertices 1 .. n-1 (+ the fresh sample)
+                emit_skip_first = true;
+                bs = bsdf_sample(sc, rng, cur.s, cur.omega);
+                O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);
+                ray_mesh_only = 0;
+                want_trace = true;
+              }
+            }
+          }
+        }
+      }
+
+      if (finished) {
+        pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+        st = kDone;
+      } else {
+        if (cur_dirty) store_slot_vertex(pool, slot, cur);
+        pool.rng[slot] = make_uint2(rng.key, rng.ctr);
+        pool.lp_head[slot] = head; pool.lp_count[slot] = count;
+        if (st0 == kEyeWait) pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+        if (want_trace) {
+          pool.bs_omega[slot] = make_float4(bs.omega.x, bs.omega.y, bs.omega.z, bs.density);
+          pool.bs_thr[slot] = make_float4(bs.throughput.x, bs.throughput.y, bs.throughput.z, bs.density_rev);
+          pool.ray_o[slot] = make_float4(O.x, O.y, O.z, __uint_as_float((bs.finite & 1u) | (ray_mesh_only << 1)));
+        }
+      }
+      pool.state[slot] = st;
+    }
+
+    // ---- converged: queue appends
+    {
+      const unsigned mask = __ballot_sync(0xFFFFFFFFu, finished);
+      if (mask && (threadIdx.x & 31u) == 0) atomicAdd(&cnt->done, unsigned(__popc(mask)));
+    }
+    const unsigned tq = warp_append(&cnt->trace_count[parity], want_trace);
+    if (want_trace) pool.trace_q[tq] = slot;
+    unsigned pq = warp_reserve(&cnt->pair_count[parity], emit_n);
+    if (emit_n) {
+      if (pq + emit_n > pool.q_capacity) {
+        atomicAdd(&cnt->capacity_events, 1ull);
+      } else {
+        if (emit_nee) pool.pair_q[pq++] = make_uint2(slot, kNeeVertex);
+        for (uint32_t v = head; v != kInvalid;) {
+          const uint32_t prev = pool.lv_link[v];
+          if (!(emit_skip_first && prev == kInvalid)) pool.pair_q[pq++] = make_uint2(slot | emit_flags, v);
+          v = prev;
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) bpt_connect_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+  const DeviceScene& sc = cfg.scene;
+  const uint32_t n = min(cnt->pair_count[parity], pool.q_capacity);
+  const float beta = cfg.params.beta;
+  const float roulette_inv = 1.0f / cfg.params.roulette;
+  const uint32_t rounds = (n + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
+  for (uint32_t r = 0; r < rounds; ++r) {
+    const uint32_t i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+    bool want = false;
+    float3 a = f3(0.f), d = f3(0.f), c = f3(0.f);
+    uint32_t target = 0, flags = 0;
+    if (i < n) {
+      const uint2 desc = pool.pair_q[i];
+      const uint32_t slot = desc.x & ~kPairCamera;
+      const bool camera = (desc.x & kPairCamera) != 0u;
+      const Vertex eye = load_slot_vertex(pool, slot);
+      Vertex light;
+      if (desc.y == kNeeVertex) {
+        const float4 nr = pool.nee[slot];
+        light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), roulette_inv, beta);
+      } else {
+        light = load_pool_vertex(pool, desc.y);
+      }
+      bool inside = true;
+      if (camera) {
+        // Technique::_accumulate (Technique.cpp:276-305): which pixel the light vertex projects to
+        const float3 omega = normalize(light.s.pos - eye.s.pos);
+        mat3 w2v;
+        const float* m = cfg.params.camera.world_to_view;
+        w2v.c0 = f3(m[0], m[1], m[2]); w2v.c1 = f3(m[3], m[4], m[5]); w2v.c2 = f3(m[6], m[7], m[8]);
+        const float3 vd = mul(w2v, omega);
+        const float2 pp = pixel_position(vd, cfg.width_f, cfg.height_f, cfg.res_y_inv, cfg.params.camera.focal_length_y);
+        inside = (0 <= pp.x) && (pp.x < cfg.width_f) && (0 <= pp.y) && (pp.y < cfg.height_f);
+        if (inside) {
+          const uint32_t pixel = uint32_t(int(pp.y)) * cfg.params.width + uint32_t(int(pp.x));
+          target = (slot / cfg.pixels) * cfg.pixels + pixel;  // same pass, other pixel
+          flags = kShadowSplat;
+          const float cc = camera_coefficient(light.omega, light.s.gnormal, light.s.normal(), omega, eye.s.normal());
+          c = connect_vertices(sc, light, eye, beta) * cfg.focal_factor_y * cc;
+        }
+      } else {
+        target = slot;
+        c = connect_vertices(sc, light, eye, beta);
+      }
+      if (inside) {
+        const float l1 = l1norm(c);
+        if (!isfinite(l1)) {
+          // the reference multiplies by occluded() first: 0 * inf = NaN, so a non-finite connection poisons the
+          // sample whether or not it is visible, and _commit_images drops it (Technique.cpp:224-230)
+          if (flags & kShadowSplat) {
+            atomicAdd(pool.splat + size_t(target) * 3, double(NAN));
+          } else {
+            atomicAdd(&pool.rad[target].x, NAN);
+          }
+        } else if (l1 != 0.0f) {
+          // Scene::occluded(eye.surface, light.surface) (Scene.cpp:151-171)
+          const float3 direction = normalize(light.s.pos - eye.s.pos);
+          a = eye.s.pos + (dot(eye.s.gnormal, direction) > 0.0f ? 1.0f : -1.0f) * eye.s.gnormal * 0.0001f;
+          const float3 b = light.s.pos + (dot(light.s.gnormal, direction) < 0.0f ? 1.0f : -1.0f) * light.s.gnormal * 0.0001f;
+          d = b - a;
+          want = true;
+        }
+      }
+    }
+    const unsigned sq = warp_append(&cnt->shadow_count[parity], want);
+    if (want) {
+      if (sq < pool.q_capacity) {
+        float4* e = pool.shadow_q + size_t(sq) * 3;
+        e[0] = make_float4(a.x, a.y, a.z, __uint_as_float(target));
+        e[1] = make_float4(d.x, d.y, d.z, __uint_as_float(flags));
+        e[2] = make_float4(c.x, c.y, c.z, 0.f);
+      } else {
+        atomicAdd(&cnt->capacity_events, 1ull);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) bpt_trace_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+  const uint32_t n = cnt->trace_count[parity];
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t slot = pool.trace_q[i];
+    const float4 o = pool.ray_o[slot], d = pool.bs_omega[slot];
+    const uint32_t mask = (__float_as_uint(o.w) & 2u) ? kMaskMesh : kMaskAll;
+    const Hit h = trace_ray_masked<false>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY, mask);
+    pool.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+  }
+}
+
+__global__ void __launch_bounds__(256) bpt_shadow_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+  const uint32_t n = min(cnt->shadow_count[parity], pool.q_capacity);
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->shadow_rays, (unsigned long long)n);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4* e = pool.shadow_q + size_t(i) * 3;
+    const float4 o = e[0], d = e[1], c = e[2];
+    const uint32_t target = __float_as_uint(o.w), flags = __float_as_uint(d.w);
+    const Hit h = trace_ray<true, true>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, 1.0f);
+    if (h.tri == kInvalid) {
+      if (flags & kShadowSplat) {
+        double* s = pool.splat + size_t(target) * 3;
+        atomicAdd(s + 0, double(c.x)); atomicAdd(s + 1, double(c.y)); atomicAdd(s + 2, double(c.z));
+      } else {
+        float* r = &pool.rad[target].x;
+        atomicAdd(r + 0, c.x); atomicAdd(r + 1, c.y); atomicAdd(r + 2, c.z);
+      }
+    }
+  }
+}
+
+// Technique::_commit_images (Technique.cpp:194-244) for the passes of one batch: per pixel and pass,
+// view[p] += (light[p] + eye[p], 1) unless non-finite; the helpers are zeroed for the next batch.
+__global__ void __launch_bounds__(256) bpt_commit_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, uint32_t batch_pass0,
+                                                         uint32_t batch_passes) {
+  for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < cfg.pixels; pixel += gridDim.x * blockDim.x) {
+    double sum[4] = {0.0, 0.0, 0.0, 0.0};
+    for (uint32_t k = 0; k < batch_passes; ++k) {
+      const uint32_t slot = k * cfg.pixels + pixel;
+      const float4 e = pool.rad[slot];
+      double* s = pool.splat + size_t(slot) * 3;
+      const double r = s[0] + double(e.x), g = s[1] + double(e.y), b = s[2] + double(e.z);
+      s[0] = 0.0; s[1] = 0.0; s[2] = 0.0;
+      if (cfg.path_radiance) {
+        float* o = cfg.path_radiance + (size_t(batch_pass0 + k) * cfg.pixels + pixel) * 3;
+        o[0] = e.x; o[1] = e.y; o[2] = e.z;
+      }
+      if (isfinite(fabs(r) + fabs(g) + fabs(b))) {
+        sum[0] += r; sum[1] += g; sum[2] += b; sum[3] += 1.0;
+      } else {
+        atomicAdd(&cnt->numeric_errors, 1ull);
+      }
+    }
+    double* a = cfg.accum + size_t(pixel) * 4;
+    a[0] += sum[0]; a[1] += sum[1]; a[2] += sum[2]; a[3] += sum[3];
+  }
+}
+
+struct BptWorkspace {
+  BptPool pool{};
+  BptCounters* counters = nullptr;
+  BptCounters* host_counters = nullptr;  // pinned
+  std::vector<void*> blocks;
+};
+
+void bpt_workspace_free(void* p) {
+  BptWorkspace* w = (BptWorkspace*)p;
+  for (void* q : w->blocks) cudaFree(q);
+  if (w->host_counters) cudaFreeHost(w->host_counters);
+  delete w;
+}
+
+template <class T>
+int ws_alloc(BptWorkspace* w, T** p, size_t count) {
+  void* q = nullptr;
+  B2_CUDA(cudaMalloc(&q, count * sizeof(T)));
+  w->blocks.push_back(q);
+  *p = (T*)q;
+  return B2PT_OK;
+}
+
+int bpt_workspace(b2pt_scene_s* scene, uint32_t size, BptWorkspace** out) {
+  BptWorkspace* w = (BptWorkspace*)scene->workspace;
+  if (w && scene->workspace_free == bpt_workspace_free && w->pool.size == size) { *out = w; return B2PT_OK; }
+  if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
+  scene->workspace = nullptr;
+  w = new BptWorkspace();
+  scene->workspace = w; scene->workspace_free = bpt_workspace_free;
+  BptPool& p = w->pool;
+  p.size = size;
+  p.lv_capacity = size * 12u < 4096u ? 4096u : size * 12u;
+  p.q_capacity = p.lv_capacity + size;
+  int rc;
+  if ((rc = ws_alloc(w, &p.state, size))) return rc;
+  if ((rc = ws_alloc(w, &p.rng, size))) return rc;
+  if ((rc = ws_alloc(w, &p.cv, size_t(size) * kVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.bs_omega, size))) return rc;
+  if ((rc = ws_alloc(w, &p.bs_thr, size))) return rc;
+  if ((rc = ws_alloc(w, &p.ray_o, size))) return rc;
+  if ((rc = ws_alloc(w, &p.hit, size))) return rc;
+  if ((rc = ws_alloc(w, &p.rad, size))) return rc;
+  if ((rc = ws_alloc(w, &p.nee, size))) return rc;
+  if ((rc = ws_alloc(w, &p.splat, size_t(size) * 3))) return rc;
+  if ((rc = ws_alloc(w, &p.lp_head, size))) return rc;
+  if ((rc = ws_alloc(w, &p.lp_count, size))) return rc;
+  if ((rc = ws_alloc(w, &p.lv, size_t(p.lv_capacity) * kVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.lv_link, p.lv_capacity))) return rc;
+  if ((rc = ws_alloc(w, &p.trace_q, size))) return rc;
+  if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
+  if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
+  if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
+  B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(BptCounters)));
+  B2_CUDA(cudaMemset(p.splat, 0, size_t(size) * 3 * sizeof(double)));
+  *out = w;
+  return B2PT_OK;
+}
+
+}  // namespace
+
+int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
+  const int block = 256;
+  const uint32_t pixels = base.pixels;
+  const uint32_t num_passes = base.params.num_samples;
+  // a batch is a whole number of passes, at most 2^21 paths (or one pass if the window is larger)
+  uint32_t passes_per_batch = (1u << 21) / pixels;
+  if (passes_per_batch < 1) passes_per_batch = 1;
+  if (passes_per_batch > num_passes) passes_per_batch = num_passes;
+  const uint32_t size = (passes_per_batch * pixels + block - 1) / block * block;
+  BptWorkspace* w = nullptr;
+  if (int rc = bpt_workspace(scene, size, &w)) return rc;
+  RenderConfig cfg = base;
+  cfg.pool_size = size;
+  StageTimer timer(stream);
+  const int grid = grid_for(size, block);
+  unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
+  const int kBatchIters = 8;
+  for (uint32_t pass0 = 0; pass0 < num_passes; pass0 += passes_per_batch) {
+    const uint32_t passes = min(passes_per_batch, num_passes - pass0);
+    BptPool pool = w->pool;
+    pool.valid = passes * pixels;  // the last batch may be shorter; SoA strides shrink with it, which is fine
+    pool.size = (pool.valid + block - 1) / block * block;
+    B2_CUDA(cudaMemsetAsync(w->counters, 0, sizeof(BptCounters), stream));
+    B2_CUDA(cudaMemsetAsync(pool.state, 0, size_t(pool.size) * 4, stream));
+    for (int it = 0;;) {
+      for (int k = 0; k < kBatchIters; ++k, ++it) {
+        const int parity = it & 1;
+        timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, stream>>>(cfg, pool, w->counters, parity, pass0); timer.end();
+        timer.begin(kStageShade); bpt_connect_kernel<<<grid, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+        timer.begin(kStageTrace); bpt_trace_kernel<<<grid, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+        timer.begin(kStageShadow); bpt_shadow_kernel<<<grid, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+      }
+      B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, stream));
+      B2_CUDA(cudaStreamSynchronize(stream));
+      timer.resolve();
+      if (w->host_counters->done >= pool.size) break;
+      if (it > (1 << 20)) { set_error("render_bpt: the batch did not drain"); return B2PT_ERR_CUDA; }
+    }
+    timer.begin(kStageShade);
+    bpt_commit_kernel<<<grid_for(pixels, block), block, 0, stream>>>(cfg, pool, w->counters, pass0, passes);
+    timer.end();
+    B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));
+    timer.resolve();
+    basic += w->host_counters->basic_rays; shadow += w->host_counters->shadow_rays;
+    numeric += w->host_counters->numeric_errors; capacity += w->host_counters->capacity_events;
+  }
+  B2_CUDA(cudaGetLastError());
+  if (stats) {
+    stats->num_basic_rays = basic;
+    stats->num_shadow_rays = shadow;
+    stats->numeric_errors = numeric;
+    stats->capacity_events = capacity;
+    timer.fill(stats);
+  }
+  return B2PT_OK;
+}
+
+}  // namespace b2pt

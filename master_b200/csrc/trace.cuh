@@ -41,16 +41,14 @@ __device__ __forceinline__ float3 cross_embree(float3 a, float3 b) {
 }
 
 // Returns true and updates (tfar, u, v) when triangle `pos` is hit inside (tnear, tfar).
-template <bool kMeshOnly>
+// ray_mask: RTCRay::mask — 0xFFFFFFFF (Scene::intersect) or 1 << entity_type::mesh (intersectMesh / occluded).
 __device__ __forceinline__ bool intersect_triangle(const DeviceScene& sc, uint32_t pos, float3 O, float3 D, float tnear,
-                                                   float& tfar, float& u, float& v) {
+                                                   float& tfar, float& u, float& v, uint32_t ray_mask) {
   const float4 q0 = __ldg(&sc.tri_v0[pos]);
   const float4 q1 = __ldg(&sc.tri_e1[pos]);
   const float4 q2 = __ldg(&sc.tri_e2[pos]);
-  if (kMeshOnly) {
-    // ray.mask = 1 << entity_type::mesh (Scene.cpp:169); geometry mask = 1 << (material_id & 3) (Scene.cpp:47)
-    if ((__float_as_uint(q2.w) & (1u << B2PT_ENTITY_MESH)) == 0u) return false;
-  }
+  // geometry mask = 1 << (material_id & 3) (rtcSetMask, Scene.cpp:47); Embree skips the triangle when (mask & ray.mask) == 0
+  if ((__float_as_uint(q2.w) & ray_mask) == 0u) return false;
   const float3 v0 = f3(q0.x, q0.y, q0.z), e1 = f3(q1.x, q1.y, q1.z), e2 = f3(q2.x, q2.y, q2.z);
   const float3 Ng = cross_embree(e1, e2);  // Triangle4 stores Ng = cross(e1, e2)
   const float3 C = f3(__fsub_rn(v0.x, O.x), __fsub_rn(v0.y, O.y), __fsub_rn(v0.z, O.z));
@@ -74,9 +72,12 @@ __device__ __forceinline__ void cswap(float& ta, uint32_t& ca, float& tb, uint32
   if (tb < ta) { float t = ta; ta = tb; tb = t; uint32_t c = ca; ca = cb; cb = c; }
 }
 
-// kAnyHit: stop at the first accepted triangle (rtcOccluded).  kMeshOnly: ray mask = meshes only.
-template <bool kAnyHit, bool kMeshOnly>
-__device__ __forceinline__ Hit trace_ray(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar) {
+constexpr uint32_t kMaskAll = 0xFFFFFFFFu;
+constexpr uint32_t kMaskMesh = 1u << B2PT_ENTITY_MESH;
+
+// kAnyHit: stop at the first accepted triangle (rtcOccluded).
+template <bool kAnyHit>
+__device__ __forceinline__ Hit trace_ray_masked(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar, uint32_t ray_mask) {
   Hit hit; hit.t = tfar; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
   // safe reciprocal direction: a zero component becomes +-huge instead of inf so 0*inf never appears
   const float kHuge = 1e30f;
@@ -124,7 +125,7 @@ __device__ __forceinline__ Hit trace_ray(const DeviceScene& sc, float3 O, float3
     } else {
       const uint32_t first = leaf_first(cur), count = leaf_count(cur);
       for (uint32_t k = 0; k < count; ++k) {
-        if (intersect_triangle<kMeshOnly>(sc, first + k, O, D, tnear, hit.t, hit.u, hit.v)) {
+        if (intersect_triangle(sc, first + k, O, D, tnear, hit.t, hit.u, hit.v, ray_mask)) {
           hit.tri = first + k;
           if (kAnyHit) return hit;
         }
@@ -134,6 +135,12 @@ __device__ __forceinline__ Hit trace_ray(const DeviceScene& sc, float3 O, float3
     }
   }
   return hit;
+}
+
+// kMeshOnly: ray mask = meshes only (compile-time form of the above)
+template <bool kAnyHit, bool kMeshOnly>
+__device__ __forceinline__ Hit trace_ray(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar) {
+  return trace_ray_masked<kAnyHit>(sc, O, D, tnear, tfar, kMeshOnly ? kMaskMesh : kMaskAll);
 }
 
 // geomID / primID of a triangle in leaf order
