@@ -1,0 +1,39 @@
+"""The C++ drop-in: the reference's own Technique interface (haste::Technique::render, driven like
+Application::render / Framework::runBatch do) with master_b200/host/GpuTechnique plugged in.  The binary is the
+reference's classes + GpuTechnique.cpp + libb2pt.so (master_b200/host/build_host.sh)."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, golden_path
+
+HOST = os.path.join(ROOT, "master_b200", "host", "_build", "b2pt_master")
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not os.path.exists(HOST), reason="master_b200/host/_build/b2pt_master not built")]
+
+
+@pytest.mark.parametrize("name,tech", [("CornellBoxDiffuse", "PT"), ("CornellBoxDiffuse", "BPT"), ("CornellBoxSpecular", "BPT")])
+def test_gpu_technique_behind_the_reference_interface(name, tech, tmp_path):
+    g = np.load(golden_path("render_%s_%s.npz" % (name, tech)))
+    w, h, spp = int(g["width"]), int(g["height"]), g["paths"].shape[0]
+    out = str(tmp_path / "accum.f64")
+    r = subprocess.run([HOST, golden_path("scenes", name + ".b2s"), "technique=" + tech, "width=%d" % w, "height=%d" % h,
+                        "num_samples=%d" % spp, "seed=%d" % int(g["seed"]), "out=" + out], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    info = json.loads(r.stdout.strip().splitlines()[-1])
+    accum = np.fromfile(out, dtype=np.float64).reshape(-1, 4)
+    ref = g["accum"]
+    assert info["num_samples"] == spp and np.all(accum[:, 3] == ref[:, 3])
+    # same streams as the golden: pixels whose paths took the same decisions agree to 1e-4
+    scale = np.maximum(np.abs(ref[:, :3]).max(axis=1), 1e-6)
+    close = (np.abs(accum[:, :3] - ref[:, :3]).max(axis=1) / scale <= 1e-4).mean()
+    print(json.dumps(dict(scene=name, technique=tech, pixels_within_1e4=float(close), info=info)))
+    assert close >= 0.98
+    np.testing.assert_allclose(accum[:, :3].mean(axis=0), ref[:, :3].mean(axis=0), rtol=3e-2)
+
+
+def test_missing_scene_is_an_exception_not_a_crash():
+    r = subprocess.run([HOST, "/nonexistent.b2s"], capture_output=True, text=True)
+    assert r.returncode == 1 and "cannot open" in r.stderr
