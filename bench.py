@@ -169,6 +169,7 @@ def main():
 
     from master_b200 import api
     from master_b200.scene import load_b2s
+    from master_b200.dist import reduce_film, sample_split
     from master_b200.technique import GpuTechnique
 
     if not torch.cuda.is_available():
@@ -187,9 +188,8 @@ def main():
     N = world
 
     def step(i):
-        # global sample index = (i * spp + j) * N + rank  for pass j of step i
-        return tech.render_device(accum.data_ptr(), W, H, passes=a.spp, stream=stream,
-                                  first_sample=i * a.spp * N + rank, sample_stride=N)
+        first, stride = sample_split(rank, N, i, a.spp)  # global sample (i * spp + j) * N + rank for pass j
+        return tech.render_device(accum.data_ptr(), W, H, passes=a.spp, stream=stream, first_sample=first, sample_stride=stride)
 
     def barrier():
         if world > 1:
@@ -213,8 +213,7 @@ def main():
             tot[k] += getattr(s, k)
         for k in ms:
             ms[k] += getattr(s, k)
-    if world > 1:
-        dist.all_reduce(accum)  # the one collective of the path: sum of the per-rank films
+    reduce_film(accum)  # the one collective of the path: sum of the per-rank films (no-op at N = 1)
     e1.record()
     barrier()
     sampler.stop_flag = True
