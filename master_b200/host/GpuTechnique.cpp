@@ -18,6 +18,21 @@ static void check(int rc, const char* what) {
   if (rc != B2PT_OK) throw std::runtime_error(std::string(what) + ": " + b2pt_last_error());
 }
 
+#ifdef B2PT_HAVE_OPTIONS_HPP
+// Options -> GpuOptions, the argument sets of make_bpt_technique / make_upg_technique / PT (make_technique.cpp:86-139)
+GpuOptions GpuOptions::from(const haste::Options& o) {
+  GpuOptions g;
+  g.technique = o.technique == Options::PT ? B2PT_TECHNIQUE_PT : o.technique == Options::BPT ? B2PT_TECHNIQUE_BPT
+              : o.technique == Options::VCM ? B2PT_TECHNIQUE_VCM : B2PT_TECHNIQUE_UPG;
+  g.beta = float(o.beta); g.roulette = float(o.roulette); g.lights = o.lights;
+  g.max_path = o.max_path == size_t(PTRDIFF_MAX) ? 0 : o.max_path;
+  g.radius = float(o.radius); g.alpha = float(o.alpha); g.num_photons = o.num_photons;
+  g.enable_vc = o.enable_vc; g.enable_vm = o.enable_vm; g.from_light = o.from_light;
+  g.fixed_seed = o.enable_seed; g.seed = uint32_t(o.seed);
+  return g;
+}
+#endif
+
 GpuTechnique::GpuTechnique(const shared<const Scene>& scene, const GpuOptions& options)
     : Technique(scene, 1), _options(options) {
   FlatSceneArrays flat(*scene);

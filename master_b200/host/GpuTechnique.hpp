@@ -12,6 +12,9 @@
 // caller's RandomEngine on the first call, so a seeded run is reproducible on any number of GPUs.
 #pragma once
 #include <Technique.hpp>
+#ifdef B2PT_HAVE_OPTIONS_HPP
+#include <Options.hpp>
+#endif
 
 #include "../../include/b2pt.h"
 
