@@ -588,22 +588,41 @@ __global__ void __launch_bounds__(256) bpt_commit_kernel(RenderConfig cfg, BptPo
         atomicAdd(&cnt->numeric_errors, 1ull);
       }
     }
+    // two batches (lanes) may commit at the same time: red.global.add.f64
     double* a = cfg.accum + size_t(pixel) * 4;
-    a[0] += sum[0]; a[1] += sum[1]; a[2] += sum[2]; a[3] += sum[3];
+    atomicAdd(a + 0, sum[0]); atomicAdd(a + 1, sum[1]); atomicAdd(a + 2, sum[2]); atomicAdd(a + 3, sum[3]);
   }
 }
 
-struct BptWorkspace {
+// Two batches are kept in flight on two streams ("lanes"): the late iterations of a batch have few live paths,
+// so its kernels are small and end in long single-ray tails; the other lane's kernels fill the machine meanwhile.
+constexpr int kLanes = 2;
+
+struct BptLane {
   BptPool pool{};
   BptCounters* counters = nullptr;
   BptCounters* host_counters = nullptr;  // pinned
+  cudaStream_t stream = nullptr;         // lane 0 runs on the caller's stream, lane 1 on `own_stream`
+  cudaStream_t own_stream = nullptr;
+  cudaEvent_t done = nullptr;
+};
+
+struct BptWorkspace {
+  BptLane lane[kLanes];
+  uint32_t size = 0;
+  cudaEvent_t fork = nullptr;
   std::vector<void*> blocks;
 };
 
 void bpt_workspace_free(void* p) {
   BptWorkspace* w = (BptWorkspace*)p;
   for (void* q : w->blocks) cudaFree(q);
-  if (w->host_counters) cudaFreeHost(w->host_counters);
+  for (auto& l : w->lane) {
+    if (l.host_counters) cudaFreeHost(l.host_counters);
+    if (l.own_stream) cudaStreamDestroy(l.own_stream);
+    if (l.done) cudaEventDestroy(l.done);
+  }
+  if (w->fork) cudaEventDestroy(w->fork);
   delete w;
 }
 
@@ -616,38 +635,45 @@ int ws_alloc(BptWorkspace* w, T** p, size_t count) {
   return B2PT_OK;
 }
 
-int bpt_workspace(b2pt_scene_s* scene, uint32_t size, BptWorkspace** out) {
+int bpt_workspace(b2pt_scene_s* scene, uint32_t size, int lanes, BptWorkspace** out) {
   BptWorkspace* w = (BptWorkspace*)scene->workspace;
-  if (w && scene->workspace_free == bpt_workspace_free && w->pool.size == size) { *out = w; return B2PT_OK; }
+  if (w && scene->workspace_free == bpt_workspace_free && w->size == size && (lanes == 1 || w->lane[1].counters)) { *out = w; return B2PT_OK; }
   if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
   scene->workspace = nullptr;
   w = new BptWorkspace();
   scene->workspace = w; scene->workspace_free = bpt_workspace_free;
-  BptPool& p = w->pool;
-  p.size = size;
-  p.lv_capacity = size * 12u < 4096u ? 4096u : size * 12u;
-  p.q_capacity = p.lv_capacity + size;
-  int rc;
-  if ((rc = ws_alloc(w, &p.state, size))) return rc;
-  if ((rc = ws_alloc(w, &p.rng, size))) return rc;
-  if ((rc = ws_alloc(w, &p.cv, size_t(size) * kVertexFloat4s))) return rc;
-  if ((rc = ws_alloc(w, &p.bs_omega, size))) return rc;
-  if ((rc = ws_alloc(w, &p.bs_thr, size))) return rc;
-  if ((rc = ws_alloc(w, &p.ray_o, size))) return rc;
-  if ((rc = ws_alloc(w, &p.hit, size))) return rc;
-  if ((rc = ws_alloc(w, &p.rad, size))) return rc;
-  if ((rc = ws_alloc(w, &p.nee, size))) return rc;
-  if ((rc = ws_alloc(w, &p.splat, size_t(size) * 3))) return rc;
-  if ((rc = ws_alloc(w, &p.lp_head, size))) return rc;
-  if ((rc = ws_alloc(w, &p.lp_count, size))) return rc;
-  if ((rc = ws_alloc(w, &p.lv, size_t(p.lv_capacity) * kVertexFloat4s))) return rc;
-  if ((rc = ws_alloc(w, &p.lv_link, p.lv_capacity))) return rc;
-  if ((rc = ws_alloc(w, &p.trace_q, size))) return rc;
-  if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
-  if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
-  if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
-  B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(BptCounters)));
-  B2_CUDA(cudaMemset(p.splat, 0, size_t(size) * 3 * sizeof(double)));
+  w->size = size;
+  B2_CUDA(cudaEventCreateWithFlags(&w->fork, cudaEventDisableTiming));
+  for (int k = 0; k < lanes; ++k) {
+    BptLane& l = w->lane[k];
+    BptPool& p = l.pool;
+    p.size = size;
+    p.lv_capacity = size * 12u < 4096u ? 4096u : size * 12u;
+    p.q_capacity = p.lv_capacity + size;
+    int rc;
+    if ((rc = ws_alloc(w, &p.state, size))) return rc;
+    if ((rc = ws_alloc(w, &p.rng, size))) return rc;
+    if ((rc = ws_alloc(w, &p.cv, size_t(size) * kVertexFloat4s))) return rc;
+    if ((rc = ws_alloc(w, &p.bs_omega, size))) return rc;
+    if ((rc = ws_alloc(w, &p.bs_thr, size))) return rc;
+    if ((rc = ws_alloc(w, &p.ray_o, size))) return rc;
+    if ((rc = ws_alloc(w, &p.hit, size))) return rc;
+    if ((rc = ws_alloc(w, &p.rad, size))) return rc;
+    if ((rc = ws_alloc(w, &p.nee, size))) return rc;
+    if ((rc = ws_alloc(w, &p.splat, size_t(size) * 3))) return rc;
+    if ((rc = ws_alloc(w, &p.lp_head, size))) return rc;
+    if ((rc = ws_alloc(w, &p.lp_count, size))) return rc;
+    if ((rc = ws_alloc(w, &p.lv, size_t(p.lv_capacity) * kVertexFloat4s))) return rc;
+    if ((rc = ws_alloc(w, &p.lv_link, p.lv_capacity))) return rc;
+    if ((rc = ws_alloc(w, &p.trace_q, size))) return rc;
+    if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
+    if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
+    if ((rc = ws_alloc(w, &l.counters, 1))) return rc;
+    B2_CUDA(cudaMallocHost((void**)&l.host_counters, sizeof(BptCounters)));
+    B2_CUDA(cudaMemset(p.splat, 0, size_t(size) * 3 * sizeof(double)));
+    B2_CUDA(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
+    if (k > 0) B2_CUDA(cudaStreamCreateWithFlags(&l.own_stream, cudaStreamNonBlocking));
+  }
   *out = w;
   return B2PT_OK;
 }
@@ -658,48 +684,94 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   const int block = 256;
   const uint32_t pixels = base.pixels;
   const uint32_t num_passes = base.params.num_samples;
-  // a batch is a whole number of passes, at most 2^21 paths (or one pass if the window is larger)
+  // a batch is a whole number of passes, at most 2^21 paths (or one pass if the window is larger); with more than one
+  // pass to render the passes are spread over kLanes concurrent batches
   uint32_t passes_per_batch = (1u << 21) / pixels;
   if (passes_per_batch < 1) passes_per_batch = 1;
-  if (passes_per_batch > num_passes) passes_per_batch = num_passes;
+  if (passes_per_batch > (num_passes + kLanes - 1) / kLanes) passes_per_batch = (num_passes + kLanes - 1) / kLanes;
+  const uint32_t num_batches = (num_passes + passes_per_batch - 1) / passes_per_batch;
+  const int lanes = num_batches > 1 ? kLanes : 1;
   const uint32_t size = (passes_per_batch * pixels + block - 1) / block * block;
   BptWorkspace* w = nullptr;
-  if (int rc = bpt_workspace(scene, size, &w)) return rc;
+  if (int rc = bpt_workspace(scene, size, lanes, &w)) return rc;
   RenderConfig cfg = base;
   cfg.pool_size = size;
-  StageTimer timer(stream);
   const int grid = grid_for(size, block);
   unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
   const int kBatchIters = 8;
-  for (uint32_t pass0 = 0; pass0 < num_passes; pass0 += passes_per_batch) {
-    const uint32_t passes = min(passes_per_batch, num_passes - pass0);
-    BptPool pool = w->pool;
-    pool.valid = passes * pixels;  // the last batch may be shorter; SoA strides shrink with it, which is fine
-    pool.size = (pool.valid + block - 1) / block * block;
-    B2_CUDA(cudaMemsetAsync(w->counters, 0, sizeof(BptCounters), stream));
-    B2_CUDA(cudaMemsetAsync(pool.state, 0, size_t(pool.size) * 4, stream));
-    for (int it = 0;;) {
-      for (int k = 0; k < kBatchIters; ++k, ++it) {
-        const int parity = it & 1;
-        timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, stream>>>(cfg, pool, w->counters, parity, pass0); timer.end();
-        timer.begin(kStageShade); bpt_connect_kernel<<<grid, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
-        timer.begin(kStageTrace); bpt_trace_kernel<<<grid, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
-        timer.begin(kStageShadow); bpt_shadow_kernel<<<grid, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+
+  // per-lane progress
+  struct Progress { bool active = false; uint32_t pass0 = 0, passes = 0; int it = 0; BptPool pool; };
+  Progress prog[kLanes];
+  StageTimer timer0(stream);
+  w->lane[0].stream = stream;
+  StageTimer* timers[kLanes] = {&timer0, nullptr};
+  StageTimer timer1(w->lane[1].own_stream);
+  if (lanes > 1) {
+    w->lane[1].stream = w->lane[1].own_stream;
+    timers[1] = &timer1;
+    // lane 1 starts after whatever the caller queued before this call
+    B2_CUDA(cudaEventRecord(w->fork, stream));
+    B2_CUDA(cudaStreamWaitEvent(w->lane[1].stream, w->fork, 0));
+  }
+  uint32_t next_pass = 0;
+  auto start_batch = [&](int k) -> int {
+    Progress& g = prog[k];
+    BptLane& l = w->lane[k];
+    g.active = true; g.pass0 = next_pass; g.passes = min(passes_per_batch, num_passes - next_pass); g.it = 0;
+    next_pass += g.passes;
+    g.pool = l.pool;
+    g.pool.valid = g.passes * pixels;  // the last batch may be shorter; SoA strides shrink with it, which is fine
+    g.pool.size = (g.pool.valid + block - 1) / block * block;
+    B2_CUDA(cudaMemsetAsync(l.counters, 0, sizeof(BptCounters), l.stream));
+    B2_CUDA(cudaMemsetAsync(g.pool.state, 0, size_t(g.pool.size) * 4, l.stream));
+    return B2PT_OK;
+  };
+  for (int k = 0; k < lanes && next_pass < num_passes; ++k)
+    if (int rc = start_batch(k)) return rc;
+  for (;;) {
+    bool any = false;
+    // enqueue a burst of stage iterations on every active lane, then look at the counters
+    for (int k = 0; k < lanes; ++k) {
+      Progress& g = prog[k];
+      if (!g.active) continue;
+      any = true;
+      BptLane& l = w->lane[k];
+      StageTimer& timer = *timers[k];
+      for (int j = 0; j < kBatchIters; ++j, ++g.it) {
+        const int parity = g.it & 1;
+        timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0); timer.end();
+        timer.begin(kStageShade); bpt_connect_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
+        timer.begin(kStageTrace); bpt_trace_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
+        timer.begin(kStageShadow); bpt_shadow_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
       }
-      B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, stream));
-      B2_CUDA(cudaStreamSynchronize(stream));
-      timer.resolve();
-      if (w->host_counters->done >= pool.size) break;
-      if (it > (1 << 20)) { set_error("render_bpt: the batch did not drain"); return B2PT_ERR_CUDA; }
+      B2_CUDA(cudaMemcpyAsync(l.host_counters, l.counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, l.stream));
     }
-    timer.begin(kStageShade);
-    bpt_commit_kernel<<<grid_for(pixels, block), block, 0, stream>>>(cfg, pool, w->counters, pass0, passes);
-    timer.end();
-    B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, stream));
-    B2_CUDA(cudaStreamSynchronize(stream));
-    timer.resolve();
-    basic += w->host_counters->basic_rays; shadow += w->host_counters->shadow_rays;
-    numeric += w->host_counters->numeric_errors; capacity += w->host_counters->capacity_events;
+    if (!any) break;
+    for (int k = 0; k < lanes; ++k) {
+      Progress& g = prog[k];
+      if (!g.active) continue;
+      BptLane& l = w->lane[k];
+      B2_CUDA(cudaStreamSynchronize(l.stream));
+      timers[k]->resolve();
+      if (g.it > (1 << 20)) { set_error("render_bpt: the batch did not drain"); return B2PT_ERR_CUDA; }
+      if (l.host_counters->done < g.pool.size) continue;
+      timers[k]->begin(kStageShade);
+      bpt_commit_kernel<<<grid_for(pixels, block), block, 0, l.stream>>>(cfg, g.pool, l.counters, g.pass0, g.passes);
+      timers[k]->end();
+      B2_CUDA(cudaMemcpyAsync(l.host_counters, l.counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, l.stream));
+      B2_CUDA(cudaStreamSynchronize(l.stream));
+      timers[k]->resolve();
+      basic += l.host_counters->basic_rays; shadow += l.host_counters->shadow_rays;
+      numeric += l.host_counters->numeric_errors; capacity += l.host_counters->capacity_events;
+      g.active = false;
+      if (next_pass < num_passes)
+        if (int rc = start_batch(k)) return rc;
+    }
+  }
+  if (lanes > 1) {  // the caller's stream continues after lane 1
+    B2_CUDA(cudaEventRecord(w->lane[1].done, w->lane[1].stream));
+    B2_CUDA(cudaStreamWaitEvent(stream, w->lane[1].done, 0));
   }
   B2_CUDA(cudaGetLastError());
   if (stats) {
@@ -707,7 +779,14 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     stats->num_shadow_rays = shadow;
     stats->numeric_errors = numeric;
     stats->capacity_events = capacity;
-    timer.fill(stats);
+    timer0.fill(stats);
+    if (lanes > 1) {
+      B2ptStats s1{};
+      timer1.fill(&s1);
+      stats->trace_ms += s1.trace_ms; stats->shadow_ms += s1.shadow_ms; stats->shade_ms += s1.shade_ms;
+      stats->trace_launches += s1.trace_launches; stats->shadow_launches += s1.shadow_launches;
+      stats->kernel_launches += s1.kernel_launches;
+    }
   }
   return B2PT_OK;
 }

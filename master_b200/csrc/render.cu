@@ -84,21 +84,22 @@ int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* params, double*
   using namespace b2pt;
   B2_CHECK(scene && params && view_host, B2PT_ERR_INVALID, "b2pt_render_host: null argument");
   const size_t n = size_t(params->width) * params->height * 4;
-  double* d = nullptr;
-  B2_CUDA(cudaMalloc(&d, n * sizeof(double)));
-  cudaError_t e = cudaMemset(d, 0, n * sizeof(double));
-  int rc = e == cudaSuccess ? b2pt_render(scene, params, d, nullptr, nullptr, stats) : cuda_fail(e, "cudaMemset", __FILE__, __LINE__);
-  if (rc == B2PT_OK) {
-    // view += pass sums (Technique::_commit_images adds into the caller's dvec4 buffer)
-    double* h = nullptr;
-    e = cudaMallocHost((void**)&h, n * sizeof(double));
-    if (e == cudaSuccess) e = cudaMemcpy(h, d, n * sizeof(double), cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess) for (size_t i = 0; i < n; ++i) view_host[i] += h[i];
-    if (h) cudaFreeHost(h);
-    if (e != cudaSuccess) rc = cuda_fail(e, "b2pt_render_host copy", __FILE__, __LINE__);
+  if (scene->film_doubles != n) {  // staging buffers live with the scene: one allocation per resolution, not per pass
+    if (scene->film_dev) cudaFree(scene->film_dev);
+    if (scene->film_host) cudaFreeHost(scene->film_host);
+    scene->film_dev = nullptr; scene->film_host = nullptr; scene->film_doubles = 0;
+    B2_CUDA(cudaMalloc(&scene->film_dev, n * sizeof(double)));
+    B2_CUDA(cudaMallocHost((void**)&scene->film_host, n * sizeof(double)));
+    scene->film_doubles = n;
   }
-  cudaFree(d);
-  return rc;
+  B2_CUDA(cudaMemsetAsync(scene->film_dev, 0, n * sizeof(double), nullptr));
+  int rc = b2pt_render(scene, params, scene->film_dev, nullptr, nullptr, stats);
+  if (rc != B2PT_OK) return rc;
+  // view += pass sums (Technique::_commit_images adds into the caller's dvec4 buffer)
+  B2_CUDA(cudaMemcpy(scene->film_host, scene->film_dev, n * sizeof(double), cudaMemcpyDeviceToHost));
+  const double* h = scene->film_host;
+  for (size_t i = 0; i < n; ++i) view_host[i] += h[i];
+  return B2PT_OK;
 }
 
 }  // extern "C"

@@ -16,6 +16,8 @@
 #include <cub/cub.cuh>
 #include <float.h>
 #include <math.h>
+#include <stdlib.h>
+#include <string.h>
 #include <vector>
 
 #include "scene.cuh"
@@ -187,6 +189,103 @@ __global__ void fit_kernel(int n, const uint64_t* keys, const float4* tri_lo, co
     box_hi[p] = make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), 0.f);
     p = parent_inner[p];
   }
+}
+
+// ---------------------------------------------------------------- PLOC: parallel locally-ordered clustering
+// Bottom-up agglomerative build over the Morton-sorted triangles (Meister & Bittner 2017): every cluster looks
+// kPlocRadius neighbours to either side for the partner that minimises the surface area of the union; mutual
+// nearest neighbours merge; the survivors are compacted and the search repeats until one cluster is left.
+// Cluster ids: [0, n) are the sorted triangles, [n, 2n-1) inner nodes in order of creation.
+constexpr int kPlocRadius = 16;
+
+__global__ void ploc_init_kernel(uint32_t n, const uint64_t* keys, const float4* tri_lo, const float4* tri_hi, uint32_t* cid,
+                                 float4* clo, float4* chi, float4* node_lo, float4* node_hi, uint32_t* size, uint32_t* parent) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t t = uint32_t(keys[i]);
+  cid[i] = i;
+  clo[i] = tri_lo[t]; chi[i] = tri_hi[t];
+  node_lo[i] = tri_lo[t]; node_hi[i] = tri_hi[t];
+  size[i] = 1u;
+  parent[i] = kInvalid;
+}
+
+__global__ void ploc_nearest_kernel(uint32_t m, const float4* clo, const float4* chi, uint32_t* nn) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const float4 lo = clo[i], hi = chi[i];
+  float best = INFINITY; uint32_t bj = kInvalid;
+  const int j0 = int(i) - kPlocRadius < 0 ? 0 : int(i) - kPlocRadius;
+  const int j1 = int(i) + kPlocRadius >= int(m) ? int(m) - 1 : int(i) + kPlocRadius;
+  for (int j = j0; j <= j1; ++j) {
+    if (j == int(i)) continue;
+    const float4 l2 = clo[j], h2 = chi[j];
+    const float dx = fmaxf(hi.x, h2.x) - fminf(lo.x, l2.x), dy = fmaxf(hi.y, h2.y) - fminf(lo.y, l2.y),
+                dz = fmaxf(hi.z, h2.z) - fminf(lo.z, l2.z);
+    const float a = dx * dy + dy * dz + dz * dx;
+    if (a < best) { best = a; bj = uint32_t(j); }  // ties keep the smaller index: symmetric and deterministic
+  }
+  nn[i] = bj;
+}
+
+__global__ void ploc_merge_kernel(uint32_t m, uint32_t n, const uint32_t* nn, const uint32_t* cid, const float4* clo,
+                                  const float4* chi, uint32_t* out_cid, float4* out_lo, float4* out_hi, uint32_t* valid,
+                                  uint32_t* next_node, uint32_t* left, uint32_t* right, float4* node_lo, float4* node_hi,
+                                  uint32_t* size, uint32_t* parent) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const uint32_t j = nn[i];
+  const bool mutual = j != kInvalid && nn[j] == i;
+  if (mutual && i > j) { valid[i] = 0u; return; }  // absorbed by the partner
+  valid[i] = 1u;
+  if (!mutual) { out_cid[i] = cid[i]; out_lo[i] = clo[i]; out_hi[i] = chi[i]; return; }
+  const uint32_t id = atomicAdd(next_node, 1u);
+  const uint32_t a = cid[i], b = cid[j];
+  const float4 l1 = clo[i], h1 = chi[i], l2 = clo[j], h2 = chi[j];
+  const float4 lo = make_float4(fminf(l1.x, l2.x), fminf(l1.y, l2.y), fminf(l1.z, l2.z), 0.f);
+  const float4 hi = make_float4(fmaxf(h1.x, h2.x), fmaxf(h1.y, h2.y), fmaxf(h1.z, h2.z), 0.f);
+  left[id - n] = a; right[id - n] = b;
+  node_lo[id] = lo; node_hi[id] = hi;
+  size[id] = size[a] + size[b];
+  parent[a] = id; parent[b] = id; parent[id] = kInvalid;
+  out_cid[i] = id; out_lo[i] = lo; out_hi[i] = hi;
+}
+
+__global__ void ploc_compact_kernel(uint32_t m, const uint32_t* valid, const uint32_t* offset, const uint32_t* in_cid,
+                                    const float4* in_lo, const float4* in_hi, uint32_t* cid, float4* clo, float4* chi) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m || !valid[i]) return;
+  const uint32_t o = offset[i];
+  cid[o] = in_cid[i]; clo[o] = in_lo[i]; chi[o] = in_hi[i];
+}
+
+// position of a cluster's first triangle in depth-first (left to right) leaf order
+__global__ void ploc_first_kernel(uint32_t total, uint32_t n, const uint32_t* parent, const uint32_t* left, const uint32_t* size,
+                                  uint32_t* first) {
+  uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= total) return;
+  uint32_t pos = 0, k = c;
+  for (uint32_t p = parent[k]; p != kInvalid; k = p, p = parent[k]) {
+    const uint32_t l = left[p - n];
+    if (l != k) pos += size[l];
+  }
+  first[c] = pos;
+}
+
+// PLOC tree -> the BinNode form collapse_kernel reads; the leaf order becomes the new triangle order
+__global__ void ploc_finish_kernel(uint32_t n, const uint64_t* keys, const uint32_t* left, const uint32_t* right, const uint32_t* size,
+                                   const uint32_t* first, const float4* node_lo, const float4* node_hi, BinNode* bin, float4* box_lo,
+                                   float4* box_hi, uint64_t* order) {
+  uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= 2u * n - 1u) return;
+  if (c < n) { order[first[c]] = keys[c] & 0xFFFFFFFFull; return; }
+  const uint32_t k = c - n, l = left[k], r = right[k];
+  BinNode nd;
+  nd.left = l < n ? (first[l] | 0x80000000u) : l - n;
+  nd.right = r < n ? (first[r] | 0x80000000u) : r - n;
+  nd.first = first[c]; nd.last = first[c] + size[c] - 1u;
+  bin[k] = nd;
+  box_lo[k] = node_lo[c]; box_hi[k] = node_hi[c];
 }
 
 struct CollapseItem { uint32_t wide, bin; };
@@ -377,12 +476,58 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
     uint32_t* counters = (uint32_t*)tmp(16);  // [0] num_wide, [1] next_count
     B2_CHECK(bin && parent_inner && parent_leaf && box_lo && box_hi && visit && items_a && items_b && counters, B2PT_ERR_CUDA,
              "cudaMalloc failed for BVH build");
-    B2_CUDA(cudaMemset(visit, 0, size_t(n) * 4));
-    radix_tree_kernel<<<G, B>>>(int(n), keys, bin, parent_inner, parent_leaf);
-    fit_kernel<<<G, B>>>(int(n), keys, tri_lo, tri_hi, bin, parent_inner, parent_leaf, box_lo, box_hi, visit);
+    uint32_t root_bin = 0;
+    const char* builder = getenv("B2PT_BUILDER");
+    if (builder && !strcmp(builder, "lbvh")) {
+      B2_CUDA(cudaMemset(visit, 0, size_t(n) * 4));
+      radix_tree_kernel<<<G, B>>>(int(n), keys, bin, parent_inner, parent_leaf);
+      fit_kernel<<<G, B>>>(int(n), keys, tri_lo, tri_hi, bin, parent_inner, parent_leaf, box_lo, box_hi, visit);
+    } else {
+      // PLOC over the Morton order (default): near-SAH quality, still entirely on the device
+      const uint32_t total = 2u * n - 1u;
+      uint32_t* cid_a = (uint32_t*)tmp(size_t(n) * 4); uint32_t* cid_b = (uint32_t*)tmp(size_t(n) * 4);
+      float4* clo_a = (float4*)tmp(size_t(n) * 16); float4* chi_a = (float4*)tmp(size_t(n) * 16);
+      float4* clo_b = (float4*)tmp(size_t(n) * 16); float4* chi_b = (float4*)tmp(size_t(n) * 16);
+      float4* node_lo = (float4*)tmp(size_t(total) * 16); float4* node_hi = (float4*)tmp(size_t(total) * 16);
+      uint32_t* size = (uint32_t*)tmp(size_t(total) * 4); uint32_t* parent = (uint32_t*)tmp(size_t(total) * 4);
+      uint32_t* first = (uint32_t*)tmp(size_t(total) * 4);
+      uint32_t* left = (uint32_t*)tmp(size_t(n) * 4); uint32_t* right = (uint32_t*)tmp(size_t(n) * 4);
+      uint32_t* nn = visit;  // reuse: nearest-neighbour index per cluster
+      uint32_t* valid = parent_inner; uint32_t* offset = parent_leaf;
+      uint32_t* next_node = (uint32_t*)tmp(16);
+      uint64_t* order = (uint64_t*)tmp(size_t(n) * 8);
+      B2_CHECK(cid_a && cid_b && clo_a && chi_a && clo_b && chi_b && node_lo && node_hi && size && parent && first && left && right &&
+                   next_node && order, B2PT_ERR_CUDA, "cudaMalloc failed for the PLOC build");
+      size_t scan_bytes = 0;
+      B2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, valid, offset, int(n)));
+      void* scan_tmp = tmp(scan_bytes);
+      B2_CHECK(scan_tmp, B2PT_ERR_CUDA, "cudaMalloc failed for scan");
+      B2_CUDA(cudaMemcpy(next_node, &n, 4, cudaMemcpyHostToDevice));
+      ploc_init_kernel<<<G, B>>>(n, keys, tri_lo, tri_hi, cid_a, clo_a, chi_a, node_lo, node_hi, size, parent);
+      uint32_t m = n;
+      int guard = 0;
+      while (m > 1) {
+        const uint32_t g = (m + B - 1) / B;
+        ploc_nearest_kernel<<<g, B>>>(m, clo_a, chi_a, nn);
+        ploc_merge_kernel<<<g, B>>>(m, n, nn, cid_a, clo_a, chi_a, cid_b, clo_b, chi_b, valid, next_node, left, right, node_lo, node_hi,
+                                    size, parent);
+        B2_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, valid, offset, int(m)));
+        ploc_compact_kernel<<<g, B>>>(m, valid, offset, cid_b, clo_b, chi_b, cid_a, clo_a, chi_a);
+        uint32_t tail[2];
+        B2_CUDA(cudaMemcpy(&tail[0], offset + (m - 1), 4, cudaMemcpyDeviceToHost));
+        B2_CUDA(cudaMemcpy(&tail[1], valid + (m - 1), 4, cudaMemcpyDeviceToHost));
+        const uint32_t m2 = tail[0] + tail[1];
+        B2_CHECK(m2 < m && ++guard < 4096, B2PT_ERR_CUDA, "PLOC build made no progress");
+        m = m2;
+      }
+      ploc_first_kernel<<<(total + B - 1) / B, B>>>(total, n, parent, left, size, first);
+      ploc_finish_kernel<<<(total + B - 1) / B, B>>>(n, keys, left, right, size, first, node_lo, node_hi, bin, box_lo, box_hi, order);
+      keys = order;  // triangles are now in depth-first leaf order of the PLOC tree
+      root_bin = n - 2u;
+    }
     // worst case one wide node per binary inner node
     if (int rc = dev_alloc(s, &nodes, size_t(n) * kNodeFloat4s, true)) return rc;
-    CollapseItem root{0u, 0u};
+    CollapseItem root{0u, root_bin};
     B2_CUDA(cudaMemcpy(items_a, &root, sizeof root, cudaMemcpyHostToDevice));
     uint32_t h_counters[2] = {1u, 0u};
     B2_CUDA(cudaMemcpy(counters, h_counters, 8, cudaMemcpyHostToDevice));
@@ -485,6 +630,8 @@ void b2pt_scene_destroy(b2pt_scene_t s) {
   if (!s) return;
   if (s->workspace && s->workspace_free) s->workspace_free(s->workspace);
   for (int i = 0; i < s->num_allocations; ++i) cudaFree(s->allocations[i]);
+  if (s->film_dev) cudaFree(s->film_dev);
+  if (s->film_host) cudaFreeHost(s->film_host);
   delete s;
 }
 

@@ -63,4 +63,8 @@ struct b2pt_scene_s {
   // per-scene render workspace (path pool, queues), created lazily by render.cu
   void* workspace = nullptr;
   void (*workspace_free)(void*) = nullptr;
+  // film staging of b2pt_render_host, kept between calls (device dvec4 + pinned host copy)
+  double* film_dev = nullptr;
+  double* film_host = nullptr;
+  size_t film_doubles = 0;
 };

@@ -143,6 +143,138 @@ __device__ __forceinline__ Hit trace_ray(const DeviceScene& sc, float3 O, float3
   return trace_ray_masked<kAnyHit>(sc, O, D, tnear, tfar, kMeshOnly ? kMaskMesh : kMaskAll);
 }
 
+// ---------------------------------------------------------------- warp-voted persistent traversal
+//
+// trace_ray_masked above runs one ray per thread to completion; ncu (profiles/r01_bpt_trace_full_summary.md)
+// shows what that costs on incoherent rays: 6.9 of 32 lanes active per issued instruction, the triangle test
+// running with 2-3 lanes because a lane that reaches a leaf tests its triangles while the other 31 wait at
+// the reconvergence point, and finished lanes idling until the slowest ray of the warp ends.
+//
+// trace_stream keeps the same tree, the same box test and the same (Embree-exact) triangle test, but changes
+// who does what when:
+//   * ROUNDS.  Every lane holds one pending item `cur`: an inner node, one triangle of a leaf, or nothing.
+//     Each round the warp votes (two ballots): if more lanes hold triangles than inner nodes the round is a
+//     triangle round, otherwise a node round; only the lanes of the winning class work, each on exactly ONE
+//     item, so the instructions of a round run with at least half of the busy lanes.  Lanes of the other class
+//     keep their item for a later round ("postponed leaves").
+//   * PERSISTENT WARPS, DYNAMIC FETCH.  A warp does not own 32 fixed rays: when kFetchMin or more lanes are
+//     idle they take the next rays from a global ticket counter (one atomic per refill), so a long ray no
+//     longer holds 31 finished lanes hostage.
+// Io supplies the rays and consumes the hits:  uint32_t tag = io.load(i, O, D, tnear, tfar, mask);
+// io.store(tag, hit).  Must be entered by complete warps; `ticket` must be zero at kernel start.
+constexpr uint32_t kSentinel = 0x7FFFFFFFu;  // bottom of every traversal stack: this lane has no item
+constexpr unsigned kFullMask = 0xFFFFFFFFu;
+constexpr int kFetchMin = 8;
+
+template <bool kAnyHit, class Io, bool kCount = false>
+__device__ __forceinline__ void trace_stream(const DeviceScene& sc, uint32_t n, unsigned* ticket, Io& io) {
+  uint32_t n_nodes = 0, n_tris = 0;  // kCount (diagnostic builds only): work items of the current ray
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned lane_lt = (1u << lane) - 1u;
+  uint32_t stack[kStackSize];
+  int sp = 1;
+  stack[0] = kSentinel;
+  uint32_t cur = kSentinel, tag = kInvalid, ray_mask = 0u;
+  bool has_ray = false, exhausted = false;
+  float3 O = f3(0.f), D = f3(0.f), idir = f3(0.f), ood = f3(0.f);
+  float tnear = 0.f;
+  Hit hit; hit.t = 0.f; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
+  for (;;) {
+    // ---- refill idle lanes
+    const unsigned idle = __ballot_sync(kFullMask, cur == kSentinel);
+    if (!exhausted && __popc(idle) >= kFetchMin) {
+      const unsigned cnt = __popc(idle);
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(ticket, cnt);
+      base = __shfl_sync(kFullMask, base, 0);
+      exhausted = base + cnt >= n;
+      if (cur == kSentinel) {
+        const uint32_t i = base + __popc(idle & lane_lt);
+        if (i < n) {
+          float tfar;
+          tag = io.load(i, O, D, tnear, tfar, ray_mask);
+          hit.t = tfar; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
+          const float kHuge = 1e30f;
+          idir = f3(fabsf(D.x) > 1e-30f ? 1.0f / D.x : copysignf(kHuge, D.x),
+                    fabsf(D.y) > 1e-30f ? 1.0f / D.y : copysignf(kHuge, D.y),
+                    fabsf(D.z) > 1e-30f ? 1.0f / D.z : copysignf(kHuge, D.z));
+          ood = f3(O.x * idir.x, O.y * idir.y, O.z * idir.z);
+          sp = 1;
+          cur = 0;  // the root is always an inner node
+          has_ray = true;
+          if (kCount) { n_nodes = 0; n_tris = 0; }
+        }
+      }
+    }
+    // ---- vote
+    const bool is_inner = cur < kSentinel;
+    const bool is_leaf = (cur & 0x80000000u) != 0u;
+    const unsigned mi = __ballot_sync(kFullMask, is_inner), ml = __ballot_sync(kFullMask, is_leaf);
+    if ((mi | ml) == 0u) {
+      if (exhausted) break;
+      continue;
+    }
+    if (__popc(ml) > __popc(mi)) {
+      // ---- triangle round: one triangle per lane
+      if (is_leaf) {
+        const uint32_t pos = cur & 0x0FFFFFFFu;
+        const bool h = intersect_triangle(sc, pos, O, D, tnear, hit.t, hit.u, hit.v, ray_mask);
+        if (h) hit.tri = pos;
+        if (kCount) ++n_tris;
+        if (kAnyHit && h) cur = kSentinel;
+        else if (cur & 0x70000000u) cur += 1u - 0x10000000u;  // next triangle of the same leaf
+        else cur = stack[--sp];
+      }
+    } else if (is_inner) {
+      // ---- node round: one 4-wide node per lane
+      if (kCount) ++n_nodes;
+      const float4* nd = sc.nodes + size_t(cur) * kNodeFloat4s;
+      const float4 lox = __ldg(nd + 0), loy = __ldg(nd + 1), loz = __ldg(nd + 2);
+      const float4 hix = __ldg(nd + 3), hiy = __ldg(nd + 4), hiz = __ldg(nd + 5);
+      const float4 lk = __ldg(nd + 6);
+      float tn[4];
+      uint32_t ch[4] = {__float_as_uint(lk.x), __float_as_uint(lk.y), __float_as_uint(lk.z), __float_as_uint(lk.w)};
+      const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
+      const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float x0 = __fmaf_rn(lx[k], idir.x, -ood.x), x1 = __fmaf_rn(hx[k], idir.x, -ood.x);
+        const float y0 = __fmaf_rn(ly[k], idir.y, -ood.y), y1 = __fmaf_rn(hy[k], idir.y, -ood.y);
+        const float z0 = __fmaf_rn(lz[k], idir.z, -ood.z), z1 = __fmaf_rn(hz[k], idir.z, -ood.z);
+        const float t0 = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tnear));
+        const float t1 = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), hit.t)) * 1.0000003f;
+        const bool ok = (t0 <= t1) & (ch[k] != kInvalid);
+        tn[k] = ok ? t0 : INFINITY;
+      }
+      cswap(tn[0], ch[0], tn[1], ch[1]); cswap(tn[2], ch[2], tn[3], ch[3]);
+      cswap(tn[0], ch[0], tn[2], ch[2]); cswap(tn[1], ch[1], tn[3], ch[3]);
+      cswap(tn[1], ch[1], tn[2], ch[2]);
+      if (tn[0] == INFINITY) {
+        cur = stack[--sp];
+      } else {
+        if (tn[3] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[3]; else atomicOr(sc.error_flags, 1u); }
+        if (tn[2] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[2]; else atomicOr(sc.error_flags, 1u); }
+        if (tn[1] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[1]; else atomicOr(sc.error_flags, 1u); }
+        cur = ch[0];
+      }
+    }
+    // ---- a lane whose stack ran empty hands its hit over
+    if (has_ray && cur == kSentinel) {
+      if (kCount) { hit.u = float(n_nodes); hit.v = float(n_tris); }
+      io.store(tag, hit);
+      has_ray = false;
+    }
+  }
+}
+
+// blocks of a persistent traversal launch over n rays: one wave of 256-thread CTAs, 4 per SM
+inline int persistent_grid(size_t n, int block) {
+  size_t want = (n + block - 1) / block;
+  size_t cap = size_t(kNumSMs) * 4;
+  if (want < 1) want = 1;
+  return int(want < cap ? want : cap);
+}
+
 // geomID / primID of a triangle in leaf order
 __device__ __forceinline__ uint32_t tri_geom(const DeviceScene& sc, uint32_t pos) { return __float_as_uint(__ldg(&sc.tri_v0[pos]).w); }
 __device__ __forceinline__ uint32_t tri_prim(const DeviceScene& sc, uint32_t pos) { return __float_as_uint(__ldg(&sc.tri_e1[pos]).w); }

@@ -4,6 +4,8 @@
 // (an RTCRay with org, dir, tnear, tfar and a mask, Scene.cpp:162-171,186-196,209-219) and what
 // they read back (tfar, u, v, geomID, primID).  Used by the ray-level parity tests and the
 // Mrays/s micro-benchmark; the renderers call trace_ray() from their own stages.
+#include <stdlib.h>
+
 #include "trace.cuh"
 
 namespace b2pt {
@@ -24,9 +26,73 @@ __global__ void __launch_bounds__(256) trace_rays_kernel(DeviceScene sc, const f
   }
 }
 
-int launch_trace(const DeviceScene& sc, const B2ptRay* rays, size_t n, unsigned mode, B2ptHit* hits, cudaStream_t stream) {
+// explicit rays in, RTCRay-style hits out
+template <bool kAnyHit, bool kMeshOnly>
+struct ApiIo {
+  const DeviceScene* sc;
+  const float4* rays;
+  B2ptHit* hits;
+  __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
+    const float4 a = __ldg(&rays[size_t(i) * 2 + 0]);  // org.xyz, tnear
+    const float4 b = __ldg(&rays[size_t(i) * 2 + 1]);  // dir.xyz, tfar
+    O = f3(a.x, a.y, a.z); D = f3(b.x, b.y, b.z); tnear = a.w; tfar = b.w;
+    mask = kMeshOnly ? kMaskMesh : kMaskAll;
+    return i;
+  }
+  __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
+    B2ptHit o;
+    o.t = h.t; o.u = h.u; o.v = h.v;
+    if (h.tri == kInvalid) { o.geom = kInvalid; o.prim = kInvalid; }
+    else if (kAnyHit) { o.geom = 0u; o.prim = kInvalid; }  // rtcOccluded reports geomID = 0 (Scene.cpp:179)
+    else { o.geom = tri_geom(*sc, h.tri); o.prim = tri_prim(*sc, h.tri); }
+    hits[i] = o;
+  }
+};
+
+template <bool kAnyHit, bool kMeshOnly>
+__global__ void __launch_bounds__(256) trace_stream_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
+                                                           B2ptHit* __restrict__ hits, unsigned* ticket) {
+  ApiIo<kAnyHit, kMeshOnly> io{&sc, rays, hits};
+  trace_stream<kAnyHit>(sc, n, ticket, io);
+}
+
+// diagnostic: u, v of every hit are replaced by the ray's node / triangle test counts (B2PT_TRACE_VARIANT=2)
+__global__ void __launch_bounds__(256) trace_count_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
+                                                          B2ptHit* __restrict__ hits, unsigned* ticket) {
+  ApiIo<false, false> io{&sc, rays, hits};
+  trace_stream<false, ApiIo<false, false>, true>(sc, n, ticket, io);
+}
+
+static int trace_variant() {
+  const char* e = getenv("B2PT_TRACE_VARIANT");
+  return e ? atoi(e) : 0;
+}
+
+int launch_trace(b2pt_scene_s* scene, const B2ptRay* rays, size_t n, unsigned mode, B2ptHit* hits, cudaStream_t stream) {
+  const DeviceScene& sc = scene->dev;
   if (n == 0) return B2PT_OK;
+  B2_CHECK(n < (size_t(1) << 31), B2PT_ERR_CAPACITY, "b2pt_trace: more than 2^31 rays in one call");
+  B2_CHECK(mode <= B2PT_TRACE_OCCLUDED_MESH, B2PT_ERR_INVALID, "b2pt_trace: unknown mode");
   const int block = 256;
+  if (trace_variant() != 0) {
+    // warp-voted persistent traversal (trace.cuh: trace_stream); the ticket is the scene's, zeroed per launch
+    unsigned* ticket = scene->dev.error_flags + 1;
+    B2_CUDA(cudaMemsetAsync(ticket, 0, 4, stream));
+    const int grid = persistent_grid(n, block);
+    const float4* r = reinterpret_cast<const float4*>(rays);
+    if (trace_variant() == 2 && mode == B2PT_TRACE_CLOSEST_ALL) {
+      trace_count_kernel<<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket);
+      B2_CUDA(cudaGetLastError());
+      return B2PT_OK;
+    }
+    switch (mode) {
+      case B2PT_TRACE_CLOSEST_ALL: trace_stream_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+      case B2PT_TRACE_CLOSEST_MESH: trace_stream_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+      default: trace_stream_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+    }
+    B2_CUDA(cudaGetLastError());
+    return B2PT_OK;
+  }
   size_t want = (n + block - 1) / block;
   // persistent-style grid: a multiple of the SM count, each thread strides over the rays
   size_t cap = size_t(kNumSMs) * 8 * 4;
@@ -48,7 +114,7 @@ extern "C" {
 
 int b2pt_trace_device(b2pt_scene_t scene, const B2ptRay* rays_dev, size_t n, unsigned mode, B2ptHit* hits_dev, void* stream) {
   B2_CHECK(scene && (n == 0 || (rays_dev && hits_dev)), B2PT_ERR_INVALID, "b2pt_trace_device: null argument");
-  return b2pt::launch_trace(scene->dev, rays_dev, n, mode, hits_dev, (cudaStream_t)stream);
+  return b2pt::launch_trace(scene, rays_dev, n, mode, hits_dev, (cudaStream_t)stream);
 }
 
 int b2pt_trace(b2pt_scene_t scene, const B2ptRay* rays, size_t n, unsigned mode, B2ptHit* hits) {
@@ -61,7 +127,7 @@ int b2pt_trace(b2pt_scene_t scene, const B2ptRay* rays, size_t n, unsigned mode,
   int rc = B2PT_OK;
   e = cudaMemcpy(d_rays, rays, n * sizeof(B2ptRay), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) {
-    rc = b2pt::launch_trace(scene->dev, d_rays, n, mode, d_hits, 0);
+    rc = b2pt::launch_trace(scene, d_rays, n, mode, d_hits, 0);
     if (rc == B2PT_OK) e = cudaMemcpy(hits, d_hits, n * sizeof(B2ptHit), cudaMemcpyDeviceToHost);
   }
   cudaFree(d_rays); cudaFree(d_hits);
