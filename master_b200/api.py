@@ -229,3 +229,32 @@ def make_params(flat, technique="PT", width=512, height=512, camera=0, beta=None
     p.sky_zenith[:] = list(sky_zenith)
     p.max_subpath = max_subpath
     return p
+
+
+class PhotonGrid:
+    """b2pt_grid_*: the photon index (v3::HashGrid3D<T>::build / rQuery, HashGrid3D.hpp:181-325) on the device."""
+
+    def __init__(self, points, radius):
+        pts = np.ascontiguousarray(points, dtype=np.float32).reshape(-1, 3)
+        h = C.c_void_p()
+        check(load_library().b2pt_grid_build(_ptr(pts), len(pts), C.c_float(radius), C.byref(h)))
+        self.handle, self.radius, self.num_points = h, float(radius), len(pts)
+
+    def query(self, queries, max_per_query=64):
+        """-> (counts[nq], indices[nq, max_per_query]); indices[q, :min(counts[q], max)] are valid, unordered."""
+        q = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, 3)
+        counts = np.zeros(len(q), dtype=np.uint32)
+        indices = np.zeros((len(q), max(max_per_query, 1)), dtype=np.uint32)
+        check(load_library().b2pt_grid_query(self.handle, _ptr(q), len(q), max_per_query, _ptr(counts), _ptr(indices)))
+        return counts, indices
+
+    def close(self):
+        if getattr(self, "handle", None):
+            load_library().b2pt_grid_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

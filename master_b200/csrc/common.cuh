@@ -81,6 +81,19 @@ constexpr float kTwoPi = 6.28318530717958647692528676655900576f;
 constexpr float kFltEpsilon = 1.192092896e-07f;
 constexpr float kFltMin = 1.175494351e-38f;
 
+// ---------------------------------------------------------------- libm parity
+// The reference calls glibc's float sin / cos / asin / atan2 / pow, which return the correctly rounded result in all
+// but a vanishing fraction of cases; CUDA's float versions are 1-2 ulp functions.  A last-bit difference in a sampled
+// direction flips discrete decisions further down a path (which triangle, which side of a roulette threshold), and in
+// VCM / UPG a flipped photon path changes every eye path that merges with it.  Evaluating in double and rounding once
+// reproduces the correctly rounded float result (double error ~1e-16 relative, far below half a float ulp except on
+// exact ties) and removes most of those flips.  Shading is a small share of the step; the FP64 pipe is otherwise idle.
+__device__ __forceinline__ float cr_sinf(float x) { return float(sin(double(x))); }
+__device__ __forceinline__ float cr_cosf(float x) { return float(cos(double(x))); }
+__device__ __forceinline__ float cr_asinf(float x) { return float(asin(double(x))); }
+__device__ __forceinline__ float cr_atan2f(float y, float x) { return float(atan2(double(y), double(x))); }
+__device__ __forceinline__ float cr_powf(float x, float y) { return float(pow(double(x), double(y))); }
+
 // ---------------------------------------------------------------- warp-aggregated queue append
 // One atomic per warp: ballot the lanes that append, lane 0 of the group reserves, everyone
 // computes its slot from the prefix popcount.  Returns the slot (valid only where `want`).

@@ -54,13 +54,13 @@ __device__ __forceinline__ float beta_fn(float x, float beta) {
   if (beta == 2.0f) return x * x;
   if (beta == 1.0f) return x;
   if (beta == 0.0f) return x == 0.0f ? 0.0f : 1.0f;
-  return powf(x, beta);
+  return cr_powf(x, beta);
 }
 __device__ __forceinline__ float pow_beta(float x, float beta) {  // std::pow(x, beta) as PT.cpp calls it
   if (beta == 1.0f) return x;
   if (beta == 2.0f) return x * x;
   if (beta == 0.0f) return 1.0f;
-  return powf(x, beta);
+  return cr_powf(x, beta);
 }
 
 // ---------------------------------------------------------------- Scene::querySurface (Scene.cpp:80-126)
@@ -114,15 +114,15 @@ __device__ __forceinline__ AngularBound angular_bound(float3 center, float radiu
   if (radius_sq < distance_sq) {
     const float lateral_distance = sqrtf(lateral_distance_sq);
     const float distance = sqrtf(distance_sq);
-    const float theta_center = asinf(lateral_distance / distance);
-    const float theta_radius = asinf(radius / distance);
+    const float theta_center = cr_asinf(lateral_distance / distance);
+    const float theta_radius = cr_asinf(radius / distance);
     if (lateral_distance_sq < radius_sq) {
       b.theta_sup = fminf(kHalfPi, theta_center + theta_radius);
     } else if (radius_sq < distance_sq) {
       b.theta_inf = theta_center - theta_radius;
       b.theta_sup = fminf(kHalfPi, theta_center + theta_radius);
-      const float phi_center = atan2f(center.z, center.x);
-      const float phi_radius = asinf(radius / lateral_distance);
+      const float phi_center = cr_atan2f(center.z, center.x);
+      const float phi_radius = cr_asinf(radius / lateral_distance);
       b.phi_inf = phi_center - phi_radius;
       b.phi_sup = phi_center + phi_radius;
     }
@@ -135,8 +135,8 @@ struct LambertRange { float theta_inf, theta_range, phi_inf, phi_range; };
 __device__ __forceinline__ LambertRange lambert_range(float3 center, float radius) {
   const AngularBound bound = angular_bound(center, radius);
   LambertRange r;
-  const float uniform_theta_inf = cosf(bound.theta_sup) * cosf(bound.theta_sup);
-  const float uniform_theta_sup = cosf(bound.theta_inf) * cosf(bound.theta_inf);
+  const float uniform_theta_inf = cr_cosf(bound.theta_sup) * cr_cosf(bound.theta_sup);
+  const float uniform_theta_sup = cr_cosf(bound.theta_inf) * cr_cosf(bound.theta_inf);
   const float uniform_phi_inf = bound.phi_inf * kOneOverPi * 0.5f;
   const float uniform_phi_sup = bound.phi_sup * kOneOverPi * 0.5f;
   r.theta_inf = uniform_theta_inf;
@@ -157,7 +157,7 @@ __device__ __forceinline__ float3 sample_lambert(Rng& rng, float3 omega) {
   const float y = sqrtf(rng.sample()) * sign_glm(omega.y);
   const float r = sqrtf(1.0f - y * y);
   const float phi = rng.sample() * 2.0f * kPi;
-  return f3(r * cosf(phi), y, r * sinf(phi));
+  return f3(r * cr_cosf(phi), y, r * cr_sinf(phi));
 }
 
 // sample_lambert(generator, sphere, omega) (Sample.inl:58-82): lobe restricted to the cone around a sphere
@@ -168,7 +168,7 @@ __device__ __forceinline__ float3 sample_lambert_bounded(Rng& rng, float3 center
   const float y = sqrtf(rng.sample() * lr.theta_range + lr.theta_inf) * sign_glm(omega.y);
   const float phi = kTwoPi * (rng.sample() * lr.phi_range + lr.phi_inf);
   const float r = sqrtf(1 - y * y);
-  return f3(r * cosf(phi), y, r * sinf(phi));
+  return f3(r * cr_cosf(phi), y, r * cr_sinf(phi));
 }
 
 // reflection_to_surface (Sample.inl:39-46)
@@ -183,10 +183,40 @@ __device__ __forceinline__ mat3 reflection_to_surface(float3 reflection) {
 // sample_phong(generator, omega, power) (Sample.inl:137-149)
 __device__ __forceinline__ float3 sample_phong(Rng& rng, float3 omega, float power) {
   const mat3 refl_to_surf = reflection_to_surface(f3(-omega.x, omega.y, -omega.z));
-  const float y = powf(rng.sample(), 1.0f / (power + 1.0f));
+  const float y = cr_powf(rng.sample(), 1.0f / (power + 1.0f));
   const float r = sqrtf(1.0f - y * y);
   const float phi = rng.sample() * 2.0f * kPi;
-  return mul(refl_to_surf, f3(r * cosf(phi), y, r * sinf(phi)));
+  return mul(refl_to_surf, f3(r * cr_cosf(phi), y, r * cr_sinf(phi)));
+}
+
+// sample_phong(generator, omega, power, sphere) / phong_adjust (Sample.inl:151-205): Phong lobe restricted to the cone
+// that subtends a sphere given in the local frame
+struct PhongRange { mat3 reflection; float theta_inf, theta_range, phi_inf, phi_range; };
+
+__device__ __forceinline__ PhongRange phong_range(float3 omega, float power, float3 center, float radius) {
+  PhongRange r;
+  r.reflection = reflection_to_surface(f3(-omega.x, omega.y, -omega.z));
+  const AngularBound bound = angular_bound(mul(center, r.reflection), radius);  // sphere.center * reflection
+  const float uniform_theta_inf = cr_powf(cr_cosf(bound.theta_sup), power + 1.0f);
+  const float uniform_theta_sup = cr_powf(cr_cosf(bound.theta_inf), power + 1.0f);
+  const float uniform_phi_inf = bound.phi_inf * kOneOverPi * 0.5f;
+  const float uniform_phi_sup = bound.phi_sup * kOneOverPi * 0.5f;
+  r.theta_inf = uniform_theta_inf;
+  r.theta_range = uniform_theta_sup - uniform_theta_inf;
+  r.phi_inf = uniform_phi_inf;
+  r.phi_range = uniform_phi_sup - uniform_phi_inf;
+  return r;
+}
+__device__ __forceinline__ float phong_adjust(float3 omega, float power, float3 center, float radius) {
+  const PhongRange r = phong_range(omega, power, center, radius);
+  return r.theta_range * r.phi_range;
+}
+__device__ __forceinline__ float3 sample_phong_bounded(Rng& rng, float3 omega, float power, float3 center, float radius) {
+  const PhongRange pr = phong_range(omega, power, center, radius);
+  const float y = cr_powf(rng.sample() * pr.theta_range + pr.theta_inf, 1.0f / (power + 1.0f));
+  const float phi = kTwoPi * (rng.sample() * pr.phi_range + pr.phi_inf);
+  const float r = sqrtf(1 - y * y);
+  return mul(pr.reflection, f3(r * cr_cosf(phi), y, r * cr_sinf(phi)));
 }
 
 // ---------------------------------------------------------------- BSDF::query (BSDF.cpp)
@@ -211,7 +241,7 @@ __device__ __forceinline__ BsdfQuery phong_query(const B2ptMaterial& m, float3 i
   const float half_over_pi = 0.5f * kOneOverPi;
   const float3 reflected = f3(-incident.x, incident.y, -incident.z);
   const float cos_alpha = clampf(dot(outgoing, reflected), 0.0f, 1.0f);
-  const float cos_alpha_pow = powf(cos_alpha, m.power);
+  const float cos_alpha_pow = cr_powf(cos_alpha, m.power);
   const float specular_density = (m.power + 1.0f) * half_over_pi * cos_alpha_pow;
   const float specular_density_rev = specular_density;
   const float3 specular = f3(m.specular[0], m.specular[1], m.specular[2]) * (m.power + 2.0f) * half_over_pi * cos_alpha_pow;

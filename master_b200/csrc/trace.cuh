@@ -9,8 +9,8 @@
 // finalisation :40-50) operation by operation, with Embree's dot/cross association
 // (common/math/vec3.h:188,193: dot = a.x*b.x + (a.y*b.y + a.z*b.z)) and unfused multiplies
 // (the oracle build caps Embree at the AVX ISA, which has no FMA), so den, U, V, T — and with
-// them the accept/reject decision for a given triangle — are bit-identical to the reference's.
-// t = T * rcp(|den|) differs from Embree's Newton-refined _mm_rcp_ps by <= 1 ulp.
+// them the accept/reject decision for a given triangle — are bit-identical to the reference's, and so are
+// t, u, v: rcp(|den|) goes through the same RCPPS table + one Newton step as Embree's (rcp_embree below).
 //
 // Box tests are NOT part of the parity contract (the tree is a different tree); they use fused
 // multiply-adds and are made conservative: child boxes carry a small absolute pad (scene.cu) and
@@ -40,6 +40,19 @@ __device__ __forceinline__ float3 cross_embree(float3 a, float3 b) {
             __fsub_rn(__fmul_rn(a.x, b.y), __fmul_rn(a.y, b.x)));
 }
 
+// Embree's rcp(a) = r * (2 - r * a) with r = _mm_rcp_ps(a) (common/simd/vfloat4_sse2.h:181-188, non-AVX2 branch): RCPPS is
+// a 2048-entry table instruction (tools/make_rcp_table.c extracts and verifies the table), so with the table here the hit
+// finalisation t = T * rcp(|den|), u = U * rcp, v = V * rcp (triangle_intersector_moeller.h:44-50) is bit-identical.
+static __device__ const uint32_t kRcpTable[2048] = {
+#include "rcp_table.inc"
+};
+__device__ __forceinline__ float rcp_embree(float a) {  // a > 0
+  const uint32_t b = __float_as_uint(a), e = b >> 23;
+  if (e < 2u || e > 252u) return __frcp_rn(a);  // results near the ends of the exponent range: not table territory
+  const float r = __uint_as_float(kRcpTable[(b >> 12) & 0x7FFu] - ((e - 127u) << 23));
+  return __fmul_rn(r, __fsub_rn(2.0f, __fmul_rn(r, a)));
+}
+
 // Returns true and updates (tfar, u, v) when triangle `pos` is hit inside (tnear, tfar).
 // ray_mask: RTCRay::mask — 0xFFFFFFFF (Scene::intersect) or 1 << entity_type::mesh (intersectMesh / occluded).
 __device__ __forceinline__ bool intersect_triangle(const DeviceScene& sc, uint32_t pos, float3 O, float3 D, float tnear,
@@ -61,7 +74,7 @@ __device__ __forceinline__ bool intersect_triangle(const DeviceScene& sc, uint32
   if (!((den != 0.0f) & (U >= 0.0f) & (V >= 0.0f) & (__fadd_rn(U, V) <= absDen))) return false;
   const float T = xor_sign(dot_embree(Ng, C), sgnDen);
   if (!((T > __fmul_rn(absDen, tnear)) & (T < __fmul_rn(absDen, tfar)))) return false;
-  const float rcpAbsDen = __frcp_rn(absDen);
+  const float rcpAbsDen = rcp_embree(absDen);
   tfar = __fmul_rn(T, rcpAbsDen);
   u = __fmul_rn(U, rcpAbsDen);
   v = __fmul_rn(V, rcpAbsDen);

@@ -1,5 +1,985 @@
-// vcm.cu — placeholder until the wavefront VCM/UPG lands.
+// vcm.cu — wavefront VCM / UPG: UPGBase<Beta>::_preprocess / _scatter / _traceLight / _traceEye / _connect* /
+// _gather* / _merge* and the VC / VM MIS sub-weights (UPG.cpp:40-831).
+//
+// One pass (= one Technique::render call of the reference) is three device phases:
+//
+//   photons  (vcm_photon_kernel + trace)   num_photons light paths, one slot each, walk the reference's _traceLight
+//            state machine; every accepted vertex is bump-allocated in ONE pool in HBM (112 B records) and linked
+//            to its predecessor, so `_light_paths[index - 1]` of the reference is `link[index]` here and
+//            `_light_offsets[p] .. [p + 1]` is the chain hanging off head[p].
+//   grid     (grid.cuh)                    the non-light vertices are radix-sorted by cell into the photon index.
+//   eye      (vcm_eye_kernel -> vcm_gather_kernel -> vcm_connect_kernel -> trace -> shadow)
+//            per pixel the reference's _traceEye state machine.  Vertex CONNECTION work (own light path of the
+//            pixel + one next-event sample) is expanded into (eye vertex, light vertex) pairs exactly as in bpt.cu;
+//            vertex MERGING is a range query of the photon index per new eye vertex, evaluated in the gather stage.
+//
+// VCM (biased, shrinking radius r_i = r_0 (i + 1)^((alpha - 1) / 2), UPG.cpp:180-183) draws nothing inside a merge, so
+// given the same per-(pixel, sample) and per-(photon, sample) streams the eye-path radiance is the reference's.
+// UPG (unbiased) estimates the merge density by rejection ray casting (BSDF::gathering_density, BSDF.cpp:42-66,
+// 264-289, 393-434): a data-dependent loop of bounded rays (Intersector::intersectFast, Intersector.cpp:17-46) that
+// consumes random numbers in an order the reference leaves to std::sort; here every merge owns a sub-stream keyed by
+// (path stream, eye vertex, photon), so UPG agrees with the reference in distribution, not per path.
+//
+// Restrictions, stated: merging from the light side only (Options::from_light = true, the default); sun lights are
+// skipped in connections like in bpt.cu (counted in B2ptStats::capacity_events).
+#include "grid.cuh"
 #include "render_common.cuh"
+
 namespace b2pt {
-int render_vcm(b2pt_scene_s*, const RenderConfig&, cudaStream_t, B2ptStats*) { set_error("VCM/UPG: not built yet"); return B2PT_ERR_INVALID; }
+
+namespace {
+
+enum : uint32_t { kNew = 0, kLightWait = 1, kEyeStart = 2, kEyeWait = 3, kDone = 4 };
+constexpr uint32_t kPairCamera = 0x80000000u;
+constexpr uint32_t kNeeVertex = 0xFFFFFFFFu;
+constexpr uint32_t kShadowSplat = 1u;
+constexpr int kVertexFloat4s = 7;
+constexpr uint32_t kFlagFinite = 1u, kFlagDirectional = 2u, kFlagDead = 0x80000000u;
+constexpr float kDensityTestLimit = 16777216.f;  // DENSITY_ESTIMATION_TEST_LIMIT, BSDF.cpp:9
+
+struct VcmCounters {
+  unsigned long long basic_rays, shadow_rays, numeric_errors, capacity_events, density_rays;
+  unsigned int done;
+  unsigned int lv_count;
+  unsigned int trace_count[2], pair_count[2], shadow_count[2], gather_count[2];
+};
+
+// the per-pass constants of UPGBase (UPG.hpp:119-137)
+struct VcmParams {
+  float beta, roulette, roulette_inv;
+  float radius, circle, clamp_const;
+  float num_scattered, num_scattered_inv;
+  uint32_t unbiased, enable_vc, enable_vm;
+  uint32_t num_photons, max_subpath;
+  uint32_t brute_vertices;  // diagnostic (B2PT_VCM_BRUTE=1): gather scans every stored vertex instead of the grid
+};
+
+// UPGBase::LightVertex / EyeVertex (UPG.hpp:19-43): w0 = a | c, w1 = A | C, w2 = B | D
+struct Vertex {
+  Surface s;
+  float3 omega, thr;
+  float w0, w1, w2, bgeo;
+  uint32_t flags;  // kFlagFinite | kFlagDirectional | length << 2
+
+  __device__ __forceinline__ uint32_t finite() const { return flags & kFlagFinite; }
+  __device__ __forceinline__ float length() const { return float((flags & ~kFlagDead) >> 2); }
+  __device__ __forceinline__ void set(uint32_t finite, uint32_t directional, uint32_t length) {
+    flags = (finite & 1u) | (directional ? kFlagDirectional : 0u) | (length << 2);
+  }
+  __device__ __forceinline__ void set_finite(uint32_t f) { flags = (flags & ~kFlagFinite) | (f & 1u); }
+};
+
+struct VcmPool {
+  uint32_t photons;      // photon slots (rounded up to the block size)
+  uint32_t pixels_pad;   // eye slots (rounded up)
+  uint32_t lv_capacity, q_capacity;
+  // photon phase, per photon slot
+  uint32_t* p_state; uint2* p_rng; float4* p_cv; float4* p_bs_omega; float4* p_bs_thr; float4* p_ray_o; float4* p_hit;
+  uint32_t* lp_head; uint32_t* lp_count;
+  // eye phase, per pixel slot
+  uint32_t* state; uint2* rng; float4* cv; float4* bs_omega; float4* bs_thr; float4* ray_o; float4* hit; float4* rad; float4* nee;
+  double* splat;
+  // vertex pool
+  float4* lv; uint32_t* lv_link; float4* grid_points;
+  // queues
+  uint32_t* trace_q; uint2* pair_q; float4* shadow_q; uint32_t* gather_q;
+};
+
+__device__ __forceinline__ void pack_vertex(const Vertex& v, float4* q) {
+  q[0] = make_float4(v.s.pos.x, v.s.pos.y, v.s.pos.z, __uint_as_float(v.s.material_id));
+  q[1] = make_float4(v.s.gnormal.x, v.s.gnormal.y, v.s.gnormal.z, __uint_as_float(v.flags));
+  q[2] = make_float4(v.s.tan.c0.x, v.s.tan.c0.y, v.s.tan.c0.z, v.w0);
+  q[3] = make_float4(v.s.tan.c1.x, v.s.tan.c1.y, v.s.tan.c1.z, v.w1);
+  q[4] = make_float4(v.s.tan.c2.x, v.s.tan.c2.y, v.s.tan.c2.z, v.w2);
+  q[5] = make_float4(v.omega.x, v.omega.y, v.omega.z, v.bgeo);
+  q[6] = make_float4(v.thr.x, v.thr.y, v.thr.z, 0.f);
 }
+__device__ __forceinline__ Vertex unpack_vertex(const float4* q) {
+  Vertex v;
+  v.s.pos = f3(q[0].x, q[0].y, q[0].z); v.s.material_id = __float_as_uint(q[0].w);
+  v.s.gnormal = f3(q[1].x, q[1].y, q[1].z); v.flags = __float_as_uint(q[1].w);
+  v.s.tan.c0 = f3(q[2].x, q[2].y, q[2].z); v.w0 = q[2].w;
+  v.s.tan.c1 = f3(q[3].x, q[3].y, q[3].z); v.w1 = q[3].w;
+  v.s.tan.c2 = f3(q[4].x, q[4].y, q[4].z); v.w2 = q[4].w;
+  v.omega = f3(q[5].x, q[5].y, q[5].z); v.bgeo = q[5].w;
+  v.thr = f3(q[6].x, q[6].y, q[6].z);
+  return v;
+}
+// slot vertices are SoA (stride = number of slots), pool vertices AoS
+__device__ __forceinline__ void store_slot_vertex(float4* base, uint32_t stride, uint32_t slot, const Vertex& v) {
+  float4 q[kVertexFloat4s];
+  pack_vertex(v, q);
+#pragma unroll
+  for (int k = 0; k < kVertexFloat4s; ++k) base[size_t(k) * stride + slot] = q[k];
+}
+__device__ __forceinline__ Vertex load_slot_vertex(const float4* base, uint32_t stride, uint32_t slot) {
+  float4 q[kVertexFloat4s];
+#pragma unroll
+  for (int k = 0; k < kVertexFloat4s; ++k) q[k] = base[size_t(k) * stride + slot];
+  return unpack_vertex(q);
+}
+__device__ __forceinline__ void store_pool_vertex(const VcmPool& p, uint32_t idx, const Vertex& v) {
+  float4 q[kVertexFloat4s];
+  pack_vertex(v, q);
+  float4* o = p.lv + size_t(idx) * kVertexFloat4s;
+#pragma unroll
+  for (int k = 0; k < kVertexFloat4s; ++k) o[k] = q[k];
+}
+__device__ __forceinline__ Vertex load_pool_vertex(const VcmPool& p, uint32_t idx) {
+  float4 q[kVertexFloat4s];
+  const float4* o = p.lv + size_t(idx) * kVertexFloat4s;
+#pragma unroll
+  for (int k = 0; k < kVertexFloat4s; ++k) q[k] = __ldg(o + k);
+  return unpack_vertex(q);
+}
+
+__device__ __forceinline__ float clamp_vm(const VcmParams& P, float x) { return fminf(P.clamp_const, x); }  // UPGBase::_clamp
+
+// UPGBase::_sample_to_vertex (UPG.cpp:188-201)
+__device__ __forceinline__ Vertex sample_to_vertex(const LightSample& sample, const VcmParams& P) {
+  Vertex v;
+  v.s = sample.surface;
+  v.omega = v.s.normal();
+  v.thr = sample.radiance / sample.combined_density() * P.roulette_inv;
+  v.w0 = sample.directional ? 0.0f : 1.0f / sample.combined_density();
+  v.w1 = 0.0f; v.w2 = 0.0f; v.bgeo = 0.0f;
+  v.set(1u, sample.directional ? 1u : 0u, 0u);
+  return v;
+}
+
+__device__ __forceinline__ LightSample light_sample_at(const DeviceScene& sc, uint32_t id, float3 pos) {
+  const B2ptLight& l = sc.lights[id];
+  LightSample r;
+  r.surface.pos = pos;
+  r.surface.tan.c0 = f3(l.tangent[0], l.tangent[1], l.tangent[2]);
+  r.surface.tan.c1 = f3(l.tangent[3], l.tangent[4], l.tangent[5]);
+  r.surface.tan.c2 = f3(l.tangent[6], l.tangent[7], l.tangent[8]);
+  r.surface.gnormal = r.surface.tan.c1;
+  r.surface.material_id = l.material_id;
+  r.radiance = f3(l.exitance[0], l.exitance[1], l.exitance[2]) * kOneOverPi;
+  r.area_density = 1.0f / (l.size[0] * l.size[1]);
+  r.light_density = l.weight;
+  r.directional = l.diffuse == 0.0f;
+  return r;
+}
+
+// UPGBase::Connection (UPG.hpp:45-53)
+struct Connection {
+  const Vertex& light;
+  const Vertex& eye;
+  BsdfQuery lb, eb;
+  Edge edge;
+  __device__ __forceinline__ Connection(const DeviceScene& sc, const Vertex& l, const Vertex& e, float3 omega)
+      : light(l), eye(e), lb(bsdf_query(sc, l.s, l.omega, omega)), eb(bsdf_query(sc, e.s, -omega, e.omega)),
+        edge(l.s.pos, l.s.normal(), e.s.pos, e.s.normal(), omega) {}
+  // _connect(connection) without the visibility factor (UPG.cpp:438-447)
+  __device__ __forceinline__ float3 unoccluded() const { return light.thr * lb.throughput * eye.thr * eb.throughput * edge.b_cos * edge.f_geometry; }
+};
+
+// _vc_subweight_inv (UPG.cpp:294-305)
+__device__ __forceinline__ float vc_subweight_inv(const Connection& c, const VcmParams& P) {
+  const float b = P.beta;
+  const float Ap = (c.light.w1 * beta_fn(c.lb.density_rev, b) + float(c.light.finite()) * beta_fn(c.light.w0, b)) * beta_fn(c.edge.b_geometry * c.eb.density_rev, b);
+  const float Cp = (c.eye.w1 * beta_fn(c.eb.density, b) + float(c.eye.finite()) * beta_fn(c.eye.w0, b)) * beta_fn(c.edge.f_geometry * c.lb.density, b);
+  return Ap + Cp + 1.0f;
+}
+
+// the Bp + Dp part shared by _vm_subweight_inv and _vm_biased_subweight_inv (from_light branch, UPG.cpp:308-377)
+__device__ __forceinline__ float vm_bd(const Connection& c, const VcmParams& P) {
+  const float b = P.beta;
+  const float light_vm = clamp_vm(P, beta_fn(P.circle / c.light.w0, b));
+  const float eye_vm = clamp_vm(P, beta_fn(P.circle * c.eye.bgeo * c.eb.density, b)) * (c.eye.length() <= 1.0f ? 0.0f : 1.0f);
+  const float Bp = (c.light.w2 * beta_fn(c.lb.density_rev, b) + float(c.lb.finite) * light_vm * beta_fn(c.light.w0, b) * (c.light.length() <= 1.0f ? 0.0f : 1.0f)) *
+                   beta_fn(c.edge.b_geometry * c.eb.density_rev, b);
+  const float Dp = (c.eye.w2 * beta_fn(c.eb.density, b) + float(c.eb.finite) * eye_vm * beta_fn(c.eye.w0, b) * (c.eye.length() <= 1.0f ? 0.0f : 1.0f)) *
+                   beta_fn(c.edge.f_geometry * c.lb.density, b);
+  return Bp + Dp;
+}
+__device__ __forceinline__ float vm_subweight_inv(const Connection& c, const VcmParams& P) {
+  const float connect_vm = clamp_vm(P, beta_fn(P.circle * c.edge.f_geometry * c.lb.density, P.beta)) * (c.eye.length() * c.light.length() == 0.0f ? 0.0f : 1.0f);
+  return beta_fn(P.num_scattered, P.beta) * (vm_bd(c, P) + connect_vm);
+}
+__device__ __forceinline__ float vm_biased_subweight_inv(const Connection& c, const VcmParams& P, float connect_vm) {
+  return beta_fn(P.num_scattered, P.beta) * (vm_bd(c, P) + connect_vm);
+}
+// _vc_weight / _vc_biased_weight (UPG.cpp:379-403)
+__device__ __forceinline__ float vc_weight(const Connection& c, const VcmParams& P) {
+  if (c.eye.length() + c.light.length() < 2.0f) return 1.0f / vc_subweight_inv(c, P);
+  return 1.0f / (float(P.enable_vc) * vc_subweight_inv(c, P) + float(P.enable_vm) * vm_subweight_inv(c, P));
+}
+__device__ __forceinline__ float vc_biased_weight(const Connection& c, const VcmParams& P, float vm_current) {
+  if (c.eye.length() + c.light.length() < 2.0f) return 1.0f / vc_subweight_inv(c, P);
+  return 1.0f / (float(P.enable_vc) * vc_subweight_inv(c, P) + float(P.enable_vm) * vm_biased_subweight_inv(c, P, vm_current));
+}
+
+// UPGBase::_connect(light, eye) without the visibility factor (UPG.cpp:527-551)
+__device__ __forceinline__ float3 connect_vertices(const DeviceScene& sc, const Vertex& light, const Vertex& eye, const VcmParams& P) {
+  const float3 omega = normalize(eye.s.pos - light.s.pos);
+  const Connection c(sc, light, eye, omega);
+  const float3 throughput = c.unoccluded();
+  if (!(l1norm(throughput) > kFltEpsilon)) return f3(0.0f);
+  const float vm_current = clamp_vm(P, beta_fn(P.circle * c.edge.f_geometry * c.lb.density, P.beta)) * (eye.length() == 0.0f ? 0.0f : 1.0f);
+  const float weight = P.unbiased ? vc_weight(c, P) : vc_biased_weight(c, P, vm_current);
+  return throughput * weight;
+}
+
+// Technique::_camera_coefficient (Technique.cpp:246-274)
+__device__ __forceinline__ float camera_coefficient(float3 light_omega, float3 light_gnormal, float3 light_normal, float3 eye_omega, float3 eye_normal) {
+  const float normal_c = fabsf(dot(eye_omega, light_gnormal) * dot(light_omega, light_normal) / (dot(eye_omega, light_normal) * dot(light_omega, light_gnormal)));
+  const float c = fabsf(dot(eye_normal, eye_omega));
+  return normal_c * (1.0f / cr_powf(c, 3.0f));
+}
+
+__device__ __forceinline__ unsigned warp_reserve(unsigned* counter, unsigned n) {
+  const unsigned lane = threadIdx.x & 31u;
+  unsigned incl = n;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= unsigned(o)) incl += t;
+  }
+  const unsigned total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+  unsigned base = 0;
+  if (lane == 31 && total > 0) base = atomicAdd(counter, total);
+  base = __shfl_sync(0xFFFFFFFFu, base, 31);
+  return base + incl - n;
+}
+
+// ---------------------------------------------------------------- photon phase: UPGBase::_traceLight (UPG.cpp:208-292)
+// One slot per photon path; stream (seed, kDomainPhoton, photon, sample).  States: kNew -> kLightWait (an
+// intersectMesh ray is in flight) -> kDone.
+__global__ void __launch_bounds__(256) vcm_photon_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample) {
+  const DeviceScene& sc = cfg.scene;
+  if (blockIdx.x == 0 && threadIdx.x == 0) cnt->trace_count[parity ^ 1] = 0;
+  const float beta = P.beta;
+  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < pool.photons; slot += gridDim.x * blockDim.x) {
+    uint32_t st = pool.p_state[slot];
+    bool want_trace = false, finished = false, terminate = false;
+    uint32_t head = kInvalid, count = 0;
+    Rng rng; rng.key = 0; rng.ctr = 0;
+    Vertex cur;
+    BsdfSample bs;
+    bs.omega = f3(0.f); bs.throughput = f3(0.f); bs.density = 0.f; bs.density_rev = 0.f; bs.finite = 1;
+    float3 O = f3(0.f);
+    if (st != kDone) {
+      if (st == kNew && slot >= P.num_photons) {
+        finished = true;  // padding slot
+      } else if (st == kNew) {
+        rng.key = stream_key(cfg.params.seed, kDomainPhoton, slot, sample);
+        pool.lp_head[slot] = kInvalid; pool.lp_count[slot] = 0;
+        if (P.roulette < rng.sample()) {  // UPG.cpp:210-212
+          finished = true;
+        } else {
+          cur = sample_to_vertex(sample_light(sc, rng), P);
+          const unsigned idx = atomicAdd(&cnt->lv_count, 1u);
+          if (idx >= pool.lv_capacity) {
+            atomicAdd(&cnt->capacity_events, 1ull);
+            finished = true;
+          } else {
+            store_pool_vertex(pool, idx, cur);
+            pool.lv_link[idx] = kInvalid;
+            head = idx; count = 1;
+            bs = bsdf_sample(sc, rng, cur.s, cur.omega);
+            st = kLightWait;
+            // while (!_russian_roulette(generator)) -> intersectMesh
+            if (P.roulette < rng.sample()) terminate = true; else want_trace = true;
+          }
+        }
+      } else {  // kLightWait: consume the closest mesh hit (UPG.cpp:227-285)
+        const uint2 rs = pool.p_rng[slot];
+        rng.key = rs.x; rng.ctr = rs.y;
+        head = pool.lp_head[slot]; count = pool.lp_count[slot];
+        cur = load_slot_vertex(pool.p_cv, pool.photons, slot);
+        const float4 bo = pool.p_bs_omega[slot], bt = pool.p_bs_thr[slot], ro = pool.p_ray_o[slot], hv = pool.p_hit[slot];
+        bs.omega = f3(bo.x, bo.y, bo.z); bs.density = bo.w;
+        bs.throughput = f3(bt.x, bt.y, bt.z); bs.density_rev = bt.w;
+        bs.finite = __float_as_uint(ro.w) & 1u;
+        O = f3(ro.x, ro.y, ro.z);
+        const uint32_t tri = __float_as_uint(hv.w);
+        if (tri == kInvalid) {
+          terminate = true;
+        } else {
+          Vertex nv;
+          nv.s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, bs.omega);
+          nv.omega = -bs.omega;
+          const BsdfSample nbs = bsdf_sample(sc, rng, nv.s, nv.omega);  // new_bsdf is drawn before the throughput test
+          const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
+          nv.thr = cur.thr * bs.throughput * edge.b_cos * P.roulette_inv;
+          if (l1norm(nv.thr) < kFltEpsilon) {
+            terminate = true;
+          } else {
+            nv.thr /= bs.density;
+            nv.bgeo = edge.b_geometry;
+            const uint32_t len = uint32_t(cur.length()) + 1u;
+            cur.set_finite(min(cur.finite(), bs.finite));
+            nv.set(bs.finite, 0u, len);
+            nv.w0 = 1.0f / (edge.f_geometry * bs.density);
+            nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + float(cur.finite()) * beta_fn(cur.w0, beta)) * beta_fn(edge.b_geometry * nv.w0, beta);
+            const float vertex_merging = clamp_vm(P, beta_fn(P.circle / cur.w0, beta));  // from_light
+            nv.w2 = (cur.w2 * beta_fn(bs.density_rev, beta) + float(bs.finite) * vertex_merging * (cur.length() <= 1.0f ? 0.0f : 1.0f) * beta_fn(cur.w0, beta)) *
+                    beta_fn(edge.b_geometry * nv.w0, beta);
+            pool.lv[size_t(head) * kVertexFloat4s + 1].w = __uint_as_float(cur.flags);  // prv->finite, updated in place
+            unsigned idx = kInvalid;
+            if (count < P.max_subpath) idx = atomicAdd(&cnt->lv_count, 1u);
+            if (idx >= pool.lv_capacity) {
+              atomicAdd(&cnt->capacity_events, 1ull);  // truncated: the stored prefix stays valid
+              terminate = true;
+            } else {
+              store_pool_vertex(pool, idx, nv);
+              pool.lv_link[idx] = head;
+              head = idx; ++count;
+              cur = nv; bs = nbs;
+              if (P.roulette < rng.sample()) terminate = true; else want_trace = true;
+            }
+          }
+        }
+      }
+      if (terminate) {
+        // UPG.cpp:287-289: a path may not end in a vertex whose pending BSDF sample is a delta lobe
+        if (bs.finite == 0) {
+          pool.lv[size_t(head) * kVertexFloat4s + 1].w = __uint_as_float(cur.flags | kFlagDead);
+          head = pool.lv_link[head];
+          --count;
+        }
+        finished = true;
+      }
+      if (finished) {
+        st = kDone;
+        if (head != kInvalid || count) { pool.lp_head[slot] = head; pool.lp_count[slot] = count; }
+      } else {
+        O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);  // Scene::intersectMesh (Scene.cpp:204-208)
+        store_slot_vertex(pool.p_cv, pool.photons, slot, cur);
+        pool.p_rng[slot] = make_uint2(rng.key, rng.ctr);
+        pool.lp_head[slot] = head; pool.lp_count[slot] = count;
+        pool.p_bs_omega[slot] = make_float4(bs.omega.x, bs.omega.y, bs.omega.z, bs.density);
+        pool.p_bs_thr[slot] = make_float4(bs.throughput.x, bs.throughput.y, bs.throughput.z, bs.density_rev);
+        pool.p_ray_o[slot] = make_float4(O.x, O.y, O.z, __uint_as_float(bs.finite & 1u));
+      }
+      pool.p_state[slot] = st;
+    }
+    {
+      const unsigned mask = __ballot_sync(0xFFFFFFFFu, finished);
+      if (mask && (threadIdx.x & 31u) == 0) atomicAdd(&cnt->done, unsigned(__popc(mask)));
+    }
+    const unsigned tq = warp_append(&cnt->trace_count[parity], want_trace);
+    if (want_trace) pool.trace_q[tq] = slot;
+  }
+}
+
+__global__ void __launch_bounds__(256) vcm_photon_trace_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
+  const uint32_t n = cnt->trace_count[parity];
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t slot = pool.trace_q[i];
+    const float4 o = pool.p_ray_o[slot], d = pool.p_bs_omega[slot];
+    const Hit h = trace_ray<false, true>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY);
+    pool.p_hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+  }
+}
+
+// the points of the photon index: every stored vertex that is not on a light (HashGrid3D.hpp:252-255) and was not
+// dropped at the end of its path
+__global__ void vcm_grid_points_kernel(VcmPool pool, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 q0 = pool.lv[size_t(i) * kVertexFloat4s + 0], q1 = pool.lv[size_t(i) * kVertexFloat4s + 1];
+  const bool is_light = (__float_as_uint(q0.w) & 3u) == B2PT_ENTITY_LIGHT;
+  const bool dead = (__float_as_uint(q1.w) & kFlagDead) != 0u;
+  pool.grid_points[i] = make_float4(q0.x, q0.y, q0.z, __uint_as_float(is_light || dead ? kInvalidPoint : i));
+}
+
+// ---------------------------------------------------------------- eye phase: UPGBase::_traceEye (UPG.cpp:40-174)
+// UPGBase::_connect_light (UPG.cpp:449-476)
+__device__ __forceinline__ float3 connect_light(const DeviceScene& sc, const Vertex& eye, float Dp, const VcmParams& P) {
+  const BsdfQuery cb = bsdf_query(sc, eye.s, f3(0.0f), eye.omega);
+  if (l1norm(cb.throughput) < kFltMin) return f3(0.0f);
+  float3 lr; float ld;
+  query_lsdf(sc, eye.s, eye.omega, lr, ld);
+  const float Cp = (eye.w1 * beta_fn(cb.density, P.beta) + beta_fn(eye.w0, P.beta) * float(eye.finite())) * beta_fn(ld, P.beta);
+  const float weight_inv = Cp + 1.0f + beta_fn(P.num_scattered, P.beta) * Dp;
+  return lr * eye.thr / weight_inv;
+}
+
+__global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample) {
+  const DeviceScene& sc = cfg.scene;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    cnt->trace_count[parity ^ 1] = 0; cnt->pair_count[parity ^ 1] = 0;
+    cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0;
+  }
+  const float beta = P.beta;
+  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < pool.pixels_pad; slot += gridDim.x * blockDim.x) {
+    uint32_t st = pool.state[slot];
+    bool want_trace = false, want_gather = false, finished = false, store_cur = false;
+    uint32_t emit_n = 0, emit_flags = 0;
+    bool emit_nee = false, emit_skip_first = false;
+    uint32_t head = kInvalid, count = 0;
+    float3 O = f3(0.f), rad = f3(0.f);
+    Rng rng; rng.key = 0; rng.ctr = 0;
+    Vertex cur;
+    BsdfSample bs;
+    bs.omega = f3(0.f); bs.throughput = f3(0.f); bs.density = 0.f; bs.density_rev = 0.f; bs.finite = 1;
+    if (st != kDone) {
+      if (st == kNew && slot >= cfg.pixels) {
+        finished = true;  // padding slot
+      } else if (st == kNew) {
+        rng.key = stream_key(cfg.params.seed, kDomainPixel, slot, sample);
+        const float3 dir = shoot_primary(cfg, rng, slot);  // Technique::_for_each_ray (Technique.cpp:321-331)
+        if (P.roulette < rng.sample()) {  // UPG.cpp:45-47
+          finished = true;
+        } else {
+          cur.s = cfg.camera;
+          cur.omega = -dir;
+          cur.thr = f3(1.0f) * P.roulette_inv;
+          cur.w0 = 0.0f; cur.w1 = 0.0f; cur.w2 = 0.0f; cur.bgeo = 0.0f;
+          cur.set(1u, 0u, 0u);
+          store_cur = true;
+          head = pool.lp_head[slot]; count = pool.lp_count[slot];
+          if (P.enable_vc) { emit_n = count; emit_flags = kPairCamera; }  // _connect(context, camera vertex), UPG.cpp:559-578
+          bs = bsdf_sample(sc, rng, cur.s, cur.omega);  // CameraBSDF::sample: no draws
+          O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);
+          want_trace = true;
+          st = kEyeWait;
+        }
+      } else {  // kEyeWait: UPG.cpp:71-143
+        const uint2 rs = pool.rng[slot];
+        rng.key = rs.x; rng.ctr = rs.y;
+        head = pool.lp_head[slot]; count = pool.lp_count[slot];
+        const float4 rv = pool.rad[slot];
+        rad = f3(rv.x, rv.y, rv.z);
+        cur = load_slot_vertex(pool.cv, pool.pixels_pad, slot);
+        const float4 bo = pool.bs_omega[slot], bt = pool.bs_thr[slot], ro = pool.ray_o[slot], hv = pool.hit[slot];
+        bs.omega = f3(bo.x, bo.y, bo.z); bs.density = bo.w;
+        bs.throughput = f3(bt.x, bt.y, bt.z); bs.density_rev = bt.w;
+        bs.finite = __float_as_uint(ro.w) & 1u;
+        O = f3(ro.x, ro.y, ro.z);
+        const uint32_t tri = __float_as_uint(hv.w);
+        if (tri == kInvalid) {
+          if (cur.s.is_camera()) {  // return sky_gradient(bsdf.omega) *= _roulette_inv (UPG.cpp:76-78)
+            const float3 h = f3(cfg.params.sky_horizon[0], cfg.params.sky_horizon[1], cfg.params.sky_horizon[2]);
+            const float3 z = f3(cfg.params.sky_zenith[0], cfg.params.sky_zenith[1], cfg.params.sky_zenith[2]);
+            rad = (h * (1 - bs.omega.z) + z * bs.omega.z) * P.roulette_inv;
+          }
+          finished = true;
+        } else {
+          Vertex nv;
+          nv.s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, bs.omega);
+          nv.omega = -bs.omega;
+          const BsdfSample nbs = bsdf_sample(sc, rng, nv.s, nv.omega);  // new_bsdf: drawn on every hit, lights included
+          const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
+          nv.thr = cur.thr * bs.throughput * edge.b_cos;
+          if (l1norm(nv.thr) < kFltEpsilon) {
+            finished = true;
+          } else {
+            nv.thr /= bs.density;
+            nv.bgeo = edge.b_geometry;
+            const uint32_t len = uint32_t(cur.length()) + 1u;
+            cur.set_finite(min(cur.finite(), bs.finite));
+            nv.set(bs.finite, 0u, len);
+            nv.w0 = 1.0f / (edge.f_geometry * bs.density);
+            nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + float(cur.finite()) * beta_fn(cur.w0, beta)) * beta_fn(edge.b_geometry * nv.w0, beta);
+            const float trim = cur.length() <= 1.0f ? 0.0f : 1.0f;
+            const float vertex_merging = clamp_vm(P, beta_fn(P.circle * cur.bgeo * bs.density_rev, beta)) * trim;  // from_light
+            const float dterm = cur.w2 * beta_fn(bs.density_rev, beta) + float(cur.finite()) * vertex_merging * trim * beta_fn(cur.w0, beta);
+            nv.w2 = dterm * beta_fn(edge.b_geometry * nv.w0, beta);
+            if (nv.s.is_light()) {
+              if (P.enable_vc) {  // UPG.cpp:121-139
+                float3 lr; float ld;
+                query_lsdf(sc, nv.s, nv.omega, lr, ld);
+                const BsdfQuery cb = bsdf_query(sc, nv.s, f3(0.0f), nv.omega);
+                float Dp = dterm * beta_fn(edge.b_geometry * cb.density, beta);
+                Dp *= (nv.length() <= 2.0f ? 0.0f : 1.0f) * float(P.enable_vm);
+                Dp *= beta_fn(ld * nv.w0, beta);
+                rad += connect_light(sc, nv, Dp, P);
+              }
+              // on through the light: prv and bsdf stay, the next ray starts at the light's surface
+              O = offset_origin(nv.s.pos, nv.s.gnormal, bs.omega);
+              store_cur = true;  // prv->finite
+              want_trace = true;
+            } else {
+              nv.thr = nv.thr * P.roulette_inv;
+              cur = nv; bs = nbs;
+              store_cur = true;
+              want_gather = P.enable_vm != 0u;  // _gather / _gather_biased(context, *prv, *itr), UPG.cpp:148-156
+              if (P.roulette < rng.sample()) {  // UPG.cpp:160-162
+                finished = true;
+              } else {
+                if (P.enable_vc) {  // _connect(context, eye) on a surface vertex (UPG.cpp:579-595)
+                  if (!(P.roulette < rng.sample())) {
+                    const LightSample ls = sample_light(sc, rng);
+                    if (!ls.directional) {
+                      emit_nee = true;
+                      const uint32_t light_id = sc.materials[ls.surface.material_index()].light_id;
+                      pool.nee[slot] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
+                    } else {
+                      atomicAdd(&cnt->capacity_events, 1ull);  // _connect_directional: sun lights are not wired in yet
+                    }
+                  }
+                  emit_n = (count > 0 ? count - 1u : 0u) + (emit_nee ? 1u : 0u);
+                  emit_skip_first = true;
+                }
+                O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);
+                want_trace = true;
+              }
+            }
+          }
+        }
+      }
+      if (store_cur) store_slot_vertex(pool.cv, pool.pixels_pad, slot, cur);
+      if (finished) {
+        pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+        st = kDone;
+      } else {
+        pool.rng[slot] = make_uint2(rng.key, rng.ctr);
+        if (st == kEyeWait) pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+        if (want_trace) {
+          pool.bs_omega[slot] = make_float4(bs.omega.x, bs.omega.y, bs.omega.z, bs.density);
+          pool.bs_thr[slot] = make_float4(bs.throughput.x, bs.throughput.y, bs.throughput.z, bs.density_rev);
+          pool.ray_o[slot] = make_float4(O.x, O.y, O.z, __uint_as_float(bs.finite & 1u));
+        }
+      }
+      pool.state[slot] = st;
+    }
+    {
+      const unsigned mask = __ballot_sync(0xFFFFFFFFu, finished);
+      if (mask && (threadIdx.x & 31u) == 0) atomicAdd(&cnt->done, unsigned(__popc(mask)));
+    }
+    const unsigned tq = warp_append(&cnt->trace_count[parity], want_trace);
+    if (want_trace) pool.trace_q[tq] = slot;
+    const unsigned gq = warp_append(&cnt->gather_count[parity], want_gather);
+    if (want_gather) pool.gather_q[gq] = slot;
+    unsigned pq = warp_reserve(&cnt->pair_count[parity], emit_n);
+    if (emit_n) {
+      if (pq + emit_n > pool.q_capacity) {
+        atomicAdd(&cnt->capacity_events, 1ull);
+      } else {
+        if (emit_nee) pool.pair_q[pq++] = make_uint2(slot, kNeeVertex);
+        for (uint32_t v = head; v != kInvalid;) {
+          const uint32_t prev = pool.lv_link[v];
+          if (!(emit_skip_first && prev == kInvalid)) pool.pair_q[pq++] = make_uint2(slot | emit_flags, v);
+          v = prev;
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------- connection stage (one thread per pair)
+__global__ void __launch_bounds__(256) vcm_connect_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity) {
+  const DeviceScene& sc = cfg.scene;
+  const uint32_t n = min(cnt->pair_count[parity], pool.q_capacity);
+  const uint32_t rounds = (n + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
+  for (uint32_t r = 0; r < rounds; ++r) {
+    const uint32_t i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+    bool want = false;
+    float3 a = f3(0.f), d = f3(0.f), c = f3(0.f);
+    uint32_t target = 0, flags = 0;
+    if (i < n) {
+      const uint2 desc = pool.pair_q[i];
+      const uint32_t slot = desc.x & ~kPairCamera;
+      const bool camera = (desc.x & kPairCamera) != 0u;
+      const Vertex eye = load_slot_vertex(pool.cv, pool.pixels_pad, slot);
+      Vertex light;
+      if (desc.y == kNeeVertex) {
+        const float4 nr = pool.nee[slot];
+        light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), P);
+      } else {
+        light = load_pool_vertex(pool, desc.y);
+      }
+      bool inside = true;
+      if (camera) {  // Technique::_accumulate (Technique.cpp:276-305)
+        const float3 omega = normalize(light.s.pos - eye.s.pos);
+        mat3 w2v;
+        const float* m = cfg.params.camera.world_to_view;
+        w2v.c0 = f3(m[0], m[1], m[2]); w2v.c1 = f3(m[3], m[4], m[5]); w2v.c2 = f3(m[6], m[7], m[8]);
+        const float2 pp = pixel_position(mul(w2v, omega), cfg.width_f, cfg.height_f, cfg.res_y_inv, cfg.params.camera.focal_length_y);
+        inside = (0 <= pp.x) && (pp.x < cfg.width_f) && (0 <= pp.y) && (pp.y < cfg.height_f);
+        if (inside) {
+          target = uint32_t(int(pp.y)) * cfg.params.width + uint32_t(int(pp.x));
+          flags = kShadowSplat;
+          const float cc = camera_coefficient(light.omega, light.s.gnormal, light.s.normal(), omega, eye.s.normal());
+          c = connect_vertices(sc, light, eye, P) * cfg.focal_factor_y * cc;
+        }
+      } else {
+        target = slot;
+        c = connect_vertices(sc, light, eye, P);
+      }
+      if (inside) {
+        const float l1 = l1norm(c);
+        if (!isfinite(l1)) {
+          // a non-finite connection poisons the sample whether or not it is visible (0 * inf); _commit_images drops it
+          if (flags & kShadowSplat) atomicAdd(pool.splat + size_t(target) * 3, double(NAN));
+          else atomicAdd(&pool.rad[target].x, NAN);
+        } else if (l1 != 0.0f) {
+          // Scene::occluded(eye.surface, light.surface) (Scene.cpp:151-171)
+          const float3 direction = normalize(light.s.pos - eye.s.pos);
+          a = eye.s.pos + (dot(eye.s.gnormal, direction) > 0.0f ? 1.0f : -1.0f) * eye.s.gnormal * 0.0001f;
+          const float3 b = light.s.pos + (dot(light.s.gnormal, direction) < 0.0f ? 1.0f : -1.0f) * light.s.gnormal * 0.0001f;
+          d = b - a;
+          want = true;
+        }
+      }
+    }
+    const unsigned sq = warp_append(&cnt->shadow_count[parity], want);
+    if (want) {
+      if (sq < pool.q_capacity) {
+        float4* e = pool.shadow_q + size_t(sq) * 3;
+        e[0] = make_float4(a.x, a.y, a.z, __uint_as_float(target));
+        e[1] = make_float4(d.x, d.y, d.z, __uint_as_float(flags));
+        e[2] = make_float4(c.x, c.y, c.z, 0.f);
+      } else {
+        atomicAdd(&cnt->capacity_events, 1ull);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) vcm_trace_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
+  const uint32_t n = cnt->trace_count[parity];
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t slot = pool.trace_q[i];
+    const float4 o = pool.ray_o[slot], d = pool.bs_omega[slot];
+    const Hit h = trace_ray<false, false>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY);  // Scene::intersect
+    pool.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+  }
+}
+
+__global__ void __launch_bounds__(256) vcm_shadow_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
+  const uint32_t n = min(cnt->shadow_count[parity], pool.q_capacity);
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->shadow_rays, (unsigned long long)n);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4* e = pool.shadow_q + size_t(i) * 3;
+    const float4 o = e[0], d = e[1], c = e[2];
+    const uint32_t target = __float_as_uint(o.w), flags = __float_as_uint(d.w);
+    const Hit h = trace_ray<true, true>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, 1.0f);
+    if (h.tri == kInvalid) {
+      if (flags & kShadowSplat) {
+        double* s = pool.splat + size_t(target) * 3;
+        atomicAdd(s + 0, double(c.x)); atomicAdd(s + 1, double(c.y)); atomicAdd(s + 2, double(c.z));
+      } else {
+        float* r = &pool.rad[target].x;
+        atomicAdd(r + 0, c.x); atomicAdd(r + 1, c.y); atomicAdd(r + 2, c.z);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------- merging stage
+// Intersector::intersectFast (Intersector.cpp:17-46): bounded mesh-only closest hit, then "hit point inside the sphere"
+__device__ __forceinline__ bool intersect_fast(const DeviceScene& sc, const Surface& s, float3 direction, float target_length, float3 world_center,
+                                               float radius) {
+  const float3 org = offset_origin(s.pos, s.gnormal, direction);
+  const Hit h = trace_ray<false, true>(sc, org, direction, 0.0f, target_length + radius);
+  const float3 isect = org + direction * h.t;
+  return h.tri != kInvalid && distance2(world_center, isect) < radius * radius;
+}
+
+// BSDF::gathering_density of the surface's material (DiffuseBSDF BSDF.cpp:264-289, PhongBSDF :393-434): the number of
+// bounded-lobe samples until one lands inside the merge sphere, over the lobe restriction factor
+__device__ float gathering_density(const DeviceScene& sc, Rng& rng, const Surface& s, float3 target, float radius, float3 omega_world,
+                                   unsigned long long& rays) {
+  const B2ptMaterial& m = sc.materials[s.material_index()];
+  const float3 center = s.to_surface(target - s.pos);
+  const float3 omega = s.to_surface(omega_world);
+  const float target_length = length(center);
+  float N = 1.0f;
+  if (m.type == B2PT_BSDF_DIFFUSE) {
+    while (N < kDensityTestLimit) {
+      float adjust;
+      const float3 d = sample_lambert_bounded(rng, center, radius, omega, adjust);
+      ++rays;
+      if (intersect_fast(sc, s, s.to_world(d), target_length, target, radius)) return N / adjust;
+      N += 1.0f;
+    }
+    return INFINITY;
+  }
+  if (m.type == B2PT_BSDF_PHONG) {
+    const float diffuse_adjust = lambert_adjust(center, radius);
+    const float specular_adjust = phong_adjust(omega, m.power, center, radius);
+    const float combined_adjust = diffuse_adjust * m.diffuse_probability + specular_adjust * (1.0f - m.diffuse_probability);
+    const float diffuse_probability =
+        diffuse_adjust * m.diffuse_probability / (diffuse_adjust * m.diffuse_probability + specular_adjust * (1.0f - m.diffuse_probability));
+    while (N < kDensityTestLimit) {
+      float3 d;
+      if (rng.sample() < diffuse_probability) { float adjust; d = sample_lambert_bounded(rng, center, radius, omega, adjust); }
+      else d = sample_phong_bounded(rng, omega, m.power, center, radius);
+      ++rays;
+      if (intersect_fast(sc, s, s.to_world(d), target_length, target, radius)) return N / combined_adjust;
+      N += 1.0f;
+    }
+    return INFINITY;
+  }
+  return INFINITY;  // delta lobes never reach here: their connection throughput is zero
+}
+
+// _merge_biased (UPG.cpp:783-817) with light = _light_paths[index - 1], tentative = _light_paths[index]
+__device__ __forceinline__ float3 merge_biased(const DeviceScene& sc, const Vertex& light, const Vertex& tentative, const Vertex& eye, const VcmParams& P) {
+  const float3 omega = normalize(eye.s.pos - light.s.pos);
+  const Connection c(sc, light, eye, omega);
+  const float3 throughput = tentative.thr * eye.thr * c.eb.throughput * P.roulette;
+  if (l1norm(throughput) < kFltEpsilon) return f3(0.0f);
+  const float vm_current = beta_fn(P.circle / tentative.w0, P.beta);
+  // _vm_biased_weight (UPG.cpp:405-410)
+  const float weight = beta_fn(P.num_scattered, P.beta) * vm_current * vc_biased_weight(c, P, vm_current * (eye.length() == 0.0f ? 0.0f : 1.0f));
+  const float density = 1.0f / P.circle;
+  return throughput * density * weight;
+}
+
+// _merge_light (UPG.cpp:727-753), unbiased mode
+__device__ __forceinline__ float3 merge_light(const DeviceScene& sc, Rng& rng, const Vertex& light, const Vertex& eye, const VcmParams& P,
+                                              unsigned long long& shadow_rays, unsigned long long& density_rays) {
+  const float3 omega = normalize(eye.s.pos - light.s.pos);
+  const Connection c(sc, light, eye, omega);
+  const float3 unoccluded = c.unoccluded();
+  if (!(l1norm(unoccluded) >= kFltEpsilon)) return f3(0.0f);
+  // Scene::occluded(eye.surface, light.surface)
+  const float3 direction = normalize(light.s.pos - eye.s.pos);
+  const float3 a = eye.s.pos + (dot(eye.s.gnormal, direction) > 0.0f ? 1.0f : -1.0f) * eye.s.gnormal * 0.0001f;
+  const float3 b = light.s.pos + (dot(light.s.gnormal, direction) < 0.0f ? 1.0f : -1.0f) * light.s.gnormal * 0.0001f;
+  ++shadow_rays;
+  if (trace_ray<true, true>(sc, a, b - a, 0.0f, 1.0f).tri != kInvalid) return f3(0.0f);
+  // _weight_vm_light (UPG.cpp:420-426)
+  const float weight = beta_fn(P.num_scattered * clamp_vm(P, P.circle * c.edge.f_geometry * c.lb.density), P.beta) * vc_weight(c, P);
+  const float density = gathering_density(sc, rng, light.s, eye.s.pos, P.radius, light.omega, density_rays);
+  return unoccluded * density * weight;
+}
+
+// _gather / _gather_biased (UPG.cpp:675-724): one thread per new eye vertex
+__global__ void __launch_bounds__(128) vcm_gather_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, DeviceGrid grid, VcmCounters* cnt, int parity) {
+  const DeviceScene& sc = cfg.scene;
+  const uint32_t n = cnt->gather_count[parity];
+  unsigned long long shadow_rays = 0, density_rays = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t slot = pool.gather_q[i];
+    const Vertex eye = load_slot_vertex(pool.cv, pool.pixels_pad, slot);  // the tentative vertex, throughput already * 1 / roulette
+    const uint32_t path_key = pool.rng[slot].x;
+    float3 sum = f3(0.0f);
+    auto merge = [&](uint32_t index, float3) {
+      const uint32_t prev = pool.lv_link[index];
+      if (prev == kInvalid) return;
+      const Vertex light = load_pool_vertex(pool, prev);
+      if (light.s.is_light()) return;  // UPG.cpp:689,713: the predecessor must be a surface vertex
+      float3 v;
+      if (P.unbiased) {
+        Rng sub; sub.key = mix32(path_key ^ mix32(index * 0x9E3779B9u + uint32_t(eye.length()))); sub.ctr = 0;
+        v = merge_light(sc, sub, light, eye, P, shadow_rays, density_rays);
+      } else {
+        const Vertex tentative = load_pool_vertex(pool, index);
+        v = merge_biased(sc, light, tentative, eye, P);
+      }
+      sum += v * P.num_scattered_inv;
+    };
+    if (P.brute_vertices) {
+      for (uint32_t k = 0; k < P.brute_vertices; ++k) {
+        const float4 q = pool.grid_points[k];
+        if (__float_as_uint(q.w) != kInvalidPoint && distance2(eye.s.pos, f3(q.x, q.y, q.z)) < P.radius * P.radius) merge(k, f3(q.x, q.y, q.z));
+      }
+    } else {
+      grid_query(grid, eye.s.pos, P.radius * P.radius, merge);
+    }
+    if (sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) {
+      float* r = &pool.rad[slot].x;
+      atomicAdd(r + 0, sum.x); atomicAdd(r + 1, sum.y); atomicAdd(r + 2, sum.z);
+    }
+  }
+  if (shadow_rays) atomicAdd(&cnt->shadow_rays, shadow_rays);
+  if (density_rays) { atomicAdd(&cnt->density_rays, density_rays); atomicAdd(&cnt->basic_rays, density_rays); }
+}
+
+// Technique::_commit_images (Technique.cpp:194-244) for one pass
+__global__ void __launch_bounds__(256) vcm_commit_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, uint32_t pass) {
+  for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < cfg.pixels; pixel += gridDim.x * blockDim.x) {
+    const float4 e = pool.rad[pixel];
+    double* s = pool.splat + size_t(pixel) * 3;
+    const double r = s[0] + double(e.x), g = s[1] + double(e.y), b = s[2] + double(e.z);
+    s[0] = 0.0; s[1] = 0.0; s[2] = 0.0;
+    if (cfg.path_radiance) {
+      float* o = cfg.path_radiance + (size_t(pass) * cfg.pixels + pixel) * 3;
+      o[0] = e.x; o[1] = e.y; o[2] = e.z;
+    }
+    double* a = cfg.accum + size_t(pixel) * 4;
+    if (isfinite(fabs(r) + fabs(g) + fabs(b))) {
+      a[0] += r; a[1] += g; a[2] += b; a[3] += 1.0;
+    } else {
+      atomicAdd(&cnt->numeric_errors, 1ull);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- host driver
+struct VcmWorkspace {
+  VcmPool pool{};
+  uint32_t pixels = 0, photons = 0;
+  VcmCounters* counters = nullptr;
+  VcmCounters* host_counters = nullptr;  // pinned
+  GridStorage grid;
+  std::vector<void*> blocks;
+};
+
+void vcm_workspace_free(void* p) {
+  VcmWorkspace* w = (VcmWorkspace*)p;
+  for (void* q : w->blocks) cudaFree(q);
+  if (w->host_counters) cudaFreeHost(w->host_counters);
+  w->grid.release();
+  delete w;
+}
+
+template <class T>
+int ws_alloc(VcmWorkspace* w, T** p, size_t count) {
+  void* q = nullptr;
+  B2_CUDA(cudaMalloc(&q, count * sizeof(T)));
+  w->blocks.push_back(q);
+  *p = (T*)q;
+  return B2PT_OK;
+}
+
+int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWorkspace** out) {
+  VcmWorkspace* w = (VcmWorkspace*)scene->workspace;
+  if (w && scene->workspace_free == vcm_workspace_free && w->pixels == pixels && w->photons == photons) { *out = w; return B2PT_OK; }
+  if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
+  scene->workspace = nullptr;
+  w = new VcmWorkspace();
+  scene->workspace = w; scene->workspace_free = vcm_workspace_free;
+  w->pixels = pixels; w->photons = photons;
+  const uint32_t block = 256;
+  VcmPool& p = w->pool;
+  p.photons = (photons + block - 1) / block * block;
+  p.pixels_pad = (pixels + block - 1) / block * block;
+  const size_t np = p.photons, ne = p.pixels_pad, nl = np > ne ? np : ne;
+  p.lv_capacity = uint32_t(np * 12u < 4096u ? 4096u : np * 12u);
+  p.q_capacity = p.lv_capacity + uint32_t(ne);
+  int rc;
+  if ((rc = ws_alloc(w, &p.p_state, np))) return rc;
+  if ((rc = ws_alloc(w, &p.p_rng, np))) return rc;
+  if ((rc = ws_alloc(w, &p.p_cv, np * kVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.p_bs_omega, np))) return rc;
+  if ((rc = ws_alloc(w, &p.p_bs_thr, np))) return rc;
+  if ((rc = ws_alloc(w, &p.p_ray_o, np))) return rc;
+  if ((rc = ws_alloc(w, &p.p_hit, np))) return rc;
+  if ((rc = ws_alloc(w, &p.lp_head, nl))) return rc;
+  if ((rc = ws_alloc(w, &p.lp_count, nl))) return rc;
+  if ((rc = ws_alloc(w, &p.state, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.rng, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.cv, ne * kVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.bs_omega, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.bs_thr, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.ray_o, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.hit, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.rad, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.nee, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.splat, ne * 3))) return rc;
+  if ((rc = ws_alloc(w, &p.lv, size_t(p.lv_capacity) * kVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.lv_link, p.lv_capacity))) return rc;
+  if ((rc = ws_alloc(w, &p.grid_points, p.lv_capacity))) return rc;
+  if ((rc = ws_alloc(w, &p.trace_q, nl))) return rc;
+  if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
+  if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
+  if ((rc = ws_alloc(w, &p.gather_q, ne))) return rc;
+  if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
+  B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(VcmCounters)));
+  B2_CUDA(cudaMemset(p.splat, 0, ne * 3 * sizeof(double)));
+  B2_CUDA(cudaMemset(p.lp_head, 0xFF, nl * 4));
+  B2_CUDA(cudaMemset(p.lp_count, 0, nl * 4));
+  *out = w;
+  return B2PT_OK;
+}
+
+}  // namespace
+
+int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
+  const B2ptRenderParams& rp = base.params;
+  B2_CHECK(rp.from_light != 0, B2PT_ERR_INVALID, "VCM/UPG: only merging from the light side (from_light = 1) is built");
+  B2_CHECK(rp.radius > 0.0f, B2PT_ERR_INVALID, "VCM/UPG: radius must be positive");
+  const uint32_t pixels = base.pixels;
+  const uint32_t photons = rp.num_photons ? rp.num_photons : pixels;  // Options.cpp:914-916
+  // UPGBase::_connect reads _light_offsets[pixel_index + 1] (UPG.cpp:556-560): one light path per pixel is assumed
+  B2_CHECK(photons >= pixels, B2PT_ERR_INVALID, "VCM/UPG: num_photons must be at least width * height (UPG.cpp:556-560)");
+  B2_CHECK(photons <= (1u << 24), B2PT_ERR_CAPACITY, "VCM/UPG: more than 2^24 light paths per pass");
+  const int block = 256;
+  VcmWorkspace* w = nullptr;
+  if (int rc = vcm_workspace(scene, pixels, photons, &w)) return rc;
+  VcmPool& pool = w->pool;
+  RenderConfig cfg = base;
+  StageTimer timer(stream);
+  unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
+  const int kBatchIters = 8;
+  const uint32_t stride = rp.sample_stride ? rp.sample_stride : 1u;
+  const int grid_p = grid_for(pool.photons, block), grid_e = grid_for(pool.pixels_pad, block);
+  for (uint32_t pass = 0; pass < rp.num_samples; ++pass) {
+    const uint32_t sample = rp.first_sample + pass * stride;
+    VcmParams P;
+    P.beta = rp.beta; P.roulette = rp.roulette; P.roulette_inv = 1.0f / rp.roulette;
+    P.unbiased = rp.technique == B2PT_TECHNIQUE_UPG; P.enable_vc = rp.enable_vc != 0; P.enable_vm = rp.enable_vm != 0;
+    P.radius = rp.radius;
+    // UPGBase::_preprocess (UPG.cpp:180-183), double arithmetic like the reference; num_samples = the pass index
+    if (!P.unbiased) P.radius = float(rp.radius * pow(double(sample) + 1.0f, double(rp.alpha * 0.5f - 0.5f)));
+    P.circle = kPi * P.radius * P.radius;
+    P.clamp_const = P.unbiased ? 1.0f : 3.402823466e+38f;
+    P.num_scattered = float(photons); P.num_scattered_inv = 1.0f / float(photons);
+    P.num_photons = photons;
+    P.max_subpath = rp.max_subpath ? rp.max_subpath : 1024u;
+    P.brute_vertices = 0;
+
+    // ---- photons
+    B2_CUDA(cudaMemsetAsync(w->counters, 0, sizeof(VcmCounters), stream));
+    B2_CUDA(cudaMemsetAsync(pool.p_state, 0, size_t(pool.photons) * 4, stream));
+    for (int it = 0;;) {
+      for (int k = 0; k < kBatchIters; ++k, ++it) {
+        const int parity = it & 1;
+        timer.begin(kStageShade); vcm_photon_kernel<<<grid_p, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample); timer.end();
+        timer.begin(kStageTrace); vcm_photon_trace_kernel<<<grid_p, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+      }
+      B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(VcmCounters), cudaMemcpyDeviceToHost, stream));
+      B2_CUDA(cudaStreamSynchronize(stream));
+      timer.resolve();
+      if (w->host_counters->done >= pool.photons) break;
+      if (it > (1 << 20)) { set_error("render_vcm: the photon pass did not drain"); return B2PT_ERR_CUDA; }
+    }
+    const uint32_t num_vertices = min(w->host_counters->lv_count, pool.lv_capacity);
+    // ---- photon index
+    timer.begin(kStageShade);
+    if (num_vertices) vcm_grid_points_kernel<<<(num_vertices + block - 1) / block, block, 0, stream>>>(pool, num_vertices);
+    timer.end();
+    if (int rc = grid_build_device(w->grid, pool.grid_points, num_vertices, P.radius, stream)) return rc;
+    { const char* e = getenv("B2PT_VCM_BRUTE"); if (e && e[0] == '1') P.brute_vertices = num_vertices; }
+    // ---- eye paths
+    B2_CUDA(cudaMemsetAsync(&w->counters->done, 0, sizeof(unsigned int), stream));
+    B2_CUDA(cudaMemsetAsync(w->counters->trace_count, 0, sizeof(unsigned int) * 8, stream));
+    B2_CUDA(cudaMemsetAsync(pool.state, 0, size_t(pool.pixels_pad) * 4, stream));
+    const int grid_g = grid_for(pool.pixels_pad, 128);
+    for (int it = 0;;) {
+      for (int k = 0; k < kBatchIters; ++k, ++it) {
+        const int parity = it & 1;
+        timer.begin(kStageShade); vcm_eye_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample); timer.end();
+        timer.begin(kStageShade); vcm_gather_kernel<<<grid_g, 128, 0, stream>>>(cfg, P, pool, w->grid.dev, w->counters, parity); timer.end();
+        timer.begin(kStageShade); vcm_connect_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity); timer.end();
+        timer.begin(kStageTrace); vcm_trace_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+        timer.begin(kStageShadow); vcm_shadow_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+      }
+      B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(VcmCounters), cudaMemcpyDeviceToHost, stream));
+      B2_CUDA(cudaStreamSynchronize(stream));
+      timer.resolve();
+      if (w->host_counters->done >= pool.pixels_pad) break;
+      if (it > (1 << 20)) { set_error("render_vcm: the eye pass did not drain"); return B2PT_ERR_CUDA; }
+    }
+    timer.begin(kStageShade);
+    vcm_commit_kernel<<<grid_for(pixels, block), block, 0, stream>>>(cfg, pool, w->counters, pass);
+    timer.end();
+    B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(VcmCounters), cudaMemcpyDeviceToHost, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));
+    timer.resolve();
+    basic += w->host_counters->basic_rays; shadow += w->host_counters->shadow_rays;
+    numeric += w->host_counters->numeric_errors; capacity += w->host_counters->capacity_events;
+  }
+  B2_CUDA(cudaGetLastError());
+  if (stats) {
+    stats->num_basic_rays = basic;
+    stats->num_shadow_rays = shadow;
+    stats->numeric_errors = numeric;
+    stats->capacity_events = capacity;
+    timer.fill(stats);
+  }
+  return B2PT_OK;
+}
+
+}  // namespace b2pt

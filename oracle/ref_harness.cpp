@@ -14,6 +14,7 @@
 //   rays   <scene> <mode 0|1|2> <rays.bin> <hits.bin>       (B2ptRay in, B2ptHit out)
 //   render <scene> key=value ...   per-(pixel,sample) streams, 1 thread, golden outputs
 //   time   <scene> key=value ...   the reference's own Technique::render loop, N threads
+//   grid   <in.bin> <out.bin>      v3::HashGrid3D build + rQuery on explicit points / queries
 // <scene> is a .blend (needs the reference's models/) or a .b2s written by `dump`.
 #include <chrono>
 #include <cstdio>
@@ -30,6 +31,7 @@
 #include <BPT.hpp>
 #include <PT.hpp>
 #include <UPG.hpp>
+#include <HashGrid3D.hpp>
 #include <Scene.hpp>
 #include <loader.hpp>
 
@@ -144,6 +146,50 @@ template <class T> static void write_vec(const string& path, const std::vector<T
   f.write((const char*)v.data(), v.size() * sizeof(T));
 }
 
+// UPGBase::_preprocess + _scatter (UPG.cpp:177-186, 599-672) with ONE stream per photon path instead of one
+// sequential generator: photon j of pass `sample` draws from stream (seed, domain 2, j, sample).  Everything the
+// photon does — _traceLight, the vertex records, the v3::HashGrid3D build — is the reference's own code; only the
+// seeding between two _traceLight calls is the harness's.  Returns false if T is not this UPGBase instantiation.
+template <class U>
+static bool upg_photon_pass(Technique& T, random_generator_t& gen, uint32_t seed, uint32_t sample, const string& dump) {
+  U* u = dynamic_cast<U*>(&T);
+  if (!u) return false;
+  if (!u->_unbiased) {  // UPG.cpp:180-183 with num_samples = the pass index
+    u->_radius = u->_initial_radius * pow((double(sample) + 1.0f), u->_alpha * 0.5f - 0.5f);
+    u->_circle = pi<float>() * u->_radius * u->_radius;
+  }
+  size_t size = 0;
+  u->_light_offsets.assign(1, 0);
+  for (size_t j = 0; j < u->_num_photons; ++j) {
+    gen.seed(std::b2pt_counter_engine::stream_key(seed, 2, uint32_t(j), sample));
+    u->_traceLight(gen, u->_light_paths, size);
+    u->_light_offsets.push_back(uint32_t(size));
+  }
+  u->_light_paths.resize(size);
+  u->_num_scattered = u->_num_photons;
+  u->_num_scattered_inv = 1.0f / float(u->_num_scattered);
+  u->_statistics.num_scattered += u->_num_scattered;
+  u->_vertices = v3::HashGrid3D<typename U::LightVertex>(&u->_light_paths, u->_radius);
+  if (!dump.empty()) {
+    std::vector<float> v;
+    for (auto& x : u->_light_paths) {
+      v.push_back(x.surface.position().x); v.push_back(x.surface.position().y); v.push_back(x.surface.position().z);
+      v.push_back(x.throughput.x); v.push_back(x.throughput.y); v.push_back(x.throughput.z);
+      v.push_back(x.a); v.push_back(x.A); v.push_back(x.B); v.push_back(x.bGeometry);
+    }
+    write_vec(dump + ".photons.f32", v);
+    write_vec(dump + ".offsets.u32", u->_light_offsets);
+    std::vector<float> r(1, u->_radius);
+    write_vec(dump + ".radius.f32", r);
+  }
+  return true;
+}
+
+static bool photon_pass(Technique& T, random_generator_t& gen, uint32_t seed, uint32_t sample, const string& dump) {
+  return upg_photon_pass<UPG0>(T, gen, seed, sample, dump) || upg_photon_pass<UPG1>(T, gen, seed, sample, dump) ||
+         upg_photon_pass<UPG2>(T, gen, seed, sample, dump) || upg_photon_pass<UPGb>(T, gen, seed, sample, dump);
+}
+
 // ---------------------------------------------------------------- sub-commands
 static int cmd_dump(int argc, char** argv) {
   if (argc < 4) return 2;
@@ -218,9 +264,11 @@ static int cmd_render(int argc, char** argv) {
   for (size_t s = 0; s < spp; ++s) {
     uint32_t sample = first + uint32_t(s) * stride;
     T._adjust_helper_image(view);
-    // domain 1 = whole-pass preprocessing (UPG/VCM photon scatter, UPG.cpp:177-186)
-    gen.seed(std::b2pt_counter_engine::stream_key(seed, 1, 0, sample));
-    T._preprocess(gen, double(T._statistics.num_samples));
+    // UPG/VCM: the photon pass with one stream per photon (domain 2); PT/BPT: _preprocess is a no-op
+    if (!photon_pass(T, gen, seed, sample, s + 1 == spp ? arg(a, "dump_photons", "") : string())) {
+      gen.seed(std::b2pt_counter_engine::stream_key(seed, 1, 0, sample));
+      T._preprocess(gen, double(sample));
+    }
     for (size_t y = 0; y < H; ++y) {
       for (size_t x = 0; x < W; ++x) {
         gen.seed(std::b2pt_counter_engine::stream_key(seed, 0, uint32_t(y * W + x), sample));
@@ -285,6 +333,46 @@ static int cmd_time(int argc, char** argv) {
   return 0;
 }
 
+// v3::HashGrid3D<T>::build / rQuery (HashGrid3D.hpp:181-325) on explicit points and queries.
+//   in:  u32 n, f32 points[3n], u32 nq, f32 queries[3nq], f32 radius
+//   out: per query u32 count, u32 indices[count]   (the callback order of rQuery)
+struct GridPoint {
+  vec3 p;
+  const vec3& position() const { return p; }
+  bool is_light() const { return false; }
+};
+
+static int cmd_grid(int argc, char** argv) {
+  if (argc < 4) return 2;
+  std::ifstream f(argv[2], std::ios::binary);
+  uint32_t n = 0, nq = 0; float radius = 0;
+  f.read((char*)&n, 4);
+  std::vector<GridPoint> pts(n);
+  f.read((char*)pts.data(), size_t(n) * 12);
+  f.read((char*)&nq, 4);
+  std::vector<vec3> q(nq);
+  f.read((char*)q.data(), size_t(nq) * 12);
+  f.read((char*)&radius, 4);
+  auto t0 = std::chrono::steady_clock::now();
+  v3::HashGrid3D<GridPoint> grid(&pts, radius);
+  double build = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  std::vector<uint32_t> out;
+  size_t total = 0;
+  t0 = std::chrono::steady_clock::now();
+  for (uint32_t i = 0; i < nq; ++i) {
+    size_t at = out.size();
+    out.push_back(0);
+    grid.rQuery([&](uint32_t index) { out.push_back(index); }, q[i], radius);
+    out[at] = uint32_t(out.size() - at - 1);
+    total += out[at];
+  }
+  double query = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  write_vec(argv[3], out);
+  printf("{\"points\": %u, \"queries\": %u, \"radius\": %.9g, \"found\": %zu, \"build_s\": %.6f, \"query_s\": %.6f}\n", n, nq, radius, total,
+         build, query);
+  return 0;
+}
+
 int main(int argc, char** argv) {
   _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);          // main.cpp:70-71
   _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
@@ -294,6 +382,7 @@ int main(int argc, char** argv) {
     if (c == "rays") return cmd_rays(argc, argv);
     if (c == "render") return cmd_render(argc, argv);
     if (c == "time") return cmd_time(argc, argv);
+    if (c == "grid") return cmd_grid(argc, argv);
     fprintf(stderr, "usage: ref_harness dump|rays|render|time ...\n");
     return 2;
   } catch (const std::exception& e) {

@@ -135,14 +135,15 @@ def ref_render(scene_path, technique, width, height, num_samples, **kw):
     info = run(*args)
     n = width * height
     return dict(info=json.dumps(info),
-                paths=np.fromfile(TMP + "/r.paths.f32", dtype=np.float32).reshape(num_samples, n, 3),
+                paths=(np.fromfile(TMP + "/r.paths.f32", dtype=np.float32).reshape(num_samples, n, 3)
+                       if str(kw.get("per_path", 1)) != "0" else np.zeros((0, n, 3), np.float32)),
                 accum=np.fromfile(TMP + "/r.accum.f64", dtype=np.float64).reshape(n, 4),
                 light=np.fromfile(TMP + "/r.light.f64", dtype=np.float64).reshape(n, 3))
 
 
 def main():
     os.makedirs(os.path.join(HERE, "scenes"), exist_ok=True)
-    for name in SMALL_SCENES:
+    for name in ([] if [a for a in sys.argv[1:] if not a.startswith("-")] else SMALL_SCENES):
         dst = os.path.join(HERE, "scenes", name + ".b2s")
         print(name, run("dump", os.path.join(REF, "models", name + ".blend"), dst))
         flat = load_b2s(dst)
@@ -159,11 +160,22 @@ def main():
         ("TestCaseFurnace", "PT", 32, 32, 4, dict(beta=1)),
         ("TestCaseFurnace", "BPT", 32, 32, 2, dict(beta=2)),
         ("TestCase9", "PT", 32, 32, 2, dict(beta=1)),
+        # VCM / UPG (UPG.cpp): photons = width * height per pass, one stream per photon path (domain 2)
+        ("CornellBoxDiffuse", "VCM", 32, 32, 3, dict(beta=2, radius=0.1)),
+        ("CornellBoxSpecular", "VCM", 32, 32, 2, dict(beta=2, radius=0.1)),
+        ("MetalRings", "VCM", 32, 32, 2, dict(beta=2, radius=0.05)),
+        ("TestCaseFurnace", "VCM", 32, 32, 2, dict(beta=2, radius=0.1)),
+        ("CornellBoxDiffuse", "UPG", 32, 32, 16, dict(beta=2, radius=0.1, per_path=0)),
+        ("TestCaseFurnace", "UPG", 24, 24, 16, dict(beta=2, radius=0.1, per_path=0)),
     ]
+    only = [a for a in sys.argv[1:] if not a.startswith("-")]
+    if only:
+        renders = [r for r in renders if r[1] in only]
     for name, tech, w, h, spp, kw in renders:
         scene = os.path.join(HERE, "scenes", name + ".b2s")
         out = ref_render(scene, tech, w, h, spp, seed=1234, **kw)
-        np.savez_compressed(os.path.join(HERE, "render_%s_%s.npz" % (name, tech)), width=w, height=h, seed=1234, **out)
+        extra = {k: v for k, v in kw.items() if k in ("radius", "beta")}
+        np.savez_compressed(os.path.join(HERE, "render_%s_%s.npz" % (name, tech)), width=w, height=h, seed=1234, spp=spp, **extra, **out)
         print(name, tech, out["info"])
 
 

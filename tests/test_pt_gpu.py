@@ -40,8 +40,8 @@ def test_pt_per_path_radiance(name, device_scenes, flat_scenes):
     mean_ref, mean_ours = g["accum"][:, :3].mean(axis=0), accum[:, :3].mean(axis=0)
     print(json.dumps(dict(scene=name, paths=int(err.size), within_1e4=frac, rays=[stats["num_basic_rays"], stats["num_shadow_rays"]],
                           ref_rays=[info["basic_rays"], info["shadow_rays"]], mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist())))
-    # paths whose discrete decisions (roulette, light pick, triangle id) all agree match to 1e-4;
-    # the rest are decision flips caused by last-bit differences in transcendental functions
-    assert frac >= 0.995
+    # hits are bit-identical to Embree's (rcp_embree, trace.cuh) and the float transcendentals are evaluated in double
+    # (common.cuh: libm parity), so essentially every path takes the reference's decisions
+    assert frac >= 0.999
     assert np.all(accum[:, 3] == spp)
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=2e-2, atol=1e-4)

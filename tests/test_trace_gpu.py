@@ -28,6 +28,11 @@ def compare_closest(ours, ref, what, min_agree=0.9999):
                 mismatches=int(bad.sum()), mismatch_max_rel_dt=float(tie_rel.max() if tie_rel.size else 0))
     print(json.dumps(info))
     assert agree >= min_agree, info
+    # same triangle -> same bits: the leaf test and the hit finalisation are Embree's arithmetic operation by operation
+    for k in ("t", "u", "v"):
+        exact = (ours[k][hit].view(np.uint32) == ref[k][hit].view(np.uint32)).mean() if hit.any() else 1.0
+        info["%s_bit_exact" % k] = float(exact)
+        assert exact >= 0.9999, info
     assert rel.size == 0 or rel.max() <= 1e-5, info
     if hit.any():
         assert np.abs(ours["u"][hit] - ref["u"][hit]).max() <= 1e-5, info

@@ -1,0 +1,71 @@
+"""VCM / UPG (UPG.cpp) on the GPU against the UNMODIFIED reference (UPG2, beta = 2) driven with one random stream per
+(pixel, sample) and per (photon path, sample) — tests/golden/make_golden.py.
+
+VCM draws nothing inside a merge, so eye-path radiance is compared per pixel-sample at 1e-4 relative, and the light image
+(camera connections of the pixel's own light path) per pixel.  UPG estimates merge densities by rejection sampling in an
+order the reference leaves to std::sort, so it is compared in distribution: image means at equal spp and the analytic
+furnace answer (image mean 1)."""
+import json
+
+import numpy as np
+import pytest
+
+from conftest import golden_path
+from test_pt_gpu import gpu_render, path_agreement
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace"])
+def test_vcm_per_path_radiance_and_light_image(name, device_scenes, flat_scenes):
+    g = np.load(golden_path("render_%s_VCM.npz" % name))
+    w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
+    info = json.loads(str(g["info"]))
+    accum, paths, stats = gpu_render(device_scenes(name), flat_scenes(name), "VCM", w, h, spp, int(g["seed"]), beta=2.0,
+                                     radius=float(g["radius"]))
+    frac, err = path_agreement(paths, g["paths"])
+    light_ours = accum[:, :3] - paths.astype(np.float64).sum(axis=0)
+    light_ref = g["light"]
+    scale = max(np.abs(light_ref).max(), 1e-6)
+    light_bad = float((np.abs(light_ours - light_ref).max(axis=1) > 1e-4 * scale + 1e-4 * np.abs(light_ref).max(axis=1)).mean())
+    mean_ref, mean_ours = g["accum"][:, :3].mean(axis=0), accum[:, :3].mean(axis=0)
+    print(json.dumps(dict(scene=name, paths=int(err.size), within_1e4=frac, light_pixels_off=light_bad,
+                          rays=[stats["num_basic_rays"], stats["num_shadow_rays"]], ref_rays=[info["basic_rays"], info["shadow_rays"]],
+                          capacity_events=stats["capacity_events"], mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist())))
+    assert stats["capacity_events"] == 0
+    assert frac >= 0.99
+    assert light_bad <= 0.01
+    assert np.all(accum[:, 3] == g["accum"][:, 3])
+    np.testing.assert_allclose(mean_ours, mean_ref, rtol=2e-3, atol=1e-5)
+
+
+@pytest.mark.parametrize("name,tol", [("CornellBoxDiffuse", 0.08), ("TestCaseFurnace", 0.06)])
+def test_upg_image_mean_matches_reference(name, tol, device_scenes, flat_scenes):
+    g = np.load(golden_path("render_%s_UPG.npz" % name))
+    w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
+    accum, _, stats = gpu_render(device_scenes(name), flat_scenes(name), "UPG", w, h, spp, int(g["seed"]), per_path=False, beta=2.0,
+                                 radius=float(g["radius"]))
+    mean_ref, mean_ours = g["accum"][:, :3].mean(axis=0) / spp, accum[:, :3].mean(axis=0) / spp
+    print(json.dumps(dict(scene=name, mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist(),
+                          rays=[stats["num_basic_rays"], stats["num_shadow_rays"]])))
+    assert np.isfinite(accum).all() and np.all(accum[:, 3] == spp)
+    np.testing.assert_allclose(mean_ours, mean_ref, rtol=tol)
+    if name == "TestCaseFurnace":  # analytic answer: every pixel converges to 1
+        assert abs(mean_ours.mean() - 1.0) < 0.06
+
+
+def test_vcm_rejects_what_is_not_built(device_scenes, flat_scenes):
+    from master_b200 import api
+    with pytest.raises(api.B2ptError):
+        gpu_render(device_scenes("CornellBoxDiffuse"), flat_scenes("CornellBoxDiffuse"), "VCM", 16, 16, 1, 1, from_light=False)
+    with pytest.raises(api.B2ptError):  # fewer light paths than pixels: the reference would read past _light_offsets
+        gpu_render(device_scenes("CornellBoxDiffuse"), flat_scenes("CornellBoxDiffuse"), "VCM", 16, 16, 1, 1, num_photons=100)
+
+
+def test_vcm_pass_split_is_exact(device_scenes, flat_scenes):
+    """multi-GPU sample split: passes {0,1,2,3} == {0,2} + {1,3}; the radius shrink follows the GLOBAL pass index."""
+    sc, fl = device_scenes("CornellBoxDiffuse"), flat_scenes("CornellBoxDiffuse")
+    whole, _, _ = gpu_render(sc, fl, "VCM", 24, 24, 4, 5, per_path=False, beta=2.0, radius=0.1)
+    a, _, _ = gpu_render(sc, fl, "VCM", 24, 24, 2, 5, per_path=False, beta=2.0, radius=0.1, first_sample=0, sample_stride=2)
+    b, _, _ = gpu_render(sc, fl, "VCM", 24, 24, 2, 5, per_path=False, beta=2.0, radius=0.1, first_sample=1, sample_stride=2)
+    np.testing.assert_allclose(a + b, whole, rtol=1e-4, atol=1e-6)
