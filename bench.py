@@ -61,11 +61,12 @@ def plain_scene_file(path):
     return out
 
 
-def run_reference(scene_file, technique, width, height, passes, seconds, threads=0):
+def run_reference(scene_file, technique, width, height, passes, seconds, threads=0, radius=None):
     """The reference's own Technique::render loop (oracle/_ref/ref_harness time) on the host cores."""
-    cmd = [HARNESS, "time", scene_file, "technique=" + technique, "width=%d" % width, "height=%d" % height,
-           "num_samples=%d" % passes, "seconds=%g" % seconds, "threads=%d" % threads,
-           "beta=%d" % (1 if technique == "PT" else 2)]
+    extra = ["radius=%g" % radius] if radius is not None else []
+    cmd = [HARNESS, "time", scene_file, "technique=" + technique, "width=%d" % width, "height=%d" % height] + extra + [
+        "num_samples=%d" % passes, "seconds=%g" % seconds, "threads=%d" % threads,
+        "beta=%d" % (1 if technique == "PT" else 2)]
     out = subprocess.run(cmd, check=True, capture_output=True, text=True).stdout
     return json.loads(out.strip().splitlines()[-1])
 
@@ -128,6 +129,7 @@ def main():
     ap.add_argument("--width", type=int, default=1024)
     ap.add_argument("--height", type=int, default=1024)
     ap.add_argument("--spp", type=int, default=4, help="passes (samples per pixel) per step")
+    ap.add_argument("--radius", type=float, default=None, help="VCM / UPG merge radius (thesis values: UPG 0.01, VCM 0.025)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
@@ -141,6 +143,9 @@ def main():
               "technique": a.technique, "resolution": [W, H], "spp_per_step": a.spp,
               "parallelism": "sample-split x%d over a replicated scene, one all-reduce of the dvec4 film" % a.gpus}
 
+    ref_radius = None
+    if a.technique in ("VCM", "UPG"):
+        ref_radius = a.radius if a.radius is not None else (0.01 if a.technique == "UPG" else 0.025)
     # ------------------------------------------------------------ reference arm: the reference's CPU code
     if a.impl == "reference":
         if rank != 0:
@@ -148,8 +153,8 @@ def main():
         cores = os.cpu_count()
         plain = plain_scene_file(scene_path)
         # a step = ONE pass of the same window (bounded sample of the b200 arm's step of `spp` passes)
-        run_reference(plain, a.technique, W, H, max(a.warmup, 1), 0, cores) if a.warmup else None
-        r = run_reference(plain, a.technique, W, H, a.steps, 0, cores)
+        run_reference(plain, a.technique, W, H, max(a.warmup, 1), 0, cores, radius=ref_radius) if a.warmup else None
+        r = run_reference(plain, a.technique, W, H, a.steps, 0, cores, radius=ref_radius)
         val = r["msamples_per_s"]
         sample = "%d passes of 1 spp at %dx%d, %d host threads, Embree 2.12 + the reference's Technique::render" % (
             r["num_samples"], W, H, r["threads"])
@@ -182,7 +187,11 @@ def main():
     flat = load_b2s(scene_path)
     scene = api.DeviceSceneHandle(flat)
     info = scene.info()
-    tech = GpuTechnique(scene, a.technique)
+    tech_options = {}
+    if a.technique in ("VCM", "UPG"):
+        tech_options["radius"] = a.radius if a.radius is not None else (0.01 if a.technique == "UPG" else 0.025)
+        config["radius"] = tech_options["radius"]
+    tech = GpuTechnique(scene, a.technique, **tech_options)
     accum = torch.zeros(H * W, 4, dtype=torch.float64, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
     N = world
@@ -280,7 +289,7 @@ def main():
     cpu = None
     if not a.no_cpu_baseline and os.path.exists(HARNESS):
         try:
-            r = run_reference(plain_scene_file(scene_path), a.technique, W, H, 1000, 15.0, os.cpu_count())
+            r = run_reference(plain_scene_file(scene_path), a.technique, W, H, 1000, 15.0, os.cpu_count(), radius=ref_radius)
             cpu = {"value": r["msamples_per_s"], "unit": "Msamples/s", "cores": r["threads"], "kind": "reference",
                    "mrays_per_s": r["mrays_per_s"],
                    "sample": "%d passes of 1 spp at %dx%d in %.1f s: the unmodified reference (Embree 2.12 + Technique::render) "

@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 from conftest import golden_path
-from test_pt_gpu import gpu_render, path_agreement
+from test_pt_gpu import gpu_render, image_rel_rmse, path_agreement
 
 pytestmark = pytest.mark.gpu
 
@@ -37,6 +37,7 @@ def test_vcm_per_path_radiance_and_light_image(name, device_scenes, flat_scenes)
     assert light_bad <= 0.01
     assert np.all(accum[:, 3] == g["accum"][:, 3])
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=2e-3, atol=1e-5)
+    assert image_rel_rmse(accum, g["accum"]) <= 5e-2
 
 
 @pytest.mark.parametrize("name,tol", [("CornellBoxDiffuse", 0.08), ("TestCaseFurnace", 0.06)])
