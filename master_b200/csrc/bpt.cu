@@ -24,6 +24,8 @@
 // on the path: 12 vertices per path on average (the expectation with roulette 0.9 is <= 8.1) and
 // B2ptRenderParams::max_subpath (default 1024, the reference's cap) per path.
 // Every path owns one counter-based RNG stream; light phase and eye phase consume it in the reference's order.
+#include <memory>
+
 #include "render_common.cuh"
 
 namespace b2pt {
@@ -41,6 +43,7 @@ struct BptCounters {
   unsigned int done;
   unsigned int lv_count;
   unsigned int trace_count[2], pair_count[2], shadow_count[2];
+  unsigned int ticket[2];  // dynamic ray fetch of the traversal stages (trace, shadow), zeroed by the logic stage
 };
 
 // LightVertex / EyeVertex (BPT.hpp:13-27): w0 = a or c, w1 = A or C
@@ -205,6 +208,7 @@ __global__ void __launch_bounds__(256) bpt_logic_kernel(RenderConfig cfg, BptPoo
     cnt->trace_count[parity ^ 1] = 0;
     cnt->pair_count[parity ^ 1] = 0;
     cnt->shadow_count[parity ^ 1] = 0;
+    cnt->ticket[0] = 0; cnt->ticket[1] = 0;
   }
   const float beta = cfg.params.beta;
   const float roulette = cfg.params.roulette;
@@ -534,35 +538,67 @@ __global__ void __launch_bounds__(256) bpt_connect_kernel(RenderConfig cfg, BptP
   }
 }
 
+// ray sources / hit sinks of the two traversal stages (trace.cuh: trace_stream8)
+struct BptTraceIo {
+  const BptPool* pool;
+  __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
+    const uint32_t slot = pool->trace_q[i];
+    const float4 o = pool->ray_o[slot], d = pool->bs_omega[slot];
+    O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY;
+    mask = (__float_as_uint(o.w) & 2u) ? kMaskMesh : kMaskAll;  // Scene::intersectMesh (light subpaths) / Scene::intersect
+    return slot;
+  }
+  __device__ __forceinline__ void store(uint32_t slot, const Hit& h) const {
+    pool->hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+  }
+};
+struct BptShadowIo {
+  const BptPool* pool;
+  __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
+    const float4* e = pool->shadow_q + size_t(i) * 3;
+    const float4 o = e[0], d = e[1];
+    O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = 1.0f;  // Scene::occluded: t in (0, 1), meshes only
+    mask = kMaskMesh;
+    return i;
+  }
+  __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
+    if (h.tri != kInvalid) return;  // blocked
+    const float4* e = pool->shadow_q + size_t(i) * 3;
+    const uint32_t target = __float_as_uint(e[0].w), flags = __float_as_uint(e[1].w);
+    const float4 c = e[2];
+    if (flags & kShadowSplat) {
+      double* s = pool->splat + size_t(target) * 3;
+      atomicAdd(s + 0, double(c.x)); atomicAdd(s + 1, double(c.y)); atomicAdd(s + 2, double(c.z));
+    } else {
+      float* r = &pool->rad[target].x;
+      atomicAdd(r + 0, c.x); atomicAdd(r + 1, c.y); atomicAdd(r + 2, c.z);
+    }
+  }
+};
+
+template <bool kStream>
 __global__ void __launch_bounds__(256) bpt_trace_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
   const uint32_t n = cnt->trace_count[parity];
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+  BptTraceIo io{&pool};
+  if (kStream) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t slot = pool.trace_q[i];
-    const float4 o = pool.ray_o[slot], d = pool.bs_omega[slot];
-    const uint32_t mask = (__float_as_uint(o.w) & 2u) ? kMaskMesh : kMaskAll;
-    const Hit h = trace_ray_masked<false>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY, mask);
-    pool.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+    float3 O, D; float tnear, tfar; uint32_t mask;
+    const uint32_t tag = io.load(i, O, D, tnear, tfar, mask);
+    io.store(tag, trace_any_bvh<false>(cfg.scene, O, D, tnear, tfar, mask));
   }
 }
 
+template <bool kStream>
 __global__ void __launch_bounds__(256) bpt_shadow_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
   const uint32_t n = min(cnt->shadow_count[parity], pool.q_capacity);
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->shadow_rays, (unsigned long long)n);
+  BptShadowIo io{&pool};
+  if (kStream) { trace_stream8<true>(cfg.scene, n, &cnt->ticket[1], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const float4* e = pool.shadow_q + size_t(i) * 3;
-    const float4 o = e[0], d = e[1], c = e[2];
-    const uint32_t target = __float_as_uint(o.w), flags = __float_as_uint(d.w);
-    const Hit h = trace_ray<true, true>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, 1.0f);
-    if (h.tri == kInvalid) {
-      if (flags & kShadowSplat) {
-        double* s = pool.splat + size_t(target) * 3;
-        atomicAdd(s + 0, double(c.x)); atomicAdd(s + 1, double(c.y)); atomicAdd(s + 2, double(c.z));
-      } else {
-        float* r = &pool.rad[target].x;
-        atomicAdd(r + 0, c.x); atomicAdd(r + 1, c.y); atomicAdd(r + 2, c.z);
-      }
-    }
+    float3 O, D; float tnear, tfar; uint32_t mask;
+    const uint32_t tag = io.load(i, O, D, tnear, tfar, mask);
+    io.store(tag, trace_any_bvh<true>(cfg.scene, O, D, tnear, tfar, mask));
   }
 }
 
@@ -637,7 +673,7 @@ int ws_alloc(BptWorkspace* w, T** p, size_t count) {
 
 int bpt_workspace(b2pt_scene_s* scene, uint32_t size, int lanes, BptWorkspace** out) {
   BptWorkspace* w = (BptWorkspace*)scene->workspace;
-  if (w && scene->workspace_free == bpt_workspace_free && w->size == size && (lanes == 1 || w->lane[1].counters)) { *out = w; return B2PT_OK; }
+  if (w && scene->workspace_free == bpt_workspace_free && w->size == size && w->lane[lanes - 1].counters) { *out = w; return B2PT_OK; }
   if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
   scene->workspace = nullptr;
   w = new BptWorkspace();
@@ -684,9 +720,11 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   const int block = 256;
   const uint32_t pixels = base.pixels;
   const uint32_t num_passes = base.params.num_samples;
-  // a batch is a whole number of passes, at most 2^21 paths (or one pass if the window is larger); with more than one
+  // a batch is a whole number of passes, at most 2^21 paths (B2PT_BPT_BATCH_LOG2 overrides the exponent) (or one pass if the window is larger); with more than one
   // pass to render the passes are spread over kLanes concurrent batches
-  uint32_t passes_per_batch = (1u << 21) / pixels;
+  uint32_t batch_paths = 1u << 21;
+  { const char* e = getenv("B2PT_BPT_BATCH_LOG2"); if (e) { int v = atoi(e); if (v >= 10 && v <= 26) batch_paths = 1u << v; } }
+  uint32_t passes_per_batch = batch_paths / pixels;
   if (passes_per_batch < 1) passes_per_batch = 1;
   if (passes_per_batch > (num_passes + kLanes - 1) / kLanes) passes_per_batch = (num_passes + kLanes - 1) / kLanes;
   const uint32_t num_batches = (num_passes + passes_per_batch - 1) / passes_per_batch;
@@ -697,22 +735,27 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   RenderConfig cfg = base;
   cfg.pool_size = size;
   const int grid = grid_for(size, block);
+  const int grid_t = persistent_grid(size, block);  // traversal stages: persistent warps fetch rays from a ticket counter
+  // measured on the LivingRoom stand-in (profiles/README.md): with the queue sizes of a BPT batch one ray per thread is 8 % faster
+  // end to end than the persistent warp-synchronous traversal, which only wins on >= 4 M incoherent rays per launch;
+  // B2PT_TRACE_STREAM=1 selects the latter for A/B runs
+  const char* tv = getenv("B2PT_TRACE_STREAM");
+  const bool stream_trace = tv && tv[0] == '1', stream_shadow = stream_trace;
   unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
   const int kBatchIters = 8;
 
   // per-lane progress
   struct Progress { bool active = false; uint32_t pass0 = 0, passes = 0; int it = 0; BptPool pool; };
   Progress prog[kLanes];
-  StageTimer timer0(stream);
   w->lane[0].stream = stream;
-  StageTimer* timers[kLanes] = {&timer0, nullptr};
-  StageTimer timer1(w->lane[1].own_stream);
-  if (lanes > 1) {
-    w->lane[1].stream = w->lane[1].own_stream;
-    timers[1] = &timer1;
-    // lane 1 starts after whatever the caller queued before this call
-    B2_CUDA(cudaEventRecord(w->fork, stream));
-    B2_CUDA(cudaStreamWaitEvent(w->lane[1].stream, w->fork, 0));
+  std::vector<std::unique_ptr<StageTimer>> timers;
+  timers.emplace_back(new StageTimer(stream));
+  if (lanes > 1) B2_CUDA(cudaEventRecord(w->fork, stream));
+  for (int k = 1; k < lanes; ++k) {
+    w->lane[k].stream = w->lane[k].own_stream;
+    timers.emplace_back(new StageTimer(w->lane[k].stream));
+    // the extra lanes start after whatever the caller queued before this call
+    B2_CUDA(cudaStreamWaitEvent(w->lane[k].stream, w->fork, 0));
   }
   uint32_t next_pass = 0;
   auto start_batch = [&](int k) -> int {
@@ -742,8 +785,14 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         const int parity = g.it & 1;
         timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0); timer.end();
         timer.begin(kStageShade); bpt_connect_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
-        timer.begin(kStageTrace); bpt_trace_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
-        timer.begin(kStageShadow); bpt_shadow_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
+        timer.begin(kStageTrace);
+        if (stream_trace) bpt_trace_kernel<true><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else bpt_trace_kernel<false><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        timer.end();
+        timer.begin(kStageShadow);
+        if (stream_shadow) bpt_shadow_kernel<true><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else bpt_shadow_kernel<false><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        timer.end();
       }
       B2_CUDA(cudaMemcpyAsync(l.host_counters, l.counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, l.stream));
     }
@@ -769,9 +818,9 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         if (int rc = start_batch(k)) return rc;
     }
   }
-  if (lanes > 1) {  // the caller's stream continues after lane 1
-    B2_CUDA(cudaEventRecord(w->lane[1].done, w->lane[1].stream));
-    B2_CUDA(cudaStreamWaitEvent(stream, w->lane[1].done, 0));
+  for (int k = 1; k < lanes; ++k) {  // the caller's stream continues after the extra lanes
+    B2_CUDA(cudaEventRecord(w->lane[k].done, w->lane[k].stream));
+    B2_CUDA(cudaStreamWaitEvent(stream, w->lane[k].done, 0));
   }
   B2_CUDA(cudaGetLastError());
   if (stats) {
@@ -779,10 +828,10 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     stats->num_shadow_rays = shadow;
     stats->numeric_errors = numeric;
     stats->capacity_events = capacity;
-    timer0.fill(stats);
-    if (lanes > 1) {
+    timers[0]->fill(stats);
+    for (int k = 1; k < lanes; ++k) {
       B2ptStats s1{};
-      timer1.fill(&s1);
+      timers[k]->fill(&s1);
       stats->trace_ms += s1.trace_ms; stats->shadow_ms += s1.shadow_ms; stats->shade_ms += s1.shade_ms;
       stats->trace_launches += s1.trace_launches; stats->shadow_launches += s1.shadow_launches;
       stats->kernel_launches += s1.kernel_launches;

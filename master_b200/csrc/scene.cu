@@ -361,6 +361,132 @@ __global__ void collapse_kernel(uint32_t count, const CollapseItem* items, const
   out[7] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
+// ---------------------------------------------------------------- collapse to the compressed 8-wide tree (bvh8.cuh)
+// One thread per wide node of the current level: open the child with the largest surface area until eight children
+// (subtrees of <= 3 triangles stay closed and become leaves), quantise the child boxes on the node's power-of-two
+// grid, give every child the slot whose octant direction its centroid points along most (greedy assignment), make
+// the inner children and the leaf triangles of the node contiguous.
+__global__ void collapse8_kernel(uint32_t count, const CollapseItem* items, const uint64_t* keys, const float4* tri_lo, const float4* tri_hi,
+                                 const BinNode* bin, const float4* box_lo, const float4* box_hi, float4* nodes8, uint32_t* num_wide,
+                                 CollapseItem* next_items, uint32_t* next_count, uint32_t* tri_counter, uint64_t* tri_map, float pad,
+                                 uint32_t single_leaf_count) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const CollapseItem it = items[i];
+  uint32_t ref[8], cnt[8];
+  float lo[8][3], hi[8][3];
+  int n = 0;
+  auto fetch = [&](uint32_t c, int k) {
+    ref[k] = c;
+    float4 a, b;
+    if (c & 0x80000000u) { const uint32_t t = uint32_t(keys[c & 0x7FFFFFFFu]); a = tri_lo[t]; b = tri_hi[t]; cnt[k] = 1u; }
+    else { a = box_lo[c]; b = box_hi[c]; cnt[k] = bin[c].last - bin[c].first + 1u; }
+    lo[k][0] = a.x; lo[k][1] = a.y; lo[k][2] = a.z; hi[k][0] = b.x; hi[k][1] = b.y; hi[k][2] = b.z;
+  };
+  if (single_leaf_count) {  // a scene of <= 3 triangles: the root has one leaf child holding all of them
+    ref[0] = 0x80000000u; cnt[0] = single_leaf_count;
+    for (int a = 0; a < 3; ++a) { lo[0][a] = INFINITY; hi[0][a] = -INFINITY; }
+    for (uint32_t j = 0; j < single_leaf_count; ++j) {
+      const uint32_t t = uint32_t(keys[j]);
+      const float4 a = tri_lo[t], b = tri_hi[t];
+      lo[0][0] = fminf(lo[0][0], a.x); lo[0][1] = fminf(lo[0][1], a.y); lo[0][2] = fminf(lo[0][2], a.z);
+      hi[0][0] = fmaxf(hi[0][0], b.x); hi[0][1] = fmaxf(hi[0][1], b.y); hi[0][2] = fmaxf(hi[0][2], b.z);
+    }
+    n = 1;
+  } else {
+    fetch(bin[it.bin].left, 0); fetch(bin[it.bin].right, 1);
+    n = 2;
+    while (n < 8) {
+      int best = -1; float best_area = -1.f;
+      for (int k = 0; k < n; ++k) {
+        if ((ref[k] & 0x80000000u) || cnt[k] <= 3u) continue;
+        const float dx = hi[k][0] - lo[k][0], dy = hi[k][1] - lo[k][1], dz = hi[k][2] - lo[k][2];
+        const float a = dx * dy + dy * dz + dz * dx;
+        if (a > best_area) { best_area = a; best = k; }
+      }
+      if (best < 0) break;
+      const uint32_t c = ref[best];
+      fetch(bin[c].left, best);
+      fetch(bin[c].right, n++);
+    }
+  }
+  // ---- the node's grid
+  float p[3], ext[3], scale[3], inv[3];
+  uint32_t ebits[3];
+  for (int a = 0; a < 3; ++a) {
+    float mn = INFINITY, mx = -INFINITY;
+    for (int k = 0; k < n; ++k) { mn = fminf(mn, lo[k][a]); mx = fmaxf(mx, hi[k][a]); }
+    p[a] = mn - pad;
+    ext[a] = (mx + pad) - p[a];
+    int e = 0;
+    frexpf(ext[a] / 255.0f, &e);  // ext / 255 = m * 2^e with m in [0.5, 1): 2^e covers it
+    e = max(-100, min(100, e));
+    ebits[a] = uint32_t(e + 127);
+    scale[a] = __uint_as_float(ebits[a] << 23);
+    inv[a] = __uint_as_float(uint32_t(127 - e) << 23);
+  }
+  // ---- slots: greedy assignment of children to octant directions
+  int slot_of[8];
+  int child_in[8];
+  for (int k = 0; k < 8; ++k) { slot_of[k] = -1; child_in[k] = -1; }
+  float cen[8][3];
+  for (int k = 0; k < n; ++k)
+    for (int a = 0; a < 3; ++a) cen[k][a] = 0.5f * (lo[k][a] + hi[k][a]) - (p[a] + 0.5f * ext[a]);
+  for (int round = 0; round < n; ++round) {
+    float best = -INFINITY; int bk = -1, bs = -1;
+    for (int k = 0; k < n; ++k) {
+      if (slot_of[k] >= 0) continue;
+      for (int sl = 0; sl < 8; ++sl) {
+        if (child_in[sl] >= 0) continue;
+        const float c = ((sl & 1) ? cen[k][0] : -cen[k][0]) + ((sl & 2) ? cen[k][1] : -cen[k][1]) + ((sl & 4) ? cen[k][2] : -cen[k][2]);
+        if (c > best) { best = c; bk = k; bs = sl; }
+      }
+    }
+    slot_of[bk] = bs; child_in[bs] = bk;
+  }
+  // ---- children: inner nodes contiguous, leaf triangles contiguous
+  uint32_t n_inner = 0, n_tris = 0;
+  for (int k = 0; k < n; ++k) {
+    const bool leaf = single_leaf_count || (ref[k] & 0x80000000u) || cnt[k] <= 3u;
+    if (leaf) n_tris += cnt[k]; else ++n_inner;
+  }
+  const uint32_t child_base = n_inner ? atomicAdd(num_wide, n_inner) : 0u;
+  const uint32_t tri_base = n_tris ? atomicAdd(tri_counter, n_tris) : 0u;
+  uint32_t imask = 0u, rank = 0u, offset = 0u;
+  uint32_t meta[8], q[6][8];
+  for (int sl = 0; sl < 8; ++sl) {
+    const int k = child_in[sl];
+    meta[sl] = 0u;
+    for (int a = 0; a < 3; ++a) { q[a][sl] = 255u; q[3 + a][sl] = 0u; }  // empty slot: inverted box
+    if (k < 0) continue;
+    for (int a = 0; a < 3; ++a) {
+      const float l = floorf(((lo[k][a] - pad) - p[a]) * inv[a]), h = ceilf(((hi[k][a] + pad) - p[a]) * inv[a]);
+      q[a][sl] = uint32_t(fminf(fmaxf(l, 0.f), 255.f));
+      q[3 + a][sl] = uint32_t(fminf(fmaxf(h, 0.f), 255.f));
+    }
+    const bool leaf = single_leaf_count || (ref[k] & 0x80000000u) || cnt[k] <= 3u;
+    if (!leaf) {
+      imask |= 1u << sl;
+      const uint32_t w = child_base + rank++;
+      const uint32_t qi = atomicAdd(next_count, 1u);
+      next_items[qi] = CollapseItem{w, ref[k]};
+      meta[sl] = 0x20u;  // not read by the traversal (imask decides); kept non-zero for debugging dumps
+    } else {
+      const uint32_t first = single_leaf_count ? 0u : ((ref[k] & 0x80000000u) ? (ref[k] & 0x7FFFFFFFu) : bin[ref[k]].first);
+      meta[sl] = (((1u << cnt[k]) - 1u) << 5) | offset;
+      for (uint32_t j = 0; j < cnt[k]; ++j) tri_map[tri_base + offset + j] = keys[first + j] & 0xFFFFFFFFull;
+      offset += cnt[k];
+    }
+  }
+  auto pack4 = [](const uint32_t* b) { return b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24); };
+  float4* out = nodes8 + size_t(it.wide) * 5;
+  out[0] = make_float4(p[0], p[1], p[2], __uint_as_float(ebits[0] | (ebits[1] << 8) | (ebits[2] << 16) | (imask << 24)));
+  out[1] = make_float4(__uint_as_float(child_base), __uint_as_float(tri_base), __uint_as_float(pack4(meta)), __uint_as_float(pack4(meta + 4)));
+  out[2] = make_float4(__uint_as_float(pack4(q[0])), __uint_as_float(pack4(q[0] + 4)), __uint_as_float(pack4(q[1])), __uint_as_float(pack4(q[1] + 4)));
+  out[3] = make_float4(__uint_as_float(pack4(q[2])), __uint_as_float(pack4(q[2] + 4)), __uint_as_float(pack4(q[3])), __uint_as_float(pack4(q[3] + 4)));
+  out[4] = make_float4(__uint_as_float(pack4(q[4])), __uint_as_float(pack4(q[4] + 4)), __uint_as_float(pack4(q[5])), __uint_as_float(pack4(q[5] + 4)));
+}
+
 // Triangle + shading records in leaf (sorted) order.
 __global__ void pack_kernel(BuildInput in, const uint64_t* keys, const float4* tri_lo, float4* v0o, float4* e1o, float4* e2o,
                             float4* frames) {
@@ -452,7 +578,15 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
   for (int a = 0; a < 3; ++a) ext = fmaxf(ext, ordered_to_float(h_bounds[3 + a]) - ordered_to_float(h_bounds[a]));
   const float pad = ext * 1e-6f;  // conservative slack on every child box (see trace.cuh)
 
-  if (n == 1) {
+  const char* bvh_env = getenv("B2PT_BVH");
+#ifdef B2PT_EXPERIMENTS
+  const bool wide8 = !(bvh_env && bvh_env[0] == '4');  // A/B builds: B2PT_BVH=4 keeps the 4-wide uncompressed tree
+#else
+  const bool wide8 = true; (void)bvh_env;
+#endif
+  float4* nodes8 = nullptr;
+  uint64_t* tri_map = nullptr;
+  if (n == 1 && !wide8) {
     // a single leaf under the root
     if (int rc = dev_alloc(s, &nodes, kNodeFloat4s, true)) return rc;
     float4 lo, hi;
@@ -466,7 +600,7 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
     float f0, fi; memcpy(&f0, &l0, 4); memcpy(&fi, &inv, 4);
     h[6] = make_float4(f0, fi, fi, fi); h[7] = make_float4(0, 0, 0, 0);
     B2_CUDA(cudaMemcpy(nodes, h, sizeof h, cudaMemcpyHostToDevice));
-  } else {
+  } else if (n > 1) {
     BinNode* bin = (BinNode*)tmp(size_t(n - 1) * sizeof(BinNode));
     uint32_t* parent_inner = (uint32_t*)tmp(size_t(n) * 4); uint32_t* parent_leaf = (uint32_t*)tmp(size_t(n) * 4);
     float4* box_lo = (float4*)tmp(size_t(n) * 16); float4* box_hi = (float4*)tmp(size_t(n) * 16);
@@ -525,22 +659,62 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
       keys = order;  // triangles are now in depth-first leaf order of the PLOC tree
       root_bin = n - 2u;
     }
-    // worst case one wide node per binary inner node
-    if (int rc = dev_alloc(s, &nodes, size_t(n) * kNodeFloat4s, true)) return rc;
-    CollapseItem root{0u, root_bin};
-    B2_CUDA(cudaMemcpy(items_a, &root, sizeof root, cudaMemcpyHostToDevice));
-    uint32_t h_counters[2] = {1u, 0u};
-    B2_CUDA(cudaMemcpy(counters, h_counters, 8, cudaMemcpyHostToDevice));
-    uint32_t count = 1;
-    while (count > 0) {
-      collapse_kernel<<<(count + B - 1) / B, B>>>(count, items_a, keys, tri_lo, tri_hi, bin, box_lo, box_hi, nodes, &counters[0],
-                                                 items_b, &counters[1], pad);
-      B2_CUDA(cudaMemcpy(h_counters, counters, 8, cudaMemcpyDeviceToHost));
-      count = h_counters[1];
-      num_wide = h_counters[0];
-      B2_CUDA(cudaMemset(&counters[1], 0, 4));
-      std::swap(items_a, items_b);
+    if (wide8 && n > 3) {
+      // compressed 8-wide tree (bvh8.cuh); a wide inner node has at least two children, so n nodes is a safe bound
+      if (int rc = dev_alloc(s, &nodes8, size_t(n) * 5, true)) return rc;
+      tri_map = (uint64_t*)tmp(size_t(n) * 8);
+      uint32_t* counters8 = (uint32_t*)tmp(16);  // [0] num_wide, [1] next_count, [2] triangles placed
+      B2_CHECK(tri_map && counters8, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
+      CollapseItem root{0u, root_bin};
+      B2_CUDA(cudaMemcpy(items_a, &root, sizeof root, cudaMemcpyHostToDevice));
+      uint32_t h_counters[3] = {1u, 0u, 0u};
+      B2_CUDA(cudaMemcpy(counters8, h_counters, 12, cudaMemcpyHostToDevice));
+      uint32_t count = 1;
+      while (count > 0) {
+        collapse8_kernel<<<(count + B - 1) / B, B>>>(count, items_a, keys, tri_lo, tri_hi, bin, box_lo, box_hi, nodes8, &counters8[0], items_b,
+                                                    &counters8[1], &counters8[2], tri_map, pad, 0u);
+        B2_CUDA(cudaMemcpy(h_counters, counters8, 12, cudaMemcpyDeviceToHost));
+        count = h_counters[1];
+        num_wide = h_counters[0];
+        B2_CUDA(cudaMemset(&counters8[1], 0, 4));
+        std::swap(items_a, items_b);
+      }
+      B2_CHECK(h_counters[2] == n, B2PT_ERR_CUDA, "BVH8 collapse lost triangles");
+      keys = tri_map;  // final triangle order: the leaves of one node are contiguous
+    } else if (!wide8) {
+      // worst case one wide node per binary inner node
+      if (int rc = dev_alloc(s, &nodes, size_t(n) * kNodeFloat4s, true)) return rc;
+      CollapseItem root{0u, root_bin};
+      B2_CUDA(cudaMemcpy(items_a, &root, sizeof root, cudaMemcpyHostToDevice));
+      uint32_t h_counters[2] = {1u, 0u};
+      B2_CUDA(cudaMemcpy(counters, h_counters, 8, cudaMemcpyHostToDevice));
+      uint32_t count = 1;
+      while (count > 0) {
+        collapse_kernel<<<(count + B - 1) / B, B>>>(count, items_a, keys, tri_lo, tri_hi, bin, box_lo, box_hi, nodes, &counters[0],
+                                                   items_b, &counters[1], pad);
+        B2_CUDA(cudaMemcpy(h_counters, counters, 8, cudaMemcpyDeviceToHost));
+        count = h_counters[1];
+        num_wide = h_counters[0];
+        B2_CUDA(cudaMemset(&counters[1], 0, 4));
+        std::swap(items_a, items_b);
+      }
     }
+  }
+  if (wide8 && n <= 3) {
+    // a root with one leaf child that holds every triangle
+    if (int rc = dev_alloc(s, &nodes8, 5, true)) return rc;
+    tri_map = (uint64_t*)tmp(size_t(n) * 8);
+    CollapseItem* item = (CollapseItem*)tmp(sizeof(CollapseItem));
+    uint32_t* counters8 = (uint32_t*)tmp(16);
+    B2_CHECK(tri_map && item && counters8, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
+    CollapseItem root{0u, 0u};
+    B2_CUDA(cudaMemcpy(item, &root, sizeof root, cudaMemcpyHostToDevice));
+    uint32_t h_counters[3] = {1u, 0u, 0u};
+    B2_CUDA(cudaMemcpy(counters8, h_counters, 12, cudaMemcpyHostToDevice));
+    collapse8_kernel<<<1, 32>>>(1u, item, keys, tri_lo, tri_hi, nullptr, nullptr, nullptr, nodes8, &counters8[0], item, &counters8[1],
+                               &counters8[2], tri_map, pad, n);
+    keys = tri_map;
+    num_wide = 1;
   }
 
   float4 *v0o, *e1o, *e2o, *frames;
@@ -591,10 +765,10 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
 
   DeviceScene& ds = s->dev;
   ds.num_tris = n; ds.num_nodes = num_wide; ds.num_materials = d->num_materials; ds.num_lights = L;
-  ds.tri_v0 = v0o; ds.tri_e1 = e1o; ds.tri_e2 = e2o; ds.tri_frames = frames; ds.nodes = nodes;
+  ds.tri_v0 = v0o; ds.tri_e1 = e1o; ds.tri_e2 = e2o; ds.tri_frames = frames; ds.nodes = nodes; ds.nodes8 = nodes8;
   ds.materials = d_materials; ds.lights = d_lights; ds.light_cp = d_cp; ds.light_den = d_den; ds.light_int = d_int;
   ds.error_flags = d_flags;
-  s->bvh_bytes = uint64_t(num_wide) * kNodeFloat4s * 16 + uint64_t(n) * 48;
+  s->bvh_bytes = uint64_t(num_wide) * (nodes8 ? 5 : kNodeFloat4s) * 16 + uint64_t(n) * 48;
   return B2PT_OK;
 }
 

@@ -41,7 +41,8 @@ struct DeviceScene {
   const float4* tri_e1 = nullptr;
   const float4* tri_e2 = nullptr;
   const float4* tri_frames = nullptr;  // [num_tris * kFrameFloat4s]
-  const float4* nodes = nullptr;       // [num_nodes * kNodeFloat4s], root = node 0
+  const float4* nodes = nullptr;       // 4-wide tree: [num_nodes * kNodeFloat4s], root = node 0 (null when the 8-wide tree is built)
+  const float4* nodes8 = nullptr;      // compressed 8-wide tree (bvh8.cuh): [num_nodes * 5], root = node 0
   const B2ptMaterial* materials = nullptr;
   const B2ptLight* lights = nullptr;
   // std::piecewise_constant_distribution<float> state (Sample.inl:233-247), in double as libstdc++ keeps it

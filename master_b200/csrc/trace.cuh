@@ -16,6 +16,7 @@
 // multiply-adds and are made conservative: child boxes carry a small absolute pad (scene.cu) and
 // the exit distance is stretched by 2 ulp, so a triangle the leaf test would accept is never culled.
 #pragma once
+#include "bvh8.cuh"
 #include "scene.cuh"
 
 namespace b2pt {
@@ -150,58 +151,135 @@ __device__ __forceinline__ Hit trace_ray_masked(const DeviceScene& sc, float3 O,
   return hit;
 }
 
-// kMeshOnly: ray mask = meshes only (compile-time form of the above)
-template <bool kAnyHit, bool kMeshOnly>
-__device__ __forceinline__ Hit trace_ray(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar) {
-  return trace_ray_masked<kAnyHit>(sc, O, D, tnear, tfar, kMeshOnly ? kMaskMesh : kMaskAll);
+// ---------------------------------------------------------------- compressed 8-wide BVH (layout: bvh8.cuh)
+// One node of the compressed 8-wide tree against one ray: five 128-bit loads, eight quantised slab tests, and the
+// hit children split into a node group G (inner children, priority-ordered hit bits | imask) and a triangle group T.
+__device__ __forceinline__ void node8_step(const DeviceScene& sc, uint32_t child, float3 O, float3 idir, uint32_t oct, float tnear, float tmax,
+                                           uint2& G, uint2& T) {
+  struct { float t; } hit = {tmax};
+  const float4* nd = sc.nodes8 + size_t(child) * kNode8Float4s;
+  const float4 n0 = __ldg(nd + 0), n1 = __ldg(nd + 1), n2 = __ldg(nd + 2), n3 = __ldg(nd + 3), n4 = __ldg(nd + 4);
+  const uint32_t hdr = __float_as_uint(n0.w);
+  const uint32_t imask = hdr >> 24;
+  // grid step 2^e per axis (biased exponents), folded into the reciprocal direction; origin of the grid relative to the ray
+  const float adx = __uint_as_float((hdr & 0xFFu) << 23) * idir.x, ady = __uint_as_float(((hdr >> 8) & 0xFFu) << 23) * idir.y,
+              adz = __uint_as_float(((hdr >> 16) & 0xFFu) << 23) * idir.z;
+  const float ox = (n0.x - O.x) * idir.x, oy = (n0.y - O.y) * idir.y, oz = (n0.z - O.z) * idir.z;
+  // entry / exit planes per axis depend on the sign of the direction
+  uint32_t nx[2], fx[2], ny[2], fy[2], nz[2], fz[2];
+  { const uint32_t l0 = __float_as_uint(n2.x), l1 = __float_as_uint(n2.y), h0 = __float_as_uint(n3.z), h1 = __float_as_uint(n3.w);
+    const bool neg = idir.x < 0.0f; nx[0] = neg ? h0 : l0; nx[1] = neg ? h1 : l1; fx[0] = neg ? l0 : h0; fx[1] = neg ? l1 : h1; }
+  { const uint32_t l0 = __float_as_uint(n2.z), l1 = __float_as_uint(n2.w), h0 = __float_as_uint(n4.x), h1 = __float_as_uint(n4.y);
+    const bool neg = idir.y < 0.0f; ny[0] = neg ? h0 : l0; ny[1] = neg ? h1 : l1; fy[0] = neg ? l0 : h0; fy[1] = neg ? l1 : h1; }
+  { const uint32_t l0 = __float_as_uint(n3.x), l1 = __float_as_uint(n3.y), h0 = __float_as_uint(n4.z), h1 = __float_as_uint(n4.w);
+    const bool neg = idir.z < 0.0f; nz[0] = neg ? h0 : l0; nz[1] = neg ? h1 : l1; fz[0] = neg ? l0 : h0; fz[1] = neg ? l1 : h1; }
+  const uint32_t meta[2] = {__float_as_uint(n1.z), __float_as_uint(n1.w)};
+  uint32_t ghits = 0u, tmask = 0u;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t i = uint32_t(h * 4 + k);
+      const float x0 = __fmaf_rn(byte_to_float(nx[h], k), adx, ox), x1 = __fmaf_rn(byte_to_float(fx[h], k), adx, ox);
+      const float y0 = __fmaf_rn(byte_to_float(ny[h], k), ady, oy), y1 = __fmaf_rn(byte_to_float(fy[h], k), ady, oy);
+      const float z0 = __fmaf_rn(byte_to_float(nz[h], k), adz, oz), z1 = __fmaf_rn(byte_to_float(fz[h], k), adz, oz);
+      const float t0 = fmaxf(fmaxf(x0, y0), fmaxf(z0, tnear));
+      const float t1 = fminf(fminf(x1, y1), fminf(z1, hit.t)) * 1.0000003f;
+      if (t0 <= t1) {
+        const uint32_t m = (meta[h] >> (8 * k)) & 0xFFu;
+        if ((imask >> i) & 1u) ghits |= 1u << (24u + (i ^ oct));
+        else tmask |= (m >> 5) << (m & 31u);
+      }
+    }
+  }
+  G = make_uint2(__float_as_uint(n1.x), ghits | imask);
+  T = make_uint2(__float_as_uint(n1.y), tmask);
 }
 
-// ---------------------------------------------------------------- warp-voted persistent traversal
-//
-// trace_ray_masked above runs one ray per thread to completion; ncu (profiles/r01_bpt_trace_full_summary.md)
-// shows what that costs on incoherent rays: 6.9 of 32 lanes active per issued instruction, the triangle test
-// running with 2-3 lanes because a lane that reaches a leaf tests its triangles while the other 31 wait at
-// the reconvergence point, and finished lanes idling until the slowest ray of the warp ends.
-//
-// trace_stream keeps the same tree, the same box test and the same (Embree-exact) triangle test, but changes
-// who does what when:
-//   * ROUNDS.  Every lane holds one pending item `cur`: an inner node, one triangle of a leaf, or nothing.
-//     Each round the warp votes (two ballots): if more lanes hold triangles than inner nodes the round is a
-//     triangle round, otherwise a node round; only the lanes of the winning class work, each on exactly ONE
-//     item, so the instructions of a round run with at least half of the busy lanes.  Lanes of the other class
-//     keep their item for a later round ("postponed leaves").
-//   * PERSISTENT WARPS, DYNAMIC FETCH.  A warp does not own 32 fixed rays: when kFetchMin or more lanes are
-//     idle they take the next rays from a global ticket counter (one atomic per refill), so a long ray no
-//     longer holds 31 finished lanes hostage.
-// Io supplies the rays and consumes the hits:  uint32_t tag = io.load(i, O, D, tnear, tfar, mask);
-// io.store(tag, hit).  Must be entered by complete warps; `ticket` must be zero at kernel start.
-constexpr uint32_t kSentinel = 0x7FFFFFFFu;  // bottom of every traversal stack: this lane has no item
-constexpr unsigned kFullMask = 0xFFFFFFFFu;
-constexpr int kFetchMin = 8;
+template <bool kAnyHit>
+__device__ __forceinline__ Hit trace_ray8(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar, uint32_t ray_mask) {
+  Hit hit; hit.t = tfar; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
+  const float kHuge = 1e30f;
+  const float3 idir = f3(fabsf(D.x) > 1e-30f ? 1.0f / D.x : copysignf(kHuge, D.x),
+                         fabsf(D.y) > 1e-30f ? 1.0f / D.y : copysignf(kHuge, D.y),
+                         fabsf(D.z) > 1e-30f ? 1.0f / D.z : copysignf(kHuge, D.z));
+  // slot s was given to the child lying most towards (s&1 ? +x : -x, s&2 ? +y : -y, s&4 ? +z : -z); with `oct` = the
+  // octant the ray travels into, slot ^ oct is 7 for the corner the ray enters first and 0 for the one it leaves last
+  const uint32_t oct = (idir.x >= 0.0f ? 1u : 0u) | (idir.y >= 0.0f ? 2u : 0u) | (idir.z >= 0.0f ? 4u : 0u);
+  uint2 stack[kStack8];
+  int sp = 0;
+  uint2 G = make_uint2(0u, (1u << (24u + oct)) | 1u);  // node group: the root as the only (inner) child of a virtual parent
+  uint2 T = make_uint2(0u, 0u);                        // triangle group: base, bit j = triangle base + j still to test
+  for (;;) {
+    if (G.y & 0xFF000000u) {
+      // ---- next inner child of the group, nearest corner first
+      const int pos = 31 - __clz(int(G.y));
+      G.y &= ~(1u << pos);
+      const uint32_t slot = uint32_t(pos - 24) ^ oct;
+      const uint32_t child = G.x + __popc(G.y & 0xFFu & ((1u << slot) - 1u));
+      if (G.y & 0xFF000000u) { if (sp < kStack8) stack[sp++] = G; else atomicOr(sc.error_flags, 1u); }
+      node8_step(sc, child, O, idir, oct, tnear, hit.t, G, T);
+    } else {
+      T = G;  // a postponed triangle group (or nothing)
+      G = make_uint2(0u, 0u);
+    }
+    // ---- the triangles hanging off this node
+    while (T.y) {
+      const uint32_t j = uint32_t(__ffs(int(T.y)) - 1);
+      T.y &= T.y - 1u;
+      const uint32_t tri = T.x + j;
+      if (intersect_triangle(sc, tri, O, D, tnear, hit.t, hit.u, hit.v, ray_mask)) {
+        hit.tri = tri;
+        if (kAnyHit) return hit;
+      }
+    }
+    if (!(G.y & 0xFF000000u)) {
+      if (sp == 0) break;
+      G = stack[--sp];
+    }
+  }
+  return hit;
+}
 
-template <bool kAnyHit, class Io, bool kCount = false>
-__device__ __forceinline__ void trace_stream(const DeviceScene& sc, uint32_t n, unsigned* ticket, Io& io) {
-  uint32_t n_nodes = 0, n_tris = 0;  // kCount (diagnostic builds only): work items of the current ray
+// kMeshOnly: ray mask = meshes only (compile-time form of the above)
+// ---------------------------------------------------------------- persistent, warp-synchronous traversal of the 8-wide tree
+//
+// trace_ray8 run by one thread per ray leaves most of the machine idle on incoherent rays (ncu, profiles/): the node
+// step runs with 11 of 32 lanes (finished rays wait for the slowest of their warp) and the triangle test with 2 of 32
+// (few lanes hold a triangle at any given step).  trace_stream8 keeps the same tree and the same tests but makes the warp
+// the unit of scheduling:
+//   * a warp is persistent and refills idle lanes from a global ticket counter once kFetchMin8 of them are idle;
+//   * every round is warp-synchronous: first every lane with node work advances ONE node (popping its stack if needed),
+//     then every lane that holds triangles tests ONE — both code paths run once per round with all the lanes that can
+//     use them, instead of once per lane.  Triangles found while earlier ones are still pending are postponed on the
+//     stack as a triangle group.
+// Io:  uint32_t tag = io.load(i, O, D, tnear, tfar, mask);  io.store(tag, hit).  Must be entered by complete warps;
+// *ticket must be zero at kernel start.
+constexpr unsigned kFullMask = 0xFFFFFFFFu;
+constexpr int kFetchMin8 = 8;
+
+template <bool kAnyHit, class Io>
+__device__ __forceinline__ void trace_stream8(const DeviceScene& sc, uint32_t n, unsigned* ticket, Io& io) {
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lane_lt = (1u << lane) - 1u;
-  uint32_t stack[kStackSize];
-  int sp = 1;
-  stack[0] = kSentinel;
-  uint32_t cur = kSentinel, tag = kInvalid, ray_mask = 0u;
+  uint2 stack[kStack8];
+  int sp = 0;
+  uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
+  uint32_t tag = kInvalid, ray_mask = 0u, oct = 0u;
   bool has_ray = false, exhausted = false;
-  float3 O = f3(0.f), D = f3(0.f), idir = f3(0.f), ood = f3(0.f);
+  float3 O = f3(0.f), D = f3(0.f), idir = f3(0.f);
   float tnear = 0.f;
   Hit hit; hit.t = 0.f; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
   for (;;) {
-    // ---- refill idle lanes
-    const unsigned idle = __ballot_sync(kFullMask, cur == kSentinel);
-    if (!exhausted && __popc(idle) >= kFetchMin) {
+    // ---- refill
+    const unsigned idle = __ballot_sync(kFullMask, !has_ray);
+    if (!exhausted && __popc(idle) >= kFetchMin8) {
       const unsigned cnt = __popc(idle);
       unsigned base = 0;
       if (lane == 0) base = atomicAdd(ticket, cnt);
       base = __shfl_sync(kFullMask, base, 0);
       exhausted = base + cnt >= n;
-      if (cur == kSentinel) {
+      if (!has_ray) {
         const uint32_t i = base + __popc(idle & lane_lt);
         if (i < n) {
           float tfar;
@@ -211,76 +289,79 @@ __device__ __forceinline__ void trace_stream(const DeviceScene& sc, uint32_t n, 
           idir = f3(fabsf(D.x) > 1e-30f ? 1.0f / D.x : copysignf(kHuge, D.x),
                     fabsf(D.y) > 1e-30f ? 1.0f / D.y : copysignf(kHuge, D.y),
                     fabsf(D.z) > 1e-30f ? 1.0f / D.z : copysignf(kHuge, D.z));
-          ood = f3(O.x * idir.x, O.y * idir.y, O.z * idir.z);
-          sp = 1;
-          cur = 0;  // the root is always an inner node
+          oct = (idir.x >= 0.0f ? 1u : 0u) | (idir.y >= 0.0f ? 2u : 0u) | (idir.z >= 0.0f ? 4u : 0u);
+          sp = 0;
+          G = make_uint2(0u, (1u << (24u + oct)) | 1u);
+          T = make_uint2(0u, 0u);
           has_ray = true;
-          if (kCount) { n_nodes = 0; n_tris = 0; }
         }
       }
     }
-    // ---- vote
-    const bool is_inner = cur < kSentinel;
-    const bool is_leaf = (cur & 0x80000000u) != 0u;
-    const unsigned mi = __ballot_sync(kFullMask, is_inner), ml = __ballot_sync(kFullMask, is_leaf);
-    if ((mi | ml) == 0u) {
+    if (__ballot_sync(kFullMask, has_ray) == 0u) {
       if (exhausted) break;
       continue;
     }
-    if (__popc(ml) > __popc(mi)) {
-      // ---- triangle round: one triangle per lane
-      if (is_leaf) {
-        const uint32_t pos = cur & 0x0FFFFFFFu;
-        const bool h = intersect_triangle(sc, pos, O, D, tnear, hit.t, hit.u, hit.v, ray_mask);
-        if (h) hit.tri = pos;
-        if (kCount) ++n_tris;
-        if (kAnyHit && h) cur = kSentinel;
-        else if (cur & 0x70000000u) cur += 1u - 0x10000000u;  // next triangle of the same leaf
-        else cur = stack[--sp];
+    // ---- node phase: every lane with node work advances one node; triangles found while others are still pending are
+    // postponed onto the stack as a triangle group (they are popped like any other entry)
+    if (has_ray) {
+      if (!(G.y & 0xFF000000u) && sp > 0) {
+        const uint2 e = stack[sp - 1];
+        if (e.y & 0xFF000000u) { G = e; --sp; }
+        else if (T.y == 0u) { T = e; --sp; }
       }
-    } else if (is_inner) {
-      // ---- node round: one 4-wide node per lane
-      if (kCount) ++n_nodes;
-      const float4* nd = sc.nodes + size_t(cur) * kNodeFloat4s;
-      const float4 lox = __ldg(nd + 0), loy = __ldg(nd + 1), loz = __ldg(nd + 2);
-      const float4 hix = __ldg(nd + 3), hiy = __ldg(nd + 4), hiz = __ldg(nd + 5);
-      const float4 lk = __ldg(nd + 6);
-      float tn[4];
-      uint32_t ch[4] = {__float_as_uint(lk.x), __float_as_uint(lk.y), __float_as_uint(lk.z), __float_as_uint(lk.w)};
-      const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
-      const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float x0 = __fmaf_rn(lx[k], idir.x, -ood.x), x1 = __fmaf_rn(hx[k], idir.x, -ood.x);
-        const float y0 = __fmaf_rn(ly[k], idir.y, -ood.y), y1 = __fmaf_rn(hy[k], idir.y, -ood.y);
-        const float z0 = __fmaf_rn(lz[k], idir.z, -ood.z), z1 = __fmaf_rn(hz[k], idir.z, -ood.z);
-        const float t0 = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tnear));
-        const float t1 = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), hit.t)) * 1.0000003f;
-        const bool ok = (t0 <= t1) & (ch[k] != kInvalid);
-        tn[k] = ok ? t0 : INFINITY;
-      }
-      cswap(tn[0], ch[0], tn[1], ch[1]); cswap(tn[2], ch[2], tn[3], ch[3]);
-      cswap(tn[0], ch[0], tn[2], ch[2]); cswap(tn[1], ch[1], tn[3], ch[3]);
-      cswap(tn[1], ch[1], tn[2], ch[2]);
-      if (tn[0] == INFINITY) {
-        cur = stack[--sp];
-      } else {
-        if (tn[3] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[3]; else atomicOr(sc.error_flags, 1u); }
-        if (tn[2] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[2]; else atomicOr(sc.error_flags, 1u); }
-        if (tn[1] != INFINITY) { if (sp < kStackSize) stack[sp++] = ch[1]; else atomicOr(sc.error_flags, 1u); }
-        cur = ch[0];
+      if (G.y & 0xFF000000u) {
+        const int pos = 31 - __clz(int(G.y));
+        G.y &= ~(1u << pos);
+        const uint32_t slot = uint32_t(pos - 24) ^ oct;
+        const uint32_t child = G.x + __popc(G.y & 0xFFu & ((1u << slot) - 1u));
+        if (G.y & 0xFF000000u) { if (sp < kStack8) stack[sp++] = G; else atomicOr(sc.error_flags, 1u); }
+        uint2 Tn;
+        node8_step(sc, child, O, idir, oct, tnear, hit.t, G, Tn);
+        if (Tn.y != 0u) {
+          if (T.y != 0u) { if (sp < kStack8) stack[sp++] = T; else atomicOr(sc.error_flags, 1u); }
+          T = Tn;
+        }
       }
     }
-    // ---- a lane whose stack ran empty hands its hit over
-    if (has_ray && cur == kSentinel) {
-      if (kCount) { hit.u = float(n_nodes); hit.v = float(n_tris); }
+    // ---- triangle phase: lanes that hold triangles test one
+    if (has_ray && T.y != 0u) {
+      const uint32_t j = uint32_t(__ffs(int(T.y)) - 1);
+      T.y &= T.y - 1u;
+      const uint32_t tri = T.x + j;
+      if (intersect_triangle(sc, tri, O, D, tnear, hit.t, hit.u, hit.v, ray_mask)) {
+        hit.tri = tri;
+        if (kAnyHit) { T.y = 0u; G.y = 0u; sp = 0; }
+      }
+    }
+    // ---- a ray with nothing left hands its hit over
+    if (has_ray && T.y == 0u && !(G.y & 0xFF000000u) && sp == 0) {
       io.store(tag, hit);
       has_ray = false;
     }
   }
 }
 
+template <bool kAnyHit>
+__device__ __forceinline__ Hit trace_any_bvh(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar, uint32_t ray_mask) {
+#ifdef B2PT_EXPERIMENTS
+  // A/B builds (-DB2PT_EXPERIMENTS): the scene carries one tree or the other (B2PT_BVH=4 builds the 4-wide uncompressed tree)
+  if (!sc.nodes8) return trace_ray_masked<kAnyHit>(sc, O, D, tnear, tfar, ray_mask);
+#endif
+  return trace_ray8<kAnyHit>(sc, O, D, tnear, tfar, ray_mask);
+}
+template <bool kAnyHit, bool kMeshOnly>
+__device__ __forceinline__ Hit trace_ray(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar) {
+  return trace_any_bvh<kAnyHit>(sc, O, D, tnear, tfar, kMeshOnly ? kMaskMesh : kMaskAll);
+}
+
+
 // blocks of a persistent traversal launch over n rays: one wave of 256-thread CTAs, 4 per SM
+inline int grid_for_trace(size_t n, int block) {
+  size_t want = (n + block - 1) / block;
+  size_t cap = size_t(kNumSMs) * 8 * 4;
+  if (want < 1) want = 1;
+  return int(want < cap ? want : cap);
+}
 inline int persistent_grid(size_t n, int block) {
   size_t want = (n + block - 1) / block;
   size_t cap = size_t(kNumSMs) * 4;

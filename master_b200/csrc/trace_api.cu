@@ -10,22 +10,6 @@
 
 namespace b2pt {
 
-template <bool kAnyHit, bool kMeshOnly>
-__global__ void __launch_bounds__(256) trace_rays_kernel(DeviceScene sc, const float4* __restrict__ rays, size_t n,
-                                                         B2ptHit* __restrict__ hits) {
-  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
-    const float4 a = __ldg(&rays[i * 2 + 0]);  // org.xyz, tnear
-    const float4 b = __ldg(&rays[i * 2 + 1]);  // dir.xyz, tfar
-    Hit h = trace_ray<kAnyHit, kMeshOnly>(sc, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), a.w, b.w);
-    B2ptHit o;
-    o.t = h.t; o.u = h.u; o.v = h.v;
-    if (h.tri == kInvalid) { o.geom = kInvalid; o.prim = kInvalid; }
-    else if (kAnyHit) { o.geom = 0u; o.prim = kInvalid; }  // rtcOccluded reports geomID = 0 (Scene.cpp:179)
-    else { o.geom = tri_geom(sc, h.tri); o.prim = tri_prim(sc, h.tri); }
-    hits[i] = o;
-  }
-}
-
 // explicit rays in, RTCRay-style hits out
 template <bool kAnyHit, bool kMeshOnly>
 struct ApiIo {
@@ -49,23 +33,24 @@ struct ApiIo {
   }
 };
 
+// persistent warps, dynamic ray fetch, warp-synchronous rounds (trace.cuh: trace_stream8); B2PT_TRACE_STREAM=1
 template <bool kAnyHit, bool kMeshOnly>
-__global__ void __launch_bounds__(256) trace_stream_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
-                                                           B2ptHit* __restrict__ hits, unsigned* ticket) {
+__global__ void __launch_bounds__(256) trace_stream8_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
+                                                            B2ptHit* __restrict__ hits, unsigned* ticket) {
   ApiIo<kAnyHit, kMeshOnly> io{&sc, rays, hits};
-  trace_stream<kAnyHit>(sc, n, ticket, io);
+  trace_stream8<kAnyHit>(sc, n, ticket, io);
 }
 
-// diagnostic: u, v of every hit are replaced by the ray's node / triangle test counts (B2PT_TRACE_VARIANT=2)
-__global__ void __launch_bounds__(256) trace_count_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
-                                                          B2ptHit* __restrict__ hits, unsigned* ticket) {
-  ApiIo<false, false> io{&sc, rays, hits};
-  trace_stream<false, ApiIo<false, false>, true>(sc, n, ticket, io);
-}
-
-static int trace_variant() {
-  const char* e = getenv("B2PT_TRACE_VARIANT");
-  return e ? atoi(e) : 0;
+// one ray per thread, run to completion (trace.cuh: trace_ray8): the default
+template <bool kAnyHit, bool kMeshOnly>
+__global__ void __launch_bounds__(256, 5) trace_rays_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
+                                                            B2ptHit* __restrict__ hits) {
+  ApiIo<kAnyHit, kMeshOnly> io{&sc, rays, hits};
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    float3 O, D; float tnear, tfar; uint32_t mask;
+    io.load(i, O, D, tnear, tfar, mask);
+    io.store(i, trace_any_bvh<kAnyHit>(sc, O, D, tnear, tfar, mask));
+  }
 }
 
 int launch_trace(b2pt_scene_s* scene, const B2ptRay* rays, size_t n, unsigned mode, B2ptHit* hits, cudaStream_t stream) {
@@ -74,35 +59,24 @@ int launch_trace(b2pt_scene_s* scene, const B2ptRay* rays, size_t n, unsigned mo
   B2_CHECK(n < (size_t(1) << 31), B2PT_ERR_CAPACITY, "b2pt_trace: more than 2^31 rays in one call");
   B2_CHECK(mode <= B2PT_TRACE_OCCLUDED_MESH, B2PT_ERR_INVALID, "b2pt_trace: unknown mode");
   const int block = 256;
-  if (trace_variant() != 0) {
-    // warp-voted persistent traversal (trace.cuh: trace_stream); the ticket is the scene's, zeroed per launch
-    unsigned* ticket = scene->dev.error_flags + 1;
+  const float4* r = reinterpret_cast<const float4*>(rays);
+  const char* stream_env = getenv("B2PT_TRACE_STREAM");  // 1: persistent warp-synchronous traversal (wins on >= 4 M incoherent rays)
+  if (!(stream_env && stream_env[0] == '1') || !sc.nodes8) {
+    const int grid = grid_for_trace(n, block);
+    switch (mode) {
+      case B2PT_TRACE_CLOSEST_ALL: trace_rays_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
+      case B2PT_TRACE_CLOSEST_MESH: trace_rays_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
+      default: trace_rays_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
+    }
+  } else {
+    unsigned* ticket = scene->dev.error_flags + 1;  // the scene's ticket counter, zeroed per launch
     B2_CUDA(cudaMemsetAsync(ticket, 0, 4, stream));
     const int grid = persistent_grid(n, block);
-    const float4* r = reinterpret_cast<const float4*>(rays);
-    if (trace_variant() == 2 && mode == B2PT_TRACE_CLOSEST_ALL) {
-      trace_count_kernel<<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket);
-      B2_CUDA(cudaGetLastError());
-      return B2PT_OK;
-    }
     switch (mode) {
-      case B2PT_TRACE_CLOSEST_ALL: trace_stream_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
-      case B2PT_TRACE_CLOSEST_MESH: trace_stream_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
-      default: trace_stream_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+      case B2PT_TRACE_CLOSEST_ALL: trace_stream8_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+      case B2PT_TRACE_CLOSEST_MESH: trace_stream8_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+      default: trace_stream8_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
     }
-    B2_CUDA(cudaGetLastError());
-    return B2PT_OK;
-  }
-  size_t want = (n + block - 1) / block;
-  // persistent-style grid: a multiple of the SM count, each thread strides over the rays
-  size_t cap = size_t(kNumSMs) * 8 * 4;
-  int grid = int(want < cap ? want : cap);
-  const float4* r = reinterpret_cast<const float4*>(rays);
-  switch (mode) {
-    case B2PT_TRACE_CLOSEST_ALL: trace_rays_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, n, hits); break;
-    case B2PT_TRACE_CLOSEST_MESH: trace_rays_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, n, hits); break;
-    case B2PT_TRACE_OCCLUDED_MESH: trace_rays_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, n, hits); break;
-    default: set_error("b2pt_trace: unknown mode"); return B2PT_ERR_INVALID;
   }
   B2_CUDA(cudaGetLastError());
   return B2PT_OK;

@@ -5,8 +5,8 @@
 
 Ray classes: jittered camera rays, their cosine-sampled bounce rays (1st, 2nd, 3rd bounce:
 increasingly incoherent), and shadow segments towards the lights.  Each class is timed with CUDA events around
-`reps` launches on the current stream, rays and hits resident in HBM.  With several --variants (the
-B2PT_TRACE_VARIANT environment variable selects the traversal kernel) the hits are also compared between variants.
+`reps` launches on the current stream, rays and hits resident in HBM.  With several --variants (B2PT_TRACE_STREAM: 0 = one ray per thread, the default;
+1 = persistent warp-synchronous traversal) the hits are also compared between variants.
 """
 import argparse
 import json
@@ -56,7 +56,7 @@ def main():
         d_hits = torch.zeros(n, 5, dtype=torch.int32, device="cuda")
         row = {"rays": n}
         for v in a.variants.split(","):
-            os.environ["B2PT_TRACE_VARIANT"] = v
+            os.environ["B2PT_TRACE_STREAM"] = v
             for _ in range(2):
                 scene.trace_device(d_rays.data_ptr(), n, mode, d_hits.data_ptr(), stream)
             torch.cuda.synchronize()
