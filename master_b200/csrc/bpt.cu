@@ -43,6 +43,7 @@ struct BptCounters {
   unsigned int done;
   unsigned int lv_count;
   unsigned int trace_count[2], pair_count[2], shadow_count[2];
+  unsigned int dir_count[2];
   unsigned int ticket[2];  // dynamic ray fetch of the traversal stages (trace, shadow), zeroed by the logic stage
 };
 
@@ -76,6 +77,7 @@ struct BptPool {
   uint32_t* trace_q;
   uint2* pair_q;
   float4* shadow_q;  // 3 float4 per entry
+  float4* dir_q;     // connections to sun lights, 4 float4 per entry (render_common.cuh: directional_kernel)
 };
 
 __device__ __forceinline__ void pack_vertex(const Vertex& v, float4* q) {
@@ -209,6 +211,7 @@ __global__ void __launch_bounds__(256) bpt_logic_kernel(RenderConfig cfg, BptPoo
     cnt->pair_count[parity ^ 1] = 0;
     cnt->shadow_count[parity ^ 1] = 0;
     cnt->ticket[0] = 0; cnt->ticket[1] = 0;
+    cnt->dir_count[parity ^ 1] = 0;
   }
   const float beta = cfg.params.beta;
   const float roulette = cfg.params.roulette;
@@ -405,7 +408,23 @@ __global__ void __launch_bounds__(256) bpt_logic_kernel(RenderConfig cfg, BptPoo
                     const uint32_t light_id = sc.materials[ls.surface.material_index()].light_id;
                     pool.nee[slot] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
                   } else {
-                    atomicAdd(&cnt->capacity_events, 1ull);  // _connect_directional: sun lights are not wired into the GPU BPT yet
+                    // _connect_directional (BPT.cpp:245-269): queued for the directional stage
+                    const float3 n = ls.surface.normal();
+                    const BsdfQuery eb = bsdf_query(sc, cur.s, -n, cur.omega);
+                    const float cosine = fabsf(dot(n, cur.s.normal()));
+                    const float3 result = ls.radiance / ls.light_density * roulette_inv * cur.thr * eb.throughput * cosine;
+                    const float KC = cur.w1 * beta_fn(eb.density, beta) + cur.w0 * float(cur.finite);
+                    const float3 org = offset_origin(cur.s.pos, cur.s.gnormal, -n);
+                    const unsigned dq = atomicAdd(&cnt->dir_count[parity], 1u);
+                    if (dq < pool.size) {
+                      float4* e = pool.dir_q + size_t(dq) * 4;
+                      e[0] = make_float4(org.x, org.y, org.z, __uint_as_float(slot));
+                      e[1] = make_float4(cur.s.pos.x, cur.s.pos.y, cur.s.pos.z, cosine);
+                      e[2] = make_float4(result.x, result.y, result.z, KC);
+                      e[3] = make_float4(__uint_as_float(sc.materials[ls.surface.material_index()].light_id), 0.f, 0.f, 0.f);
+                    } else {
+                      atomicAdd(&cnt->capacity_events, 1ull);
+                    }
                   }
                 }
                 emit_n = (count > 0 ? count - 1u : 0u) + (emit_nee ? 1u : 0u);  // light vertices 1 .. n-1 (+ the fresh sample)
@@ -704,6 +723,7 @@ int bpt_workspace(b2pt_scene_s* scene, uint32_t size, int lanes, BptWorkspace** 
     if ((rc = ws_alloc(w, &p.trace_q, size))) return rc;
     if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
     if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
+    if ((rc = ws_alloc(w, &p.dir_q, size_t(size) * 4))) return rc;
     if ((rc = ws_alloc(w, &l.counters, 1))) return rc;
     B2_CUDA(cudaMallocHost((void**)&l.host_counters, sizeof(BptCounters)));
     B2_CUDA(cudaMemset(p.splat, 0, size_t(size) * 3 * sizeof(double)));
@@ -785,6 +805,12 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         const int parity = g.it & 1;
         timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0); timer.end();
         timer.begin(kStageShade); bpt_connect_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
+        if (cfg.scene.has_directional) {
+          timer.begin(kStageTrace);
+          directional_kernel<<<grid, block, 0, l.stream>>>(cfg.scene, g.pool.dir_q, &l.counters->dir_count[parity], g.pool.size,
+                                                          DirectionalParams{cfg.params.beta, 1.0f, 0.0f, 0.0f}, g.pool.rad, &l.counters->basic_rays);
+          timer.end();
+        }
         timer.begin(kStageTrace);
         if (stream_trace) bpt_trace_kernel<true><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         else bpt_trace_kernel<false><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);

@@ -64,6 +64,42 @@ __device__ __forceinline__ float3 shoot_primary(const RenderConfig& cfg, Rng& rn
   return camera_ray_direction(cfg.params.camera, float(px) + jx, float(py) + jy, cfg.width_f, cfg.res_y_inv);
 }
 
+// ---------------------------------------------------------------- connections to directional (sun) lights
+// BPTBase::_connect_directional (BPT.cpp:245-269) / UPGBase::_connect_directional (UPG.cpp:480-525): instead of an occlusion
+// test towards a sampled point, a CLOSEST-hit ray is shot from the eye vertex against the light's direction; the light is
+// seen iff the first thing hit is the light's own quad (material ids match), and the MIS weight depends on where it was hit.
+// The logic stage queues what it knows (4 float4 per entry); this stage traces and finishes the arithmetic.
+//   e0 = ray origin (already offset), bits(target path slot)     e1 = eye position, |dot(light normal, eye normal)|
+//   e2 = unweighted contribution, KC                             e3 = bits(light id), KD, 0, 0
+//   Cp = KC * beta(cos / d^2),  Dp = KD * beta(cos / d^2),  weightInv = (Cp + 1) * vc + beta_n * Dp * vm
+// (BPT: vc = 1, vm = 0.)
+struct DirectionalParams { float beta, vc, vm, beta_n; };
+
+static __global__ void __launch_bounds__(256) directional_kernel(DeviceScene sc, const float4* __restrict__ queue, const unsigned* __restrict__ count,
+                                                          uint32_t capacity, DirectionalParams P, float4* rad, unsigned long long* basic_rays) {
+  const uint32_t n = min(*count, capacity);
+  if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(basic_rays, (unsigned long long)n);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 e0 = queue[size_t(i) * 4 + 0], e1 = queue[size_t(i) * 4 + 1], e2 = queue[size_t(i) * 4 + 2], e3 = queue[size_t(i) * 4 + 3];
+    const B2ptLight& l = sc.lights[__float_as_uint(e3.x)];
+    const float3 dir = -f3(l.tangent[3], l.tangent[4], l.tangent[5]);
+    const float3 org = f3(e0.x, e0.y, e0.z);
+    const Hit h = trace_ray<false, false>(sc, org, dir, 0.0f, INFINITY);  // Scene::intersect
+    if (h.tri == kInvalid) continue;
+    const uint32_t material = __float_as_uint(__ldg(&sc.tri_frames[size_t(h.tri) * kFrameFloat4s + 6]).w);
+    if (material != l.material_id) continue;
+    const float3 isect = org + dir * h.t;
+    const float coeff = beta_fn(e1.w / distance2(isect, f3(e1.x, e1.y, e1.z)), P.beta);
+    const float Cp = e2.w * coeff, Dp = e3.y * coeff;
+    const float weight_inv = (Cp + 1.0f) * P.vc + P.beta_n * Dp * P.vm;
+    const float3 result = f3(e2.x, e2.y, e2.z);
+    if (l1norm(result) < kFltEpsilon) continue;
+    const float3 c = result / weight_inv;
+    float* r = &rad[__float_as_uint(e0.w)].x;
+    atomicAdd(r + 0, c.x); atomicAdd(r + 1, c.y); atomicAdd(r + 2, c.z);
+  }
+}
+
 // Per-stage device time (B2ptStats::trace_ms / shadow_ms / shade_ms): a CUDA-event pair around every
 // launch of a stage, on the stream the kernels are launched on.  Counts launches always; records
 // events only when B2PT_PROFILE_STAGES=1, because the pairs serialise nothing but do cost host time.

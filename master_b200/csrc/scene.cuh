@@ -37,6 +37,7 @@ struct DeviceScene {
   uint32_t num_nodes = 0;
   uint32_t num_materials = 0;
   uint32_t num_lights = 0;
+  uint32_t has_directional = 0;  // some light is a sun (AreaLight::diffuse == false): the integrators run the directional stage
   const float4* tri_v0 = nullptr;
   const float4* tri_e1 = nullptr;
   const float4* tri_e2 = nullptr;

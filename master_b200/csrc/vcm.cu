@@ -20,8 +20,7 @@
 // consumes random numbers in an order the reference leaves to std::sort; here every merge owns a sub-stream keyed by
 // (path stream, eye vertex, photon), so UPG agrees with the reference in distribution, not per path.
 //
-// Restrictions, stated: merging from the light side only (Options::from_light = true, the default); sun lights are
-// skipped in connections like in bpt.cu (counted in B2ptStats::capacity_events).
+// Restriction, stated: merging from the light side only (Options::from_light = true, the default).
 #include "grid.cuh"
 #include "render_common.cuh"
 
@@ -41,7 +40,7 @@ struct VcmCounters {
   unsigned long long basic_rays, shadow_rays, numeric_errors, capacity_events, density_rays;
   unsigned int done;
   unsigned int lv_count;
-  unsigned int trace_count[2], pair_count[2], shadow_count[2], gather_count[2];
+  unsigned int trace_count[2], pair_count[2], shadow_count[2], gather_count[2], dir_count[2];
 };
 
 // the per-pass constants of UPGBase (UPG.hpp:119-137)
@@ -83,6 +82,7 @@ struct VcmPool {
   float4* lv; uint32_t* lv_link; float4* grid_points;
   // queues
   uint32_t* trace_q; uint2* pair_q; float4* shadow_q; uint32_t* gather_q;
+  float4* dir_q;  // connections to sun lights, 4 float4 per entry (render_common.cuh: directional_kernel)
 };
 
 __device__ __forceinline__ void pack_vertex(const Vertex& v, float4* q) {
@@ -404,7 +404,7 @@ __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParam
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     cnt->trace_count[parity ^ 1] = 0; cnt->pair_count[parity ^ 1] = 0;
-    cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0;
+    cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0; cnt->dir_count[parity ^ 1] = 0;
   }
   const float beta = P.beta;
   for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < pool.pixels_pad; slot += gridDim.x * blockDim.x) {
@@ -511,7 +511,26 @@ __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParam
                       const uint32_t light_id = sc.materials[ls.surface.material_index()].light_id;
                       pool.nee[slot] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
                     } else {
-                      atomicAdd(&cnt->capacity_events, 1ull);  // _connect_directional: sun lights are not wired in yet
+                      // _connect_directional (UPG.cpp:480-525): queued for the directional stage
+                      const float3 n = ls.surface.normal();
+                      const BsdfQuery cb = bsdf_query(sc, cur.s, -n, cur.omega);
+                      const float trim1 = cur.length() <= 1.0f ? 0.0f : 1.0f;
+                      const float eye_vm = clamp_vm(P, beta_fn(P.circle * cur.bgeo * cb.density, beta)) * trim1;  // from_light
+                      const float cosine = fabsf(dot(n, cur.s.normal()));
+                      const float KD = cur.w2 * beta_fn(cb.density, beta) + float(cb.finite) * eye_vm * beta_fn(cur.w0, beta) * trim1;
+                      const float KC = cur.w1 * beta_fn(cb.density, beta) + beta_fn(cur.w0, beta) * float(cur.finite());
+                      const float3 result = ls.radiance / ls.light_density * P.roulette_inv * cur.thr * cb.throughput * cosine;
+                      const float3 org = offset_origin(cur.s.pos, cur.s.gnormal, -n);
+                      const unsigned dq = atomicAdd(&cnt->dir_count[parity], 1u);
+                      if (dq < pool.pixels_pad) {
+                        float4* e = pool.dir_q + size_t(dq) * 4;
+                        e[0] = make_float4(org.x, org.y, org.z, __uint_as_float(slot));
+                        e[1] = make_float4(cur.s.pos.x, cur.s.pos.y, cur.s.pos.z, cosine);
+                        e[2] = make_float4(result.x, result.y, result.z, KC);
+                        e[3] = make_float4(__uint_as_float(sc.materials[ls.surface.material_index()].light_id), KD, 0.f, 0.f);
+                      } else {
+                        atomicAdd(&cnt->capacity_events, 1ull);
+                      }
                     }
                   }
                   emit_n = (count > 0 ? count - 1u : 0u) + (emit_nee ? 1u : 0u);
@@ -807,6 +826,13 @@ __global__ void __launch_bounds__(256) vcm_commit_kernel(RenderConfig cfg, VcmPo
 }
 
 // ---------------------------------------------------------------- host driver
+inline float beta_fn_host(float x, float beta) {  // Beta::beta on the host (Beta.hpp:24-42)
+  if (beta == 2.0f) return x * x;
+  if (beta == 1.0f) return x;
+  if (beta == 0.0f) return x == 0.0f ? 0.0f : 1.0f;
+  return powf(x, beta);
+}
+
 struct VcmWorkspace {
   VcmPool pool{};
   uint32_t pixels = 0, photons = 0;
@@ -875,6 +901,7 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWor
   if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
   if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
   if ((rc = ws_alloc(w, &p.gather_q, ne))) return rc;
+  if ((rc = ws_alloc(w, &p.dir_q, ne * 4))) return rc;
   if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
   B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(VcmCounters)));
   B2_CUDA(cudaMemset(p.splat, 0, ne * 3 * sizeof(double)));
@@ -944,7 +971,7 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     { const char* e = getenv("B2PT_VCM_BRUTE"); if (e && e[0] == '1') P.brute_vertices = num_vertices; }
     // ---- eye paths
     B2_CUDA(cudaMemsetAsync(&w->counters->done, 0, sizeof(unsigned int), stream));
-    B2_CUDA(cudaMemsetAsync(w->counters->trace_count, 0, sizeof(unsigned int) * 8, stream));
+    B2_CUDA(cudaMemsetAsync(w->counters->trace_count, 0, sizeof(unsigned int) * 10, stream));
     B2_CUDA(cudaMemsetAsync(pool.state, 0, size_t(pool.pixels_pad) * 4, stream));
     const int grid_g = grid_for(pool.pixels_pad, 128);
     for (int it = 0;;) {
@@ -953,6 +980,13 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         timer.begin(kStageShade); vcm_eye_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample); timer.end();
         timer.begin(kStageShade); vcm_gather_kernel<<<grid_g, 128, 0, stream>>>(cfg, P, pool, w->grid.dev, w->counters, parity); timer.end();
         timer.begin(kStageShade); vcm_connect_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity); timer.end();
+        if (cfg.scene.has_directional) {
+          timer.begin(kStageTrace);
+          directional_kernel<<<grid_e, block, 0, stream>>>(cfg.scene, pool.dir_q, &w->counters->dir_count[parity], pool.pixels_pad,
+                                                          DirectionalParams{P.beta, float(P.enable_vc), float(P.enable_vm), beta_fn_host(P.num_scattered, P.beta)},
+                                                          pool.rad, &w->counters->basic_rays);
+          timer.end();
+        }
         timer.begin(kStageTrace); vcm_trace_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
         timer.begin(kStageShadow); vcm_shadow_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
       }

@@ -30,6 +30,7 @@ HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
 TMP = os.environ.get("TMPDIR", "/tmp") + "/b2pt_golden"
 
 SMALL_SCENES = ["CornellBoxDiffuse", "CornellBoxSpecular", "TestCaseFurnace", "TestCase9", "MetalRings"]
+SUN_SCENES = ["TestCase12", "TestCase18", "TestCase33"]  # directional (sun) lights: _connect_directional, sun_light_bsdf
 
 
 def run(*args):
@@ -165,12 +166,22 @@ def main():
         ("CornellBoxSpecular", "VCM", 32, 32, 2, dict(beta=2, radius=0.1)),
         ("MetalRings", "VCM", 32, 32, 2, dict(beta=2, radius=0.05)),
         ("TestCaseFurnace", "VCM", 32, 32, 2, dict(beta=2, radius=0.1)),
+        ("TestCase12", "PT", 32, 32, 2, dict(beta=1)),
+        ("TestCase12", "BPT", 32, 32, 2, dict(beta=2)),
+        ("TestCase18", "BPT", 32, 32, 2, dict(beta=2)),
+        ("TestCase33", "BPT", 32, 32, 2, dict(beta=2)),
+        ("TestCase18", "VCM", 32, 32, 2, dict(beta=2, radius=0.1)),
+        ("TestCase33", "VCM", 32, 32, 2, dict(beta=2, radius=0.05)),
         ("CornellBoxDiffuse", "UPG", 32, 32, 16, dict(beta=2, radius=0.1, per_path=0)),
         ("TestCaseFurnace", "UPG", 24, 24, 16, dict(beta=2, radius=0.1, per_path=0)),
     ]
     only = [a for a in sys.argv[1:] if not a.startswith("-")]
     if only:
-        renders = [r for r in renders if r[1] in only]
+        renders = [r for r in renders if r[1] in only or r[0] in only]
+    for name in SUN_SCENES:
+        dst = os.path.join(HERE, "scenes", name + ".b2s")
+        if not os.path.exists(dst):
+            print(name, run("dump", os.path.join(REF, "models", name + ".blend"), dst))
     for name, tech, w, h, spp, kw in renders:
         scene = os.path.join(HERE, "scenes", name + ".b2s")
         out = ref_render(scene, tech, w, h, spp, seed=1234, **kw)

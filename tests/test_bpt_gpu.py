@@ -12,7 +12,8 @@ from test_pt_gpu import gpu_render, image_rel_rmse, path_agreement
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("name", ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace"])
+# TestCase12 / 18 / 33 are lit by directional (sun) lights: _connect_directional (BPT.cpp:245-269) and sun_light_bsdf
+@pytest.mark.parametrize("name", ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace", "TestCase12", "TestCase18", "TestCase33"])
 def test_bpt_per_path_radiance_and_light_image(name, device_scenes, flat_scenes):
     g = np.load(golden_path("render_%s_BPT.npz" % name))
     w, h, spp = int(g["width"]), int(g["height"]), g["paths"].shape[0]

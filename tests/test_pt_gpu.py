@@ -37,7 +37,7 @@ def path_agreement(ours, ref, rel=1e-4):
     return float((err <= rel).mean()), err
 
 
-@pytest.mark.parametrize("name", ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace", "TestCase9"])
+@pytest.mark.parametrize("name", ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace", "TestCase9", "TestCase12"])
 def test_pt_per_path_radiance(name, device_scenes, flat_scenes):
     g = np.load(golden_path("render_%s_PT.npz" % name))
     w, h, spp = int(g["width"]), int(g["height"]), g["paths"].shape[0]

@@ -16,7 +16,7 @@ from test_pt_gpu import gpu_render, image_rel_rmse, path_agreement
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("name", ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace"])
+@pytest.mark.parametrize("name", ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace", "TestCase18", "TestCase33"])
 def test_vcm_per_path_radiance_and_light_image(name, device_scenes, flat_scenes):
     g = np.load(golden_path("render_%s_VCM.npz" % name))
     w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
