@@ -118,10 +118,11 @@ def load_library():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    path = os.environ.get("B2PT_LIB", LIB_PATH)  # A/B builds (master_b200/build.py --variant=...)
+    if not os.path.exists(path):
         raise B2ptError(-1, "%s not found: build it with `python -m master_b200.build` "
-                            "(there is no CPU fallback)" % LIB_PATH)
-    lib = C.CDLL(LIB_PATH)
+                            "(there is no CPU fallback)" % path)
+    lib = C.CDLL(path)
     lib.b2pt_last_error.restype = C.c_char_p
     lib.b2pt_abi_version.restype = C.c_int
     lib.b2pt_device_count.restype = C.c_int

@@ -38,8 +38,16 @@ def _stamp(paths):
     return h.hexdigest()
 
 
-def build_library(force=False, verbose=False):
-    """Compile every .cu under csrc/ and link libb2pt.so. Returns the library path."""
+def build_library(force=False, verbose=False, variant=None, extra_flags=()):
+    """Compile every .cu under csrc/ and link libb2pt.so. Returns the library path.
+
+    `variant` + `extra_flags` build an A/B copy (libb2pt_<variant>.so, own object directory) that tools select with
+    B2PT_LIB=<path>; the product library is always the flag set above."""
+    global OBJ, LIB
+    flags = NVCC_FLAGS + list(extra_flags)
+    if variant:
+        OBJ = os.path.join(HERE, "build", variant)
+        LIB = os.path.join(HERE, "libb2pt_%s.so" % variant)
     os.makedirs(OBJ, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h", ".hpp"))]
     headers.append(os.path.join(HERE, "..", "include", "b2pt.h"))
@@ -49,11 +57,11 @@ def build_library(force=False, verbose=False):
         path = os.path.join(CSRC, src)
         obj = os.path.join(OBJ, src[:-3] + ".o")
         stamp_file = obj + ".stamp"
-        stamp = _stamp([path] + headers)
+        stamp = _stamp([path] + headers) + " ".join(extra_flags)
         objs.append(obj)
         if not force and os.path.exists(obj) and os.path.exists(stamp_file) and open(stamp_file).read() == stamp:
             continue
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", path, "-o", obj]
+        cmd = [nvcc] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-c", path, "-o", obj]
         procs.append((src, stamp_file, stamp, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
     failed = False
     for src, stamp_file, stamp, p in procs:
@@ -75,4 +83,9 @@ def build_library(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    variant = None
+    extra = [a for a in sys.argv[1:] if a.startswith("-D")]
+    for a in sys.argv[1:]:
+        if a.startswith("--variant="):
+            variant = a.split("=", 1)[1]
+    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv, variant=variant, extra_flags=extra))

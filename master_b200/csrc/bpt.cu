@@ -28,6 +28,13 @@
 
 #include "render_common.cuh"
 
+#ifndef B2PT_LOGIC_MIN_BLOCKS
+#define B2PT_LOGIC_MIN_BLOCKS 3  // resident CTAs per SM the shading stages are compiled for (register cap = 65536 / (256 * this))
+#endif
+#ifndef B2PT_TRACE_MIN_BLOCKS
+#define B2PT_TRACE_MIN_BLOCKS 4  // traversal stages: 64 registers per thread
+#endif
+
 namespace b2pt {
 
 namespace {
@@ -204,7 +211,7 @@ __device__ __forceinline__ unsigned warp_reserve(unsigned* counter, unsigned n) 
   return base + incl - n;
 }
 
-__global__ void __launch_bounds__(256) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0) {
+__global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0) {
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     cnt->trace_count[parity ^ 1] = 0;
@@ -479,7 +486,7 @@ __global__ void __launch_bounds__(256) bpt_logic_kernel(RenderConfig cfg, BptPoo
   }
 }
 
-__global__ void __launch_bounds__(256) bpt_connect_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+__global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
   const DeviceScene& sc = cfg.scene;
   const uint32_t n = min(cnt->pair_count[parity], pool.q_capacity);
   const float beta = cfg.params.beta;
@@ -595,12 +602,13 @@ struct BptShadowIo {
   }
 };
 
-template <bool kStream>
-__global__ void __launch_bounds__(256) bpt_trace_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+template <int kStream>
+__global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
   const uint32_t n = cnt->trace_count[parity];
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->basic_rays, (unsigned long long)n);
   BptTraceIo io{&pool};
-  if (kStream) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
+  if (kStream == 2) { trace_dyn8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
+  if (kStream == 1) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     float3 O, D; float tnear, tfar; uint32_t mask;
     const uint32_t tag = io.load(i, O, D, tnear, tfar, mask);
@@ -608,12 +616,13 @@ __global__ void __launch_bounds__(256) bpt_trace_kernel(RenderConfig cfg, BptPoo
   }
 }
 
-template <bool kStream>
-__global__ void __launch_bounds__(256) bpt_shadow_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+template <int kStream>
+__global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_shadow_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
   const uint32_t n = min(cnt->shadow_count[parity], pool.q_capacity);
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->shadow_rays, (unsigned long long)n);
   BptShadowIo io{&pool};
-  if (kStream) { trace_stream8<true>(cfg.scene, n, &cnt->ticket[1], io); return; }
+  if (kStream == 2) { trace_dyn8<true>(cfg.scene, n, &cnt->ticket[1], io); return; }
+  if (kStream == 1) { trace_stream8<true>(cfg.scene, n, &cnt->ticket[1], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     float3 O, D; float tnear, tfar; uint32_t mask;
     const uint32_t tag = io.load(i, O, D, tnear, tfar, mask);
@@ -651,7 +660,13 @@ __global__ void __launch_bounds__(256) bpt_commit_kernel(RenderConfig cfg, BptPo
 
 // Two batches are kept in flight on two streams ("lanes"): the late iterations of a batch have few live paths,
 // so its kernels are small and end in long single-ray tails; the other lane's kernels fill the machine meanwhile.
-constexpr int kLanes = 2;
+constexpr int kMaxLanes = 8;
+constexpr int kDefaultLanes = 2;
+inline int bpt_lanes() {  // B2PT_BPT_LANES overrides the number of concurrent batches for A/B runs
+  const char* e = getenv("B2PT_BPT_LANES");
+  const int v = e ? atoi(e) : kDefaultLanes;
+  return v < 1 ? 1 : v > kMaxLanes ? kMaxLanes : v;
+}
 
 struct BptLane {
   BptPool pool{};
@@ -663,7 +678,7 @@ struct BptLane {
 };
 
 struct BptWorkspace {
-  BptLane lane[kLanes];
+  BptLane lane[kMaxLanes];
   uint32_t size = 0;
   cudaEvent_t fork = nullptr;
   std::vector<void*> blocks;
@@ -741,14 +756,15 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   const uint32_t pixels = base.pixels;
   const uint32_t num_passes = base.params.num_samples;
   // a batch is a whole number of passes, at most 2^21 paths (B2PT_BPT_BATCH_LOG2 overrides the exponent) (or one pass if the window is larger); with more than one
-  // pass to render the passes are spread over kLanes concurrent batches
+  // pass to render the passes are spread over bpt_lanes() concurrent batches
   uint32_t batch_paths = 1u << 21;
   { const char* e = getenv("B2PT_BPT_BATCH_LOG2"); if (e) { int v = atoi(e); if (v >= 10 && v <= 26) batch_paths = 1u << v; } }
   uint32_t passes_per_batch = batch_paths / pixels;
   if (passes_per_batch < 1) passes_per_batch = 1;
+  const int kLanes = bpt_lanes();
   if (passes_per_batch > (num_passes + kLanes - 1) / kLanes) passes_per_batch = (num_passes + kLanes - 1) / kLanes;
   const uint32_t num_batches = (num_passes + passes_per_batch - 1) / passes_per_batch;
-  const int lanes = num_batches > 1 ? kLanes : 1;
+  const int lanes = int(num_batches) < kLanes ? int(num_batches) : kLanes;
   const uint32_t size = (passes_per_batch * pixels + block - 1) / block * block;
   BptWorkspace* w = nullptr;
   if (int rc = bpt_workspace(scene, size, lanes, &w)) return rc;
@@ -760,13 +776,13 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   // end to end than the persistent warp-synchronous traversal, which only wins on >= 4 M incoherent rays per launch;
   // B2PT_TRACE_STREAM=1 selects the latter for A/B runs
   const char* tv = getenv("B2PT_TRACE_STREAM");
-  const bool stream_trace = tv && tv[0] == '1', stream_shadow = stream_trace;
+  const int stream_trace = tv ? (tv[0] == '1' ? 1 : tv[0] == '2' ? 2 : 0) : 0, stream_shadow = stream_trace;
   unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
   const int kBatchIters = 8;
 
   // per-lane progress
   struct Progress { bool active = false; uint32_t pass0 = 0, passes = 0; int it = 0; BptPool pool; };
-  Progress prog[kLanes];
+  Progress prog[kMaxLanes];
   w->lane[0].stream = stream;
   std::vector<std::unique_ptr<StageTimer>> timers;
   timers.emplace_back(new StageTimer(stream));
@@ -812,12 +828,14 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
           timer.end();
         }
         timer.begin(kStageTrace);
-        if (stream_trace) bpt_trace_kernel<true><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
-        else bpt_trace_kernel<false><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        if (stream_trace == 2) bpt_trace_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else if (stream_trace == 1) bpt_trace_kernel<1><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else bpt_trace_kernel<0><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         timer.end();
         timer.begin(kStageShadow);
-        if (stream_shadow) bpt_shadow_kernel<true><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
-        else bpt_shadow_kernel<false><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        if (stream_shadow == 2) bpt_shadow_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else if (stream_shadow == 1) bpt_shadow_kernel<1><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else bpt_shadow_kernel<0><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         timer.end();
       }
       B2_CUDA(cudaMemcpyAsync(l.host_counters, l.counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, l.stream));

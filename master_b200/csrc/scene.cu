@@ -768,6 +768,8 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
   ds.tri_v0 = v0o; ds.tri_e1 = e1o; ds.tri_e2 = e2o; ds.tri_frames = frames; ds.nodes = nodes; ds.nodes8 = nodes8;
   ds.materials = d_materials; ds.lights = d_lights; ds.light_cp = d_cp; ds.light_den = d_den; ds.light_int = d_int;
   ds.error_flags = d_flags;
+  { const char* e = getenv("B2PT_DYN_FETCH"); if (e) ds.dyn_fetch_lanes = atoi(e); }
+  { const char* e = getenv("B2PT_DYN_TRI"); if (e) ds.dyn_tri_lanes = atoi(e); }
   for (uint32_t k = 0; k < L; ++k) if (d->lights[k].diffuse == 0.0f) ds.has_directional = 1u;
   s->bvh_bytes = uint64_t(num_wide) * (nodes8 ? 5 : kNodeFloat4s) * 16 + uint64_t(n) * 48;
   return B2PT_OK;

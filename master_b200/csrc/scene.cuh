@@ -51,6 +51,9 @@ struct DeviceScene {
   const double* light_den = nullptr;   // densities [num_lights]
   const float* light_int = nullptr;    // interval boundaries [num_lights + 1]
   uint32_t* error_flags = nullptr;     // bit 0: traversal stack overflow
+  // scheduling thresholds of trace_dyn8 (trace.cuh); B2PT_DYN_FETCH / B2PT_DYN_TRI override them for A/B runs
+  int dyn_fetch_lanes = 20;
+  int dyn_tri_lanes = 8;
 };
 
 }  // namespace b2pt

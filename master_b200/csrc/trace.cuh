@@ -341,6 +341,104 @@ __device__ __forceinline__ void trace_stream8(const DeviceScene& sc, uint32_t n,
   }
 }
 
+// ---------------------------------------------------------------- persistent warps, free-running lanes, postponed triangles
+//
+// trace_dyn8 keeps trace_ray8's per-lane loop (the hardware handles the divergence, no per-round votes) and adds the two
+// scheduling rules of Aila & Laine / Ylitie et al.:
+//   * dynamic fetch: a warp leaves the traversal loop to refill its idle lanes from the ticket counter once fewer than
+//     DeviceScene::dyn_fetch_lanes lanes are still running together;
+//   * postponed triangles: a lane that reaches the triangle loop with fewer than DeviceScene::dyn_tri_lanes lanes beside it, and that
+//     still has inner children of the current node to visit, pushes the triangle group and goes on with the nodes; the
+//     group is popped like any other entry, by which time more lanes tend to hold triangles.  A group is never postponed
+//     when the lane has no pending child of the current node, so every postponement is followed by a node step and the
+//     loop terminates.
+// The tests are the same ones in a different order: a closest hit can differ from trace_ray8's only where two triangles
+// are hit at exactly the same distance.
+
+template <bool kAnyHit, class Io>
+__device__ __forceinline__ void trace_dyn8(const DeviceScene& sc, uint32_t n, unsigned* ticket, Io& io) {
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned lane_lt = (1u << lane) - 1u;
+  uint2 stack[kStack8];
+  int sp = 0;
+  uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
+  uint32_t tag = kInvalid, ray_mask = 0u, oct = 0u;
+  bool has_ray = false, exhausted = false;
+  float3 O = f3(0.f), D = f3(0.f), idir = f3(0.f);
+  float tnear = 0.f;
+  Hit hit; hit.t = 0.f; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
+  for (;;) {
+    __syncwarp();
+    // ---- refill the idle lanes
+    const unsigned idle = __ballot_sync(kFullMask, !has_ray);
+    if (!exhausted && idle) {
+      const unsigned cnt = __popc(idle);
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(ticket, cnt);
+      base = __shfl_sync(kFullMask, base, 0);
+      exhausted = base + cnt >= n;
+      if (!has_ray) {
+        const uint32_t i = base + __popc(idle & lane_lt);
+        if (i < n) {
+          float tfar;
+          tag = io.load(i, O, D, tnear, tfar, ray_mask);
+          hit.t = tfar; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
+          const float kHuge = 1e30f;
+          idir = f3(fabsf(D.x) > 1e-30f ? 1.0f / D.x : copysignf(kHuge, D.x),
+                    fabsf(D.y) > 1e-30f ? 1.0f / D.y : copysignf(kHuge, D.y),
+                    fabsf(D.z) > 1e-30f ? 1.0f / D.z : copysignf(kHuge, D.z));
+          oct = (idir.x >= 0.0f ? 1u : 0u) | (idir.y >= 0.0f ? 2u : 0u) | (idir.z >= 0.0f ? 4u : 0u);
+          sp = 0;
+          G = make_uint2(0u, (1u << (24u + oct)) | 1u);
+          T = make_uint2(0u, 0u);
+          has_ray = true;
+        }
+      }
+    }
+    if (__ballot_sync(kFullMask, has_ray) == 0u) break;  // nothing in flight and nothing fetched: the queue is drained
+    // ---- traversal, lanes run freely
+    if (has_ray) {
+      for (;;) {
+        if (G.y & 0xFF000000u) {
+          const int pos = 31 - __clz(int(G.y));
+          G.y &= ~(1u << pos);
+          const uint32_t slot = uint32_t(pos - 24) ^ oct;
+          const uint32_t child = G.x + __popc(G.y & 0xFFu & ((1u << slot) - 1u));
+          if (G.y & 0xFF000000u) { if (sp < kStack8) stack[sp++] = G; else atomicOr(sc.error_flags, 1u); }
+          node8_step(sc, child, O, idir, oct, tnear, hit.t, G, T);
+        } else {
+          T = G;  // a postponed triangle group (or nothing)
+          G = make_uint2(0u, 0u);
+        }
+        bool done = false;
+        while (T.y) {
+          if ((G.y & 0xFF000000u) && __popc(__activemask()) < sc.dyn_tri_lanes) {
+            if (sp < kStack8) { stack[sp++] = T; T.y = 0u; break; }
+          }
+          const uint32_t j = uint32_t(__ffs(int(T.y)) - 1);
+          T.y &= T.y - 1u;
+          const uint32_t tri = T.x + j;
+          if (intersect_triangle(sc, tri, O, D, tnear, hit.t, hit.u, hit.v, ray_mask)) {
+            hit.tri = tri;
+            if (kAnyHit) { done = true; break; }
+          }
+        }
+        if (!done && !(G.y & 0xFF000000u)) {
+          if (sp == 0) done = true;
+          else G = stack[--sp];
+        }
+        if (done) {
+          io.store(tag, hit);
+          has_ray = false;
+          T.y = 0u; G.y = 0u; sp = 0;
+          break;
+        }
+        if (!exhausted && __popc(__activemask()) < sc.dyn_fetch_lanes) break;
+      }
+    }
+  }
+}
+
 template <bool kAnyHit>
 __device__ __forceinline__ Hit trace_any_bvh(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar, uint32_t ray_mask) {
 #ifdef B2PT_EXPERIMENTS

@@ -20,7 +20,9 @@
 // consumes random numbers in an order the reference leaves to std::sort; here every merge owns a sub-stream keyed by
 // (path stream, eye vertex, photon), so UPG agrees with the reference in distribution, not per path.
 //
-// Restriction, stated: merging from the light side only (Options::from_light = true, the default).
+// Both merge directions of the reference are built: from the light side (Options::from_light = true, the default:
+// the photon's predecessor is connected to the tentative eye vertex) and from the camera side (--from-camera: the
+// eye vertex BEFORE the tentative one is connected to the photon itself; UPG.cpp:687-719).
 #include "grid.cuh"
 #include "render_common.cuh"
 
@@ -48,7 +50,7 @@ struct VcmParams {
   float beta, roulette, roulette_inv;
   float radius, circle, clamp_const;
   float num_scattered, num_scattered_inv;
-  uint32_t unbiased, enable_vc, enable_vm;
+  uint32_t unbiased, enable_vc, enable_vm, from_light;
   uint32_t num_photons, max_subpath;
   uint32_t brute_vertices;  // diagnostic (B2PT_VCM_BRUTE=1): gather scans every stored vertex instead of the grid
 };
@@ -76,7 +78,7 @@ struct VcmPool {
   uint32_t* p_state; uint2* p_rng; float4* p_cv; float4* p_bs_omega; float4* p_bs_thr; float4* p_ray_o; float4* p_hit;
   uint32_t* lp_head; uint32_t* lp_count;
   // eye phase, per pixel slot
-  uint32_t* state; uint2* rng; float4* cv; float4* bs_omega; float4* bs_thr; float4* ray_o; float4* hit; float4* rad; float4* nee;
+  uint32_t* state; uint2* rng; float4* cv; float4* pv; float4* bs_omega; float4* bs_thr; float4* ray_o; float4* hit; float4* rad; float4* nee;
   double* splat;
   // vertex pool
   float4* lv; uint32_t* lv_link; float4* grid_points;
@@ -184,11 +186,17 @@ __device__ __forceinline__ float vc_subweight_inv(const Connection& c, const Vcm
   return Ap + Cp + 1.0f;
 }
 
-// the Bp + Dp part shared by _vm_subweight_inv and _vm_biased_subweight_inv (from_light branch, UPG.cpp:308-377)
+// the Bp + Dp part shared by _vm_subweight_inv and _vm_biased_subweight_inv (UPG.cpp:308-377)
 __device__ __forceinline__ float vm_bd(const Connection& c, const VcmParams& P) {
   const float b = P.beta;
-  const float light_vm = clamp_vm(P, beta_fn(P.circle / c.light.w0, b));
-  const float eye_vm = clamp_vm(P, beta_fn(P.circle * c.eye.bgeo * c.eb.density, b)) * (c.eye.length() <= 1.0f ? 0.0f : 1.0f);
+  float light_vm, eye_vm;
+  if (P.from_light) {
+    light_vm = clamp_vm(P, beta_fn(P.circle / c.light.w0, b));
+    eye_vm = clamp_vm(P, beta_fn(P.circle * c.eye.bgeo * c.eb.density, b)) * (c.eye.length() <= 1.0f ? 0.0f : 1.0f);
+  } else {
+    light_vm = clamp_vm(P, beta_fn(P.circle * c.light.bgeo * c.lb.density_rev, b)) * (c.light.length() <= 1.0f ? 0.0f : 1.0f);
+    eye_vm = clamp_vm(P, beta_fn(P.circle / c.eye.w0, b));
+  }
   const float Bp = (c.light.w2 * beta_fn(c.lb.density_rev, b) + float(c.lb.finite) * light_vm * beta_fn(c.light.w0, b) * (c.light.length() <= 1.0f ? 0.0f : 1.0f)) *
                    beta_fn(c.edge.b_geometry * c.eb.density_rev, b);
   const float Dp = (c.eye.w2 * beta_fn(c.eb.density, b) + float(c.eb.finite) * eye_vm * beta_fn(c.eye.w0, b) * (c.eye.length() <= 1.0f ? 0.0f : 1.0f)) *
@@ -196,7 +204,8 @@ __device__ __forceinline__ float vm_bd(const Connection& c, const VcmParams& P) 
   return Bp + Dp;
 }
 __device__ __forceinline__ float vm_subweight_inv(const Connection& c, const VcmParams& P) {
-  const float connect_vm = clamp_vm(P, beta_fn(P.circle * c.edge.f_geometry * c.lb.density, P.beta)) * (c.eye.length() * c.light.length() == 0.0f ? 0.0f : 1.0f);
+  const float area_density = P.from_light ? c.edge.f_geometry * c.lb.density : c.edge.b_geometry * c.eb.density_rev;
+  const float connect_vm = clamp_vm(P, beta_fn(P.circle * area_density, P.beta)) * (c.eye.length() * c.light.length() == 0.0f ? 0.0f : 1.0f);
   return beta_fn(P.num_scattered, P.beta) * (vm_bd(c, P) + connect_vm);
 }
 __device__ __forceinline__ float vm_biased_subweight_inv(const Connection& c, const VcmParams& P, float connect_vm) {
@@ -315,7 +324,8 @@ __global__ void __launch_bounds__(256) vcm_photon_kernel(RenderConfig cfg, VcmPa
             nv.set(bs.finite, 0u, len);
             nv.w0 = 1.0f / (edge.f_geometry * bs.density);
             nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + float(cur.finite()) * beta_fn(cur.w0, beta)) * beta_fn(edge.b_geometry * nv.w0, beta);
-            const float vertex_merging = clamp_vm(P, beta_fn(P.circle / cur.w0, beta));  // from_light
+            const float vertex_merging = P.from_light ? clamp_vm(P, beta_fn(P.circle / cur.w0, beta))
+                                                      : clamp_vm(P, beta_fn(P.circle * cur.bgeo * bs.density_rev, beta)) * (cur.length() <= 1.0f ? 0.0f : 1.0f);
             nv.w2 = (cur.w2 * beta_fn(bs.density_rev, beta) + float(bs.finite) * vertex_merging * (cur.length() <= 1.0f ? 0.0f : 1.0f) * beta_fn(cur.w0, beta)) *
                     beta_fn(edge.b_geometry * nv.w0, beta);
             pool.lv[size_t(head) * kVertexFloat4s + 1].w = __uint_as_float(cur.flags);  // prv->finite, updated in place
@@ -478,7 +488,8 @@ __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParam
             nv.w0 = 1.0f / (edge.f_geometry * bs.density);
             nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + float(cur.finite()) * beta_fn(cur.w0, beta)) * beta_fn(edge.b_geometry * nv.w0, beta);
             const float trim = cur.length() <= 1.0f ? 0.0f : 1.0f;
-            const float vertex_merging = clamp_vm(P, beta_fn(P.circle * cur.bgeo * bs.density_rev, beta)) * trim;  // from_light
+            const float vertex_merging = P.from_light ? clamp_vm(P, beta_fn(P.circle * cur.bgeo * bs.density_rev, beta)) * trim
+                                                      : clamp_vm(P, beta_fn(P.circle / cur.w0, beta));
             const float dterm = cur.w2 * beta_fn(bs.density_rev, beta) + float(cur.finite()) * vertex_merging * trim * beta_fn(cur.w0, beta);
             nv.w2 = dterm * beta_fn(edge.b_geometry * nv.w0, beta);
             if (nv.s.is_light()) {
@@ -497,9 +508,12 @@ __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParam
               want_trace = true;
             } else {
               nv.thr = nv.thr * P.roulette_inv;
+              // _gather / _gather_biased(context, *prv, *itr), UPG.cpp:148-156; from the camera side the merge is evaluated at
+              // *prv (with prv->finite already updated) and a camera prv never merges (UPG.cpp:690,716)
+              want_gather = P.enable_vm != 0u && (P.from_light || !cur.s.is_camera());
+              if (!P.from_light && want_gather) store_slot_vertex(pool.pv, pool.pixels_pad, slot, cur);
               cur = nv; bs = nbs;
               store_cur = true;
-              want_gather = P.enable_vm != 0u;  // _gather / _gather_biased(context, *prv, *itr), UPG.cpp:148-156
               if (P.roulette < rng.sample()) {  // UPG.cpp:160-162
                 finished = true;
               } else {
@@ -515,7 +529,8 @@ __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParam
                       const float3 n = ls.surface.normal();
                       const BsdfQuery cb = bsdf_query(sc, cur.s, -n, cur.omega);
                       const float trim1 = cur.length() <= 1.0f ? 0.0f : 1.0f;
-                      const float eye_vm = clamp_vm(P, beta_fn(P.circle * cur.bgeo * cb.density, beta)) * trim1;  // from_light
+                      const float eye_vm = P.from_light ? clamp_vm(P, beta_fn(P.circle * cur.bgeo * cb.density, beta)) * trim1
+                                                        : clamp_vm(P, beta_fn(P.circle / cur.w0, beta));
                       const float cosine = fabsf(dot(n, cur.s.normal()));
                       const float KD = cur.w2 * beta_fn(cb.density, beta) + float(cb.finite) * eye_vm * beta_fn(cur.w0, beta) * trim1;
                       const float KC = cur.w1 * beta_fn(cb.density, beta) + beta_fn(cur.w0, beta) * float(cur.finite());
@@ -763,6 +778,24 @@ __device__ __forceinline__ float3 merge_light(const DeviceScene& sc, Rng& rng, c
   return unoccluded * density * weight;
 }
 
+// _merge_eye (UPG.cpp:755-781), unbiased mode, merging from the camera side: the density is estimated from the eye vertex
+__device__ __forceinline__ float3 merge_eye(const DeviceScene& sc, Rng& rng, const Vertex& light, const Vertex& eye, const VcmParams& P,
+                                            unsigned long long& shadow_rays, unsigned long long& density_rays) {
+  const float3 omega = normalize(eye.s.pos - light.s.pos);
+  const Connection c(sc, light, eye, omega);
+  const float3 unoccluded = c.unoccluded();
+  if (!(l1norm(unoccluded) >= kFltEpsilon)) return f3(0.0f);
+  const float3 direction = normalize(light.s.pos - eye.s.pos);
+  const float3 a = eye.s.pos + (dot(eye.s.gnormal, direction) > 0.0f ? 1.0f : -1.0f) * eye.s.gnormal * 0.0001f;
+  const float3 b = light.s.pos + (dot(light.s.gnormal, direction) < 0.0f ? 1.0f : -1.0f) * light.s.gnormal * 0.0001f;
+  ++shadow_rays;
+  if (trace_ray<true, true>(sc, a, b - a, 0.0f, 1.0f).tri != kInvalid) return f3(0.0f);
+  // _weight_vm_eye (UPG.cpp:412-418)
+  const float weight = beta_fn(P.num_scattered * clamp_vm(P, P.circle * c.edge.b_geometry * c.eb.density_rev), P.beta) * vc_weight(c, P);
+  const float density = gathering_density(sc, rng, eye.s, light.s.pos, P.radius, eye.omega, density_rays);
+  return unoccluded * density * weight;
+}
+
 // _gather / _gather_biased (UPG.cpp:675-724): one thread per new eye vertex
 __global__ void __launch_bounds__(128) vcm_gather_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, DeviceGrid grid, VcmCounters* cnt, int parity) {
   const DeviceScene& sc = cfg.scene;
@@ -773,7 +806,21 @@ __global__ void __launch_bounds__(128) vcm_gather_kernel(RenderConfig cfg, VcmPa
     const Vertex eye = load_slot_vertex(pool.cv, pool.pixels_pad, slot);  // the tentative vertex, throughput already * 1 / roulette
     const uint32_t path_key = pool.rng[slot].x;
     float3 sum = f3(0.0f);
+    Vertex prev_eye;
+    if (!P.from_light) prev_eye = load_slot_vertex(pool.pv, pool.pixels_pad, slot);
     auto merge = [&](uint32_t index, float3) {
+      if (!P.from_light) {  // UPG.cpp:690-692, 716-718: the photon itself against the eye vertex before the tentative one
+        const Vertex light = load_pool_vertex(pool, index);
+        float3 v;
+        if (P.unbiased) {
+          Rng sub; sub.key = mix32(path_key ^ mix32(index * 0x9E3779B9u + uint32_t(eye.length()))); sub.ctr = 0;
+          v = merge_eye(sc, sub, light, prev_eye, P, shadow_rays, density_rays);
+        } else {
+          v = merge_biased(sc, light, light, prev_eye, P);
+        }
+        sum += v * P.num_scattered_inv;
+        return;
+      }
       const uint32_t prev = pool.lv_link[index];
       if (prev == kInvalid) return;
       const Vertex light = load_pool_vertex(pool, prev);
@@ -887,6 +934,7 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWor
   if ((rc = ws_alloc(w, &p.state, ne))) return rc;
   if ((rc = ws_alloc(w, &p.rng, ne))) return rc;
   if ((rc = ws_alloc(w, &p.cv, ne * kVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.pv, ne * kVertexFloat4s))) return rc;
   if ((rc = ws_alloc(w, &p.bs_omega, ne))) return rc;
   if ((rc = ws_alloc(w, &p.bs_thr, ne))) return rc;
   if ((rc = ws_alloc(w, &p.ray_o, ne))) return rc;
@@ -915,7 +963,6 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWor
 
 int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
   const B2ptRenderParams& rp = base.params;
-  B2_CHECK(rp.from_light != 0, B2PT_ERR_INVALID, "VCM/UPG: only merging from the light side (from_light = 1) is built");
   B2_CHECK(rp.radius > 0.0f, B2PT_ERR_INVALID, "VCM/UPG: radius must be positive");
   const uint32_t pixels = base.pixels;
   const uint32_t photons = rp.num_photons ? rp.num_photons : pixels;  // Options.cpp:914-916
@@ -936,7 +983,7 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     const uint32_t sample = rp.first_sample + pass * stride;
     VcmParams P;
     P.beta = rp.beta; P.roulette = rp.roulette; P.roulette_inv = 1.0f / rp.roulette;
-    P.unbiased = rp.technique == B2PT_TECHNIQUE_UPG; P.enable_vc = rp.enable_vc != 0; P.enable_vm = rp.enable_vm != 0;
+    P.unbiased = rp.technique == B2PT_TECHNIQUE_UPG; P.enable_vc = rp.enable_vc != 0; P.enable_vm = rp.enable_vm != 0; P.from_light = rp.from_light != 0;
     P.radius = rp.radius;
     // UPGBase::_preprocess (UPG.cpp:180-183), double arithmetic like the reference; num_samples = the pass index
     if (!P.unbiased) P.radius = float(rp.radius * pow(double(sample) + 1.0f, double(rp.alpha * 0.5f - 0.5f)));

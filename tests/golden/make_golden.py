@@ -174,10 +174,18 @@ def main():
         ("TestCase33", "VCM", 32, 32, 2, dict(beta=2, radius=0.05)),
         ("CornellBoxDiffuse", "UPG", 32, 32, 16, dict(beta=2, radius=0.1, per_path=0)),
         ("TestCaseFurnace", "UPG", 24, 24, 16, dict(beta=2, radius=0.1, per_path=0)),
+        # merging from the camera side (--from-camera, Options.cpp:59): files are tagged VCMc / UPGc
+        ("CornellBoxDiffuse", "VCM", 32, 32, 3, dict(beta=2, radius=0.1, from_light=0)),
+        ("CornellBoxSpecular", "VCM", 32, 32, 2, dict(beta=2, radius=0.1, from_light=0)),
+        ("MetalRings", "VCM", 32, 32, 2, dict(beta=2, radius=0.05, from_light=0)),
+        ("TestCase18", "VCM", 32, 32, 2, dict(beta=2, radius=0.1, from_light=0)),
+        ("CornellBoxDiffuse", "UPG", 32, 32, 16, dict(beta=2, radius=0.1, per_path=0, from_light=0)),
+        ("TestCaseFurnace", "UPG", 24, 24, 16, dict(beta=2, radius=0.1, per_path=0, from_light=0)),
     ]
+    tag = lambda r: r[1] + ("c" if r[5].get("from_light", 1) == 0 else "")
     only = [a for a in sys.argv[1:] if not a.startswith("-")]
     if only:
-        renders = [r for r in renders if r[1] in only or r[0] in only]
+        renders = [r for r in renders if tag(r) in only or r[0] in only]
     for name in SUN_SCENES:
         dst = os.path.join(HERE, "scenes", name + ".b2s")
         if not os.path.exists(dst):
@@ -185,8 +193,8 @@ def main():
     for name, tech, w, h, spp, kw in renders:
         scene = os.path.join(HERE, "scenes", name + ".b2s")
         out = ref_render(scene, tech, w, h, spp, seed=1234, **kw)
-        extra = {k: v for k, v in kw.items() if k in ("radius", "beta")}
-        np.savez_compressed(os.path.join(HERE, "render_%s_%s.npz" % (name, tech)), width=w, height=h, seed=1234, spp=spp, **extra, **out)
+        extra = {k: v for k, v in kw.items() if k in ("radius", "beta", "from_light")}
+        np.savez_compressed(os.path.join(HERE, "render_%s_%s.npz" % (name, tag((name, tech, w, h, spp, kw)))), width=w, height=h, seed=1234, spp=spp, **extra, **out)
         print(name, tech, out["info"])
 
 

@@ -16,13 +16,18 @@ from test_pt_gpu import gpu_render, image_rel_rmse, path_agreement
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("name", ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace", "TestCase18", "TestCase33"])
-def test_vcm_per_path_radiance_and_light_image(name, device_scenes, flat_scenes):
-    g = np.load(golden_path("render_%s_VCM.npz" % name))
+VCM_CASES = [(n, "VCM") for n in ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCaseFurnace", "TestCase18", "TestCase33"]] + [
+    # merging from the camera side (--from-camera, UPG.cpp:690-692,716-718): goldens tagged VCMc
+    (n, "VCMc") for n in ["CornellBoxDiffuse", "CornellBoxSpecular", "MetalRings", "TestCase18"]]
+
+
+@pytest.mark.parametrize("name,tag", VCM_CASES)
+def test_vcm_per_path_radiance_and_light_image(name, tag, device_scenes, flat_scenes):
+    g = np.load(golden_path("render_%s_%s.npz" % (name, tag)))
     w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
     info = json.loads(str(g["info"]))
     accum, paths, stats = gpu_render(device_scenes(name), flat_scenes(name), "VCM", w, h, spp, int(g["seed"]), beta=2.0,
-                                     radius=float(g["radius"]))
+                                     radius=float(g["radius"]), from_light=not tag.endswith("c"))
     frac, err = path_agreement(paths, g["paths"])
     light_ours = accum[:, :3] - paths.astype(np.float64).sum(axis=0)
     light_ref = g["light"]
@@ -40,12 +45,13 @@ def test_vcm_per_path_radiance_and_light_image(name, device_scenes, flat_scenes)
     assert image_rel_rmse(accum, g["accum"]) <= 5e-2
 
 
-@pytest.mark.parametrize("name,tol", [("CornellBoxDiffuse", 0.08), ("TestCaseFurnace", 0.06)])
-def test_upg_image_mean_matches_reference(name, tol, device_scenes, flat_scenes):
-    g = np.load(golden_path("render_%s_UPG.npz" % name))
+@pytest.mark.parametrize("name,tol,tag", [("CornellBoxDiffuse", 0.08, "UPG"), ("TestCaseFurnace", 0.06, "UPG"),
+                                          ("CornellBoxDiffuse", 0.08, "UPGc"), ("TestCaseFurnace", 0.06, "UPGc")])
+def test_upg_image_mean_matches_reference(name, tol, tag, device_scenes, flat_scenes):
+    g = np.load(golden_path("render_%s_%s.npz" % (name, tag)))
     w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
     accum, _, stats = gpu_render(device_scenes(name), flat_scenes(name), "UPG", w, h, spp, int(g["seed"]), per_path=False, beta=2.0,
-                                 radius=float(g["radius"]))
+                                 radius=float(g["radius"]), from_light=not tag.endswith("c"))
     mean_ref, mean_ours = g["accum"][:, :3].mean(axis=0) / spp, accum[:, :3].mean(axis=0) / spp
     print(json.dumps(dict(scene=name, mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist(),
                           rays=[stats["num_basic_rays"], stats["num_shadow_rays"]])))
@@ -57,8 +63,6 @@ def test_upg_image_mean_matches_reference(name, tol, device_scenes, flat_scenes)
 
 def test_vcm_rejects_what_is_not_built(device_scenes, flat_scenes):
     from master_b200 import api
-    with pytest.raises(api.B2ptError):
-        gpu_render(device_scenes("CornellBoxDiffuse"), flat_scenes("CornellBoxDiffuse"), "VCM", 16, 16, 1, 1, from_light=False)
     with pytest.raises(api.B2ptError):  # fewer light paths than pixels: the reference would read past _light_offsets
         gpu_render(device_scenes("CornellBoxDiffuse"), flat_scenes("CornellBoxDiffuse"), "VCM", 16, 16, 1, 1, num_photons=100)
 
