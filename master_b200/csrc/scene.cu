@@ -470,7 +470,7 @@ __global__ void collapse8_kernel(uint32_t count, const CollapseItem* items, cons
       const uint32_t w = child_base + rank++;
       const uint32_t qi = atomicAdd(next_count, 1u);
       next_items[qi] = CollapseItem{w, ref[k]};
-      meta[sl] = 0x20u;  // not read by the traversal (imask decides); kept non-zero for debugging dumps
+      meta[sl] = 0x20u | (24u + uint32_t(sl));  // one hit bit at position 24 + slot (the traversal XORs the ray octant into the slot)
     } else {
       const uint32_t first = single_leaf_count ? 0u : ((ref[k] & 0x80000000u) ? (ref[k] & 0x7FFFFFFFu) : bin[ref[k]].first);
       meta[sl] = (((1u << cnt[k]) - 1u) << 5) | offset;

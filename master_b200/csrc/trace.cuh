@@ -173,25 +173,30 @@ __device__ __forceinline__ void node8_step(const DeviceScene& sc, uint32_t child
     const bool neg = idir.y < 0.0f; ny[0] = neg ? h0 : l0; ny[1] = neg ? h1 : l1; fy[0] = neg ? l0 : h0; fy[1] = neg ? l1 : h1; }
   { const uint32_t l0 = __float_as_uint(n3.x), l1 = __float_as_uint(n3.y), h0 = __float_as_uint(n4.z), h1 = __float_as_uint(n4.w);
     const bool neg = idir.z < 0.0f; nz[0] = neg ? h0 : l0; nz[1] = neg ? h1 : l1; fz[0] = neg ? l0 : h0; fz[1] = neg ? l1 : h1; }
-  const uint32_t meta[2] = {__float_as_uint(n1.z), __float_as_uint(n1.w)};
-  uint32_t ghits = 0u, tmask = 0u;
+  // meta byte of a child = bits << 5 | position: an inner child contributes ONE bit at 24 + (slot ^ octant) (stored position 24 + slot),
+  // a leaf its unary triangle count at its offset from tri_base; both become `hits |= bits << position`, no branch per child
+  uint32_t bits4[2], pos4[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const uint32_t m4 = __float_as_uint(h ? n1.w : n1.z);
+    const uint32_t inner4 = (m4 & (m4 << 1) & 0x10101010u) >> 4;  // 0x01 in the bytes of inner children (position >= 24: bits 3 and 4 set)
+    pos4[h] = (m4 ^ (inner4 * oct)) & 0x1F1F1F1Fu;
+    bits4[h] = (m4 >> 5) & 0x07070707u;
+  }
+  uint32_t hits = 0u;
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const uint32_t i = uint32_t(h * 4 + k);
       const float x0 = __fmaf_rn(byte_to_float(nx[h], k), adx, ox), x1 = __fmaf_rn(byte_to_float(fx[h], k), adx, ox);
       const float y0 = __fmaf_rn(byte_to_float(ny[h], k), ady, oy), y1 = __fmaf_rn(byte_to_float(fy[h], k), ady, oy);
       const float z0 = __fmaf_rn(byte_to_float(nz[h], k), adz, oz), z1 = __fmaf_rn(byte_to_float(fz[h], k), adz, oz);
       const float t0 = fmaxf(fmaxf(x0, y0), fmaxf(z0, tnear));
       const float t1 = fminf(fminf(x1, y1), fminf(z1, hit.t)) * 1.0000003f;
-      if (t0 <= t1) {
-        const uint32_t m = (meta[h] >> (8 * k)) & 0xFFu;
-        if ((imask >> i) & 1u) ghits |= 1u << (24u + (i ^ oct));
-        else tmask |= (m >> 5) << (m & 31u);
-      }
+      if (t0 <= t1) hits |= ((bits4[h] >> (8 * k)) & 0xFFu) << ((pos4[h] >> (8 * k)) & 0xFFu);
     }
   }
+  const uint32_t ghits = hits & 0xFF000000u, tmask = hits & 0x00FFFFFFu;
   G = make_uint2(__float_as_uint(n1.x), ghits | imask);
   T = make_uint2(__float_as_uint(n1.y), tmask);
 }

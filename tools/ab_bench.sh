@@ -6,7 +6,7 @@ for spec in "$@"; do
   label=${spec%%:*}; envs=${spec#*:}
   (
     IFS=','; for kv in $envs; do [ -n "$kv" ] && export "$kv"; done
-    timeout 600 python bench.py --steps ${AB_STEPS:-6} --warmup 3 --no-cpu-baseline ${AB_ARGS} > gpurun_out/ab_${label}.json 2> gpurun_out/ab_${label}.err
+    timeout 600 python bench.py --steps ${AB_STEPS:-6} --warmup 3 --no-cpu-baseline $AB_ARGS > gpurun_out/ab_${label}.json 2> gpurun_out/ab_${label}.err
   )
   python - "$label" <<'PY'
 import json, sys
