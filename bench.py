@@ -10,7 +10,7 @@ models/CrytekSponza.blend is stripped from the reference mount, so the large-mes
 the way loader.cpp:434-456 adds lights; tests/golden/make_large_scene.py), camera 0, 1024 x 1024 (the thesis
 resolution, GenerateResults.psm1:22), roulette 0.9, beta 2 (BPT) / 1 (PT).
 
-A STEP is `--spp` passes (default 4) of one sample per pixel over the whole window, i.e. one
+A STEP is `--spp` passes (default 16) of one sample per pixel over the whole window, i.e. one
 Technique::render call per pass in the reference's terms.  Scaling is weak: every rank renders `--spp`
 passes per step of ITS OWN sample indices (rank g of N takes samples g, g+N, ...) over a replicated scene;
 after the K timed steps the float64 accumulators are summed with ONE all-reduce over NCCL, inside the timed
@@ -128,7 +128,7 @@ def main():
     ap.add_argument("--technique", default=os.environ.get("B2PT_BENCH_TECHNIQUE", "BPT"), choices=["PT", "BPT", "VCM", "UPG"])
     ap.add_argument("--width", type=int, default=1024)
     ap.add_argument("--height", type=int, default=1024)
-    ap.add_argument("--spp", type=int, default=4, help="passes (samples per pixel) per step")
+    ap.add_argument("--spp", type=int, default=16, help="passes (samples per pixel) per step")
     ap.add_argument("--radius", type=float, default=None, help="VCM / UPG merge radius (thesis values: UPG 0.01, VCM 0.025)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")

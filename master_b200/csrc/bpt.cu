@@ -44,6 +44,10 @@ constexpr uint32_t kPairCamera = 0x80000000u;  // descriptor.x bit 31: the eye v
 constexpr uint32_t kNeeVertex = 0xFFFFFFFFu;   // descriptor.y: the freshly sampled emitter point instead of a stored vertex
 constexpr uint32_t kShadowSplat = 1u;
 constexpr int kVertexFloat4s = 7;
+// Expanding a path's connections into pair descriptors by walking its vertex chain is a string of dependent loads
+// (one L2 / HBM round trip per vertex); the first kLpTable vertex indices are therefore also kept by position, so the
+// expansion reads them independently.  Longer paths (3 % at roulette 0.9) walk the chain for the rest.
+constexpr uint32_t kLpTable = 32;
 
 struct BptCounters {
   unsigned long long basic_rays, shadow_rays, numeric_errors, capacity_events;
@@ -81,7 +85,8 @@ struct BptPool {
   uint32_t* lp_count;
   float4* lv;        // light vertex pool, AoS: 7 float4 per vertex
   uint32_t* lv_link; // previous vertex of the same path
-  uint32_t* trace_q;
+  uint32_t* lp_idx;  // the first kLpTable vertices of every light path by position, SoA: lp_idx[k * size + slot]
+  uint32_t* trace_q[2];  // live slots = the slots with an extension ray in flight; written by the logic stage of iteration i into [i & 1]
   uint2* pair_q;
   float4* shadow_q;  // 3 float4 per entry
   float4* dir_q;     // connections to sun lights, 4 float4 per entry (render_common.cuh: directional_kernel)
@@ -211,10 +216,15 @@ __device__ __forceinline__ unsigned warp_reserve(unsigned* counter, unsigned n) 
   return base + incl - n;
 }
 
-__global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0) {
+// The stage runs over the LIVE paths only: after every iteration a path is either done or waiting for the hit of its
+// extension ray, so the trace queue the previous iteration wrote is exactly the list of live slots (`first` = iteration 0
+// of a batch walks every slot instead).  A pool-order loop would leave a warp with as many busy lanes as the pool has
+// live paths — 4 of 32 halfway through a batch (ncu, profiles/).
+__global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
+                                                                               int first) {
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    cnt->trace_count[parity ^ 1] = 0;
+    // trace_count[parity ^ 1] is this launch's input; the closest-hit stage clears it afterwards
     cnt->pair_count[parity ^ 1] = 0;
     cnt->shadow_count[parity ^ 1] = 0;
     cnt->ticket[0] = 0; cnt->ticket[1] = 0;
@@ -224,9 +234,15 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
   const float roulette = cfg.params.roulette;
   const float roulette_inv = 1.0f / roulette;
   const uint32_t max_subpath = cfg.params.max_subpath ? cfg.params.max_subpath : 1024u;
-  // pool.size is a multiple of the block size: all lanes of a warp run the same trip count (warp_* helpers below)
-  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < pool.size; slot += gridDim.x * blockDim.x) {
-    const uint32_t st0 = pool.state[slot];
+  // trip counts are rounded up to whole warps: every lane of a warp reaches the warp_* helpers below
+  const uint32_t n_live = first ? pool.size : cnt->trace_count[parity ^ 1];
+  const uint32_t n_round = (n_live + 31u) & ~31u;
+  const uint32_t* live_q = pool.trace_q[parity ^ 1];
+  uint32_t* next_q = pool.trace_q[parity];
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+    const bool lane_on = i < n_live;
+    const uint32_t slot = lane_on ? (first ? i : live_q[i]) : 0u;
+    const uint32_t st0 = lane_on ? pool.state[slot] : uint32_t(kDone);
     uint32_t st = st0;
     bool want_trace = false, finished = false;
     uint32_t emit_n = 0, emit_flags = 0;  // pair descriptors to write after the branches
@@ -268,6 +284,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
           } else {
             store_pool_vertex(pool, idx, cur);
             pool.lv_link[idx] = kInvalid;
+            pool.lp_idx[slot] = idx;
             head = idx; count = 1;
             cur_dirty = true;
             st = kLightLoop;
@@ -323,6 +340,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
               } else {
                 store_pool_vertex(pool, idx, nv);
                 pool.lv_link[idx] = head;
+                if (count < kLpTable) pool.lp_idx[size_t(count) * pool.size + slot] = idx;
                 head = idx; ++count;
                 cur = nv; cur_dirty = true;
                 st = kLightLoop;
@@ -469,17 +487,27 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
       if (mask && (threadIdx.x & 31u) == 0) atomicAdd(&cnt->done, unsigned(__popc(mask)));
     }
     const unsigned tq = warp_append(&cnt->trace_count[parity], want_trace);
-    if (want_trace) pool.trace_q[tq] = slot;
+    if (want_trace) next_q[tq] = slot;
     unsigned pq = warp_reserve(&cnt->pair_count[parity], emit_n);
     if (emit_n) {
       if (pq + emit_n > pool.q_capacity) {
         atomicAdd(&cnt->capacity_events, 1ull);
       } else {
         if (emit_nee) pool.pair_q[pq++] = make_uint2(slot, kNeeVertex);
-        for (uint32_t v = head; v != kInvalid;) {
-          const uint32_t prev = pool.lv_link[v];
-          if (!(emit_skip_first && prev == kInvalid)) pool.pair_q[pq++] = make_uint2(slot | emit_flags, v);
-          v = prev;
+        // vertices kLpTable .. count-1 hang off the head of the chain; the rest come from the position table, four loads in flight
+        uint32_t v = head;
+        for (uint32_t k = count; k > kLpTable; --k) {
+          pool.pair_q[pq++] = make_uint2(slot | emit_flags, v);
+          v = pool.lv_link[v];
+        }
+        const uint32_t kt = count < kLpTable ? count : kLpTable;
+        for (uint32_t k = emit_skip_first ? 1u : 0u; k < kt; k += 4u) {
+          uint32_t a[4];
+#pragma unroll
+          for (uint32_t j = 0; j < 4u; ++j) a[j] = k + j < kt ? pool.lp_idx[size_t(k + j) * pool.size + slot] : 0u;
+#pragma unroll
+          for (uint32_t j = 0; j < 4u; ++j)
+            if (k + j < kt) pool.pair_q[pq++] = make_uint2(slot | emit_flags, a[j]);
         }
       }
     }
@@ -567,8 +595,9 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel
 // ray sources / hit sinks of the two traversal stages (trace.cuh: trace_stream8)
 struct BptTraceIo {
   const BptPool* pool;
+  const uint32_t* q;
   __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
-    const uint32_t slot = pool->trace_q[i];
+    const uint32_t slot = q[i];
     const float4 o = pool->ray_o[slot], d = pool->bs_omega[slot];
     O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY;
     mask = (__float_as_uint(o.w) & 2u) ? kMaskMesh : kMaskAll;  // Scene::intersectMesh (light subpaths) / Scene::intersect
@@ -605,8 +634,11 @@ struct BptShadowIo {
 template <int kStream>
 __global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
   const uint32_t n = cnt->trace_count[parity];
-  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->basic_rays, (unsigned long long)n);
-  BptTraceIo io{&pool};
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+    cnt->trace_count[parity ^ 1] = 0;  // consumed by this iteration's logic stage; the next one appends to it
+  }
+  BptTraceIo io{&pool, pool.trace_q[parity]};
   if (kStream == 2) { trace_dyn8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   if (kStream == 1) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -735,7 +767,9 @@ int bpt_workspace(b2pt_scene_s* scene, uint32_t size, int lanes, BptWorkspace** 
     if ((rc = ws_alloc(w, &p.lp_count, size))) return rc;
     if ((rc = ws_alloc(w, &p.lv, size_t(p.lv_capacity) * kVertexFloat4s))) return rc;
     if ((rc = ws_alloc(w, &p.lv_link, p.lv_capacity))) return rc;
-    if ((rc = ws_alloc(w, &p.trace_q, size))) return rc;
+    if ((rc = ws_alloc(w, &p.lp_idx, size_t(size) * kLpTable))) return rc;
+    if ((rc = ws_alloc(w, &p.trace_q[0], size))) return rc;
+    if ((rc = ws_alloc(w, &p.trace_q[1], size))) return rc;
     if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
     if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
     if ((rc = ws_alloc(w, &p.dir_q, size_t(size) * 4))) return rc;
@@ -755,9 +789,11 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   const int block = 256;
   const uint32_t pixels = base.pixels;
   const uint32_t num_passes = base.params.num_samples;
-  // a batch is a whole number of passes, at most 2^21 paths (B2PT_BPT_BATCH_LOG2 overrides the exponent) (or one pass if the window is larger); with more than one
-  // pass to render the passes are spread over bpt_lanes() concurrent batches
-  uint32_t batch_paths = 1u << 21;
+  // a batch is a whole number of passes, at most 2^23 paths (B2PT_BPT_BATCH_LOG2 overrides the exponent; one pass if the window is larger):
+  // measured on the LivingRoom stand-in, 16 passes of 1024 x 1024 run at 46 / 53 / 60 Msamples/s with 2^21 / 2^22 / 2^23 paths per batch
+  // (the late iterations of a batch have few live paths; the more paths a batch starts with, the longer its launches stay large).
+  // With more than one pass to render the passes are spread over bpt_lanes() concurrent batches.
+  uint32_t batch_paths = 1u << 23;
   { const char* e = getenv("B2PT_BPT_BATCH_LOG2"); if (e) { int v = atoi(e); if (v >= 10 && v <= 26) batch_paths = 1u << v; } }
   uint32_t passes_per_batch = batch_paths / pixels;
   if (passes_per_batch < 1) passes_per_batch = 1;
@@ -819,7 +855,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       StageTimer& timer = *timers[k];
       for (int j = 0; j < kBatchIters; ++j, ++g.it) {
         const int parity = g.it & 1;
-        timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0); timer.end();
+        timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0); timer.end();
         timer.begin(kStageShade); bpt_connect_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);

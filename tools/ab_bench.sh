@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 for spec in "$@"; do
   label=${spec%%:*}; envs=${spec#*:}
   (
-    IFS=','; for kv in $envs; do [ -n "$kv" ] && export "$kv"; done
+    IFS=','; for kv in $envs; do [ -n "$kv" ] && export "$kv"; done; unset IFS
     timeout 600 python bench.py --steps ${AB_STEPS:-6} --warmup 3 --no-cpu-baseline $AB_ARGS > gpurun_out/ab_${label}.json 2> gpurun_out/ab_${label}.err
   )
   python - "$label" <<'PY'
