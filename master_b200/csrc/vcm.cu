@@ -83,7 +83,8 @@ struct VcmPool {
   // vertex pool
   float4* lv; uint32_t* lv_link; float4* grid_points;
   // queues
-  uint32_t* trace_q; uint2* pair_q; float4* shadow_q; uint32_t* gather_q;
+  uint32_t* trace_q[2];  // live slots (extension ray in flight), written by iteration i into [i & 1]: the next logic stage walks it
+  uint2* pair_q; float4* shadow_q; uint32_t* gather_q;
   float4* dir_q;  // connections to sun lights, 4 float4 per entry (render_common.cuh: directional_kernel)
 };
 
@@ -257,12 +258,18 @@ __device__ __forceinline__ unsigned warp_reserve(unsigned* counter, unsigned n) 
 // ---------------------------------------------------------------- photon phase: UPGBase::_traceLight (UPG.cpp:208-292)
 // One slot per photon path; stream (seed, kDomainPhoton, photon, sample).  States: kNew -> kLightWait (an
 // intersectMesh ray is in flight) -> kDone.
-__global__ void __launch_bounds__(256) vcm_photon_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample) {
+// Like every logic stage here it walks the LIVE paths only (the trace queue of the previous iteration; `first` walks all slots).
+__global__ void __launch_bounds__(256) vcm_photon_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample, int first) {
   const DeviceScene& sc = cfg.scene;
-  if (blockIdx.x == 0 && threadIdx.x == 0) cnt->trace_count[parity ^ 1] = 0;
   const float beta = P.beta;
-  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < pool.photons; slot += gridDim.x * blockDim.x) {
-    uint32_t st = pool.p_state[slot];
+  const uint32_t n_live = first ? pool.photons : cnt->trace_count[parity ^ 1];
+  const uint32_t n_round = (n_live + 31u) & ~31u;
+  const uint32_t* live_q = pool.trace_q[parity ^ 1];
+  uint32_t* next_q = pool.trace_q[parity];
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+    const bool lane_on = i < n_live;
+    const uint32_t slot = lane_on ? (first ? i : live_q[i]) : 0u;
+    uint32_t st = lane_on ? pool.p_state[slot] : uint32_t(kDone);
     bool want_trace = false, finished = false, terminate = false;
     uint32_t head = kInvalid, count = 0;
     Rng rng; rng.key = 0; rng.ctr = 0;
@@ -372,15 +379,18 @@ __global__ void __launch_bounds__(256) vcm_photon_kernel(RenderConfig cfg, VcmPa
       if (mask && (threadIdx.x & 31u) == 0) atomicAdd(&cnt->done, unsigned(__popc(mask)));
     }
     const unsigned tq = warp_append(&cnt->trace_count[parity], want_trace);
-    if (want_trace) pool.trace_q[tq] = slot;
+    if (want_trace) next_q[tq] = slot;
   }
 }
 
 __global__ void __launch_bounds__(256) vcm_photon_trace_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
   const uint32_t n = cnt->trace_count[parity];
-  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+    cnt->trace_count[parity ^ 1] = 0;  // consumed by this iteration's logic stage
+  }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t slot = pool.trace_q[i];
+    const uint32_t slot = pool.trace_q[parity][i];
     const float4 o = pool.p_ray_o[slot], d = pool.p_bs_omega[slot];
     const Hit h = trace_ray<false, true>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY);
     pool.p_hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
@@ -410,15 +420,21 @@ __device__ __forceinline__ float3 connect_light(const DeviceScene& sc, const Ver
   return lr * eye.thr / weight_inv;
 }
 
-__global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample) {
+__global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample, int first) {
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    cnt->trace_count[parity ^ 1] = 0; cnt->pair_count[parity ^ 1] = 0;
+    cnt->pair_count[parity ^ 1] = 0;
     cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0; cnt->dir_count[parity ^ 1] = 0;
   }
   const float beta = P.beta;
-  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < pool.pixels_pad; slot += gridDim.x * blockDim.x) {
-    uint32_t st = pool.state[slot];
+  const uint32_t n_live = first ? pool.pixels_pad : cnt->trace_count[parity ^ 1];
+  const uint32_t n_round = (n_live + 31u) & ~31u;
+  const uint32_t* live_q = pool.trace_q[parity ^ 1];
+  uint32_t* next_q = pool.trace_q[parity];
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+    const bool lane_on = i < n_live;
+    const uint32_t slot = lane_on ? (first ? i : live_q[i]) : 0u;
+    uint32_t st = lane_on ? pool.state[slot] : uint32_t(kDone);
     bool want_trace = false, want_gather = false, finished = false, store_cur = false;
     uint32_t emit_n = 0, emit_flags = 0;
     bool emit_nee = false, emit_skip_first = false;
@@ -578,7 +594,7 @@ __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParam
       if (mask && (threadIdx.x & 31u) == 0) atomicAdd(&cnt->done, unsigned(__popc(mask)));
     }
     const unsigned tq = warp_append(&cnt->trace_count[parity], want_trace);
-    if (want_trace) pool.trace_q[tq] = slot;
+    if (want_trace) next_q[tq] = slot;
     const unsigned gq = warp_append(&cnt->gather_count[parity], want_gather);
     if (want_gather) pool.gather_q[gq] = slot;
     unsigned pq = warp_reserve(&cnt->pair_count[parity], emit_n);
@@ -669,9 +685,12 @@ __global__ void __launch_bounds__(256) vcm_connect_kernel(RenderConfig cfg, VcmP
 
 __global__ void __launch_bounds__(256) vcm_trace_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
   const uint32_t n = cnt->trace_count[parity];
-  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+    cnt->trace_count[parity ^ 1] = 0;  // consumed by this iteration's logic stage
+  }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t slot = pool.trace_q[i];
+    const uint32_t slot = pool.trace_q[parity][i];
     const float4 o = pool.ray_o[slot], d = pool.bs_omega[slot];
     const Hit h = trace_ray<false, false>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY);  // Scene::intersect
     pool.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
@@ -945,7 +964,8 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWor
   if ((rc = ws_alloc(w, &p.lv, size_t(p.lv_capacity) * kVertexFloat4s))) return rc;
   if ((rc = ws_alloc(w, &p.lv_link, p.lv_capacity))) return rc;
   if ((rc = ws_alloc(w, &p.grid_points, p.lv_capacity))) return rc;
-  if ((rc = ws_alloc(w, &p.trace_q, nl))) return rc;
+  if ((rc = ws_alloc(w, &p.trace_q[0], nl))) return rc;
+  if ((rc = ws_alloc(w, &p.trace_q[1], nl))) return rc;
   if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
   if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
   if ((rc = ws_alloc(w, &p.gather_q, ne))) return rc;
@@ -1000,7 +1020,7 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     for (int it = 0;;) {
       for (int k = 0; k < kBatchIters; ++k, ++it) {
         const int parity = it & 1;
-        timer.begin(kStageShade); vcm_photon_kernel<<<grid_p, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample); timer.end();
+        timer.begin(kStageShade); vcm_photon_kernel<<<grid_p, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample, it == 0 ? 1 : 0); timer.end();
         timer.begin(kStageTrace); vcm_photon_trace_kernel<<<grid_p, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
       }
       B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(VcmCounters), cudaMemcpyDeviceToHost, stream));
@@ -1024,7 +1044,7 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     for (int it = 0;;) {
       for (int k = 0; k < kBatchIters; ++k, ++it) {
         const int parity = it & 1;
-        timer.begin(kStageShade); vcm_eye_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample); timer.end();
+        timer.begin(kStageShade); vcm_eye_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample, it == 0 ? 1 : 0); timer.end();
         timer.begin(kStageShade); vcm_gather_kernel<<<grid_g, 128, 0, stream>>>(cfg, P, pool, w->grid.dev, w->counters, parity); timer.end();
         timer.begin(kStageShade); vcm_connect_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity); timer.end();
         if (cfg.scene.has_directional) {
