@@ -44,6 +44,8 @@ constexpr uint32_t kPairCamera = 0x80000000u;  // descriptor.x bit 31: the eye v
 constexpr uint32_t kNeeVertex = 0xFFFFFFFFu;   // descriptor.y: the freshly sampled emitter point instead of a stored vertex
 constexpr uint32_t kShadowSplat = 1u;
 constexpr int kVertexFloat4s = 7;
+constexpr int kRecFloat4s = 16;
+enum { kRecThr = 7, kRecOmega = 8, kRecRayO = 9, kRecHit = 10, kRecRad = 11, kRecCtl = 12, kRecNee = 13, kRecState = 14 };
 // Expanding a path's connections into pair descriptors by walking its vertex chain is a string of dependent loads
 // (one L2 / HBM round trip per vertex); the first kLpTable vertex indices are therefore also kept by position, so the
 // expansion reads them independently.  Longer paths (3 % at roulette 0.9) walk the chain for the rest.
@@ -71,21 +73,19 @@ struct BptPool {
   uint32_t valid;        // paths in the batch = passes * pixels
   uint32_t lv_capacity;  // light vertex pool
   uint32_t q_capacity;   // pair / shadow queues
-  uint32_t* state;
-  uint2* rng;
-  float4* cv;        // current vertex, SoA: cv[k * size + slot], k < 7
-  float4* bs_omega;  // pending BSDF sample: omega.xyz, density
-  float4* bs_thr;    //                      throughput.xyz, density_rev
-  float4* ray_o;     // extension ray origin, w = bits(bsdf.finite | ray mask selector << 1)
-  float4* hit;       // t, u, v, bits(triangle)
-  float4* rad;       // eye-path radiance (float atomics from the shadow stage)
-  float4* nee;       // next-event sample: position, bits(light id)
+  // One 256-byte record per path slot (AoS): the stages reach slots through queues of live slots, i.e. as gathers, and a
+  // record that is contiguous is fetched as whole 32-byte sectors that are used in full; the same words kept as SoA streams
+  // cost 2.5x their size in HBM traffic once most neighbours of a live slot are dead (ncu, profiles/).
+  //   float4 0..6  current vertex (pack_vertex)            7  pending BSDF sample: throughput.xyz, density_rev
+  //   8  pending BSDF sample: omega.xyz, density           9  extension ray origin, w = bits(bsdf.finite | ray mask selector << 1)
+  //   10 hit: t, u, v, bits(triangle)                      11 eye-path radiance (float atomics from the shadow stage)
+  //   12 bits(rng key, rng counter, light path head, light path count)
+  //   13 next-event sample: position, bits(light id)       14 bits(state), -, -, -
+  float4* rec;
   double* splat;     // light image of the pass the path belongs to: 3 doubles per slot (= per pixel of that pass)
-  uint32_t* lp_head;
-  uint32_t* lp_count;
   float4* lv;        // light vertex pool, AoS: 7 float4 per vertex
   uint32_t* lv_link; // previous vertex of the same path
-  uint32_t* lp_idx;  // the first kLpTable vertices of every light path by position, SoA: lp_idx[k * size + slot]
+  uint32_t* lp_idx;  // the first kLpTable vertices of every light path by position: lp_idx[slot * kLpTable + k], one 128-byte line per path
   uint32_t* trace_q[2];  // live slots = the slots with an extension ray in flight; written by the logic stage of iteration i into [i & 1]
   uint2* pair_q;
   float4* shadow_q;  // 3 float4 per entry
@@ -116,12 +116,12 @@ __device__ __forceinline__ void store_slot_vertex(const BptPool& p, uint32_t slo
   float4 q[kVertexFloat4s];
   pack_vertex(v, q);
 #pragma unroll
-  for (int k = 0; k < kVertexFloat4s; ++k) p.cv[size_t(k) * p.size + slot] = q[k];
+  for (int k = 0; k < kVertexFloat4s; ++k) p.rec[size_t(slot) * kRecFloat4s + k] = q[k];
 }
 __device__ __forceinline__ Vertex load_slot_vertex(const BptPool& p, uint32_t slot) {
   float4 q[kVertexFloat4s];
 #pragma unroll
-  for (int k = 0; k < kVertexFloat4s; ++k) q[k] = p.cv[size_t(k) * p.size + slot];
+  for (int k = 0; k < kVertexFloat4s; ++k) q[k] = p.rec[size_t(slot) * kRecFloat4s + k];
   return unpack_vertex(q);
 }
 __device__ __forceinline__ void store_pool_vertex(const BptPool& p, uint32_t idx, const Vertex& v) {
@@ -242,7 +242,9 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
     const bool lane_on = i < n_live;
     const uint32_t slot = lane_on ? (first ? i : live_q[i]) : 0u;
-    const uint32_t st0 = lane_on ? pool.state[slot] : uint32_t(kDone);
+    float4* rec = pool.rec + size_t(slot) * kRecFloat4s;
+    // iteration 0 of a batch never reads the records: every slot is born kNew
+    const uint32_t st0 = lane_on ? (first ? uint32_t(kNew) : __float_as_uint(rec[kRecState].x)) : uint32_t(kDone);
     uint32_t st = st0;
     bool want_trace = false, finished = false;
     uint32_t emit_n = 0, emit_flags = 0;  // pair descriptors to write after the branches
@@ -267,7 +269,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
         rng.key = stream_key(cfg.params.seed, kDomainPixel, pixel, sample);
         const float3 dir = shoot_primary(cfg, rng, pixel);
         (void)dir;  // recomputed from the stream at kEyeStart; the light phase comes first (BPT.cpp:23)
-        pool.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+        rec[kRecRad] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (roulette < rng.sample()) {  // BPT.cpp:19-21
           finished = true;
         } else if (roulette < rng.sample()) {  // _traceLight, BPT.cpp:126-128: empty light path
@@ -284,20 +286,20 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
           } else {
             store_pool_vertex(pool, idx, cur);
             pool.lv_link[idx] = kInvalid;
-            pool.lp_idx[slot] = idx;
+            pool.lp_idx[size_t(slot) * kLpTable] = idx;
             head = idx; count = 1;
             cur_dirty = true;
             st = kLightLoop;
           }
         }
       } else {
-        const uint2 rs = pool.rng[slot];
-        rng.key = rs.x; rng.ctr = rs.y;
-        head = pool.lp_head[slot]; count = pool.lp_count[slot];
-        const float4 rv = pool.rad[slot];
+        const float4 ctl = rec[kRecCtl];
+        rng.key = __float_as_uint(ctl.x); rng.ctr = __float_as_uint(ctl.y);
+        head = __float_as_uint(ctl.z); count = __float_as_uint(ctl.w);
+        const float4 rv = rec[kRecRad];
         rad = f3(rv.x, rv.y, rv.z);
         cur = load_slot_vertex(pool, slot);
-        const float4 bo = pool.bs_omega[slot], bt = pool.bs_thr[slot], ro = pool.ray_o[slot];
+        const float4 bo = rec[kRecOmega], bt = rec[kRecThr], ro = rec[kRecRayO];
         bs.omega = f3(bo.x, bo.y, bo.z); bs.density = bo.w;
         bs.throughput = f3(bt.x, bt.y, bt.z); bs.density_rev = bt.w;
         bs.finite = __float_as_uint(ro.w) & 1u;
@@ -306,7 +308,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
 
       if (st == kLightWait) {
         // ---- _traceLight loop body after intersectMesh (BPT.cpp:139-176)
-        const float4 hv = pool.hit[slot];
+        const float4 hv = rec[kRecHit];
         const uint32_t tri = __float_as_uint(hv.w);
         if (tri == kInvalid) {
           st = kLightFinal;
@@ -340,7 +342,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
               } else {
                 store_pool_vertex(pool, idx, nv);
                 pool.lv_link[idx] = head;
-                if (count < kLpTable) pool.lp_idx[size_t(count) * pool.size + slot] = idx;
+                if (count < kLpTable) pool.lp_idx[size_t(slot) * kLpTable + count] = idx;
                 head = idx; ++count;
                 cur = nv; cur_dirty = true;
                 st = kLightLoop;
@@ -389,7 +391,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
         st = kEyeWait;
       } else if (st0 == kEyeWait) {
         // ---- BPT.cpp:45-97: consume the closest hit of the extension ray
-        const float4 hv = pool.hit[slot];
+        const float4 hv = rec[kRecHit];
         const uint32_t tri = __float_as_uint(hv.w);
         if (tri == kInvalid) {
           if (cur.s.is_camera()) {  // sky_gradient(bsdf.omega) *= _roulette_inv  (Technique.cpp:87-89)
@@ -431,7 +433,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
                   if (!ls.directional) {
                     emit_nee = true;
                     const uint32_t light_id = sc.materials[ls.surface.material_index()].light_id;
-                    pool.nee[slot] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
+                    rec[kRecNee] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
                   } else {
                     // _connect_directional (BPT.cpp:245-269): queued for the directional stage
                     const float3 n = ls.surface.normal();
@@ -465,20 +467,19 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
       }
 
       if (finished) {
-        pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+        rec[kRecRad] = make_float4(rad.x, rad.y, rad.z, 0.f);
         st = kDone;
       } else {
         if (cur_dirty) store_slot_vertex(pool, slot, cur);
-        pool.rng[slot] = make_uint2(rng.key, rng.ctr);
-        pool.lp_head[slot] = head; pool.lp_count[slot] = count;
-        if (st0 == kEyeWait) pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+        rec[kRecCtl] = make_float4(__uint_as_float(rng.key), __uint_as_float(rng.ctr), __uint_as_float(head), __uint_as_float(count));
+        if (st0 == kEyeWait) rec[kRecRad] = make_float4(rad.x, rad.y, rad.z, 0.f);
         if (want_trace) {
-          pool.bs_omega[slot] = make_float4(bs.omega.x, bs.omega.y, bs.omega.z, bs.density);
-          pool.bs_thr[slot] = make_float4(bs.throughput.x, bs.throughput.y, bs.throughput.z, bs.density_rev);
-          pool.ray_o[slot] = make_float4(O.x, O.y, O.z, __uint_as_float((bs.finite & 1u) | (ray_mesh_only << 1)));
+          rec[kRecOmega] = make_float4(bs.omega.x, bs.omega.y, bs.omega.z, bs.density);
+          rec[kRecThr] = make_float4(bs.throughput.x, bs.throughput.y, bs.throughput.z, bs.density_rev);
+          rec[kRecRayO] = make_float4(O.x, O.y, O.z, __uint_as_float((bs.finite & 1u) | (ray_mesh_only << 1)));
         }
       }
-      pool.state[slot] = st;
+      rec[kRecState].x = __uint_as_float(st);
     }
 
     // ---- converged: queue appends
@@ -501,13 +502,13 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
           v = pool.lv_link[v];
         }
         const uint32_t kt = count < kLpTable ? count : kLpTable;
-        for (uint32_t k = emit_skip_first ? 1u : 0u; k < kt; k += 4u) {
-          uint32_t a[4];
-#pragma unroll
-          for (uint32_t j = 0; j < 4u; ++j) a[j] = k + j < kt ? pool.lp_idx[size_t(k + j) * pool.size + slot] : 0u;
+        const uint4* table = reinterpret_cast<const uint4*>(pool.lp_idx + size_t(slot) * kLpTable);
+        for (uint32_t k = 0; k < kt; k += 4u) {
+          const uint4 a4 = table[k >> 2];
+          const uint32_t a[4] = {a4.x, a4.y, a4.z, a4.w};
 #pragma unroll
           for (uint32_t j = 0; j < 4u; ++j)
-            if (k + j < kt) pool.pair_q[pq++] = make_uint2(slot | emit_flags, a[j]);
+            if (k + j < kt && !(emit_skip_first && k + j == 0u)) pool.pair_q[pq++] = make_uint2(slot | emit_flags, a[j]);
         }
       }
     }
@@ -532,7 +533,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel
       const Vertex eye = load_slot_vertex(pool, slot);
       Vertex light;
       if (desc.y == kNeeVertex) {
-        const float4 nr = pool.nee[slot];
+        const float4 nr = pool.rec[size_t(slot) * kRecFloat4s + kRecNee];
         light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), roulette_inv, beta);
       } else {
         light = load_pool_vertex(pool, desc.y);
@@ -566,7 +567,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel
           if (flags & kShadowSplat) {
             atomicAdd(pool.splat + size_t(target) * 3, double(NAN));
           } else {
-            atomicAdd(&pool.rad[target].x, NAN);
+            atomicAdd(&pool.rec[size_t(target) * kRecFloat4s + kRecRad].x, NAN);
           }
         } else if (l1 != 0.0f) {
           // Scene::occluded(eye.surface, light.surface) (Scene.cpp:151-171)
@@ -598,13 +599,14 @@ struct BptTraceIo {
   const uint32_t* q;
   __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
     const uint32_t slot = q[i];
-    const float4 o = pool->ray_o[slot], d = pool->bs_omega[slot];
+    const float4* rec = pool->rec + size_t(slot) * kRecFloat4s;
+    const float4 o = rec[kRecRayO], d = rec[kRecOmega];
     O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY;
     mask = (__float_as_uint(o.w) & 2u) ? kMaskMesh : kMaskAll;  // Scene::intersectMesh (light subpaths) / Scene::intersect
     return slot;
   }
   __device__ __forceinline__ void store(uint32_t slot, const Hit& h) const {
-    pool->hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+    pool->rec[size_t(slot) * kRecFloat4s + kRecHit] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
   }
 };
 struct BptShadowIo {
@@ -625,7 +627,7 @@ struct BptShadowIo {
       double* s = pool->splat + size_t(target) * 3;
       atomicAdd(s + 0, double(c.x)); atomicAdd(s + 1, double(c.y)); atomicAdd(s + 2, double(c.z));
     } else {
-      float* r = &pool->rad[target].x;
+      float* r = &pool->rec[size_t(target) * kRecFloat4s + kRecRad].x;
       atomicAdd(r + 0, c.x); atomicAdd(r + 1, c.y); atomicAdd(r + 2, c.z);
     }
   }
@@ -670,7 +672,7 @@ __global__ void __launch_bounds__(256) bpt_commit_kernel(RenderConfig cfg, BptPo
     double sum[4] = {0.0, 0.0, 0.0, 0.0};
     for (uint32_t k = 0; k < batch_passes; ++k) {
       const uint32_t slot = k * cfg.pixels + pixel;
-      const float4 e = pool.rad[slot];
+      const float4 e = pool.rec[size_t(slot) * kRecFloat4s + kRecRad];
       double* s = pool.splat + size_t(slot) * 3;
       const double r = s[0] + double(e.x), g = s[1] + double(e.y), b = s[2] + double(e.z);
       s[0] = 0.0; s[1] = 0.0; s[2] = 0.0;
@@ -753,18 +755,8 @@ int bpt_workspace(b2pt_scene_s* scene, uint32_t size, int lanes, BptWorkspace** 
     p.lv_capacity = size * 12u < 4096u ? 4096u : size * 12u;
     p.q_capacity = p.lv_capacity + size;
     int rc;
-    if ((rc = ws_alloc(w, &p.state, size))) return rc;
-    if ((rc = ws_alloc(w, &p.rng, size))) return rc;
-    if ((rc = ws_alloc(w, &p.cv, size_t(size) * kVertexFloat4s))) return rc;
-    if ((rc = ws_alloc(w, &p.bs_omega, size))) return rc;
-    if ((rc = ws_alloc(w, &p.bs_thr, size))) return rc;
-    if ((rc = ws_alloc(w, &p.ray_o, size))) return rc;
-    if ((rc = ws_alloc(w, &p.hit, size))) return rc;
-    if ((rc = ws_alloc(w, &p.rad, size))) return rc;
-    if ((rc = ws_alloc(w, &p.nee, size))) return rc;
+    if ((rc = ws_alloc(w, &p.rec, size_t(size) * kRecFloat4s))) return rc;
     if ((rc = ws_alloc(w, &p.splat, size_t(size) * 3))) return rc;
-    if ((rc = ws_alloc(w, &p.lp_head, size))) return rc;
-    if ((rc = ws_alloc(w, &p.lp_count, size))) return rc;
     if ((rc = ws_alloc(w, &p.lv, size_t(p.lv_capacity) * kVertexFloat4s))) return rc;
     if ((rc = ws_alloc(w, &p.lv_link, p.lv_capacity))) return rc;
     if ((rc = ws_alloc(w, &p.lp_idx, size_t(size) * kLpTable))) return rc;
@@ -839,7 +831,6 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     g.pool.valid = g.passes * pixels;  // the last batch may be shorter; SoA strides shrink with it, which is fine
     g.pool.size = (g.pool.valid + block - 1) / block * block;
     B2_CUDA(cudaMemsetAsync(l.counters, 0, sizeof(BptCounters), l.stream));
-    B2_CUDA(cudaMemsetAsync(g.pool.state, 0, size_t(g.pool.size) * 4, l.stream));
     return B2PT_OK;
   };
   for (int k = 0; k < lanes && next_pass < num_passes; ++k)
@@ -860,7 +851,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);
           directional_kernel<<<grid, block, 0, l.stream>>>(cfg.scene, g.pool.dir_q, &l.counters->dir_count[parity], g.pool.size,
-                                                          DirectionalParams{cfg.params.beta, 1.0f, 0.0f, 0.0f}, g.pool.rad, &l.counters->basic_rays);
+                                                          DirectionalParams{cfg.params.beta, 1.0f, 0.0f, 0.0f}, g.pool.rec + kRecRad, uint32_t(kRecFloat4s), &l.counters->basic_rays);
           timer.end();
         }
         timer.begin(kStageTrace);

@@ -76,7 +76,7 @@ __device__ __forceinline__ float3 shoot_primary(const RenderConfig& cfg, Rng& rn
 struct DirectionalParams { float beta, vc, vm, beta_n; };
 
 static __global__ void __launch_bounds__(256) directional_kernel(DeviceScene sc, const float4* __restrict__ queue, const unsigned* __restrict__ count,
-                                                          uint32_t capacity, DirectionalParams P, float4* rad, unsigned long long* basic_rays) {
+                                                          uint32_t capacity, DirectionalParams P, float4* rad, uint32_t rad_stride, unsigned long long* basic_rays) {
   const uint32_t n = min(*count, capacity);
   if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(basic_rays, (unsigned long long)n);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -95,7 +95,7 @@ static __global__ void __launch_bounds__(256) directional_kernel(DeviceScene sc,
     const float3 result = f3(e2.x, e2.y, e2.z);
     if (l1norm(result) < kFltEpsilon) continue;
     const float3 c = result / weight_inv;
-    float* r = &rad[__float_as_uint(e0.w)].x;
+    float* r = &rad[size_t(__float_as_uint(e0.w)) * rad_stride].x;  // rad_stride: float4s between the radiance words of two paths
     atomicAdd(r + 0, c.x); atomicAdd(r + 1, c.y); atomicAdd(r + 2, c.z);
   }
 }

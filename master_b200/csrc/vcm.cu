@@ -1051,7 +1051,7 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
           timer.begin(kStageTrace);
           directional_kernel<<<grid_e, block, 0, stream>>>(cfg.scene, pool.dir_q, &w->counters->dir_count[parity], pool.pixels_pad,
                                                           DirectionalParams{P.beta, float(P.enable_vc), float(P.enable_vm), beta_fn_host(P.num_scattered, P.beta)},
-                                                          pool.rad, &w->counters->basic_rays);
+                                                          pool.rad, 1u, &w->counters->basic_rays);
           timer.end();
         }
         timer.begin(kStageTrace); vcm_trace_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
