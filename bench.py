@@ -119,6 +119,27 @@ def physical_gpu_index(local):
     return local
 
 
+_STDOUT_FD = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL's version banner, for one) write to fd 1; the contract is ONE JSON line on stdout, so everything else
+    goes to stderr and emit() writes the line to the real stdout."""
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _STDOUT_FD is None:
+        os.write(1, data)
+    else:
+        os.write(_STDOUT_FD, data)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -133,6 +154,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
+    quiet_stdout()
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -164,7 +186,7 @@ def main():
                 "config": config, "mrays_per_s": r["mrays_per_s"],
                 "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": r["threads"], "kind": "reference", "sample": sample},
                 "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     # ------------------------------------------------------------ B200 arm
@@ -284,7 +306,26 @@ def main():
                 "stage_ms_rank0": ms,
                 "shadow": {"achieved": tot["num_shadow_rays"] * RAY_BYTES_SHADOW / (ms["shadow_ms"] * 1e-3) * 1e-9 if ms["shadow_ms"] > 0 else None,
                            "grays_per_s_in_kernel": tot["num_shadow_rays"] / (ms["shadow_ms"] * 1e-3) * 1e-9 if ms["shadow_ms"] > 0 else None},
-                "note": "traversal is issue/latency bound by design (SURVEY.md §8(d)): the scene fits L2; see profiles/"}
+                "note": "traversal is issue bound by design (SURVEY.md §8(d)): the HBM fraction is small because the scene is served from "
+                        "L2/L1; the `issue` object is the roof that binds; see profiles/"}
+    # figures that only a profiler sees (DRAM traffic, warp instructions per ray) come from the committed ncu capture
+    try:
+        cap = json.load(open(os.path.join(ROOT, "profiles", "r01_roofline_inputs.json")))
+        per_ray = (cap["dram_bytes_read"] + cap["dram_bytes_written"]) / cap["rays_in_launch"]
+        roofline["traffic"] = per_ray * roofline["rays_per_launch"]  # bytes per launch, scaled to this run's mean launch size
+        roofline["traffic_note"] = "%.0f B/ray of DRAM traffic in the capture (%s) vs %d B/ray algorithmic: the excess is BVH nodes and " \
+                                   "triangles that missed the L2" % (per_ray, cap["capture"], RAY_BYTES_CLOSEST)
+        clk = sampler.summary()["sm_mhz"] or 1965
+        wi = cap["warp_instructions"] / cap["rays_in_launch"]
+        peak_issue = 148 * 4 * clk * 1e6 * 1e-9  # Gwarp-instr/s: 148 SMs x 4 schedulers x 1 instruction per cycle
+        ach_issue = wi * roofline["grays_per_s_in_kernel"] if roofline["grays_per_s_in_kernel"] else None
+        roofline["issue"] = {"bound": "issue", "achieved": ach_issue, "peak": peak_issue, "unit": "Gwarp-instr/s",
+                             "frac": ach_issue / peak_issue if ach_issue else None, "warp_instr_per_ray": wi,
+                             "active_lanes_per_instr": cap["active_lanes_per_instruction"],
+                             "note": "closest-hit stage while it shares the GPU with the other batch's kernels; warp instructions per ray "
+                                     "from the capture, rays/s from this run's CUDA events"}
+    except Exception as e:  # pragma: no cover
+        roofline["traffic_note"] = "profiles/r01_roofline_inputs.json unreadable: %s" % e
 
     cpu = None
     if not a.no_cpu_baseline and os.path.exists(HARNESS):
@@ -306,7 +347,7 @@ def main():
             "l2_policy": "inputs larger than L2: scene %.0f MB (BVH %.0f MB + shading frames) + path pool > 126 MB" % (
                 (info["bvh_bytes"] + info["triangles"] * 112) / 1e6, info["bvh_bytes"] / 1e6),
             "scene": info, "numeric_errors": tot["numeric_errors"], "capacity_events": tot["capacity_events"]}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
