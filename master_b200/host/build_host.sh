@@ -28,5 +28,5 @@ g++ $CXXFLAGS -c "$HERE/GpuTechnique.cpp" -o "$OUT/obj/GpuTechnique.o"
 g++ $CXXFLAGS -c "$HERE/host_main.cpp" -o "$OUT/obj/host_main.o"
 OBJS=""; for s in $SRCS GpuTechnique host_main; do OBJS="$OBJS $OUT/obj/$s.o"; done
 g++ -o "$OUT/b2pt_master" $OBJS -L"$ROOT/oracle/_ref/lib" -lembree -lembree_avx -lembree_sse42 -lsimd -llexers -lsys \
-  -L"$ROOT/master_b200" -lb2pt -Wl,-rpath,'$ORIGIN/../..' -L/usr/local/cuda/lib64 -lcudart -lpthread -ldl
+  -L"$ROOT/master_b200" -lb2pt -Wl,-rpath,'$ORIGIN/../..' -L/usr/local/cuda/lib64 -lcudart -lz -lpthread -ldl
 echo "built $OUT/b2pt_master"

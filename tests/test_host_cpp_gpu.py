@@ -37,3 +37,24 @@ def test_gpu_technique_behind_the_reference_interface(name, tech, tmp_path):
 def test_missing_scene_is_an_exception_not_a_crash():
     r = subprocess.run([HOST, "/nonexistent.b2s"], capture_output=True, text=True)
     assert r.returncode == 1 and "cannot open" in r.stderr
+
+
+def test_exr_checkpoint_and_continue(tmp_path):
+    """the host driver writes the reference's EXR checkpoint (R, G, B, denom + options / statistics /
+    records attributes) and resumes from it like `master continue`: 2 passes + 2 continued passes == 4 passes."""
+    from master_b200 import exr
+    scene = golden_path("scenes", "CornellBoxDiffuse.b2s")
+    base = [HOST, scene, "technique=PT", "width=48", "height=40", "seed=77"]
+    a, b, c = (str(tmp_path / n) for n in ("two.exr", "four_continued.exr", "four.exr"))
+    for args in (["num_samples=2", "exr=" + a], ["num_samples=4", "continue=" + a, "exr=" + b], ["num_samples=4", "exr=" + c]):
+        r = subprocess.run(base + args, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    m2, d2, has_denom = exr.load_exr(a)
+    mb, db, _ = exr.load_exr(b)
+    mc, dc, _ = exr.load_exr(c)
+    assert has_denom and d2.shape == (40, 48, 4) and np.all(d2[:, :, 3] == 2) and np.all(db[:, :, 3] == 4) and np.all(dc[:, :, 3] == 4)
+    assert m2["statistics.num_samples"] == "2" and mb["statistics.num_samples"] == "4" and mc["options.technique"] == "PT"
+    assert "records[1].frame_duration" in m2 and "records[3].frame_duration" in mb
+    assert int(mb["statistics.num_basic_rays"]) == int(mc["statistics.num_basic_rays"])  # the same paths were traced
+    np.testing.assert_allclose(db, dc, rtol=1e-5, atol=1e-6)  # the checkpoint holds float32 sums
+    assert np.abs(dc[:, :, :3]).sum() > 0
