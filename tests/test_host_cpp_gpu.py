@@ -20,7 +20,8 @@ def test_gpu_technique_behind_the_reference_interface(name, tech, tmp_path):
     w, h, spp = int(g["width"]), int(g["height"]), g["paths"].shape[0]
     out = str(tmp_path / "accum.f64")
     r = subprocess.run([HOST, golden_path("scenes", name + ".b2s"), "technique=" + tech, "width=%d" % w, "height=%d" % h,
-                        "num_samples=%d" % spp, "seed=%d" % int(g["seed"]), "out=" + out], capture_output=True, text=True)
+                        "num_samples=%d" % spp, "seed=%d" % int(g["seed"]), "beta=%d" % (1 if tech == "PT" else 2), "out=" + out],
+                       capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     info = json.loads(r.stdout.strip().splitlines()[-1])
     accum = np.fromfile(out, dtype=np.float64).reshape(-1, 4)
@@ -44,10 +45,12 @@ def test_exr_checkpoint_and_continue(tmp_path):
     records attributes) and resumes from it like `master continue`: 2 passes + 2 continued passes == 4 passes."""
     from master_b200 import exr
     scene = golden_path("scenes", "CornellBoxDiffuse.b2s")
-    base = [HOST, scene, "technique=PT", "width=48", "height=40", "seed=77"]
+    # the reference's command line: master <in> --PT --resolution=WxH --num-samples=n --seed=s --output=file; master continue <file>
     a, b, c = (str(tmp_path / n) for n in ("two.exr", "four_continued.exr", "four.exr"))
-    for args in (["num_samples=2", "exr=" + a], ["num_samples=4", "continue=" + a, "exr=" + b], ["num_samples=4", "exr=" + c]):
-        r = subprocess.run(base + args, capture_output=True, text=True)
+    base = [scene, "--PT", "--resolution=48x40", "--seed=77", "--batch"]
+    for args in (base + ["--num-samples=2", "--output=" + a], ["continue", a, "--num-samples=4", "--output=" + b],
+                 base + ["--num-samples=4", "--output=" + c]):
+        r = subprocess.run([HOST] + args, capture_output=True, text=True)
         assert r.returncode == 0, r.stderr
     m2, d2, has_denom = exr.load_exr(a)
     mb, db, _ = exr.load_exr(b)
