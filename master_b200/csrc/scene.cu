@@ -369,7 +369,7 @@ __global__ void collapse_kernel(uint32_t count, const CollapseItem* items, const
 __global__ void collapse8_kernel(uint32_t count, const CollapseItem* items, const uint64_t* keys, const float4* tri_lo, const float4* tri_hi,
                                  const BinNode* bin, const float4* box_lo, const float4* box_hi, float4* nodes8, uint32_t* num_wide,
                                  CollapseItem* next_items, uint32_t* next_count, uint32_t* tri_counter, uint64_t* tri_map, float pad,
-                                 uint32_t single_leaf_count) {
+                                 uint32_t single_leaf_count, uint32_t leaf_max) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count) return;
   const CollapseItem it = items[i];
@@ -399,7 +399,7 @@ __global__ void collapse8_kernel(uint32_t count, const CollapseItem* items, cons
     while (n < 8) {
       int best = -1; float best_area = -1.f;
       for (int k = 0; k < n; ++k) {
-        if ((ref[k] & 0x80000000u) || cnt[k] <= 3u) continue;
+        if ((ref[k] & 0x80000000u) || cnt[k] <= leaf_max) continue;
         const float dx = hi[k][0] - lo[k][0], dy = hi[k][1] - lo[k][1], dz = hi[k][2] - lo[k][2];
         const float a = dx * dy + dy * dz + dz * dx;
         if (a > best_area) { best_area = a; best = k; }
@@ -447,7 +447,7 @@ __global__ void collapse8_kernel(uint32_t count, const CollapseItem* items, cons
   // ---- children: inner nodes contiguous, leaf triangles contiguous
   uint32_t n_inner = 0, n_tris = 0;
   for (int k = 0; k < n; ++k) {
-    const bool leaf = single_leaf_count || (ref[k] & 0x80000000u) || cnt[k] <= 3u;
+    const bool leaf = single_leaf_count || (ref[k] & 0x80000000u) || cnt[k] <= leaf_max;
     if (leaf) n_tris += cnt[k]; else ++n_inner;
   }
   const uint32_t child_base = n_inner ? atomicAdd(num_wide, n_inner) : 0u;
@@ -464,7 +464,7 @@ __global__ void collapse8_kernel(uint32_t count, const CollapseItem* items, cons
       q[a][sl] = uint32_t(fminf(fmaxf(l, 0.f), 255.f));
       q[3 + a][sl] = uint32_t(fminf(fmaxf(h, 0.f), 255.f));
     }
-    const bool leaf = single_leaf_count || (ref[k] & 0x80000000u) || cnt[k] <= 3u;
+    const bool leaf = single_leaf_count || (ref[k] & 0x80000000u) || cnt[k] <= leaf_max;
     if (!leaf) {
       imask |= 1u << sl;
       const uint32_t w = child_base + rank++;
@@ -659,6 +659,9 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
       keys = order;  // triangles are now in depth-first leaf order of the PLOC tree
       root_bin = n - 2u;
     }
+    // triangles per leaf: a subtree of at most leaf_max triangles stays closed (B2PT_LEAF_MAX = 1..3 for A/B runs)
+    uint32_t leaf_max = 3u;
+    { const char* e = getenv("B2PT_LEAF_MAX"); if (e && e[0] >= '1' && e[0] <= '3') leaf_max = uint32_t(e[0] - '0'); }
     if (wide8 && n > 3) {
       // compressed 8-wide tree (bvh8.cuh); a wide inner node has at least two children, so n nodes is a safe bound
       if (int rc = dev_alloc(s, &nodes8, size_t(n) * 5, true)) return rc;
@@ -672,7 +675,7 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
       uint32_t count = 1;
       while (count > 0) {
         collapse8_kernel<<<(count + B - 1) / B, B>>>(count, items_a, keys, tri_lo, tri_hi, bin, box_lo, box_hi, nodes8, &counters8[0], items_b,
-                                                    &counters8[1], &counters8[2], tri_map, pad, 0u);
+                                                    &counters8[1], &counters8[2], tri_map, pad, 0u, leaf_max);
         B2_CUDA(cudaMemcpy(h_counters, counters8, 12, cudaMemcpyDeviceToHost));
         count = h_counters[1];
         num_wide = h_counters[0];
@@ -712,7 +715,7 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
     uint32_t h_counters[3] = {1u, 0u, 0u};
     B2_CUDA(cudaMemcpy(counters8, h_counters, 12, cudaMemcpyHostToDevice));
     collapse8_kernel<<<1, 32>>>(1u, item, keys, tri_lo, tri_hi, nullptr, nullptr, nullptr, nodes8, &counters8[0], item, &counters8[1],
-                               &counters8[2], tri_map, pad, n);
+                               &counters8[2], tri_map, pad, n, 3u);
     keys = tri_map;
     num_wide = 1;
   }

@@ -43,6 +43,7 @@ struct VcmCounters {
   unsigned int done;
   unsigned int lv_count;
   unsigned int trace_count[2], pair_count[2], shadow_count[2], gather_count[2], dir_count[2];
+  unsigned int merge_count;  // (eye vertex, photon) pairs of the current iteration; cleared by the eye stage
 };
 
 // the per-pass constants of UPGBase (UPG.hpp:119-137)
@@ -83,6 +84,7 @@ struct VcmPool {
   // vertex pool
   float4* lv; uint32_t* lv_link; float4* grid_points;
   // queues
+  uint2* merge_q; uint32_t m_capacity;  // (eye slot, photon index) pairs found by the gather stage, evaluated one per thread
   uint32_t* trace_q[2];  // live slots (extension ray in flight), written by iteration i into [i & 1]: the next logic stage walks it
   uint2* pair_q; float4* shadow_q; uint32_t* gather_q;
   float4* dir_q;  // connections to sun lights, 4 float4 per entry (render_common.cuh: directional_kernel)
@@ -423,7 +425,7 @@ __device__ __forceinline__ float3 connect_light(const DeviceScene& sc, const Ver
 __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample, int first) {
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    cnt->pair_count[parity ^ 1] = 0;
+    cnt->pair_count[parity ^ 1] = 0; cnt->merge_count = 0;
     cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0; cnt->dir_count[parity ^ 1] = 0;
   }
   const float beta = P.beta;
@@ -815,56 +817,107 @@ __device__ __forceinline__ float3 merge_eye(const DeviceScene& sc, Rng& rng, con
   return unoccluded * density * weight;
 }
 
-// _gather / _gather_biased (UPG.cpp:675-724): one thread per new eye vertex
-__global__ void __launch_bounds__(128) vcm_gather_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, DeviceGrid grid, VcmCounters* cnt, int parity) {
+// One merge of _gather / _gather_biased (UPG.cpp:684-693, 708-719): photon `index` against the eye path in `slot`.
+// eye = the tentative vertex (throughput already * 1 / roulette), prev_eye = the vertex before it (camera-side merging only).
+__device__ __forceinline__ float3 merge_one(const DeviceScene& sc, const VcmParams& P, const VcmPool& pool, uint32_t index, const Vertex& eye,
+                                            const Vertex& prev_eye, uint32_t path_key, unsigned long long& shadow_rays, unsigned long long& density_rays) {
+  if (!P.from_light) {  // UPG.cpp:690-692, 716-718: the photon itself against the eye vertex before the tentative one
+    const Vertex light = load_pool_vertex(pool, index);
+    if (P.unbiased) {
+      Rng sub; sub.key = mix32(path_key ^ mix32(index * 0x9E3779B9u + uint32_t(eye.length()))); sub.ctr = 0;
+      return merge_eye(sc, sub, light, prev_eye, P, shadow_rays, density_rays) * P.num_scattered_inv;
+    }
+    return merge_biased(sc, light, light, prev_eye, P) * P.num_scattered_inv;
+  }
+  const uint32_t prev = pool.lv_link[index];
+  if (prev == kInvalid) return f3(0.0f);
+  const Vertex light = load_pool_vertex(pool, prev);
+  if (light.s.is_light()) return f3(0.0f);  // UPG.cpp:689,713: the predecessor must be a surface vertex
+  if (P.unbiased) {
+    Rng sub; sub.key = mix32(path_key ^ mix32(index * 0x9E3779B9u + uint32_t(eye.length()))); sub.ctr = 0;
+    return merge_light(sc, sub, light, eye, P, shadow_rays, density_rays) * P.num_scattered_inv;
+  }
+  const Vertex tentative = load_pool_vertex(pool, index);
+  return merge_biased(sc, light, tentative, eye, P) * P.num_scattered_inv;
+}
+
+// _gather / _gather_biased (UPG.cpp:675-724) in two stages.
+//
+// vcm_gather_kernel: one thread per new eye vertex runs the range query (rQuery, HashGrid3D.hpp:181-204) TWICE — once to
+// count the photons inside the radius, once to write them as (eye slot, photon index) pairs into a range of the merge queue
+// reserved with one atomic per warp — and evaluates nothing.  vcm_merge_kernel: one thread per pair evaluates the merge.
+// A query finds anything between 0 and hundreds of photons, and a merge is two BSDF queries plus the MIS weights (UPG also a
+// shadow ray and the density-estimation loop): evaluated inside the query loop, a warp runs as long as its longest query with
+// whatever lanes still have photons left; as pairs, every lane always has one.  Queries that do not fit the queue any more
+// (m_capacity) evaluate their merges in place, so the result never depends on the capacity.
+__global__ void __launch_bounds__(256) vcm_gather_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, DeviceGrid grid, VcmCounters* cnt, int parity) {
   const DeviceScene& sc = cfg.scene;
   const uint32_t n = cnt->gather_count[parity];
+  const uint32_t n_round = (n + 31u) & ~31u;
+  const float radius_sq = P.radius * P.radius;
+  unsigned long long shadow_rays = 0, density_rays = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+    const bool on = i < n;
+    const uint32_t slot = on ? pool.gather_q[i] : 0u;
+    const float4 p0 = pool.cv[slot];  // float4 0 of the tentative vertex: its position
+    const float3 q = f3(p0.x, p0.y, p0.z);
+    uint32_t count = 0;
+    if (on) {
+      if (P.brute_vertices) {  // diagnostic: every stored vertex instead of the grid
+        for (uint32_t k = 0; k < P.brute_vertices; ++k) {
+          const float4 g = pool.grid_points[k];
+          if (__float_as_uint(g.w) != kInvalidPoint && distance2(q, f3(g.x, g.y, g.z)) < radius_sq) ++count;
+        }
+      } else {
+        grid_query(grid, q, radius_sq, [&](uint32_t, float3) { ++count; });
+      }
+    }
+    unsigned base = warp_reserve(&cnt->merge_count, count);
+    if (count == 0) continue;
+    if (base + count <= pool.m_capacity && !P.brute_vertices) {
+      grid_query(grid, q, radius_sq, [&](uint32_t index, float3) { pool.merge_q[base++] = make_uint2(slot, index); });
+    } else {
+      // no room (or the diagnostic mode): blank whatever part of the reservation lies inside the queue, merge in place
+      for (unsigned k = base; k < base + count && k < pool.m_capacity; ++k) pool.merge_q[k] = make_uint2(kInvalid, 0u);
+      const Vertex eye = load_slot_vertex(pool.cv, pool.pixels_pad, slot);
+      Vertex prev_eye = eye;
+      if (!P.from_light) prev_eye = load_slot_vertex(pool.pv, pool.pixels_pad, slot);
+      const uint32_t path_key = pool.rng[slot].x;
+      float3 sum = f3(0.0f);
+      auto merge = [&](uint32_t index, float3) { sum += merge_one(sc, P, pool, index, eye, prev_eye, path_key, shadow_rays, density_rays); };
+      if (P.brute_vertices) {
+        for (uint32_t k = 0; k < P.brute_vertices; ++k) {
+          const float4 g = pool.grid_points[k];
+          if (__float_as_uint(g.w) != kInvalidPoint && distance2(q, f3(g.x, g.y, g.z)) < radius_sq) merge(k, f3(g.x, g.y, g.z));
+        }
+      } else {
+        grid_query(grid, q, radius_sq, merge);
+      }
+      if (sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) {
+        float* r = &pool.rad[slot].x;
+        atomicAdd(r + 0, sum.x); atomicAdd(r + 1, sum.y); atomicAdd(r + 2, sum.z);
+      }
+    }
+  }
+  if (shadow_rays) atomicAdd(&cnt->shadow_rays, shadow_rays);
+  if (density_rays) { atomicAdd(&cnt->density_rays, density_rays); atomicAdd(&cnt->basic_rays, density_rays); }
+}
+
+__global__ void __launch_bounds__(256) vcm_merge_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
+  const DeviceScene& sc = cfg.scene;
+  const uint32_t n = min(cnt->merge_count, pool.m_capacity);
   unsigned long long shadow_rays = 0, density_rays = 0;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t slot = pool.gather_q[i];
-    const Vertex eye = load_slot_vertex(pool.cv, pool.pixels_pad, slot);  // the tentative vertex, throughput already * 1 / roulette
-    const uint32_t path_key = pool.rng[slot].x;
-    float3 sum = f3(0.0f);
-    Vertex prev_eye;
+    const uint2 e = pool.merge_q[i];
+    if (e.x == kInvalid) continue;
+    const uint32_t slot = e.x;
+    const Vertex eye = load_slot_vertex(pool.cv, pool.pixels_pad, slot);
+    Vertex prev_eye = eye;
     if (!P.from_light) prev_eye = load_slot_vertex(pool.pv, pool.pixels_pad, slot);
-    auto merge = [&](uint32_t index, float3) {
-      if (!P.from_light) {  // UPG.cpp:690-692, 716-718: the photon itself against the eye vertex before the tentative one
-        const Vertex light = load_pool_vertex(pool, index);
-        float3 v;
-        if (P.unbiased) {
-          Rng sub; sub.key = mix32(path_key ^ mix32(index * 0x9E3779B9u + uint32_t(eye.length()))); sub.ctr = 0;
-          v = merge_eye(sc, sub, light, prev_eye, P, shadow_rays, density_rays);
-        } else {
-          v = merge_biased(sc, light, light, prev_eye, P);
-        }
-        sum += v * P.num_scattered_inv;
-        return;
-      }
-      const uint32_t prev = pool.lv_link[index];
-      if (prev == kInvalid) return;
-      const Vertex light = load_pool_vertex(pool, prev);
-      if (light.s.is_light()) return;  // UPG.cpp:689,713: the predecessor must be a surface vertex
-      float3 v;
-      if (P.unbiased) {
-        Rng sub; sub.key = mix32(path_key ^ mix32(index * 0x9E3779B9u + uint32_t(eye.length()))); sub.ctr = 0;
-        v = merge_light(sc, sub, light, eye, P, shadow_rays, density_rays);
-      } else {
-        const Vertex tentative = load_pool_vertex(pool, index);
-        v = merge_biased(sc, light, tentative, eye, P);
-      }
-      sum += v * P.num_scattered_inv;
-    };
-    if (P.brute_vertices) {
-      for (uint32_t k = 0; k < P.brute_vertices; ++k) {
-        const float4 q = pool.grid_points[k];
-        if (__float_as_uint(q.w) != kInvalidPoint && distance2(eye.s.pos, f3(q.x, q.y, q.z)) < P.radius * P.radius) merge(k, f3(q.x, q.y, q.z));
-      }
-    } else {
-      grid_query(grid, eye.s.pos, P.radius * P.radius, merge);
-    }
-    if (sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) {
+    const float3 v = merge_one(sc, P, pool, e.y, eye, prev_eye, pool.rng[slot].x, shadow_rays, density_rays);
+    if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f) {
       float* r = &pool.rad[slot].x;
-      atomicAdd(r + 0, sum.x); atomicAdd(r + 1, sum.y); atomicAdd(r + 2, sum.z);
+      atomicAdd(r + 0, v.x); atomicAdd(r + 1, v.y); atomicAdd(r + 2, v.z);
     }
   }
   if (shadow_rays) atomicAdd(&cnt->shadow_rays, shadow_rays);
@@ -969,6 +1022,9 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWor
   if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
   if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
   if ((rc = ws_alloc(w, &p.gather_q, ne))) return rc;
+  // merge pairs: 64 per pixel (VCM at the thesis radius finds tens of photons per query); what does not fit is merged in place
+  p.m_capacity = uint32_t(std::min<size_t>(ne * 64, size_t(1) << 28));
+  if ((rc = ws_alloc(w, &p.merge_q, p.m_capacity))) return rc;
   if ((rc = ws_alloc(w, &p.dir_q, ne * 4))) return rc;
   if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
   B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(VcmCounters)));
@@ -1040,12 +1096,13 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     B2_CUDA(cudaMemsetAsync(&w->counters->done, 0, sizeof(unsigned int), stream));
     B2_CUDA(cudaMemsetAsync(w->counters->trace_count, 0, sizeof(unsigned int) * 10, stream));
     B2_CUDA(cudaMemsetAsync(pool.state, 0, size_t(pool.pixels_pad) * 4, stream));
-    const int grid_g = grid_for(pool.pixels_pad, 128);
+    const int grid_m = grid_for(pool.m_capacity, block);
     for (int it = 0;;) {
       for (int k = 0; k < kBatchIters; ++k, ++it) {
         const int parity = it & 1;
         timer.begin(kStageShade); vcm_eye_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample, it == 0 ? 1 : 0); timer.end();
-        timer.begin(kStageShade); vcm_gather_kernel<<<grid_g, 128, 0, stream>>>(cfg, P, pool, w->grid.dev, w->counters, parity); timer.end();
+        timer.begin(kStageShade); vcm_gather_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->grid.dev, w->counters, parity); timer.end();
+        timer.begin(kStageShade); vcm_merge_kernel<<<grid_m, block, 0, stream>>>(cfg, P, pool, w->counters); timer.end();
         timer.begin(kStageShade); vcm_connect_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity); timer.end();
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);
