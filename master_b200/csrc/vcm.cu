@@ -44,6 +44,8 @@ struct VcmCounters {
   unsigned int lv_count;
   unsigned int trace_count[2], pair_count[2], shadow_count[2], gather_count[2], dir_count[2];
   unsigned int merge_count;  // (eye vertex, photon) pairs of the current iteration; cleared by the eye stage
+  unsigned int long_count, long_ticket;  // UPG: density loops handed to whole warps (upg_density_long_kernel)
+  unsigned int job_count, job_ticket;  // UPG: merges whose density is still to be estimated, and the fetch counter of the stage that does it
 };
 
 // the per-pass constants of UPGBase (UPG.hpp:119-137)
@@ -84,6 +86,7 @@ struct VcmPool {
   // vertex pool
   float4* lv; uint32_t* lv_link; float4* grid_points;
   // queues
+  float4* job_q;  // UPG density jobs, 3 float4 each: (unoccluded * weight, bits slot) (target, bits vertex) (bits key, -, -, -); m_capacity entries
   uint2* merge_q; uint32_t m_capacity;  // (eye slot, photon index) pairs found by the gather stage, evaluated one per thread
   uint32_t* trace_q[2];  // live slots (extension ray in flight), written by iteration i into [i & 1]: the next logic stage walks it
   uint2* pair_q; float4* shadow_q; uint32_t* gather_q;
@@ -425,7 +428,7 @@ __device__ __forceinline__ float3 connect_light(const DeviceScene& sc, const Ver
 __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample, int first) {
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    cnt->pair_count[parity ^ 1] = 0; cnt->merge_count = 0;
+    cnt->pair_count[parity ^ 1] = 0; cnt->merge_count = 0; cnt->job_count = 0; cnt->job_ticket = 0; cnt->long_count = 0; cnt->long_ticket = 0;
     cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0; cnt->dir_count[parity ^ 1] = 0;
   }
   const float beta = P.beta;
@@ -730,41 +733,65 @@ __device__ __forceinline__ bool intersect_fast(const DeviceScene& sc, const Surf
 }
 
 // BSDF::gathering_density of the surface's material (DiffuseBSDF BSDF.cpp:264-289, PhongBSDF :393-434): the number of
-// bounded-lobe samples until one lands inside the merge sphere, over the lobe restriction factor
+// bounded-lobe samples until one lands inside the merge sphere, over the lobe restriction factor.  Kept as a resumable
+// loop (begin / step) so that the deferred form below can run one rejection sample per lane per round.
+struct DensityLoop {
+  Surface s;
+  float3 center, omega, target;
+  float target_length, N, diffuse_probability, combined_adjust, power;
+  uint32_t type;
+  uint32_t key;  // trial t draws from its own stream (key, t): the outcome of a trial does not depend on who runs it, or when
+};
+__device__ __forceinline__ void density_begin(DensityLoop& L, const DeviceScene& sc, const Rng& rng, const Surface& s, float3 target, float radius,
+                                              float3 omega_world) {
+  const B2ptMaterial& m = sc.materials[s.material_index()];
+  L.s = s; L.target = target; L.key = rng.key;
+  L.center = s.to_surface(target - s.pos);
+  L.omega = s.to_surface(omega_world);
+  L.target_length = length(L.center);
+  L.N = 1.0f;
+  L.type = m.type; L.power = m.power;
+  L.diffuse_probability = 1.0f; L.combined_adjust = 1.0f;
+  if (m.type == B2PT_BSDF_PHONG) {
+    const float diffuse_adjust = lambert_adjust(L.center, radius);
+    const float specular_adjust = phong_adjust(L.omega, m.power, L.center, radius);
+    L.combined_adjust = diffuse_adjust * m.diffuse_probability + specular_adjust * (1.0f - m.diffuse_probability);
+    L.diffuse_probability =
+        diffuse_adjust * m.diffuse_probability / (diffuse_adjust * m.diffuse_probability + specular_adjust * (1.0f - m.diffuse_probability));
+  }
+}
+// delta lobes never reach the estimate (their connection throughput is zero); anything else the reference answers with infinity
+__device__ __forceinline__ bool density_has_lobe(const DensityLoop& L) { return L.type == B2PT_BSDF_DIFFUSE || L.type == B2PT_BSDF_PHONG; }
+// trial number t (1, 2, ...): one bounded-lobe sample and one bounded ray; true if it lands in the merge sphere (density = t / adjust)
+__device__ __forceinline__ bool density_trial(const DensityLoop& L, const DeviceScene& sc, float radius, float t, float& density) {
+  Rng r; r.key = mix32(L.key ^ mix32(uint32_t(t) * 0x9E3779B9u + 0x85EBCA6Bu)); r.ctr = 0;
+  float3 d;
+  float adjust = 1.0f;
+  if (L.type == B2PT_BSDF_DIFFUSE) {
+    d = sample_lambert_bounded(r, L.center, radius, L.omega, adjust);
+  } else {
+    if (r.sample() < L.diffuse_probability) { float unused; d = sample_lambert_bounded(r, L.center, radius, L.omega, unused); }
+    else d = sample_phong_bounded(r, L.omega, L.power, L.center, radius);
+    adjust = L.combined_adjust;
+  }
+  density = t / adjust;
+  return intersect_fast(sc, L.s, L.s.to_world(d), L.target_length, L.target, radius);
+}
+// one rejection sample; true when the loop is over (density holds the result)
+__device__ __forceinline__ bool density_step(DensityLoop& L, const DeviceScene& sc, float radius, float& density, unsigned long long& rays) {
+  if (!density_has_lobe(L) || !(L.N < kDensityTestLimit)) { density = INFINITY; return true; }  // DENSITY_ESTIMATION_TEST_LIMIT, BSDF.cpp:9
+  ++rays;
+  if (density_trial(L, sc, radius, L.N, density)) return true;
+  L.N += 1.0f;
+  return false;
+}
 __device__ float gathering_density(const DeviceScene& sc, Rng& rng, const Surface& s, float3 target, float radius, float3 omega_world,
                                    unsigned long long& rays) {
-  const B2ptMaterial& m = sc.materials[s.material_index()];
-  const float3 center = s.to_surface(target - s.pos);
-  const float3 omega = s.to_surface(omega_world);
-  const float target_length = length(center);
-  float N = 1.0f;
-  if (m.type == B2PT_BSDF_DIFFUSE) {
-    while (N < kDensityTestLimit) {
-      float adjust;
-      const float3 d = sample_lambert_bounded(rng, center, radius, omega, adjust);
-      ++rays;
-      if (intersect_fast(sc, s, s.to_world(d), target_length, target, radius)) return N / adjust;
-      N += 1.0f;
-    }
-    return INFINITY;
-  }
-  if (m.type == B2PT_BSDF_PHONG) {
-    const float diffuse_adjust = lambert_adjust(center, radius);
-    const float specular_adjust = phong_adjust(omega, m.power, center, radius);
-    const float combined_adjust = diffuse_adjust * m.diffuse_probability + specular_adjust * (1.0f - m.diffuse_probability);
-    const float diffuse_probability =
-        diffuse_adjust * m.diffuse_probability / (diffuse_adjust * m.diffuse_probability + specular_adjust * (1.0f - m.diffuse_probability));
-    while (N < kDensityTestLimit) {
-      float3 d;
-      if (rng.sample() < diffuse_probability) { float adjust; d = sample_lambert_bounded(rng, center, radius, omega, adjust); }
-      else d = sample_phong_bounded(rng, omega, m.power, center, radius);
-      ++rays;
-      if (intersect_fast(sc, s, s.to_world(d), target_length, target, radius)) return N / combined_adjust;
-      N += 1.0f;
-    }
-    return INFINITY;
-  }
-  return INFINITY;  // delta lobes never reach here: their connection throughput is zero
+  DensityLoop L;
+  density_begin(L, sc, rng, s, target, radius, omega_world);
+  float density = INFINITY;
+  while (!density_step(L, sc, radius, density, rays)) {}
+  return density;
 }
 
 // _merge_biased (UPG.cpp:783-817) with light = _light_paths[index - 1], tentative = _light_paths[index]
@@ -781,8 +808,9 @@ __device__ __forceinline__ float3 merge_biased(const DeviceScene& sc, const Vert
 }
 
 // _merge_light (UPG.cpp:727-753), unbiased mode
+// `deferred` != nullptr: return unoccluded * weight and leave the density to upg_density_kernel (*deferred = true when there is one to estimate)
 __device__ __forceinline__ float3 merge_light(const DeviceScene& sc, Rng& rng, const Vertex& light, const Vertex& eye, const VcmParams& P,
-                                              unsigned long long& shadow_rays, unsigned long long& density_rays) {
+                                              unsigned long long& shadow_rays, unsigned long long& density_rays, bool* deferred = nullptr) {
   const float3 omega = normalize(eye.s.pos - light.s.pos);
   const Connection c(sc, light, eye, omega);
   const float3 unoccluded = c.unoccluded();
@@ -795,13 +823,14 @@ __device__ __forceinline__ float3 merge_light(const DeviceScene& sc, Rng& rng, c
   if (trace_ray<true, true>(sc, a, b - a, 0.0f, 1.0f).tri != kInvalid) return f3(0.0f);
   // _weight_vm_light (UPG.cpp:420-426)
   const float weight = beta_fn(P.num_scattered * clamp_vm(P, P.circle * c.edge.f_geometry * c.lb.density), P.beta) * vc_weight(c, P);
+  if (deferred) { *deferred = true; return unoccluded * weight; }
   const float density = gathering_density(sc, rng, light.s, eye.s.pos, P.radius, light.omega, density_rays);
   return unoccluded * density * weight;
 }
 
 // _merge_eye (UPG.cpp:755-781), unbiased mode, merging from the camera side: the density is estimated from the eye vertex
 __device__ __forceinline__ float3 merge_eye(const DeviceScene& sc, Rng& rng, const Vertex& light, const Vertex& eye, const VcmParams& P,
-                                            unsigned long long& shadow_rays, unsigned long long& density_rays) {
+                                            unsigned long long& shadow_rays, unsigned long long& density_rays, bool* deferred = nullptr) {
   const float3 omega = normalize(eye.s.pos - light.s.pos);
   const Connection c(sc, light, eye, omega);
   const float3 unoccluded = c.unoccluded();
@@ -813,19 +842,29 @@ __device__ __forceinline__ float3 merge_eye(const DeviceScene& sc, Rng& rng, con
   if (trace_ray<true, true>(sc, a, b - a, 0.0f, 1.0f).tri != kInvalid) return f3(0.0f);
   // _weight_vm_eye (UPG.cpp:412-418)
   const float weight = beta_fn(P.num_scattered * clamp_vm(P, P.circle * c.edge.b_geometry * c.eb.density_rev), P.beta) * vc_weight(c, P);
+  if (deferred) { *deferred = true; return unoccluded * weight; }
   const float density = gathering_density(sc, rng, eye.s, light.s.pos, P.radius, eye.omega, density_rays);
   return unoccluded * density * weight;
 }
 
+// what upg_density_kernel needs to finish an unbiased merge: whose surface samples (a pool vertex, or the path's previous eye
+// vertex), towards which point, with which random stream; vertex == kJobNone: nothing was deferred
+constexpr uint32_t kJobNone = 0xFFFFFFFFu, kJobEyeVertex = 0xFFFFFFFEu;
+struct DensityJob { uint32_t vertex = kJobNone; float3 target; uint32_t key = 0; };
+
 // One merge of _gather / _gather_biased (UPG.cpp:684-693, 708-719): photon `index` against the eye path in `slot`.
 // eye = the tentative vertex (throughput already * 1 / roulette), prev_eye = the vertex before it (camera-side merging only).
 __device__ __forceinline__ float3 merge_one(const DeviceScene& sc, const VcmParams& P, const VcmPool& pool, uint32_t index, const Vertex& eye,
-                                            const Vertex& prev_eye, uint32_t path_key, unsigned long long& shadow_rays, unsigned long long& density_rays) {
+                                            const Vertex& prev_eye, uint32_t path_key, unsigned long long& shadow_rays, unsigned long long& density_rays,
+                                            DensityJob* job = nullptr) {
   if (!P.from_light) {  // UPG.cpp:690-692, 716-718: the photon itself against the eye vertex before the tentative one
     const Vertex light = load_pool_vertex(pool, index);
     if (P.unbiased) {
       Rng sub; sub.key = mix32(path_key ^ mix32(index * 0x9E3779B9u + uint32_t(eye.length()))); sub.ctr = 0;
-      return merge_eye(sc, sub, light, prev_eye, P, shadow_rays, density_rays) * P.num_scattered_inv;
+      bool deferred = false;
+      const float3 v = merge_eye(sc, sub, light, prev_eye, P, shadow_rays, density_rays, job ? &deferred : nullptr) * P.num_scattered_inv;
+      if (deferred) { job->vertex = kJobEyeVertex; job->target = light.s.pos; job->key = sub.key; }
+      return v;
     }
     return merge_biased(sc, light, light, prev_eye, P) * P.num_scattered_inv;
   }
@@ -835,7 +874,10 @@ __device__ __forceinline__ float3 merge_one(const DeviceScene& sc, const VcmPara
   if (light.s.is_light()) return f3(0.0f);  // UPG.cpp:689,713: the predecessor must be a surface vertex
   if (P.unbiased) {
     Rng sub; sub.key = mix32(path_key ^ mix32(index * 0x9E3779B9u + uint32_t(eye.length()))); sub.ctr = 0;
-    return merge_light(sc, sub, light, eye, P, shadow_rays, density_rays) * P.num_scattered_inv;
+    bool deferred = false;
+    const float3 v = merge_light(sc, sub, light, eye, P, shadow_rays, density_rays, job ? &deferred : nullptr) * P.num_scattered_inv;
+    if (deferred) { job->vertex = prev; job->target = eye.s.pos; job->key = sub.key; }
+    return v;
   }
   const Vertex tentative = load_pool_vertex(pool, index);
   return merge_biased(sc, light, tentative, eye, P) * P.num_scattered_inv;
@@ -914,13 +956,124 @@ __global__ void __launch_bounds__(256) vcm_merge_kernel(RenderConfig cfg, VcmPar
     const Vertex eye = load_slot_vertex(pool.cv, pool.pixels_pad, slot);
     Vertex prev_eye = eye;
     if (!P.from_light) prev_eye = load_slot_vertex(pool.pv, pool.pixels_pad, slot);
-    const float3 v = merge_one(sc, P, pool, e.y, eye, prev_eye, pool.rng[slot].x, shadow_rays, density_rays);
-    if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f) {
+    DensityJob job;
+    const float3 v = merge_one(sc, P, pool, e.y, eye, prev_eye, pool.rng[slot].x, shadow_rays, density_rays, P.unbiased ? &job : nullptr);
+    if (job.vertex != kJobNone) {
+      // UPG: the density estimate is a rejection loop of unpredictable length — its own stage (upg_density_kernel)
+      const unsigned j = warp_append(&cnt->job_count, true);
+      float4* o = pool.job_q + size_t(j) * 3;  // job_count <= merge_count <= m_capacity
+      o[0] = make_float4(v.x, v.y, v.z, __uint_as_float(slot));
+      o[1] = make_float4(job.target.x, job.target.y, job.target.z, __uint_as_float(job.vertex));
+      o[2] = make_float4(__uint_as_float(job.key), 0.f, 0.f, 0.f);
+    } else if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f) {
       float* r = &pool.rad[slot].x;
       atomicAdd(r + 0, v.x); atomicAdd(r + 1, v.y); atomicAdd(r + 2, v.z);
     }
   }
   if (shadow_rays) atomicAdd(&cnt->shadow_rays, shadow_rays);
+  if (density_rays) { atomicAdd(&cnt->density_rays, density_rays); atomicAdd(&cnt->basic_rays, density_rays); }
+}
+
+constexpr float kLaneTrials = 16.0f;  // trials a lane runs on its own before the loop goes to a whole warp
+
+// The unbiased merge density (BSDF::gathering_density, BSDF.cpp:42-66): sample the bounded lobe, cast a bounded ray, count the
+// tries until one lands in the merge sphere — a geometric number of iterations, a handful on average, 2^24 at most.  Persistent
+// warps: every round runs ONE trial for all lanes that hold a job, a warp refills its idle lanes from the job queue once a quarter of
+// them are idle, and a loop that has not ended after kLaneTrials trials moves to upg_density_long_kernel (measured on the LivingRoom
+// stand-in: 60 density rays per pixel-sample in total, but single loops of tens of thousands of trials, which used to set the duration
+// of the whole launch).
+__global__ void __launch_bounds__(256) upg_density_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
+  const DeviceScene& sc = cfg.scene;
+  const uint32_t n = min(cnt->job_count, pool.m_capacity);
+  const unsigned lane = threadIdx.x & 31u, lane_lt = (1u << lane) - 1u;
+  unsigned long long density_rays = 0;
+  DensityLoop L;
+  float3 coef = f3(0.0f);
+  uint32_t slot = 0, job = 0;
+  bool has = false, exhausted = false;
+  for (;;) {
+    __syncwarp();
+    const unsigned idle = __ballot_sync(0xFFFFFFFFu, !has);
+    if (!exhausted && (__popc(idle) >= 8 || idle == 0xFFFFFFFFu)) {
+      const unsigned want = __popc(idle);
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&cnt->job_ticket, want);
+      base = __shfl_sync(0xFFFFFFFFu, base, 0);
+      exhausted = base + want >= n;
+      const uint32_t i = base + __popc(idle & lane_lt);
+      if (!has && i < n) {
+        job = i;
+        const float4* o = pool.job_q + size_t(i) * 3;
+        const float4 a = o[0], b = o[1], c = o[2];
+        coef = f3(a.x, a.y, a.z); slot = __float_as_uint(a.w);
+        const uint32_t vertex = __float_as_uint(b.w);
+        const Vertex v = vertex == kJobEyeVertex ? load_slot_vertex(pool.pv, pool.pixels_pad, slot) : load_pool_vertex(pool, vertex);
+        Rng sub; sub.key = __float_as_uint(c.x); sub.ctr = 0;
+        density_begin(L, sc, sub, v.s, f3(b.x, b.y, b.z), P.radius, v.omega);
+        has = true;
+      }
+    }
+    if (__ballot_sync(0xFFFFFFFFu, has) == 0u) break;
+    if (has) {
+      float density;
+      if (density_step(L, sc, P.radius, density, density_rays)) {
+        const float3 v = coef * density;
+        float* r = &pool.rad[slot].x;
+        atomicAdd(r + 0, v.x); atomicAdd(r + 1, v.y); atomicAdd(r + 2, v.z);
+        has = false;
+      } else if (L.N > kLaneTrials) {
+        // a long loop (the sphere is mostly hidden from this surface): a whole warp takes it over, 32 trials per round
+        const unsigned j = atomicAdd(&cnt->long_count, 1u);
+        pool.merge_q[j] = make_uint2(job, uint32_t(L.N));  // the merge queue is free again: vcm_merge_kernel has consumed it
+        has = false;
+      }
+    }
+  }
+  if (density_rays) { atomicAdd(&cnt->density_rays, density_rays); atomicAdd(&cnt->basic_rays, density_rays); }
+}
+
+// Long density loops, one WARP per loop: the trials are independent (trial t has its own stream), so 32 of them run per round and
+// the first one that lands is the answer — the same estimate in 1/32 of the rounds.  Only the trials up to that one count as rays.
+__global__ void __launch_bounds__(256) upg_density_long_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
+  const DeviceScene& sc = cfg.scene;
+  const uint32_t n = min(cnt->long_count, pool.m_capacity);
+  const unsigned lane = threadIdx.x & 31u;
+  unsigned long long density_rays = 0;
+  for (;;) {
+    unsigned j = 0;
+    if (lane == 0) j = atomicAdd(&cnt->long_ticket, 1u);
+    j = __shfl_sync(0xFFFFFFFFu, j, 0);
+    if (j >= n) break;
+    const uint2 e = pool.merge_q[j];
+    const float4* o = pool.job_q + size_t(e.x) * 3;
+    const float4 a = o[0], b = o[1], c = o[2];
+    const uint32_t slot = __float_as_uint(a.w), vertex = __float_as_uint(b.w);
+    const Vertex v = vertex == kJobEyeVertex ? load_slot_vertex(pool.pv, pool.pixels_pad, slot) : load_pool_vertex(pool, vertex);
+    Rng sub; sub.key = __float_as_uint(c.x); sub.ctr = 0;
+    DensityLoop L;
+    density_begin(L, sc, sub, v.s, f3(b.x, b.y, b.z), P.radius, v.omega);
+    float N = float(e.y), density = INFINITY;
+    for (;;) {
+      const float t = N + float(lane);
+      float d = INFINITY;
+      const bool ok = t < kDensityTestLimit && density_trial(L, sc, P.radius, t, d);
+      const unsigned hit = __ballot_sync(0xFFFFFFFFu, ok);
+      if (hit) {
+        const int first = __ffs(int(hit)) - 1;
+        density = __shfl_sync(0xFFFFFFFFu, d, first);
+        if (lane == 0) density_rays += unsigned(first) + 1u;
+        break;
+      }
+      if (lane == 0) density_rays += 32u;
+      N += 32.0f;
+      if (!(N < kDensityTestLimit)) break;  // DENSITY_ESTIMATION_TEST_LIMIT: the reference answers infinity
+    }
+    if (lane == 0) {
+      const float3 r3 = f3(a.x, a.y, a.z) * density;
+      float* r = &pool.rad[slot].x;
+      atomicAdd(r + 0, r3.x); atomicAdd(r + 1, r3.y); atomicAdd(r + 2, r3.z);
+    }
+  }
   if (density_rays) { atomicAdd(&cnt->density_rays, density_rays); atomicAdd(&cnt->basic_rays, density_rays); }
 }
 
@@ -1025,6 +1178,7 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWor
   // merge pairs: 64 per pixel (VCM at the thesis radius finds tens of photons per query); what does not fit is merged in place
   p.m_capacity = uint32_t(std::min<size_t>(ne * 64, size_t(1) << 28));
   if ((rc = ws_alloc(w, &p.merge_q, p.m_capacity))) return rc;
+  if ((rc = ws_alloc(w, &p.job_q, size_t(p.m_capacity) * 3))) return rc;
   if ((rc = ws_alloc(w, &p.dir_q, ne * 4))) return rc;
   if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
   B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(VcmCounters)));
@@ -1103,6 +1257,8 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         timer.begin(kStageShade); vcm_eye_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample, it == 0 ? 1 : 0); timer.end();
         timer.begin(kStageShade); vcm_gather_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->grid.dev, w->counters, parity); timer.end();
         timer.begin(kStageShade); vcm_merge_kernel<<<grid_m, block, 0, stream>>>(cfg, P, pool, w->counters); timer.end();
+        if (P.unbiased) { timer.begin(kStageShade); upg_density_kernel<<<persistent_grid(pool.m_capacity, block), block, 0, stream>>>(cfg, P, pool, w->counters); timer.end();
+                          timer.begin(kStageShade); upg_density_long_kernel<<<persistent_grid(pool.m_capacity, block), block, 0, stream>>>(cfg, P, pool, w->counters); timer.end(); }
         timer.begin(kStageShade); vcm_connect_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity); timer.end();
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);
