@@ -18,12 +18,14 @@
 // Queues hold slot indices, compacted with one warp-aggregated atomic per warp.  Path state is SoA
 // float4 streams so each stage moves 128-bit words.  Every path owns a counter-based RNG stream
 // (rng.cuh), so the draw order inside a path is the reference's whatever the stage interleaving.
+#include <stdlib.h>
+
 #include "render_common.cuh"
 
 namespace b2pt {
 
 enum { kFree = 0, kPrimary = 1, kBounce = 2, kAwaitShadow = 3 };
-enum { kQueueTrace = 0, kQueueShadow = 1 };
+enum { kQueueTrace = 0, kQueueShadow = 1, kQueueFree = 2 };
 enum { kShadowCommit = 1u };
 
 struct PtPool {
@@ -36,7 +38,8 @@ struct PtPool {
   float4* rad;      // radiance gathered so far
   uint2* rng;       // key, counter
   unsigned long long* work;
-  uint32_t* trace_q;
+  uint32_t* trace_q[2];  // slots with an extension ray in flight = the live paths; iteration i writes [i & 1], iteration i + 1 walks it
+  uint32_t* free_q[2];   // slots the shadow stage committed and freed: the next logic stage refills them
   float4* shadow_q; // 3 float4 per entry: (org, bits slot) (dir, bits flags) (contribution, 0)
 };
 
@@ -52,18 +55,25 @@ __device__ __forceinline__ unsigned long long warp_grab_work(unsigned long long*
   return base + __popc(mask & ((1u << lane) - 1u));
 }
 
-__global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool pool, int parity) {
+// The stage walks the LIVE slots only — the trace queue of the previous iteration — plus the slots the shadow stage freed
+// (`first`: every slot, all free).  Walking the pool in slot order costs a full scan per iteration however few paths are
+// left, which is what the drain phase of a render call consists of.
+__global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool pool, int parity, int first) {
   const DeviceScene& sc = cfg.scene;
   RenderCounters* cnt = cfg.counters;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    cnt->queue_count[parity ^ 1][kQueueTrace] = 0;
+    // [parity ^ 1][trace / free] are this launch's inputs; the trace stage clears them afterwards
     cnt->queue_count[parity ^ 1][kQueueShadow] = 0;
   }
   const float beta = cfg.params.beta;
   const uint32_t max_path = cfg.params.max_path ? cfg.params.max_path : 0xFFFFFFFFu;
-  // pool_size is a multiple of the block size, so every lane of a warp runs the same trip count
-  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < cfg.pool_size; slot += gridDim.x * blockDim.x) {
-    uint32_t st = pool.state[slot];
+  const uint32_t n_trace = first ? 0u : cnt->queue_count[parity ^ 1][kQueueTrace];
+  // freed slots only matter while there is work left to hand out
+  const uint32_t n_free = (first || cnt->next_work >= cfg.total_work) ? 0u : cnt->queue_count[parity ^ 1][kQueueFree];
+  const uint32_t n_live = first ? cfg.pool_size : n_trace + n_free;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_live; i += gridDim.x * blockDim.x) {
+    const uint32_t slot = first ? i : (i < n_trace ? pool.trace_q[parity ^ 1][i] : pool.free_q[parity ^ 1][i - n_trace]);
+    uint32_t st = first ? uint32_t(kFree) : pool.state[slot];
     bool want_trace = false, want_shadow = false;
     float3 sh_o = f3(0.f), sh_d = f3(0.f), sh_c = f3(0.f);
     uint32_t sh_flags = 0;
@@ -206,7 +216,7 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
     pool.state[slot] = st;
 
     const unsigned tq = warp_append(&cnt->queue_count[parity][kQueueTrace], want_trace);
-    if (want_trace) pool.trace_q[tq] = slot;
+    if (want_trace) pool.trace_q[parity][tq] = slot;
     const unsigned sq = warp_append(&cnt->queue_count[parity][kQueueShadow], want_shadow);
     if (want_shadow) {
       float4* e = pool.shadow_q + size_t(sq) * 3;
@@ -219,9 +229,13 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
 
 __global__ void __launch_bounds__(256) pt_trace_kernel(RenderConfig cfg, PtPool pool, int parity) {
   const uint32_t n = cfg.counters->queue_count[parity][kQueueTrace];
-  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cfg.counters->basic_rays, (unsigned long long)n);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(&cfg.counters->basic_rays, (unsigned long long)n);
+    cfg.counters->queue_count[parity ^ 1][kQueueTrace] = 0;  // consumed by this iteration's logic stage
+    cfg.counters->queue_count[parity ^ 1][kQueueFree] = 0;
+  }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t slot = pool.trace_q[i];
+    const uint32_t slot = pool.trace_q[parity][i];
     const float4 o = pool.ray_o[slot], d = pool.ray_d[slot];
     // Scene::intersect: tnear 0, tfar inf, mask 0xFFFFFFFF (Scene.cpp:190-197)
     const Hit h = trace_ray<false, false>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY);
@@ -246,6 +260,7 @@ __global__ void __launch_bounds__(256) pt_shadow_kernel(RenderConfig cfg, PtPool
     if (flags & kShadowCommit) {
       commit_sample(cfg, pool.work[slot], f3(r.x, r.y, r.z));
       pool.state[slot] = kFree;
+      pool.free_q[parity][warp_append(&cfg.counters->queue_count[parity][kQueueFree], true)] = slot;
     }
   }
 }
@@ -256,7 +271,7 @@ struct PtWorkspace {
   uint32_t pool_size = 0;
   RenderCounters* counters = nullptr;
   RenderCounters* host_counters = nullptr;  // pinned
-  void* blocks[16] = {nullptr};
+  void* blocks[24] = {nullptr};
   int num_blocks = 0;
 };
 
@@ -294,7 +309,10 @@ static int pt_workspace(b2pt_scene_s* scene, uint32_t pool_size, PtWorkspace** o
   if ((rc = ws_alloc(w, &w->pool.rad, pool_size))) return rc;
   if ((rc = ws_alloc(w, &w->pool.rng, pool_size))) return rc;
   if ((rc = ws_alloc(w, &w->pool.work, pool_size))) return rc;
-  if ((rc = ws_alloc(w, &w->pool.trace_q, pool_size))) return rc;
+  for (int k = 0; k < 2; ++k) {
+    if ((rc = ws_alloc(w, &w->pool.trace_q[k], pool_size))) return rc;
+    if ((rc = ws_alloc(w, &w->pool.free_q[k], pool_size))) return rc;
+  }
   if ((rc = ws_alloc(w, &w->pool.shadow_q, size_t(pool_size) * 3))) return rc;
   if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
   B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(RenderCounters)));
@@ -305,7 +323,11 @@ static int pt_workspace(b2pt_scene_s* scene, uint32_t pool_size, PtWorkspace** o
 int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
   const int block = 256;
   // pool: enough slots to fill the machine several times over, never more than the work, multiple of the block
-  unsigned long long want = base.total_work < (1ull << 21) ? base.total_work : (1ull << 21);
+  // measured (LivingRoom stand-in, 1024^2): 16 passes run at 110 / 124 / 138 / 161 Msamples/s with 2^21 / 2^22 / 2^23 / 2^24 slots, 64 passes at 154 / 197
+  // with 2^24 / 2^26: the more paths in flight the larger the launches, and refilled slots are slower to shade than fresh ones (scattered pixels)
+  unsigned long long cap = 1ull << 25;
+  { const char* e = getenv("B2PT_PT_POOL_LOG2"); if (e) { int v = atoi(e); if (v >= 10 && v <= 26) cap = 1ull << v; } }  // A/B runs
+  unsigned long long want = base.total_work < cap ? base.total_work : cap;
   uint32_t pool_size = uint32_t((want + block - 1) / block * block);
   PtWorkspace* w = nullptr;
   if (int rc = pt_workspace(scene, pool_size, &w)) return rc;
@@ -313,14 +335,13 @@ int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream
   cfg.pool_size = pool_size;
   cfg.counters = w->counters;
   B2_CUDA(cudaMemsetAsync(w->counters, 0, sizeof(RenderCounters), stream));
-  B2_CUDA(cudaMemsetAsync(w->pool.state, 0, size_t(pool_size) * 4, stream));
   const int grid = grid_for(pool_size, block);
   StageTimer timer(stream);
   const int kBatch = 8;  // stage iterations between two looks at the device counters
   for (int it = 0;; ) {
     for (int k = 0; k < kBatch; ++k, ++it) {
       const int parity = it & 1;
-      timer.begin(kStageShade); pt_logic_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity); timer.end();
+      timer.begin(kStageShade); pt_logic_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity, it == 0 ? 1 : 0); timer.end();
       timer.begin(kStageTrace); pt_trace_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity); timer.end();
       timer.begin(kStageShadow); pt_shadow_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity); timer.end();
     }
