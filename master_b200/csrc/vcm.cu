@@ -45,6 +45,7 @@ struct VcmCounters {
   unsigned int trace_count[2], pair_count[2], shadow_count[2], gather_count[2], dir_count[2];
   unsigned int merge_count;  // (eye vertex, photon) pairs of the current iteration; cleared by the eye stage
   unsigned int long_count, long_ticket;  // UPG: density loops handed to whole warps (upg_density_long_kernel)
+  unsigned int wide_count;               // UPG: density loops handed to the whole grid (upg_density_wide_kernel)
   unsigned int job_count, job_ticket;  // UPG: merges whose density is still to be estimated, and the fetch counter of the stage that does it
 };
 
@@ -88,6 +89,8 @@ struct VcmPool {
   // queues
   float4* job_q;  // UPG density jobs, 3 float4 each: (unoccluded * weight, bits slot) (target, bits vertex) (bits key, -, -, -); m_capacity entries
   uint2* merge_q; uint32_t m_capacity;  // (eye slot, photon index) pairs found by the gather stage, evaluated one per thread
+  uint2* wide_q;      // UPG: (job, first untried trial) of the density loops the whole grid finishes; kWideCap entries
+  uint2* wide_state;  // per entry: (first trial that landed, chunk ticket); (0xFFFFFFFF, 0) between uses
   uint32_t* trace_q[2];  // live slots (extension ray in flight), written by iteration i into [i & 1]: the next logic stage walks it
   uint2* pair_q; float4* shadow_q; uint32_t* gather_q;
   float4* dir_q;  // connections to sun lights, 4 float4 per entry (render_common.cuh: directional_kernel)
@@ -428,7 +431,7 @@ __device__ __forceinline__ float3 connect_light(const DeviceScene& sc, const Ver
 __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample, int first) {
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    cnt->pair_count[parity ^ 1] = 0; cnt->merge_count = 0; cnt->job_count = 0; cnt->job_ticket = 0; cnt->long_count = 0; cnt->long_ticket = 0;
+    cnt->pair_count[parity ^ 1] = 0; cnt->merge_count = 0; cnt->job_count = 0; cnt->job_ticket = 0; cnt->long_count = 0; cnt->long_ticket = 0; cnt->wide_count = 0;
     cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0; cnt->dir_count[parity ^ 1] = 0;
   }
   const float beta = P.beta;
@@ -975,6 +978,9 @@ __global__ void __launch_bounds__(256) vcm_merge_kernel(RenderConfig cfg, VcmPar
 }
 
 constexpr float kLaneTrials = 16.0f;  // trials a lane runs on its own before the loop goes to a whole warp
+constexpr float kWarpTrials = 16384.0f;  // trials a warp runs before the loop goes to the whole grid
+constexpr uint32_t kWideCap = 4096;      // loops the grid stage takes per eye iteration (the rest stay with their warp)
+constexpr int kWideChunk = 128;          // trials per ticket in the grid stage
 
 // The unbiased merge density (BSDF::gathering_density, BSDF.cpp:42-66): sample the bounded lobe, cast a bounded ray, count the
 // tries until one lands in the merge sphere — a geometric number of iterations, a handful on average, 2^24 at most.  Persistent
@@ -1053,7 +1059,17 @@ __global__ void __launch_bounds__(256) upg_density_long_kernel(RenderConfig cfg,
     DensityLoop L;
     density_begin(L, sc, sub, v.s, f3(b.x, b.y, b.z), P.radius, v.omega);
     float N = float(e.y), density = INFINITY;
+    const float N_wide = N + kWarpTrials;
+    bool handed_over = false;
     for (;;) {
+      if (N >= N_wide) {
+        // still nothing after kWarpTrials trials: most of these run to the test limit (the sphere is hidden from the surface) — 2^24 trials
+        // are two seconds for one warp and a millisecond for the grid
+        unsigned h = 0;
+        if (lane == 0) h = atomicAdd(&cnt->wide_count, 1u);
+        h = __shfl_sync(0xFFFFFFFFu, h, 0);
+        if (h < kWideCap) { if (lane == 0) pool.wide_q[h] = make_uint2(e.x, uint32_t(N)); handed_over = true; break; }
+      }
       const float t = N + float(lane);
       float d = INFINITY;
       const bool ok = t < kDensityTestLimit && density_trial(L, sc, P.radius, t, d);
@@ -1068,13 +1084,79 @@ __global__ void __launch_bounds__(256) upg_density_long_kernel(RenderConfig cfg,
       N += 32.0f;
       if (!(N < kDensityTestLimit)) break;  // DENSITY_ESTIMATION_TEST_LIMIT: the reference answers infinity
     }
-    if (lane == 0) {
+    if (lane == 0 && !handed_over) {
       const float3 r3 = f3(a.x, a.y, a.z) * density;
       float* r = &pool.rad[slot].x;
       atomicAdd(r + 0, r3.x); atomicAdd(r + 1, r3.y); atomicAdd(r + 2, r3.z);
     }
   }
   if (density_rays) { atomicAdd(&cnt->density_rays, density_rays); atomicAdd(&cnt->basic_rays, density_rays); }
+}
+
+// The longest density loops, one GRID per loop: warps draw chunks of kWideChunk trials from the loop's ticket until a chunk starts past
+// the first trial known to have landed (atomicMin) or past the test limit.  The answer is the smallest landing trial, as in the serial loop.
+__global__ void __launch_bounds__(256) upg_density_wide_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
+  const DeviceScene& sc = cfg.scene;
+  const uint32_t n = min(cnt->wide_count, kWideCap);
+  const unsigned lane = threadIdx.x & 31u;
+  for (uint32_t h = 0; h < n; ++h) {
+    const uint2 e = pool.wide_q[h];
+    const float4* o = pool.job_q + size_t(e.x) * 3;
+    const float4 a = o[0], b = o[1], c = o[2];
+    const uint32_t slot = __float_as_uint(a.w), vertex = __float_as_uint(b.w);
+    const Vertex v = vertex == kJobEyeVertex ? load_slot_vertex(pool.pv, pool.pixels_pad, slot) : load_pool_vertex(pool, vertex);
+    Rng sub; sub.key = __float_as_uint(c.x); sub.ctr = 0;
+    DensityLoop L;
+    density_begin(L, sc, sub, v.s, f3(b.x, b.y, b.z), P.radius, v.omega);
+    unsigned int* best = &pool.wide_state[h].x;
+    unsigned int* ticket = &pool.wide_state[h].y;
+    for (;;) {
+      unsigned chunk = 0;
+      if (lane == 0) chunk = atomicAdd(ticket, 1u);
+      chunk = __shfl_sync(0xFFFFFFFFu, chunk, 0);
+      const float base = float(e.y) + float(chunk) * float(kWideChunk);
+      if (!(base < kDensityTestLimit) || base > float(*(volatile unsigned int*)best)) break;
+      bool found = false;
+      for (int k = 0; k < kWideChunk / 32 && !found; ++k) {
+        const float t = base + float(k * 32) + float(lane);
+        float d;
+        const bool ok = t < kDensityTestLimit && density_trial(L, sc, P.radius, t, d);
+        const unsigned hit = __ballot_sync(0xFFFFFFFFu, ok);
+        if (hit) {
+          if (lane == 0) atomicMin(best, uint32_t(base) + uint32_t(k * 32) + uint32_t(__ffs(int(hit)) - 1));
+          found = true;
+        }
+      }
+      if (found) break;
+    }
+  }
+}
+// ... and its second half, once every warp is done: one thread per loop adds the estimate and re-arms the loop's state
+__global__ void __launch_bounds__(256) upg_density_wide_finish_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
+  const DeviceScene& sc = cfg.scene;
+  const uint32_t n = min(cnt->wide_count, kWideCap);
+  for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
+    const uint2 e = pool.wide_q[h];
+    const float4* o = pool.job_q + size_t(e.x) * 3;
+    const float4 a = o[0], b = o[1], c = o[2];
+    const uint32_t slot = __float_as_uint(a.w), vertex = __float_as_uint(b.w);
+    const uint32_t best = pool.wide_state[h].x;
+    pool.wide_state[h] = make_uint2(0xFFFFFFFFu, 0u);
+    float density = INFINITY;  // DENSITY_ESTIMATION_TEST_LIMIT reached: the reference answers infinity
+    unsigned long long rays = (unsigned long long)(kDensityTestLimit) - e.y;
+    if (best != 0xFFFFFFFFu) {
+      const Vertex v = vertex == kJobEyeVertex ? load_slot_vertex(pool.pv, pool.pixels_pad, slot) : load_pool_vertex(pool, vertex);
+      Rng sub; sub.key = __float_as_uint(c.x); sub.ctr = 0;
+      DensityLoop L;
+      density_begin(L, sc, sub, v.s, f3(b.x, b.y, b.z), P.radius, v.omega);
+      density_trial(L, sc, P.radius, float(best), density);
+      rays = best - e.y + 1u;
+    }
+    const float3 r3 = f3(a.x, a.y, a.z) * density;
+    float* r = &pool.rad[slot].x;
+    atomicAdd(r + 0, r3.x); atomicAdd(r + 1, r3.y); atomicAdd(r + 2, r3.z);
+    atomicAdd(&cnt->density_rays, rays); atomicAdd(&cnt->basic_rays, rays);
+  }
 }
 
 // Technique::_commit_images (Technique.cpp:194-244) for one pass
@@ -1179,6 +1261,12 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWor
   p.m_capacity = uint32_t(std::min<size_t>(ne * 64, size_t(1) << 28));
   if ((rc = ws_alloc(w, &p.merge_q, p.m_capacity))) return rc;
   if ((rc = ws_alloc(w, &p.job_q, size_t(p.m_capacity) * 3))) return rc;
+  if ((rc = ws_alloc(w, &p.wide_q, kWideCap))) return rc;
+  if ((rc = ws_alloc(w, &p.wide_state, kWideCap))) return rc;
+  {
+    std::vector<uint2> init(kWideCap, make_uint2(0xFFFFFFFFu, 0u));
+    if (cudaMemcpy(p.wide_state, init.data(), sizeof(uint2) * kWideCap, cudaMemcpyHostToDevice) != cudaSuccess) return B2PT_ERR_CUDA;
+  }
   if ((rc = ws_alloc(w, &p.dir_q, ne * 4))) return rc;
   if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
   B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(VcmCounters)));
@@ -1258,7 +1346,9 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         timer.begin(kStageShade); vcm_gather_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->grid.dev, w->counters, parity); timer.end();
         timer.begin(kStageShade); vcm_merge_kernel<<<grid_m, block, 0, stream>>>(cfg, P, pool, w->counters); timer.end();
         if (P.unbiased) { timer.begin(kStageShade); upg_density_kernel<<<persistent_grid(pool.m_capacity, block), block, 0, stream>>>(cfg, P, pool, w->counters); timer.end();
-                          timer.begin(kStageShade); upg_density_long_kernel<<<persistent_grid(pool.m_capacity, block), block, 0, stream>>>(cfg, P, pool, w->counters); timer.end(); }
+                          timer.begin(kStageShade); upg_density_long_kernel<<<persistent_grid(pool.m_capacity, block), block, 0, stream>>>(cfg, P, pool, w->counters);
+                          upg_density_wide_kernel<<<kNumSMs * 2, block, 0, stream>>>(cfg, P, pool, w->counters);
+                          upg_density_wide_finish_kernel<<<(kWideCap + block - 1) / block, block, 0, stream>>>(cfg, P, pool, w->counters); timer.end(); }
         timer.begin(kStageShade); vcm_connect_kernel<<<grid_e, block, 0, stream>>>(cfg, P, pool, w->counters, parity); timer.end();
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);
