@@ -197,7 +197,7 @@ __device__ __forceinline__ float camera_coefficient(float3 light_omega, float3 l
   const float normal_c = fabsf(dot(eye_omega, light_gnormal) * dot(light_omega, light_normal) /
                                (dot(eye_omega, light_normal) * dot(light_omega, light_gnormal)));
   const float c = fabsf(dot(eye_normal, eye_omega));
-  return normal_c * (1.0f / cr_powf(c, 3.0f));
+  return normal_c * (1.0f / cr_cubef(c));
 }
 
 // warp-aggregated reservation of `n` consecutive queue entries per lane (one atomic per warp)

@@ -92,7 +92,16 @@ __device__ __forceinline__ float cr_sinf(float x) { return float(sin(double(x)))
 __device__ __forceinline__ float cr_cosf(float x) { return float(cos(double(x))); }
 __device__ __forceinline__ float cr_asinf(float x) { return float(asin(double(x))); }
 __device__ __forceinline__ float cr_atan2f(float y, float x) { return float(atan2(double(y), double(x))); }
-__device__ __forceinline__ float cr_powf(float x, float y) { return float(pow(double(x), double(y))); }
+// pow for the arguments shading has (0 < x, finite): exp2(y log2 x) in double is ~2^-42 relative for the exponents used here — still
+// far inside half a float ulp — at a third of the instructions of double pow (which carries an extended-precision logarithm)
+__device__ __forceinline__ float cr_powf(float x, float y) {
+  if (x > 0.0f && x < INFINITY) return float(exp2(double(y) * log2(double(x))));
+  return float(pow(double(x), double(y)));
+}
+__device__ __forceinline__ float cr_cubef(float x) { const double d = double(x); return float(d * d * d); }  // powf(x, 3.0f)
+// sin and cos of one angle: one range reduction
+__device__ __forceinline__ void cr_sincosf(float x, float& s, float& c) { double ds, dc; sincos(double(x), &ds, &dc); s = float(ds); c = float(dc); }
+__device__ __forceinline__ float3 cr_polar(float r, float y, float phi) { float s, c; cr_sincosf(phi, s, c); return f3(r * c, y, r * s); }
 
 // ---------------------------------------------------------------- warp-aggregated queue append
 // One atomic per warp: ballot the lanes that append, lane 0 of the group reserves, everyone

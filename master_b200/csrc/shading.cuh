@@ -157,7 +157,7 @@ __device__ __forceinline__ float3 sample_lambert(Rng& rng, float3 omega) {
   const float y = sqrtf(rng.sample()) * sign_glm(omega.y);
   const float r = sqrtf(1.0f - y * y);
   const float phi = rng.sample() * 2.0f * kPi;
-  return f3(r * cr_cosf(phi), y, r * cr_sinf(phi));
+  return cr_polar(r, y, phi);
 }
 
 // sample_lambert(generator, sphere, omega) (Sample.inl:58-82): lobe restricted to the cone around a sphere
@@ -168,7 +168,7 @@ __device__ __forceinline__ float3 sample_lambert_bounded(Rng& rng, float3 center
   const float y = sqrtf(rng.sample() * lr.theta_range + lr.theta_inf) * sign_glm(omega.y);
   const float phi = kTwoPi * (rng.sample() * lr.phi_range + lr.phi_inf);
   const float r = sqrtf(1 - y * y);
-  return f3(r * cr_cosf(phi), y, r * cr_sinf(phi));
+  return cr_polar(r, y, phi);
 }
 
 // reflection_to_surface (Sample.inl:39-46)
@@ -186,7 +186,7 @@ __device__ __forceinline__ float3 sample_phong(Rng& rng, float3 omega, float pow
   const float y = cr_powf(rng.sample(), 1.0f / (power + 1.0f));
   const float r = sqrtf(1.0f - y * y);
   const float phi = rng.sample() * 2.0f * kPi;
-  return mul(refl_to_surf, f3(r * cr_cosf(phi), y, r * cr_sinf(phi)));
+  return mul(refl_to_surf, cr_polar(r, y, phi));
 }
 
 // sample_phong(generator, omega, power, sphere) / phong_adjust (Sample.inl:151-205): Phong lobe restricted to the cone
@@ -216,7 +216,7 @@ __device__ __forceinline__ float3 sample_phong_bounded(Rng& rng, float3 omega, f
   const float y = cr_powf(rng.sample() * pr.theta_range + pr.theta_inf, 1.0f / (power + 1.0f));
   const float phi = kTwoPi * (rng.sample() * pr.phi_range + pr.phi_inf);
   const float r = sqrtf(1 - y * y);
-  return mul(pr.reflection, f3(r * cr_cosf(phi), y, r * cr_sinf(phi)));
+  return mul(pr.reflection, cr_polar(r, y, phi));
 }
 
 // ---------------------------------------------------------------- BSDF::query (BSDF.cpp)

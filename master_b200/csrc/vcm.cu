@@ -245,7 +245,7 @@ __device__ __forceinline__ float3 connect_vertices(const DeviceScene& sc, const 
 __device__ __forceinline__ float camera_coefficient(float3 light_omega, float3 light_gnormal, float3 light_normal, float3 eye_omega, float3 eye_normal) {
   const float normal_c = fabsf(dot(eye_omega, light_gnormal) * dot(light_omega, light_normal) / (dot(eye_omega, light_normal) * dot(light_omega, light_gnormal)));
   const float c = fabsf(dot(eye_normal, eye_omega));
-  return normal_c * (1.0f / cr_powf(c, 3.0f));
+  return normal_c * (1.0f / cr_cubef(c));
 }
 
 __device__ __forceinline__ unsigned warp_reserve(unsigned* counter, unsigned n) {
