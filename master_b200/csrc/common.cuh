@@ -88,19 +88,22 @@ constexpr float kFltMin = 1.175494351e-38f;
 // VCM / UPG a flipped photon path changes every eye path that merges with it.  Evaluating in double and rounding once
 // reproduces the correctly rounded float result (double error ~1e-16 relative, far below half a float ulp except on
 // exact ties) and removes most of those flips.  Shading is a small share of the step; the FP64 pipe is otherwise idle.
+#ifndef B2PT_MATH_INLINE
+#define B2PT_MATH_INLINE static __noinline__  // one copy per kernel: the shading stages stall on instruction fetch (40 % of warp-state samples), code size is what they pay for
+#endif
 __device__ __forceinline__ float cr_sinf(float x) { return float(sin(double(x))); }
 __device__ __forceinline__ float cr_cosf(float x) { return float(cos(double(x))); }
 __device__ __forceinline__ float cr_asinf(float x) { return float(asin(double(x))); }
 __device__ __forceinline__ float cr_atan2f(float y, float x) { return float(atan2(double(y), double(x))); }
 // pow for the arguments shading has (0 < x, finite): exp2(y log2 x) in double is ~2^-42 relative for the exponents used here — still
 // far inside half a float ulp — at a third of the instructions of double pow (which carries an extended-precision logarithm)
-__device__ __forceinline__ float cr_powf(float x, float y) {
+__device__ B2PT_MATH_INLINE float cr_powf(float x, float y) {
   if (x > 0.0f && x < INFINITY) return float(exp2(double(y) * log2(double(x))));
   return float(pow(double(x), double(y)));
 }
 __device__ __forceinline__ float cr_cubef(float x) { const double d = double(x); return float(d * d * d); }  // powf(x, 3.0f)
 // sin and cos of one angle: one range reduction
-__device__ __forceinline__ void cr_sincosf(float x, float& s, float& c) { double ds, dc; sincos(double(x), &ds, &dc); s = float(ds); c = float(dc); }
+__device__ B2PT_MATH_INLINE void cr_sincosf(float x, float& s, float& c) { double ds, dc; sincos(double(x), &ds, &dc); s = float(ds); c = float(dc); }
 __device__ __forceinline__ float3 cr_polar(float r, float y, float phi) { float s, c; cr_sincosf(phi, s, c); return f3(r * c, y, r * s); }
 
 // ---------------------------------------------------------------- warp-aggregated queue append
