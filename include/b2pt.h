@@ -211,6 +211,19 @@ int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accu
 int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* params, double* view_host,
                      B2ptStats* stats);
 
+/*
+ * The error record of a pass (Technique.cpp:68-74) on the DEVICE film: rms_abs_errors (ImageView.cpp:60-85) of
+ * accum_dev (width*height dvec4) against reference_dev (width*height vec3, floats, same row order), or, with
+ * window = {center_x, center_y, radius}, rms_abs_errors_windowed (ImageView.cpp:87-117) over the pixels
+ * max(0, c - r + 1) <= p < min(c + r, size) — what Technique::_make_measurements evaluates per trace point.
+ * Per pixel the arithmetic is the reference's (d = |vec3(a.xyz / a.w) - b| in float, d.x + d.y + d.z, dot(d, d));
+ * the sums over pixels are taken in double (the reference adds them in float, in row order), so the results agree
+ * with the reference's to float summation error, not bit for bit.  out (HOST): out[0] = rms, out[1] = abs.
+ * The whole image divides by width*height*3, a window by its pixel count, as the reference does.
+ */
+int b2pt_film_errors(const double* accum_dev, const float* reference_dev, uint32_t width, uint32_t height,
+                     const int32_t* window, float* out, void* stream);
+
 /* ---- photon index: v3::HashGrid3D<T>::build / rQuery (HashGrid3D.hpp:181-325) ---- */
 typedef struct b2pt_grid_s* b2pt_grid_t;
 /* points: n * 3 floats (HOST).  Builds the sorted cell grid on the device. */

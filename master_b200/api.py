@@ -107,7 +107,7 @@ class Stats(C.Structure):
 EXPORTS = [
     "b2pt_last_error", "b2pt_abi_version", "b2pt_device_count", "b2pt_scene_create", "b2pt_scene_destroy",
     "b2pt_scene_info", "b2pt_trace", "b2pt_trace_device", "b2pt_render", "b2pt_render_host", "b2pt_grid_build",
-    "b2pt_grid_destroy", "b2pt_grid_query",
+    "b2pt_grid_destroy", "b2pt_grid_query", "b2pt_film_errors",
 ]
 
 _lib = None
@@ -139,6 +139,7 @@ def load_library():
     lib.b2pt_grid_destroy.argtypes = [C.c_void_p]
     lib.b2pt_grid_destroy.restype = None
     lib.b2pt_grid_query.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p, C.c_void_p]
+    lib.b2pt_film_errors.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_float), C.c_void_p]
     _lib = lib
     return lib
 

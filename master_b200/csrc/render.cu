@@ -11,6 +11,36 @@ int render_pt(b2pt_scene_s* scene, const RenderConfig& cfg, cudaStream_t stream,
 int render_bpt(b2pt_scene_s* scene, const RenderConfig& cfg, cudaStream_t stream, B2ptStats* stats);
 int render_vcm(b2pt_scene_s* scene, const RenderConfig& cfg, cudaStream_t stream, B2ptStats* stats);
 
+// rms_abs_errors / rms_abs_errors_windowed (ImageView.cpp:60-117): per-pixel terms as the reference computes them, summed in double.
+// sums[0] += dot(d, d), sums[1] += d.x + d.y + d.z, sums[2] += 1 per pixel of the window
+__global__ void __launch_bounds__(256) film_errors_kernel(const double* __restrict__ accum, const float* __restrict__ ref, uint32_t width,
+                                                          int x0, int y0, int x1, int y1, double* sums) {
+  const uint32_t w = uint32_t(x1 - x0), n = w * uint32_t(y1 - y0);
+  double sq = 0.0, ab = 0.0, cnt = 0.0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const size_t p = size_t(y0 + int(i / w)) * width + size_t(x0 + int(i % w));
+    const double2 rg = *reinterpret_cast<const double2*>(accum + p * 4), bw = *reinterpret_cast<const double2*>(accum + p * 4 + 2);
+    const float dx = fabsf(float(rg.x / bw.y) - ref[p * 3 + 0]);
+    const float dy = fabsf(float(rg.y / bw.y) - ref[p * 3 + 1]);
+    const float dz = fabsf(float(bw.x / bw.y) - ref[p * 3 + 2]);
+    ab += double(__fadd_rn(__fadd_rn(dx, dy), dz));
+    sq += double(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));  // glm::dot: tmp = a * b; tmp.x + tmp.y + tmp.z
+    cnt += 1.0;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    sq += __shfl_down_sync(0xFFFFFFFFu, sq, o); ab += __shfl_down_sync(0xFFFFFFFFu, ab, o); cnt += __shfl_down_sync(0xFFFFFFFFu, cnt, o);
+  }
+  __shared__ double part[3][8];
+  const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  if (lane == 0) { part[0][warp] = sq; part[1][warp] = ab; part[2][warp] = cnt; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double t = 0.0;
+    for (int k = 0; k < 8; ++k) t += part[threadIdx.x][k];
+    atomicAdd(sums + threadIdx.x, t);
+  }
+}
+
 static int make_config(b2pt_scene_s* scene, const B2ptRenderParams* p, double* accum, float* path_radiance, RenderConfig* cfg) {
   B2_CHECK(p->width > 0 && p->height > 0, B2PT_ERR_INVALID, "b2pt_render: empty window");
   B2_CHECK(p->technique <= B2PT_TECHNIQUE_UPG, B2PT_ERR_INVALID, "b2pt_render: unknown technique");
@@ -77,6 +107,39 @@ int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accu
   local.num_samples = params->num_samples;
   local.num_paths = cfg.total_work;
   if (stats) *stats = local;
+  return B2PT_OK;
+}
+
+int b2pt_film_errors(const double* accum_dev, const float* reference_dev, uint32_t width, uint32_t height, const int32_t* window, float* out,
+                     void* stream_) {
+  using namespace b2pt;
+  B2_CHECK(accum_dev && reference_dev && out, B2PT_ERR_INVALID, "b2pt_film_errors: null argument");
+  B2_CHECK(width > 0 && height > 0, B2PT_ERR_INVALID, "b2pt_film_errors: empty image");
+  int dev_count = 0;
+  if (cudaGetDeviceCount(&dev_count) != cudaSuccess || dev_count == 0) { cudaGetLastError(); B2_CHECK(false, B2PT_ERR_NO_DEVICE, "b2pt_film_errors: no CUDA device"); }
+  cudaStream_t stream = (cudaStream_t)stream_;
+  int x0 = 0, y0 = 0, x1 = int(width), y1 = int(height);
+  if (window) {  // ImageView.cpp:103-104
+    x0 = max(0, window[0] - window[2] + 1); x1 = min(window[0] + window[2], int(width));
+    y0 = max(0, window[1] - window[2] + 1); y1 = min(window[1] + window[2], int(height));
+  }
+  double sums[3] = {0.0, 0.0, 0.0};
+  if (x1 > x0 && y1 > y0) {
+    double* sums_dev = nullptr;
+    B2_CUDA(cudaMalloc(&sums_dev, sizeof(sums)));
+    cudaMemsetAsync(sums_dev, 0, sizeof(sums), stream);
+    const size_t n = size_t(x1 - x0) * size_t(y1 - y0);
+    const int block = 256, grid = int(std::min<size_t>((n + block - 1) / block, size_t(kNumSMs) * 4));
+    film_errors_kernel<<<grid, block, 0, stream>>>(accum_dev, reference_dev, width, x0, y0, x1, y1, sums_dev);
+    cudaError_t e = cudaMemcpyAsync(sums, sums_dev, sizeof(sums), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(sums_dev);
+    B2_CUDA(e);
+  }
+  // whole image: num = width * height * 3 (ImageView.cpp:81-84); window: num = pixels (ImageView.cpp:109-116); an empty window is 0 / 0
+  const float num = window ? float(sums[2]) : float(size_t(width) * height * 3);
+  out[0] = sqrtf(float(sums[0]) / num);
+  out[1] = float(sums[1]) / num;
   return B2PT_OK;
 }
 

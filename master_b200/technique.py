@@ -63,6 +63,19 @@ class GpuTechnique:
         return stats
 
 
+def film_errors_device(accum_ptr, reference_ptr, width, height, window=None, stream=0):
+    """(rms, abs) of a DEVICE film against a DEVICE reference image (width*height*3 floats): rms_abs_errors, or with
+    window=(center_x, center_y, radius) rms_abs_errors_windowed (ImageView.cpp:60-117) — the per-pass record of
+    Technique::render (Technique.cpp:68-74) without bringing the film to the host."""
+    out = (C.c_float * 2)()
+    win = None
+    if window is not None:
+        win = (C.c_int32 * 3)(*[int(v) for v in window])
+    api.check(api.load_library().b2pt_film_errors(C.c_void_p(accum_ptr), C.c_void_p(reference_ptr), width, height, win, out,
+                                                  C.c_void_p(stream)))
+    return float(out[0]), float(out[1])
+
+
 def make_technique(scene, options):
     """makeTechnique(scene, options) (make_technique.cpp:112-170) for the GPU techniques."""
     options = dict(options)
