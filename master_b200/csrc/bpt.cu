@@ -56,6 +56,7 @@ struct BptCounters {
   unsigned int done;
   unsigned int lv_count;
   unsigned int trace_count[2], pair_count[2], shadow_count[2];
+  unsigned int light_count[2];  // the live queue has two ends: eye-phase paths from the front (trace_count), light-phase paths from the back
   unsigned int dir_count[2];
   unsigned int ticket[2];  // dynamic ray fetch of the traversal stages (trace, shadow), zeroed by the logic stage
 };
@@ -235,13 +236,18 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
   const float roulette_inv = 1.0f / roulette;
   const uint32_t max_subpath = cfg.params.max_subpath ? cfg.params.max_subpath : 1024u;
   // trip counts are rounded up to whole warps: every lane of a warp reaches the warp_* helpers below
-  const uint32_t n_live = first ? pool.size : cnt->trace_count[parity ^ 1];
-  const uint32_t n_round = (n_live + 31u) & ~31u;
+  // the two ends of the live queue are walked one after the other, each rounded up to whole warps: a warp holds paths of one phase
+  const uint32_t n_eye = first ? 0u : cnt->trace_count[parity ^ 1];
+  const uint32_t n_light = first ? pool.size : cnt->light_count[parity ^ 1];
+  const uint32_t n_eye_round = (n_eye + 31u) & ~31u;
+  const uint32_t n_round = n_eye_round + ((n_light + 31u) & ~31u);
   const uint32_t* live_q = pool.trace_q[parity ^ 1];
   uint32_t* next_q = pool.trace_q[parity];
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
-    const bool lane_on = i < n_live;
-    const uint32_t slot = lane_on ? (first ? i : live_q[i]) : 0u;
+    const bool eye_end = i < n_eye_round;
+    const uint32_t j = eye_end ? i : i - n_eye_round;
+    const bool lane_on = j < (eye_end ? n_eye : n_light);
+    const uint32_t slot = lane_on ? (first ? j : live_q[eye_end ? j : pool.size - 1u - j]) : 0u;
     float4* rec = pool.rec + size_t(slot) * kRecFloat4s;
     // iteration 0 of a batch never reads the records: every slot is born kNew
     const uint32_t st0 = lane_on ? (first ? uint32_t(kNew) : __float_as_uint(rec[kRecState].x)) : uint32_t(kDone);
@@ -487,8 +493,10 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
       const unsigned mask = __ballot_sync(0xFFFFFFFFu, finished);
       if (mask && (threadIdx.x & 31u) == 0) atomicAdd(&cnt->done, unsigned(__popc(mask)));
     }
-    const unsigned tq = warp_append(&cnt->trace_count[parity], want_trace);
-    if (want_trace) next_q[tq] = slot;
+    const bool to_eye_end = want_trace && st == kEyeWait;
+    const unsigned tq = warp_append(&cnt->trace_count[parity], to_eye_end);
+    const unsigned lq = warp_append(&cnt->light_count[parity], want_trace && !to_eye_end);
+    if (want_trace) next_q[to_eye_end ? tq : pool.size - 1u - lq] = slot;
     unsigned pq = warp_reserve(&cnt->pair_count[parity], emit_n);
     if (emit_n) {
       if (pq + emit_n > pool.q_capacity) {
@@ -597,8 +605,9 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel
 struct BptTraceIo {
   const BptPool* pool;
   const uint32_t* q;
+  uint32_t n_eye;  // entries [0, n_eye) from the front of the queue, the rest from its back
   __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
-    const uint32_t slot = q[i];
+    const uint32_t slot = q[i < n_eye ? i : pool->size - 1u - (i - n_eye)];
     const float4* rec = pool->rec + size_t(slot) * kRecFloat4s;
     const float4 o = rec[kRecRayO], d = rec[kRecOmega];
     O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY;
@@ -635,12 +644,14 @@ struct BptShadowIo {
 
 template <int kStream>
 __global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
-  const uint32_t n = cnt->trace_count[parity];
+  const uint32_t n_eye = cnt->trace_count[parity];
+  const uint32_t n = n_eye + cnt->light_count[parity];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     atomicAdd(&cnt->basic_rays, (unsigned long long)n);
     cnt->trace_count[parity ^ 1] = 0;  // consumed by this iteration's logic stage; the next one appends to it
+    cnt->light_count[parity ^ 1] = 0;
   }
-  BptTraceIo io{&pool, pool.trace_q[parity]};
+  BptTraceIo io{&pool, pool.trace_q[parity], n_eye};
   if (kStream == 2) { trace_dyn8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   if (kStream == 1) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
