@@ -29,7 +29,10 @@
 #include "render_common.cuh"
 
 #ifndef B2PT_LOGIC_MIN_BLOCKS
-#define B2PT_LOGIC_MIN_BLOCKS 3  // resident CTAs per SM the shading stages are compiled for (register cap = 65536 / (256 * this))
+// resident CTAs per SM the shading stages are compiled for (register cap = 65536 / (256 * this)).  Measured with the two-ended live queue:
+// 1: 72.6, 2: 75.3, 3: 73.4, 4: 71.6, 5: 68.0 Msamples/s — spills cost more than occupancy gives.  (Prefetching the next item's record and
+// shading frame across grid strides was measured too: 72.8 vs 74.7 — with two batches in flight the other batch's kernels already fill the stalls.)
+#define B2PT_LOGIC_MIN_BLOCKS 2
 #endif
 #ifndef B2PT_TRACE_MIN_BLOCKS
 #define B2PT_TRACE_MIN_BLOCKS 4  // traversal stages: 64 registers per thread
