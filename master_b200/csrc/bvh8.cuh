@@ -29,4 +29,9 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t k) {
   return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u | k)) - 8388608.0f;
 }
 
+// 2^15 + byte, exactly: the byte lands in mantissa bits 8..15 of 2^15 (whose ulp is 2^-8)
+__device__ __forceinline__ float byte_to_float15(uint32_t word, uint32_t k) {
+  return __uint_as_float(__byte_perm(word, 0x47000000u, 0x7604u | (k << 4)));
+}
+
 }  // namespace b2pt
