@@ -814,11 +814,13 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   cfg.pool_size = size;
   const int grid = grid_for(size, block);
   const int grid_t = persistent_grid(size, block);  // traversal stages: persistent warps fetch rays from a ticket counter
-  // measured on the LivingRoom stand-in (profiles/README.md): with the queue sizes of a BPT batch one ray per thread is 8 % faster
-  // end to end than the persistent warp-synchronous traversal, which only wins on >= 4 M incoherent rays per launch;
-  // B2PT_TRACE_STREAM=1 selects the latter for A/B runs
+  // traversal form per stage: 0 = one ray per thread, 1 = persistent warps with dynamic fetch, 2 = the same plus postponed triangle
+  // groups (trace.cuh: trace_dyn8).  B2PT_TRACE_STREAM / B2PT_SHADOW_STREAM select them for A/B runs; measured on the LivingRoom
+  // stand-in with 2^23-path batches: closest-hit 2 / any-hit 2 = 79.4 Msamples/s against 76.3 for 0 / 0.
   const char* tv = getenv("B2PT_TRACE_STREAM");
-  const int stream_trace = tv ? (tv[0] == '1' ? 1 : tv[0] == '2' ? 2 : 0) : 0, stream_shadow = stream_trace;
+  const char* sv = getenv("B2PT_SHADOW_STREAM");
+  const int stream_trace = tv ? (tv[0] == '1' ? 1 : tv[0] == '0' ? 0 : 2) : 2;
+  const int stream_shadow = sv ? (sv[0] == '1' ? 1 : sv[0] == '0' ? 0 : 2) : stream_trace;
   unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
   const int kBatchIters = 8;
 
