@@ -24,6 +24,9 @@
 // the photon's predecessor is connected to the tentative eye vertex) and from the camera side (--from-camera: the
 // eye vertex BEFORE the tentative one is connected to the photon itself; UPG.cpp:687-719).
 #include "grid.cuh"
+#include <string>
+#include <thread>
+
 #include "render_common.cuh"
 
 namespace b2pt {
@@ -1172,7 +1175,8 @@ __global__ void __launch_bounds__(256) vcm_commit_kernel(RenderConfig cfg, VcmPo
     }
     double* a = cfg.accum + size_t(pixel) * 4;
     if (isfinite(fabs(r) + fabs(g) + fabs(b))) {
-      a[0] += r; a[1] += g; a[2] += b; a[3] += 1.0;
+      // two passes may commit the same pixel at the same time (render_vcm runs two lanes)
+      atomicAdd(a + 0, r); atomicAdd(a + 1, g); atomicAdd(a + 2, b); atomicAdd(a + 3, 1.0);
     } else {
       atomicAdd(&cnt->numeric_errors, 1ull);
     }
@@ -1213,13 +1217,48 @@ int ws_alloc(VcmWorkspace* w, T** p, size_t count) {
   return B2PT_OK;
 }
 
-int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWorkspace** out) {
-  VcmWorkspace* w = (VcmWorkspace*)scene->workspace;
-  if (w && scene->workspace_free == vcm_workspace_free && w->pixels == pixels && w->photons == photons) { *out = w; return B2PT_OK; }
-  if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
-  scene->workspace = nullptr;
-  w = new VcmWorkspace();
-  scene->workspace = w; scene->workspace_free = vcm_workspace_free;
+// Passes are independent (each builds its own photon map), so two of them run at a time, each in its own workspace on its own
+// stream, driven by its own host thread (render_vcm): one pass alone leaves the GPU to launches of a few hundred thousand rays.
+constexpr int kVcmLanes = 2;
+struct VcmWorkspaceSet {
+  VcmWorkspace* lane[kVcmLanes] = {nullptr, nullptr};
+  cudaStream_t stream1 = nullptr;  // lane 1 (lane 0 runs on the caller's stream)
+  cudaEvent_t fork = nullptr;
+  uint32_t pixels = 0, photons = 0;
+};
+void vcm_workspace_set_free(void* p) {
+  VcmWorkspaceSet* set = (VcmWorkspaceSet*)p;
+  for (VcmWorkspace* w : set->lane) if (w) vcm_workspace_free(w);
+  if (set->stream1) cudaStreamDestroy(set->stream1);
+  if (set->fork) cudaEventDestroy(set->fork);
+  delete set;
+}
+
+int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons);
+
+int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, int lanes, VcmWorkspaceSet** out) {
+  VcmWorkspaceSet* set = (VcmWorkspaceSet*)scene->workspace;
+  if (!(set && scene->workspace_free == vcm_workspace_set_free && set->pixels == pixels && set->photons == photons)) {
+    if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
+    scene->workspace = nullptr;
+    set = new VcmWorkspaceSet();
+    scene->workspace = set; scene->workspace_free = vcm_workspace_set_free;
+    set->pixels = pixels; set->photons = photons;
+  }
+  for (int k = 0; k < lanes; ++k) {
+    if (set->lane[k]) continue;
+    set->lane[k] = new VcmWorkspace();
+    if (int rc = vcm_workspace_fill(set->lane[k], pixels, photons)) return rc;
+  }
+  if (lanes > 1 && !set->stream1) {
+    B2_CUDA(cudaStreamCreateWithFlags(&set->stream1, cudaStreamNonBlocking));
+    B2_CUDA(cudaEventCreateWithFlags(&set->fork, cudaEventDisableTiming));
+  }
+  *out = set;
+  return B2PT_OK;
+}
+
+int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons) {
   w->pixels = pixels; w->photons = photons;
   const uint32_t block = 256;
   VcmPool& p = w->pool;
@@ -1273,31 +1312,34 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, VcmWor
   B2_CUDA(cudaMemset(p.splat, 0, ne * 3 * sizeof(double)));
   B2_CUDA(cudaMemset(p.lp_head, 0xFF, nl * 4));
   B2_CUDA(cudaMemset(p.lp_count, 0, nl * 4));
-  *out = w;
   return B2PT_OK;
 }
 
 }  // namespace
 
-int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
+struct VcmLaneResult {
+  int rc = B2PT_OK;
+  unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
+  float ms[kNumStages] = {0.f, 0.f, 0.f};
+  uint64_t launches[kNumStages] = {0, 0, 0};
+  std::string error;
+};
+
+// passes first, first + step, ... of the call, one after the other, in workspace w on `stream`
+static int vcm_run_passes(const RenderConfig& base, VcmWorkspace* w, cudaStream_t stream, uint32_t first, uint32_t step, uint32_t photons,
+                          VcmLaneResult* out) {
   const B2ptRenderParams& rp = base.params;
-  B2_CHECK(rp.radius > 0.0f, B2PT_ERR_INVALID, "VCM/UPG: radius must be positive");
   const uint32_t pixels = base.pixels;
-  const uint32_t photons = rp.num_photons ? rp.num_photons : pixels;  // Options.cpp:914-916
-  // UPGBase::_connect reads _light_offsets[pixel_index + 1] (UPG.cpp:556-560): one light path per pixel is assumed
-  B2_CHECK(photons >= pixels, B2PT_ERR_INVALID, "VCM/UPG: num_photons must be at least width * height (UPG.cpp:556-560)");
-  B2_CHECK(photons <= (1u << 24), B2PT_ERR_CAPACITY, "VCM/UPG: more than 2^24 light paths per pass");
   const int block = 256;
-  VcmWorkspace* w = nullptr;
-  if (int rc = vcm_workspace(scene, pixels, photons, &w)) return rc;
   VcmPool& pool = w->pool;
   RenderConfig cfg = base;
   StageTimer timer(stream);
-  unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
+  unsigned long long& basic = out->basic; unsigned long long& shadow = out->shadow;
+  unsigned long long& numeric = out->numeric; unsigned long long& capacity = out->capacity;
   const int kBatchIters = 8;
   const uint32_t stride = rp.sample_stride ? rp.sample_stride : 1u;
   const int grid_p = grid_for(pool.photons, block), grid_e = grid_for(pool.pixels_pad, block);
-  for (uint32_t pass = 0; pass < rp.num_samples; ++pass) {
+  for (uint32_t pass = first; pass < rp.num_samples; pass += step) {
     const uint32_t sample = rp.first_sample + pass * stride;
     VcmParams P;
     P.beta = rp.beta; P.roulette = rp.roulette; P.roulette_inv = 1.0f / rp.roulette;
@@ -1376,12 +1418,53 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     numeric += w->host_counters->numeric_errors; capacity += w->host_counters->capacity_events;
   }
   B2_CUDA(cudaGetLastError());
+  for (int k = 0; k < kNumStages; ++k) { out->ms[k] = timer.ms[k]; out->launches[k] = timer.launches[k]; }
+  return B2PT_OK;
+}
+
+int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
+  const B2ptRenderParams& rp = base.params;
+  B2_CHECK(rp.radius > 0.0f, B2PT_ERR_INVALID, "VCM/UPG: radius must be positive");
+  const uint32_t pixels = base.pixels;
+  const uint32_t photons = rp.num_photons ? rp.num_photons : pixels;  // Options.cpp:914-916
+  // UPGBase::_connect reads _light_offsets[pixel_index + 1] (UPG.cpp:556-560): one light path per pixel is assumed
+  B2_CHECK(photons >= pixels, B2PT_ERR_INVALID, "VCM/UPG: num_photons must be at least width * height (UPG.cpp:556-560)");
+  B2_CHECK(photons <= (1u << 24), B2PT_ERR_CAPACITY, "VCM/UPG: more than 2^24 light paths per pass");
+  int lanes = kVcmLanes;
+  { const char* e = getenv("B2PT_VCM_LANES"); if (e) lanes = std::max(1, std::min(kVcmLanes, atoi(e))); }  // A/B runs
+  lanes = int(std::min<uint32_t>(uint32_t(lanes), std::max(1u, rp.num_samples)));
+  VcmWorkspaceSet* set = nullptr;
+  if (int rc = vcm_workspace(scene, pixels, photons, lanes, &set)) return rc;
+  VcmLaneResult res[kVcmLanes];
+  if (lanes == 1) {
+    res[0].rc = vcm_run_passes(base, set->lane[0], stream, 0, 1, photons, &res[0]);
+  } else {
+    // lane 1 starts after whatever the caller has queued on `stream` (the film may have just been cleared there)
+    int device = 0;
+    B2_CUDA(cudaGetDevice(&device));
+    B2_CUDA(cudaEventRecord(set->fork, stream));
+    B2_CUDA(cudaStreamWaitEvent(set->stream1, set->fork, 0));
+    std::thread other([&]() {
+      if (cudaSetDevice(device) != cudaSuccess) { res[1].rc = B2PT_ERR_CUDA; res[1].error = "render_vcm: cudaSetDevice failed in lane 1"; return; }
+      res[1].rc = vcm_run_passes(base, set->lane[1], set->stream1, 1, 2, photons, &res[1]);
+      if (res[1].rc != B2PT_OK) res[1].error = b2pt_last_error();
+    });
+    res[0].rc = vcm_run_passes(base, set->lane[0], stream, 0, 2, photons, &res[0]);
+    if (res[0].rc != B2PT_OK) res[0].error = b2pt_last_error();
+    other.join();  // every lane synchronises its stream at the end of each pass: all work is complete here
+    for (int k = 0; k < lanes; ++k) if (res[k].rc != B2PT_OK) { set_error(res[k].error); return res[k].rc; }
+  }
+  if (res[0].rc != B2PT_OK) return res[0].rc;
   if (stats) {
-    stats->num_basic_rays = basic;
-    stats->num_shadow_rays = shadow;
-    stats->numeric_errors = numeric;
-    stats->capacity_events = capacity;
-    timer.fill(stats);
+    stats->num_basic_rays = 0; stats->num_shadow_rays = 0; stats->numeric_errors = 0; stats->capacity_events = 0;
+    stats->trace_ms = 0; stats->shadow_ms = 0; stats->shade_ms = 0; stats->trace_launches = 0; stats->shadow_launches = 0; stats->kernel_launches = 0;
+    for (int k = 0; k < lanes; ++k) {
+      stats->num_basic_rays += res[k].basic; stats->num_shadow_rays += res[k].shadow;
+      stats->numeric_errors += res[k].numeric; stats->capacity_events += res[k].capacity;
+      stats->trace_ms += res[k].ms[kStageTrace]; stats->shadow_ms += res[k].ms[kStageShadow]; stats->shade_ms += res[k].ms[kStageShade];
+      stats->trace_launches += res[k].launches[kStageTrace]; stats->shadow_launches += res[k].launches[kStageShadow];
+      stats->kernel_launches += res[k].launches[0] + res[k].launches[1] + res[k].launches[2];
+    }
   }
   return B2PT_OK;
 }
