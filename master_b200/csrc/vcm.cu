@@ -1175,7 +1175,7 @@ __global__ void __launch_bounds__(256) vcm_commit_kernel(RenderConfig cfg, VcmPo
     }
     double* a = cfg.accum + size_t(pixel) * 4;
     if (isfinite(fabs(r) + fabs(g) + fabs(b))) {
-      // two passes may commit the same pixel at the same time (render_vcm runs two lanes)
+      // passes in different lanes may commit the same pixel at the same time (render_vcm)
       atomicAdd(a + 0, r); atomicAdd(a + 1, g); atomicAdd(a + 2, b); atomicAdd(a + 3, 1.0);
     } else {
       atomicAdd(&cnt->numeric_errors, 1ull);
@@ -1219,24 +1219,26 @@ int ws_alloc(VcmWorkspace* w, T** p, size_t count) {
 
 // Passes are independent (each builds its own photon map), so two of them run at a time, each in its own workspace on its own
 // stream, driven by its own host thread (render_vcm): one pass alone leaves the GPU to launches of a few hundred thousand rays.
-constexpr int kVcmLanes = 2;
+constexpr int kVcmLanes = 8;       // most passes in flight (B2PT_VCM_LANES)
+constexpr int kVcmDefaultLanes = 4;  // measured on the LivingRoom stand-in, 1024^2: 1 lane 15.2, 2: 22.8, 3: 25.8, 4: 29.1, 8: 29.6 Msamples/s (VCM)
 struct VcmWorkspaceSet {
-  VcmWorkspace* lane[kVcmLanes] = {nullptr, nullptr};
-  cudaStream_t stream1 = nullptr;  // lane 1 (lane 0 runs on the caller's stream)
+  VcmWorkspace* lane[kVcmLanes] = {};
+  cudaStream_t stream[kVcmLanes] = {};  // lanes 1.. (lane 0 runs on the caller's stream)
   cudaEvent_t fork = nullptr;
   uint32_t pixels = 0, photons = 0;
 };
 void vcm_workspace_set_free(void* p) {
   VcmWorkspaceSet* set = (VcmWorkspaceSet*)p;
   for (VcmWorkspace* w : set->lane) if (w) vcm_workspace_free(w);
-  if (set->stream1) cudaStreamDestroy(set->stream1);
+  for (cudaStream_t st : set->stream) if (st) cudaStreamDestroy(st);
   if (set->fork) cudaEventDestroy(set->fork);
   delete set;
 }
 
 int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons);
 
-int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, int lanes, VcmWorkspaceSet** out) {
+int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, int* lanes_io, VcmWorkspaceSet** out) {
+  int lanes = *lanes_io;
   VcmWorkspaceSet* set = (VcmWorkspaceSet*)scene->workspace;
   if (!(set && scene->workspace_free == vcm_workspace_set_free && set->pixels == pixels && set->photons == photons)) {
     if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
@@ -1248,12 +1250,18 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, int la
   for (int k = 0; k < lanes; ++k) {
     if (set->lane[k]) continue;
     set->lane[k] = new VcmWorkspace();
-    if (int rc = vcm_workspace_fill(set->lane[k], pixels, photons)) return rc;
+    if (int rc = vcm_workspace_fill(set->lane[k], pixels, photons)) {
+      // not enough memory for another pass in flight: run with the lanes that fit
+      vcm_workspace_free(set->lane[k]); set->lane[k] = nullptr;
+      cudaGetLastError();
+      if (k == 0) return rc;
+      lanes = k;
+      break;
+    }
   }
-  if (lanes > 1 && !set->stream1) {
-    B2_CUDA(cudaStreamCreateWithFlags(&set->stream1, cudaStreamNonBlocking));
-    B2_CUDA(cudaEventCreateWithFlags(&set->fork, cudaEventDisableTiming));
-  }
+  *lanes_io = lanes;
+  for (int k = 1; k < lanes; ++k) if (!set->stream[k]) B2_CUDA(cudaStreamCreateWithFlags(&set->stream[k], cudaStreamNonBlocking));
+  if (lanes > 1 && !set->fork) B2_CUDA(cudaEventCreateWithFlags(&set->fork, cudaEventDisableTiming));
   *out = set;
   return B2PT_OK;
 }
@@ -1430,11 +1438,11 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   // UPGBase::_connect reads _light_offsets[pixel_index + 1] (UPG.cpp:556-560): one light path per pixel is assumed
   B2_CHECK(photons >= pixels, B2PT_ERR_INVALID, "VCM/UPG: num_photons must be at least width * height (UPG.cpp:556-560)");
   B2_CHECK(photons <= (1u << 24), B2PT_ERR_CAPACITY, "VCM/UPG: more than 2^24 light paths per pass");
-  int lanes = kVcmLanes;
+  int lanes = kVcmDefaultLanes;
   { const char* e = getenv("B2PT_VCM_LANES"); if (e) lanes = std::max(1, std::min(kVcmLanes, atoi(e))); }  // A/B runs
   lanes = int(std::min<uint32_t>(uint32_t(lanes), std::max(1u, rp.num_samples)));
   VcmWorkspaceSet* set = nullptr;
-  if (int rc = vcm_workspace(scene, pixels, photons, lanes, &set)) return rc;
+  if (int rc = vcm_workspace(scene, pixels, photons, &lanes, &set)) return rc;
   VcmLaneResult res[kVcmLanes];
   if (lanes == 1) {
     res[0].rc = vcm_run_passes(base, set->lane[0], stream, 0, 1, photons, &res[0]);
@@ -1443,15 +1451,18 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
     int device = 0;
     B2_CUDA(cudaGetDevice(&device));
     B2_CUDA(cudaEventRecord(set->fork, stream));
-    B2_CUDA(cudaStreamWaitEvent(set->stream1, set->fork, 0));
-    std::thread other([&]() {
-      if (cudaSetDevice(device) != cudaSuccess) { res[1].rc = B2PT_ERR_CUDA; res[1].error = "render_vcm: cudaSetDevice failed in lane 1"; return; }
-      res[1].rc = vcm_run_passes(base, set->lane[1], set->stream1, 1, 2, photons, &res[1]);
-      if (res[1].rc != B2PT_OK) res[1].error = b2pt_last_error();
-    });
-    res[0].rc = vcm_run_passes(base, set->lane[0], stream, 0, 2, photons, &res[0]);
+    std::vector<std::thread> others;
+    for (int k = 1; k < lanes; ++k) {
+      B2_CUDA(cudaStreamWaitEvent(set->stream[k], set->fork, 0));
+      others.emplace_back([&, k]() {
+        if (cudaSetDevice(device) != cudaSuccess) { res[k].rc = B2PT_ERR_CUDA; res[k].error = "render_vcm: cudaSetDevice failed in a lane thread"; return; }
+        res[k].rc = vcm_run_passes(base, set->lane[k], set->stream[k], uint32_t(k), uint32_t(lanes), photons, &res[k]);
+        if (res[k].rc != B2PT_OK) res[k].error = b2pt_last_error();
+      });
+    }
+    res[0].rc = vcm_run_passes(base, set->lane[0], stream, 0, uint32_t(lanes), photons, &res[0]);
     if (res[0].rc != B2PT_OK) res[0].error = b2pt_last_error();
-    other.join();  // every lane synchronises its stream at the end of each pass: all work is complete here
+    for (auto& t : others) t.join();  // every lane synchronises its stream at the end of each pass: all work is complete here
     for (int k = 0; k < lanes; ++k) if (res[k].rc != B2PT_OK) { set_error(res[k].error); return res[k].rc; }
   }
   if (res[0].rc != B2PT_OK) return res[0].rc;
