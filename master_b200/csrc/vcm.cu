@@ -50,6 +50,7 @@ struct VcmCounters {
   unsigned int long_count, long_ticket;  // UPG: density loops handed to whole warps (upg_density_long_kernel)
   unsigned int wide_count;               // UPG: density loops handed to the whole grid (upg_density_wide_kernel)
   unsigned int job_count, job_ticket;  // UPG: merges whose density is still to be estimated, and the fetch counter of the stage that does it
+  unsigned int ray_ticket;             // ray fetch counter of the persistent closest-hit stages, zeroed by the logic stage before them
 };
 
 // the per-pass constants of UPGBase (UPG.hpp:119-137)
@@ -272,6 +273,7 @@ __device__ __forceinline__ unsigned warp_reserve(unsigned* counter, unsigned n) 
 // Like every logic stage here it walks the LIVE paths only (the trace queue of the previous iteration; `first` walks all slots).
 __global__ void __launch_bounds__(256) vcm_photon_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt, int parity, uint32_t sample, int first) {
   const DeviceScene& sc = cfg.scene;
+  if (blockIdx.x == 0 && threadIdx.x == 0) cnt->ray_ticket = 0;
   const float beta = P.beta;
   const uint32_t n_live = first ? pool.photons : cnt->trace_count[parity ^ 1];
   const uint32_t n_round = (n_live + 31u) & ~31u;
@@ -394,6 +396,33 @@ __global__ void __launch_bounds__(256) vcm_photon_kernel(RenderConfig cfg, VcmPa
   }
 }
 
+// closest-hit queries of a logic stage as trace_dyn8 reads and writes them (trace.cuh): rays from (origin, direction) streams by slot
+struct VcmTraceIo {
+  const uint32_t* q;
+  const float4* ray_o; const float4* ray_d;
+  float4* hit;
+  uint32_t mask;
+  __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& m) const {
+    const uint32_t slot = q[i];
+    const float4 o = ray_o[slot], d = ray_d[slot];
+    O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY; m = mask;
+    return slot;
+  }
+  __device__ __forceinline__ void store(uint32_t slot, const Hit& h) const { hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri)); }
+};
+// kPhoton: light subpaths (Scene::intersectMesh), else eye subpaths (Scene::intersect); persistent warps, dynamic fetch
+template <bool kPhoton>
+__global__ void __launch_bounds__(256, 4) vcm_trace_dyn_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
+  const uint32_t n = cnt->trace_count[parity];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(&cnt->basic_rays, (unsigned long long)n);
+    cnt->trace_count[parity ^ 1] = 0;  // consumed by this iteration's logic stage
+  }
+  VcmTraceIo io{pool.trace_q[parity], kPhoton ? pool.p_ray_o : pool.ray_o, kPhoton ? pool.p_bs_omega : pool.bs_omega,
+                kPhoton ? pool.p_hit : pool.hit, kPhoton ? kMaskMesh : kMaskAll};
+  trace_dyn8<false>(cfg.scene, n, &cnt->ray_ticket, io);
+}
+
 __global__ void __launch_bounds__(256) vcm_photon_trace_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
   const uint32_t n = cnt->trace_count[parity];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -436,6 +465,7 @@ __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParam
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     cnt->pair_count[parity ^ 1] = 0; cnt->merge_count = 0; cnt->job_count = 0; cnt->job_ticket = 0; cnt->long_count = 0; cnt->long_ticket = 0; cnt->wide_count = 0;
     cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0; cnt->dir_count[parity ^ 1] = 0;
+    cnt->ray_ticket = 0;
   }
   const float beta = P.beta;
   const uint32_t n_live = first ? pool.pixels_pad : cnt->trace_count[parity ^ 1];
@@ -1347,6 +1377,9 @@ static int vcm_run_passes(const RenderConfig& base, VcmWorkspace* w, cudaStream_
   const int kBatchIters = 8;
   const uint32_t stride = rp.sample_stride ? rp.sample_stride : 1u;
   const int grid_p = grid_for(pool.photons, block), grid_e = grid_for(pool.pixels_pad, block);
+  // closest-hit stages through trace_dyn8 when B2PT_TRACE_STREAM=2 (A/B)
+  const char* tv = getenv("B2PT_TRACE_STREAM");
+  const bool dyn_trace = tv && tv[0] == '2' && cfg.scene.nodes8;
   for (uint32_t pass = first; pass < rp.num_samples; pass += step) {
     const uint32_t sample = rp.first_sample + pass * stride;
     VcmParams P;
@@ -1369,7 +1402,10 @@ static int vcm_run_passes(const RenderConfig& base, VcmWorkspace* w, cudaStream_
       for (int k = 0; k < kBatchIters; ++k, ++it) {
         const int parity = it & 1;
         timer.begin(kStageShade); vcm_photon_kernel<<<grid_p, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample, it == 0 ? 1 : 0); timer.end();
-        timer.begin(kStageTrace); vcm_photon_trace_kernel<<<grid_p, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+        timer.begin(kStageTrace);
+        if (dyn_trace) vcm_trace_dyn_kernel<true><<<persistent_grid(pool.photons, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
+        else vcm_photon_trace_kernel<<<grid_p, block, 0, stream>>>(cfg, pool, w->counters, parity);
+        timer.end();
       }
       B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(VcmCounters), cudaMemcpyDeviceToHost, stream));
       B2_CUDA(cudaStreamSynchronize(stream));
@@ -1407,7 +1443,10 @@ static int vcm_run_passes(const RenderConfig& base, VcmWorkspace* w, cudaStream_
                                                           pool.rad, 1u, &w->counters->basic_rays);
           timer.end();
         }
-        timer.begin(kStageTrace); vcm_trace_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+        timer.begin(kStageTrace);
+        if (dyn_trace) vcm_trace_dyn_kernel<false><<<persistent_grid(pool.pixels_pad, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
+        else vcm_trace_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity);
+        timer.end();
         timer.begin(kStageShadow); vcm_shadow_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
       }
       B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(VcmCounters), cudaMemcpyDeviceToHost, stream));
