@@ -928,6 +928,7 @@ __device__ __forceinline__ float3 merge_one(const DeviceScene& sc, const VcmPara
 // shadow ray and the density-estimation loop): evaluated inside the query loop, a warp runs as long as its longest query with
 // whatever lanes still have photons left; as pairs, every lane always has one.  Queries that do not fit the queue any more
 // (m_capacity) evaluate their merges in place, so the result never depends on the capacity.
+constexpr uint32_t kFoundMax = 48;  // photons per query kept from the counting pass (queries that find more walk the cells a second time)
 __global__ void __launch_bounds__(256) vcm_gather_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, DeviceGrid grid, VcmCounters* cnt, int parity) {
   const DeviceScene& sc = cfg.scene;
   const uint32_t n = cnt->gather_count[parity];
@@ -940,6 +941,7 @@ __global__ void __launch_bounds__(256) vcm_gather_kernel(RenderConfig cfg, VcmPa
     const float4 p0 = pool.cv[slot];  // float4 0 of the tentative vertex: its position
     const float3 q = f3(p0.x, p0.y, p0.z);
     uint32_t count = 0;
+    uint32_t found[kFoundMax];
     if (on) {
       if (P.brute_vertices) {  // diagnostic: every stored vertex instead of the grid
         for (uint32_t k = 0; k < P.brute_vertices; ++k) {
@@ -947,13 +949,18 @@ __global__ void __launch_bounds__(256) vcm_gather_kernel(RenderConfig cfg, VcmPa
           if (__float_as_uint(g.w) != kInvalidPoint && distance2(q, f3(g.x, g.y, g.z)) < radius_sq) ++count;
         }
       } else {
-        grid_query(grid, q, radius_sq, [&](uint32_t, float3) { ++count; });
+        // the first kFoundMax photons are remembered, so that the usual query walks its 27 cells once, not twice
+        grid_query(grid, q, radius_sq, [&](uint32_t index, float3) { if (count < kFoundMax) found[count] = index; ++count; });
       }
     }
     unsigned base = warp_reserve(&cnt->merge_count, count);
     if (count == 0) continue;
     if (base + count <= pool.m_capacity && !P.brute_vertices) {
-      grid_query(grid, q, radius_sq, [&](uint32_t index, float3) { pool.merge_q[base++] = make_uint2(slot, index); });
+      if (count <= kFoundMax) {
+        for (uint32_t k = 0; k < count; ++k) pool.merge_q[base + k] = make_uint2(slot, found[k]);
+      } else {
+        grid_query(grid, q, radius_sq, [&](uint32_t index, float3) { pool.merge_q[base++] = make_uint2(slot, index); });
+      }
     } else {
       // no room (or the diagnostic mode): blank whatever part of the reservation lies inside the queue, merge in place
       for (unsigned k = base; k < base + count && k < pool.m_capacity; ++k) pool.merge_q[k] = make_uint2(kInvalid, 0u);
