@@ -20,6 +20,11 @@
 // (rng.cuh), so the draw order inside a path is the reference's whatever the stage interleaving.
 #include <stdlib.h>
 
+#include <algorithm>
+#include <string>
+#include <thread>
+#include <vector>
+
 #include "render_common.cuh"
 
 namespace b2pt {
@@ -318,13 +323,42 @@ static int ws_alloc(PtWorkspace* w, T** p, size_t count) {
   return B2PT_OK;
 }
 
-static int pt_workspace(b2pt_scene_s* scene, uint32_t pool_size, PtWorkspace** out) {
-  PtWorkspace* w = (PtWorkspace*)scene->workspace;
-  if (w && scene->workspace_free == pt_workspace_free && w->pool_size == pool_size) { *out = w; return B2PT_OK; }
-  if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
-  scene->workspace = nullptr;
-  w = new PtWorkspace();
-  scene->workspace = w; scene->workspace_free = pt_workspace_free;
+// Two halves of a call's passes run at the same time, each in its own pool on its own stream with its own host thread (render_pt):
+// the latency-bound logic stage of one half overlaps the issue-bound traversal stages of the other.
+constexpr int kPtLanes = 4;        // most lanes (B2PT_PT_LANES)
+constexpr int kPtDefaultLanes = 2;
+struct PtWorkspaceSet {
+  PtWorkspace* lane[kPtLanes] = {};
+  cudaStream_t stream[kPtLanes] = {};  // lanes 1.. (lane 0 runs on the caller's stream)
+  cudaEvent_t fork = nullptr;
+};
+static void pt_workspace_set_free(void* p) {
+  PtWorkspaceSet* set = (PtWorkspaceSet*)p;
+  for (PtWorkspace* w : set->lane) if (w) pt_workspace_free(w);
+  for (cudaStream_t st : set->stream) if (st) cudaStreamDestroy(st);
+  if (set->fork) cudaEventDestroy(set->fork);
+  delete set;
+}
+
+static int pt_workspace_fill(PtWorkspace* w, uint32_t pool_size);
+
+static int pt_workspace(b2pt_scene_s* scene, int k, uint32_t pool_size, PtWorkspaceSet** out_set, PtWorkspace** out) {
+  PtWorkspaceSet* set = (PtWorkspaceSet*)scene->workspace;
+  if (!(set && scene->workspace_free == pt_workspace_set_free)) {
+    if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
+    scene->workspace = nullptr;
+    set = new PtWorkspaceSet();
+    scene->workspace = set; scene->workspace_free = pt_workspace_set_free;
+  }
+  *out_set = set;
+  if (set->lane[k] && set->lane[k]->pool_size == pool_size) { *out = set->lane[k]; return B2PT_OK; }
+  if (set->lane[k]) { pt_workspace_free(set->lane[k]); set->lane[k] = nullptr; }
+  set->lane[k] = new PtWorkspace();
+  *out = set->lane[k];
+  return pt_workspace_fill(set->lane[k], pool_size);
+}
+
+static int pt_workspace_fill(PtWorkspace* w, uint32_t pool_size) {
   w->pool_size = pool_size;
   int rc;
   if ((rc = ws_alloc(w, &w->pool.state, pool_size))) return rc;
@@ -343,11 +377,10 @@ static int pt_workspace(b2pt_scene_s* scene, uint32_t pool_size, PtWorkspace** o
   if ((rc = ws_alloc(w, &w->pool.shadow_q, size_t(pool_size) * 3))) return rc;
   if ((rc = ws_alloc(w, &w->counters, 1))) return rc;
   B2_CUDA(cudaMallocHost((void**)&w->host_counters, sizeof(RenderCounters)));
-  *out = w;
   return B2PT_OK;
 }
 
-int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
+static uint32_t pt_pool_size(const RenderConfig& base) {
   const int block = 256;
   // pool: enough slots to fill the machine several times over, never more than the work, multiple of the block
   // measured (LivingRoom stand-in, 1024^2): 16 passes run at 110 / 124 / 138 / 161 Msamples/s with 2^21 / 2^22 / 2^23 / 2^24 slots, 64 passes at 154 / 197
@@ -356,8 +389,13 @@ int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream
   { const char* e = getenv("B2PT_PT_POOL_LOG2"); if (e) { int v = atoi(e); if (v >= 10 && v <= 26) cap = 1ull << v; } }  // A/B runs
   unsigned long long want = base.total_work < cap ? base.total_work : cap;
   uint32_t pool_size = uint32_t((want + block - 1) / block * block);
-  PtWorkspace* w = nullptr;
-  if (int rc = pt_workspace(scene, pool_size, &w)) return rc;
+  return pool_size;
+}
+
+// one lane: the passes of `base` in pool w on `stream`, synchronous
+static int render_pt_lane(const RenderConfig& base, PtWorkspace* w, cudaStream_t stream, B2ptStats* stats) {
+  const int block = 256;
+  const uint32_t pool_size = w->pool_size;
   RenderConfig cfg = base;
   cfg.pool_size = pool_size;
   cfg.counters = w->counters;
@@ -395,6 +433,69 @@ int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream
     stats->numeric_errors = c.numeric_errors;
     stats->capacity_events = c.capacity_events;
     timer.fill(stats);
+  }
+  return B2PT_OK;
+}
+
+
+int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream, B2ptStats* stats) {
+  const B2ptRenderParams& rp = base.params;
+  int lanes = kPtDefaultLanes;
+  { const char* e = getenv("B2PT_PT_LANES"); if (e) lanes = std::max(1, std::min(kPtLanes, atoi(e))); }  // A/B runs
+  // per-path radiance is written by pass index: only a single lane keeps that layout
+  if (base.path_radiance) lanes = 1;
+  lanes = int(std::min<uint32_t>(uint32_t(lanes), std::max(1u, rp.num_samples)));
+  RenderConfig cfg[kPtLanes];
+  PtWorkspaceSet* set = nullptr;
+  PtWorkspace* w[kPtLanes] = {};
+  const uint32_t stride = rp.sample_stride ? rp.sample_stride : 1u;
+  for (int k = 0; k < lanes; ++k) {
+    cfg[k] = base;
+    if (lanes > 1) {  // lane k takes passes k, k + lanes, ...
+      cfg[k].params.first_sample = rp.first_sample + uint32_t(k) * stride;
+      cfg[k].params.sample_stride = stride * uint32_t(lanes);
+      cfg[k].params.num_samples = (rp.num_samples - uint32_t(k) + uint32_t(lanes) - 1u) / uint32_t(lanes);
+      cfg[k].total_work = (unsigned long long)base.pixels * cfg[k].params.num_samples;
+    }
+    if (int rc = pt_workspace(scene, k, pt_pool_size(cfg[k]), &set, &w[k])) {
+      if (k == 0) return rc;
+      cudaGetLastError();  // no memory for a second pool: one lane
+      lanes = 1; cfg[0] = base;
+      if (int rc0 = pt_workspace(scene, 0, pt_pool_size(cfg[0]), &set, &w[0])) return rc0;
+      break;
+    }
+  }
+  if (lanes == 1) return render_pt_lane(cfg[0], w[0], stream, stats);
+  for (int k = 1; k < lanes; ++k) if (!set->stream[k]) B2_CUDA(cudaStreamCreateWithFlags(&set->stream[k], cudaStreamNonBlocking));
+  if (!set->fork) B2_CUDA(cudaEventCreateWithFlags(&set->fork, cudaEventDisableTiming));
+  int device = 0;
+  B2_CUDA(cudaGetDevice(&device));
+  B2_CUDA(cudaEventRecord(set->fork, stream));  // the other lanes start after whatever the caller queued on `stream` (the film may just have been cleared there)
+  B2ptStats st[kPtLanes] = {};
+  int rcs[kPtLanes] = {};
+  std::string errs[kPtLanes];
+  std::vector<std::thread> others;
+  for (int k = 1; k < lanes; ++k) {
+    B2_CUDA(cudaStreamWaitEvent(set->stream[k], set->fork, 0));
+    others.emplace_back([&, k]() {
+      if (cudaSetDevice(device) != cudaSuccess) { rcs[k] = B2PT_ERR_CUDA; errs[k] = "render_pt: cudaSetDevice failed in a lane thread"; return; }
+      rcs[k] = render_pt_lane(cfg[k], w[k], set->stream[k], &st[k]);
+      if (rcs[k] != B2PT_OK) errs[k] = b2pt_last_error();
+    });
+  }
+  rcs[0] = render_pt_lane(cfg[0], w[0], stream, &st[0]);
+  for (auto& t : others) t.join();  // every lane ends with a synchronised stream
+  if (rcs[0] != B2PT_OK) return rcs[0];
+  for (int k = 1; k < lanes; ++k) if (rcs[k] != B2PT_OK) { set_error(errs[k]); return rcs[k]; }
+  if (stats) {
+    *stats = st[0];
+    for (int k = 1; k < lanes; ++k) {
+      stats->num_basic_rays += st[k].num_basic_rays; stats->num_shadow_rays += st[k].num_shadow_rays;
+      stats->numeric_errors += st[k].numeric_errors; stats->capacity_events += st[k].capacity_events;
+      stats->trace_ms += st[k].trace_ms; stats->shadow_ms += st[k].shadow_ms; stats->shade_ms += st[k].shade_ms;
+      stats->trace_launches += st[k].trace_launches; stats->shadow_launches += st[k].shadow_launches;
+      stats->kernel_launches += st[k].kernel_launches;
+    }
   }
   return B2PT_OK;
 }
