@@ -3,6 +3,9 @@
 // Builds the render_context_t equivalent (Technique.cpp:37-45), dispatches to the wavefront
 // integrator the Options select (make_technique.cpp:112-170) and fills the statistics_t fields a
 // device technique can know (Technique.cpp:52-76).
+#include <thread>
+#include <vector>
+
 #include "render_common.cuh"
 
 namespace b2pt {
@@ -161,7 +164,13 @@ int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* params, double*
   // view += pass sums (Technique::_commit_images adds into the caller's dvec4 buffer)
   B2_CUDA(cudaMemcpy(scene->film_host, scene->film_dev, n * sizeof(double), cudaMemcpyDeviceToHost));
   const double* h = scene->film_host;
-  for (size_t i = 0; i < n; ++i) view_host[i] += h[i];
+  // a 1024^2 film is 32 MB: four host threads add it in a quarter of the time one takes (the add is memory-bound)
+  const int parts = n >= (size_t(1) << 20) ? 4 : 1;
+  auto add = [&](int k) { for (size_t i = n * k / parts, e = n * (k + 1) / parts; i < e; ++i) view_host[i] += h[i]; };
+  std::vector<std::thread> helpers;
+  for (int k = 1; k < parts; ++k) helpers.emplace_back(add, k);
+  add(0);
+  for (auto& t : helpers) t.join();
   return B2PT_OK;
 }
 
