@@ -45,7 +45,7 @@ enum {
   B2PT_ERR_INVALID = 1,   /* bad argument (the reference's runtime_assert) */
   B2PT_ERR_NO_DEVICE = 2, /* no CUDA device / driver */
   B2PT_ERR_CUDA = 3,      /* a CUDA call failed; see b2pt_last_error() */
-  B2PT_ERR_CAPACITY = 4   /* a stated cap was exceeded (e.g. subpath length) */
+  B2PT_ERR_CAPACITY = 4   /* a stated cap was exceeded (device pool, traversal stack, > 2^28 triangles) */
 };
 
 /* entity type in the low two bits of material_id (SurfacePoint.hpp:8-17) */
@@ -139,8 +139,8 @@ typedef struct {
                              (multi-GPU: rank g of G uses first = g, stride = G); 0 means 1 */
   uint32_t num_samples;   /* passes (samples per pixel) to add */
   float sky_horizon[3], sky_zenith[3]; /* Technique::set_sky_gradient */
-  uint32_t max_subpath;   /* cap on stored light-subpath vertices per path (reference: 1024,
-                             BPT.hpp:29); 0 = library default 64 */
+  uint32_t max_subpath;   /* cap on stored light-subpath vertices per path; 0 = the reference's 1024
+                             (BPT.hpp:29, UPG.hpp:54) */
 } B2ptRenderParams;
 
 /* statistics_t fields the GPU technique can fill (statistics.hpp, Technique.cpp:52-76) */
@@ -150,7 +150,8 @@ typedef struct {
   uint64_t num_shadow_rays;  /* occlusion rays (Scene::numShadowRays) */
   uint64_t num_paths;        /* pixel-samples */
   uint64_t numeric_errors;   /* non-finite pixel samples dropped (Technique.cpp:224-230) */
-  uint64_t capacity_events;  /* light subpaths truncated at max_subpath */
+  uint64_t capacity_events;  /* light vertices / connections that did not fit the device pools; always 0 in a
+                                call that returned B2PT_OK (a non-zero count fails the call with B2PT_ERR_CAPACITY) */
   uint64_t kernel_launches;  /* CUDA kernels launched by the call */
   float device_ms;           /* CUDA-event time of the call on its stream */
   /* Per-stage device time, CUDA events around every launch of the stage on the call's stream.
@@ -199,7 +200,10 @@ int b2pt_trace_device(b2pt_scene_t scene, const B2ptRay* rays_dev, size_t n, uns
  * memory.  path_radiance_dev (nullable, device, num_samples*width*height*3
  * floats) receives the per-pixel-sample eye-path radiance that
  * Technique::_for_each_ray adds to _eye_image (Technique.cpp:338).
- * Synchronous unless stats == NULL, in which case it only enqueues on `stream`.
+ * Launches on `stream` (a cudaStream_t, may be NULL) and returns when the passes are complete: the call
+ * synchronises with the stream (the integrators read their device counters between bursts of launches).
+ * Fails with B2PT_ERR_CAPACITY — film incomplete — if a BVH traversal stack or a vertex pool overflowed
+ * during THIS call (the flags are reset per call).
  */
 int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accum_dev,
                 float* path_radiance_dev, void* stream, B2ptStats* stats);

@@ -109,6 +109,14 @@ EXPORTS = [
     "b2pt_scene_info", "b2pt_trace", "b2pt_trace_device", "b2pt_render", "b2pt_render_host", "b2pt_grid_build",
     "b2pt_grid_destroy", "b2pt_grid_query", "b2pt_film_errors",
 ]
+# parity probes of include/b2pt_debug.h (not part of the drop-in boundary)
+DEBUG_EXPORTS = [
+    "b2pt_debug_density", "b2pt_debug_primary", "b2pt_debug_camera", "b2pt_debug_light_samples", "b2pt_debug_draws",
+    "b2pt_debug_tree_stats", "b2pt_debug_trace_counts",
+]
+DENSITY_JOB_DTYPE = np.dtype([("org", "<f4", 3), ("dir", "<f4", 3), ("target", "<f4", 3), ("radius", "<f4"), ("key", "<u4")])
+DENSITY_RESULT_DTYPE = np.dtype([("trials", "<u4"), ("density", "<f4"), ("kind", "<u4"), ("t", "<f4")])
+assert DENSITY_JOB_DTYPE.itemsize == 44 and DENSITY_RESULT_DTYPE.itemsize == 16
 
 _lib = None
 
@@ -140,6 +148,13 @@ def load_library():
     lib.b2pt_grid_destroy.restype = None
     lib.b2pt_grid_query.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p, C.c_void_p]
     lib.b2pt_film_errors.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_float), C.c_void_p]
+    lib.b2pt_debug_density.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.b2pt_debug_primary.argtypes = [C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.b2pt_debug_camera.argtypes = [C.POINTER(RenderParams), C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    lib.b2pt_debug_light_samples.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.b2pt_debug_draws.argtypes = [C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.b2pt_debug_tree_stats.argtypes = [C.c_void_p, C.c_void_p]
+    lib.b2pt_debug_trace_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint, C.c_void_p]
     _lib = lib
     return lib
 
@@ -195,6 +210,32 @@ class DeviceSceneHandle:
     def trace_device(self, rays_ptr, n, mode, hits_ptr, stream=0):
         check(load_library().b2pt_trace_device(self.handle, C.c_void_p(rays_ptr), n, mode, C.c_void_p(hits_ptr),
                                                C.c_void_p(stream)))
+
+    # ---- parity probes (include/b2pt_debug.h)
+    def debug_density(self, jobs):
+        jobs = np.ascontiguousarray(jobs, dtype=DENSITY_JOB_DTYPE)
+        out = np.zeros(len(jobs), dtype=DENSITY_RESULT_DTYPE)
+        check(load_library().b2pt_debug_density(self.handle, _ptr(jobs), len(jobs), _ptr(out)))
+        return out
+
+    def debug_light_samples(self, keys):
+        keys = np.ascontiguousarray(keys, dtype=np.uint32)
+        pos = np.zeros((len(keys), 3), dtype=np.float32)
+        mat, draws = np.zeros(len(keys), dtype=np.uint32), np.zeros(len(keys), dtype=np.uint32)
+        check(load_library().b2pt_debug_light_samples(self.handle, _ptr(keys), len(keys), _ptr(pos), _ptr(mat), _ptr(draws)))
+        return pos, mat, draws
+
+    def tree_stats(self):
+        s = np.zeros(6, dtype=np.float64)
+        check(load_library().b2pt_debug_tree_stats(self.handle, _ptr(s)))
+        return {"sah_cost": s[0], "inner_nodes": int(s[1]), "leaf_children": int(s[2]), "triangle_refs": int(s[3]),
+                "expected_triangle_tests": s[4], "expected_node_visits": s[5]}
+
+    def trace_counts(self, rays, mode):
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        counts = np.zeros((len(rays), 2), dtype=np.uint32)
+        check(load_library().b2pt_debug_trace_counts(self.handle, _ptr(rays), len(rays), mode, _ptr(counts)))
+        return counts
 
     def close(self):
         if getattr(self, "handle", None):
@@ -260,3 +301,23 @@ class PhotonGrid:
             self.close()
         except Exception:
             pass
+
+
+def debug_primary(params, pixels, samples):
+    pixels, samples = np.ascontiguousarray(pixels, dtype=np.uint32), np.ascontiguousarray(samples, dtype=np.uint32)
+    out = np.zeros((len(pixels), 3), dtype=np.float32)
+    check(load_library().b2pt_debug_primary(C.byref(params), _ptr(pixels), _ptr(samples), len(pixels), _ptr(out)))
+    return out
+
+
+def debug_camera(params, positions):
+    pos = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 2)
+    dirs, pix = np.zeros((len(pos), 3), dtype=np.float32), np.zeros((len(pos), 2), dtype=np.float32)
+    check(load_library().b2pt_debug_camera(C.byref(params), _ptr(pos), len(pos), _ptr(dirs), _ptr(pix)))
+    return dirs, pix
+
+
+def debug_draws(key, n):
+    raw, fl, db = np.zeros(n, dtype=np.uint32), np.zeros(n, dtype=np.float32), np.zeros(n, dtype=np.float64)
+    check(load_library().b2pt_debug_draws(C.c_uint32(key), n, _ptr(raw), _ptr(fl), _ptr(db)))
+    return raw, fl, db

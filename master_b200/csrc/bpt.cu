@@ -24,6 +24,7 @@
 // on the path: 12 vertices per path on average (the expectation with roulette 0.9 is <= 8.1) and
 // B2ptRenderParams::max_subpath (default 1024, the reference's cap) per path.
 // Every path owns one counter-based RNG stream; light phase and eye phase consume it in the reference's order.
+#include <algorithm>
 #include <memory>
 
 #include "render_common.cuh"
@@ -727,7 +728,7 @@ struct BptLane {
 
 struct BptWorkspace {
   BptLane lane[kMaxLanes];
-  uint32_t size = 0;
+  uint32_t size = 0, per_path = 0;
   cudaEvent_t fork = nullptr;
   std::vector<void*> blocks;
 };
@@ -753,20 +754,20 @@ int ws_alloc(BptWorkspace* w, T** p, size_t count) {
   return B2PT_OK;
 }
 
-int bpt_workspace(b2pt_scene_s* scene, uint32_t size, int lanes, BptWorkspace** out) {
+int bpt_workspace(b2pt_scene_s* scene, uint32_t size, uint32_t per_path, int lanes, BptWorkspace** out) {
   BptWorkspace* w = (BptWorkspace*)scene->workspace;
-  if (w && scene->workspace_free == bpt_workspace_free && w->size == size && w->lane[lanes - 1].counters) { *out = w; return B2PT_OK; }
+  if (w && scene->workspace_free == bpt_workspace_free && w->size == size && w->per_path == per_path && w->lane[lanes - 1].counters) { *out = w; return B2PT_OK; }
   if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
   scene->workspace = nullptr;
   w = new BptWorkspace();
   scene->workspace = w; scene->workspace_free = bpt_workspace_free;
-  w->size = size;
+  w->size = size; w->per_path = per_path;
   B2_CUDA(cudaEventCreateWithFlags(&w->fork, cudaEventDisableTiming));
   for (int k = 0; k < lanes; ++k) {
     BptLane& l = w->lane[k];
     BptPool& p = l.pool;
     p.size = size;
-    p.lv_capacity = size * 12u < 4096u ? 4096u : size * 12u;
+    p.lv_capacity = uint32_t(std::min<uint64_t>(std::max<uint64_t>(uint64_t(size) * per_path, 4096u), 0x7FFFFF00u));
     p.q_capacity = p.lv_capacity + size;
     int rc;
     if ((rc = ws_alloc(w, &p.rec, size_t(size) * kRecFloat4s))) return rc;
@@ -801,6 +802,9 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   // With more than one pass to render the passes are spread over bpt_lanes() concurrent batches.
   uint32_t batch_paths = 1u << 23;
   { const char* e = getenv("B2PT_BPT_BATCH_LOG2"); if (e) { int v = atoi(e); if (v >= 10 && v <= 26) batch_paths = 1u << v; } }
+  // the light-vertex pool grows with 1 / (1 - roulette) (render_common.cuh: lv_per_path): keep it at what 2^23 paths x 12 vertices take
+  const uint32_t per_path = lv_per_path(base.params.roulette);
+  while (batch_paths > pixels && uint64_t(batch_paths) * per_path > (uint64_t(12) << 23)) batch_paths >>= 1;
   uint32_t passes_per_batch = batch_paths / pixels;
   if (passes_per_batch < 1) passes_per_batch = 1;
   const int kLanes = bpt_lanes();
@@ -809,7 +813,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   const int lanes = int(num_batches) < kLanes ? int(num_batches) : kLanes;
   const uint32_t size = (passes_per_batch * pixels + block - 1) / block * block;
   BptWorkspace* w = nullptr;
-  if (int rc = bpt_workspace(scene, size, lanes, &w)) return rc;
+  if (int rc = bpt_workspace(scene, size, per_path, lanes, &w)) return rc;
   RenderConfig cfg = base;
   cfg.pool_size = size;
   const int grid = grid_for(size, block);
@@ -924,6 +928,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       stats->kernel_launches += s1.kernel_launches;
     }
   }
+  if (capacity) return capacity_error(capacity, "render_bpt");
   return B2PT_OK;
 }
 

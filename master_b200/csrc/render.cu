@@ -87,8 +87,11 @@ int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accu
   if (int rc = make_config(scene, params, accum_dev, path_radiance_dev, &cfg)) return rc;
   B2ptStats local{};
   if (params->num_samples == 0) { if (stats) *stats = local; return B2PT_OK; }
-  cudaEvent_t e0, e1;
-  B2_CUDA(cudaEventCreate(&e0)); B2_CUDA(cudaEventCreate(&e1));
+  // a stack overflow of an earlier call must not fail this one: the flag is per call
+  B2_CUDA(cudaMemsetAsync(scene->dev.error_flags, 0, 4, stream));
+  if (!scene->ev[0]) { B2_CUDA(cudaEventCreate(&scene->ev[0])); }
+  if (!scene->ev[1]) { B2_CUDA(cudaEventCreate(&scene->ev[1])); }
+  cudaEvent_t e0 = scene->ev[0], e1 = scene->ev[1];  // kept with the scene: one pair per handle, not per call
   B2_CUDA(cudaEventRecord(e0, stream));
   int rc;
   switch (params->technique) {
@@ -102,7 +105,6 @@ int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accu
     if (e == cudaSuccess) e = cudaEventElapsedTime(&local.device_ms, e0, e1);
     if (e != cudaSuccess) rc = cuda_fail(e, "b2pt_render timing", __FILE__, __LINE__);
   }
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
   if (rc != B2PT_OK) return rc;
   uint32_t flags = 0;
   B2_CUDA(cudaMemcpy(&flags, scene->dev.error_flags, 4, cudaMemcpyDeviceToHost));
@@ -129,14 +131,14 @@ int b2pt_film_errors(const double* accum_dev, const float* reference_dev, uint32
   double sums[3] = {0.0, 0.0, 0.0};
   if (x1 > x0 && y1 > y0) {
     double* sums_dev = nullptr;
-    B2_CUDA(cudaMalloc(&sums_dev, sizeof(sums)));
+    B2_CUDA(cudaMallocAsync(&sums_dev, sizeof(sums), stream));  // stream-ordered: served from the driver's pool, no device-wide sync per record
     cudaMemsetAsync(sums_dev, 0, sizeof(sums), stream);
     const size_t n = size_t(x1 - x0) * size_t(y1 - y0);
     const int block = 256, grid = int(std::min<size_t>((n + block - 1) / block, size_t(kNumSMs) * 4));
     film_errors_kernel<<<grid, block, 0, stream>>>(accum_dev, reference_dev, width, x0, y0, x1, y1, sums_dev);
     cudaError_t e = cudaMemcpyAsync(sums, sums_dev, sizeof(sums), cudaMemcpyDeviceToHost, stream);
+    cudaFreeAsync(sums_dev, stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-    cudaFree(sums_dev);
     B2_CUDA(e);
   }
   // whole image: num = width * height * 3 (ImageView.cpp:81-84); window: num = pixels (ImageView.cpp:109-116); an empty window is 0 / 0

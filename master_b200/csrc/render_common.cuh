@@ -156,6 +156,25 @@ struct StageTimer {
   }
 };
 
+// Stored light-subpath vertices provisioned per path in the vertex pools of BPT and VCM / UPG.  The reference keeps up to 1024 per
+// path on the stack (BPT.hpp:29, UPG.hpp:54); a pool in HBM is sized from what paths actually store: a subpath survives each bounce
+// with probability `roulette`, so a closed scene stores 1 / (1 - roulette) vertices per path on average (10 at the default 0.9), and
+// the sum over >= 10^5 paths concentrates tightly around the mean.  1.2 x the mean, at least 12; B2PT_LV_PER_PATH overrides.
+// Exhausting the pool is an error (B2PT_ERR_CAPACITY), never a silently truncated subpath.
+inline uint32_t lv_per_path(float roulette) {
+  if (const char* e = getenv("B2PT_LV_PER_PATH")) { const int v = atoi(e); if (v >= 1 && v <= 1024) return uint32_t(v); }
+  const double mean = roulette < 1.0f ? 1.0 / (1.0 - double(roulette)) : 1024.0;
+  const double want = 1.2 * mean + 0.999;
+  return want < 12.0 ? 12u : want > 1024.0 ? 1024u : uint32_t(want);
+}
+inline int capacity_error(unsigned long long events, const char* who) {
+  char buf[320];
+  snprintf(buf, sizeof buf, "%s: %llu light vertices / connections did not fit the device pools (sized for 1.2 / (1 - roulette) stored vertices "
+           "per path); the film of this call is incomplete — set B2PT_LV_PER_PATH higher", who, events);
+  set_error(buf);
+  return B2PT_ERR_CAPACITY;
+}
+
 inline int grid_for(size_t n, int block) {
   size_t want = (n + block - 1) / block;
   size_t cap = size_t(kNumSMs) * 8;

@@ -812,6 +812,7 @@ void b2pt_scene_destroy(b2pt_scene_t s) {
   for (int i = 0; i < s->num_allocations; ++i) cudaFree(s->allocations[i]);
   if (s->film_dev) cudaFree(s->film_dev);
   if (s->film_host) cudaFreeHost(s->film_host);
+  for (cudaEvent_t e : s->ev) if (e) cudaEventDestroy(e);
   delete s;
 }
 

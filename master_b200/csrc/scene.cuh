@@ -72,4 +72,5 @@ struct b2pt_scene_s {
   double* film_dev = nullptr;
   double* film_host = nullptr;
   size_t film_doubles = 0;
+  cudaEvent_t ev[2] = {nullptr, nullptr};  // timing pair of b2pt_render
 };

@@ -208,8 +208,10 @@ __device__ __forceinline__ void node8_step(const DeviceScene& sc, uint32_t child
   T = make_uint2(__float_as_uint(n1.y), tmask);
 }
 
-template <bool kAnyHit>
-__device__ __forceinline__ Hit trace_ray8(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar, uint32_t ray_mask) {
+// kCount (b2pt_debug_trace_counts): counts->x += node steps, counts->y += triangle tests of this ray
+template <bool kAnyHit, bool kCount = false>
+__device__ __forceinline__ Hit trace_ray8(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar, uint32_t ray_mask,
+                                          uint2* counts = nullptr) {
   Hit hit; hit.t = tfar; hit.u = 0.f; hit.v = 0.f; hit.tri = kInvalid;
   const float kHuge = 1e24f;  // node8_step adds 2^15 grid steps to the plane offsets: keep that finite
   const float3 idir = f3(fabsf(D.x) > 1e-24f ? 1.0f / D.x : copysignf(kHuge, D.x),
@@ -231,6 +233,7 @@ __device__ __forceinline__ Hit trace_ray8(const DeviceScene& sc, float3 O, float
       const uint32_t child = G.x + __popc(G.y & 0xFFu & ((1u << slot) - 1u));
       if (G.y & 0xFF000000u) { if (sp < kStack8) stack[sp++] = G; else atomicOr(sc.error_flags, 1u); }
       node8_step(sc, child, O, idir, oct, tnear, hit.t, G, T);
+      if (kCount) ++counts->x;
     } else {
       T = G;  // a postponed triangle group (or nothing)
       G = make_uint2(0u, 0u);
@@ -240,6 +243,7 @@ __device__ __forceinline__ Hit trace_ray8(const DeviceScene& sc, float3 O, float
       const uint32_t j = uint32_t(__ffs(int(T.y)) - 1);
       T.y &= T.y - 1u;
       const uint32_t tri = T.x + j;
+      if (kCount) ++counts->y;
       if (intersect_triangle(sc, tri, O, D, tnear, hit.t, hit.u, hit.v, ray_mask)) {
         hit.tri = tri;
         if (kAnyHit) return hit;

@@ -27,6 +27,7 @@
 #include <string>
 #include <thread>
 
+#include "../../include/b2pt_debug.h"
 #include "render_common.cuh"
 
 namespace b2pt {
@@ -1262,7 +1263,7 @@ struct VcmWorkspaceSet {
   VcmWorkspace* lane[kVcmLanes] = {};
   cudaStream_t stream[kVcmLanes] = {};  // lanes 1.. (lane 0 runs on the caller's stream)
   cudaEvent_t fork = nullptr;
-  uint32_t pixels = 0, photons = 0;
+  uint32_t pixels = 0, photons = 0, per_path = 0;
 };
 void vcm_workspace_set_free(void* p) {
   VcmWorkspaceSet* set = (VcmWorkspaceSet*)p;
@@ -1272,22 +1273,22 @@ void vcm_workspace_set_free(void* p) {
   delete set;
 }
 
-int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons);
+int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons, uint32_t per_path);
 
-int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, int* lanes_io, VcmWorkspaceSet** out) {
+int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, uint32_t per_path, int* lanes_io, VcmWorkspaceSet** out) {
   int lanes = *lanes_io;
   VcmWorkspaceSet* set = (VcmWorkspaceSet*)scene->workspace;
-  if (!(set && scene->workspace_free == vcm_workspace_set_free && set->pixels == pixels && set->photons == photons)) {
+  if (!(set && scene->workspace_free == vcm_workspace_set_free && set->pixels == pixels && set->photons == photons && set->per_path == per_path)) {
     if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
     scene->workspace = nullptr;
     set = new VcmWorkspaceSet();
     scene->workspace = set; scene->workspace_free = vcm_workspace_set_free;
-    set->pixels = pixels; set->photons = photons;
+    set->pixels = pixels; set->photons = photons; set->per_path = per_path;
   }
   for (int k = 0; k < lanes; ++k) {
     if (set->lane[k]) continue;
     set->lane[k] = new VcmWorkspace();
-    if (int rc = vcm_workspace_fill(set->lane[k], pixels, photons)) {
+    if (int rc = vcm_workspace_fill(set->lane[k], pixels, photons, per_path)) {
       // not enough memory for another pass in flight: run with the lanes that fit
       vcm_workspace_free(set->lane[k]); set->lane[k] = nullptr;
       cudaGetLastError();
@@ -1303,14 +1304,14 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, int* l
   return B2PT_OK;
 }
 
-int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons) {
+int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons, uint32_t per_path) {
   w->pixels = pixels; w->photons = photons;
   const uint32_t block = 256;
   VcmPool& p = w->pool;
   p.photons = (photons + block - 1) / block * block;
   p.pixels_pad = (pixels + block - 1) / block * block;
   const size_t np = p.photons, ne = p.pixels_pad, nl = np > ne ? np : ne;
-  p.lv_capacity = uint32_t(np * 12u < 4096u ? 4096u : np * 12u);
+  p.lv_capacity = uint32_t(std::min<uint64_t>(std::max<uint64_t>(uint64_t(np) * per_path, 4096u), 0x7FFFFF00u));  // render_common.cuh: lv_per_path
   p.q_capacity = p.lv_capacity + uint32_t(ne);
   int rc;
   if ((rc = ws_alloc(w, &p.p_state, np))) return rc;
@@ -1358,6 +1359,36 @@ int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons) {
   B2_CUDA(cudaMemset(p.lp_head, 0xFF, nl * 4));
   B2_CUDA(cudaMemset(p.lp_count, 0, nl * 4));
   return B2PT_OK;
+}
+
+
+// b2pt_debug_density (include/b2pt_debug.h): ONE density loop per thread, run by the same density_begin / density_step the
+// stages above run, on explicit jobs, so that the trial count N can be set beside the reference's
+// (oracle/_ref/ref_harness density).  The surface of a job is the closest mesh hit of its ray.
+__global__ void __launch_bounds__(128) debug_density_kernel(DeviceScene sc, const B2ptDensityJob* __restrict__ jobs, uint32_t n,
+                                                            B2ptDensityResult* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const B2ptDensityJob j = jobs[i];
+  const float3 O = f3(j.org[0], j.org[1], j.org[2]), D = f3(j.dir[0], j.dir[1], j.dir[2]);
+  const Hit h = trace_ray<false, true>(sc, O, D, 0.0f, INFINITY);
+  B2ptDensityResult r;
+  r.trials = 0u; r.density = INFINITY; r.kind = 0u; r.t = h.t;
+  if (h.tri != kInvalid) {
+    const Surface s = query_surface(sc, h.tri, h.u, h.v, h.t, O, D);
+    Rng rng; rng.key = j.key; rng.ctr = 0;
+    DensityLoop L;
+    density_begin(L, sc, rng, s, f3(j.target[0], j.target[1], j.target[2]), j.radius, -D);
+    if (density_has_lobe(L)) {
+      r.kind = L.type == B2PT_BSDF_DIFFUSE ? 1u : 2u;
+      unsigned long long rays = 0;
+      float density = INFINITY;
+      while (!density_step(L, sc, j.radius, density, rays)) {}
+      r.density = density;
+      r.trials = uint32_t(L.N);  // density_step leaves N at the trial that landed (or at the limit)
+    }
+  }
+  out[i] = r;
 }
 
 }  // namespace
@@ -1488,7 +1519,7 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   { const char* e = getenv("B2PT_VCM_LANES"); if (e) lanes = std::max(1, std::min(kVcmLanes, atoi(e))); }  // A/B runs
   lanes = int(std::min<uint32_t>(uint32_t(lanes), std::max(1u, rp.num_samples)));
   VcmWorkspaceSet* set = nullptr;
-  if (int rc = vcm_workspace(scene, pixels, photons, &lanes, &set)) return rc;
+  if (int rc = vcm_workspace(scene, pixels, photons, lv_per_path(rp.roulette), &lanes, &set)) return rc;
   VcmLaneResult res[kVcmLanes];
   if (lanes == 1) {
     res[0].rc = vcm_run_passes(base, set->lane[0], stream, 0, 1, photons, &res[0]);
@@ -1523,7 +1554,29 @@ int render_vcm(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       stats->kernel_launches += res[k].launches[0] + res[k].launches[1] + res[k].launches[2];
     }
   }
+  unsigned long long capacity = 0;
+  for (int k = 0; k < lanes; ++k) capacity += res[k].capacity;
+  if (capacity) return capacity_error(capacity, "render_vcm");
   return B2PT_OK;
 }
 
 }  // namespace b2pt
+
+extern "C" int b2pt_debug_density(b2pt_scene_t scene, const B2ptDensityJob* jobs, size_t n, B2ptDensityResult* out) {
+  using namespace b2pt;
+  B2_CHECK(scene && (n == 0 || (jobs && out)), B2PT_ERR_INVALID, "b2pt_debug_density: null argument");
+  B2_CHECK(n < (size_t(1) << 28), B2PT_ERR_CAPACITY, "b2pt_debug_density: too many jobs");
+  if (n == 0) return B2PT_OK;
+  B2ptDensityJob* d_jobs = nullptr; B2ptDensityResult* d_out = nullptr;
+  B2_CUDA(cudaMalloc(&d_jobs, n * sizeof(B2ptDensityJob)));
+  cudaError_t e = cudaMalloc(&d_out, n * sizeof(B2ptDensityResult));
+  if (e == cudaSuccess) e = cudaMemcpy(d_jobs, jobs, n * sizeof(B2ptDensityJob), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    debug_density_kernel<<<unsigned((n + 127) / 128), 128>>>(scene->dev, d_jobs, uint32_t(n), d_out);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(out, d_out, n * sizeof(B2ptDensityResult), cudaMemcpyDeviceToHost);
+  cudaFree(d_jobs); cudaFree(d_out);
+  if (e != cudaSuccess) return cuda_fail(e, "b2pt_debug_density", __FILE__, __LINE__);
+  return B2PT_OK;
+}

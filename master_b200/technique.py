@@ -18,18 +18,31 @@ from . import api
 
 
 class GpuTechnique:
-    def __init__(self, scene, technique="PT", **options):
-        """scene: api.DeviceSceneHandle; options: the Options fields the techniques read (Options.hpp:30-54)."""
+    def __init__(self, scene, technique="PT", first_sample=0, sample_stride=1, **options):
+        """scene: api.DeviceSceneHandle; options: the Options fields the techniques read (Options.hpp:30-54).
+
+        first_sample / sample_stride (GpuOptions of master_b200/host/GpuTechnique.hpp): rank g of G passes (g, G) and the
+        passes this object renders are the global sample indices g, g + G, g + 2G, ... — disjoint across ranks and across
+        successive calls."""
         self.scene = scene
         self.technique = technique
         self.options = dict(options)
+        self.first_sample = int(first_sample)
+        self.sample_stride = max(int(sample_stride), 1)
         self.statistics = {"num_samples": 0, "num_basic_rays": 0, "num_shadow_rays": 0, "total_time": 0.0,
                            "numeric_errors": 0, "records": []}
 
-    def _params(self, width, height, camera_id, passes, first_sample=None, sample_stride=1):
-        first = self.statistics["num_samples"] if first_sample is None else first_sample
+    def sample_indices(self, passes, first_sample=None, sample_stride=None):
+        """(first, stride) of the next `passes` passes, as GpuTechnique::render computes them (GpuTechnique.cpp):
+        first = first_sample + num_samples * stride.  Explicit arguments override (bench.py's per-step split)."""
+        stride = self.sample_stride if sample_stride is None else max(int(sample_stride), 1)
+        first = self.first_sample + self.statistics["num_samples"] * stride if first_sample is None else int(first_sample)
+        return first, stride
+
+    def _params(self, width, height, camera_id, passes, first_sample=None, sample_stride=None):
+        first, stride = self.sample_indices(passes, first_sample, sample_stride)
         return api.make_params(self.scene.flat, technique=self.technique, width=width, height=height, camera=camera_id,
-                               first_sample=first, sample_stride=sample_stride, num_samples=passes, **self.options)
+                               first_sample=first, sample_stride=stride, num_samples=passes, **self.options)
 
     def _account(self, stats, passes):
         s = self.statistics

@@ -15,7 +15,15 @@
 //   render <scene> key=value ...   per-(pixel,sample) streams, 1 thread, golden outputs
 //   time   <scene> key=value ...   the reference's own Technique::render loop, N threads
 //   grid   <in.bin> <out.bin>      v3::HashGrid3D build + rQuery on explicit points / queries
+//   density <scene> <jobs.bin> <out.bin>   BSDF::gathering_density + Intersector::intersectFast per job (trial counts)
+//   errors <accum.f64> <ref.f32> W H [cx cy r]   rms_abs_errors / rms_abs_errors_windowed (ImageView.cpp:60-117)
+//   pinning <scene> key=value ...  raw draws, float / piecewise draws, primary rays of _for_each_ray, light samples
+//   camera                         ray_direction / pixel_position / lookAt frames at the in-source unittest() inputs
 // <scene> is a .blend (needs the reference's models/) or a .b2s written by `dump`.
+//
+// -DB2PT_STOCK_TIMING (oracle/build_ref.sh, second binary oracle/_ref/ref_harness_stock): the same driver WITHOUT the RNG shim
+// (std::mt19937 as the reference ships), compiled like the reference's own Makefile:27 (-O2, AVX2 + FMA) and linked with the AVX2
+// Embree (Makefile:30-37) — the timing-only CPU baseline; commands that need per-(pixel, sample) streams are left out.
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -125,6 +133,15 @@ static shared<Technique> make(const shared<Scene>& scene, const Args& a, size_t 
   throw std::runtime_error("unknown technique " + t);
 }
 
+// sky=hr,hg,hb,zr,zg,zb  ->  Technique::set_sky_gradient (Technique.cpp:91-93)
+static void apply_sky(Technique& T, const Args& a) {
+  string v = arg(a, "sky", "");
+  if (v.empty()) return;
+  float f[6] = {0, 0, 0, 0, 0, 0};
+  if (sscanf(v.c_str(), "%f,%f,%f,%f,%f,%f", f, f + 1, f + 2, f + 3, f + 4, f + 5) != 6) throw std::runtime_error("sky= needs six numbers");
+  T.set_sky_gradient(vec3(f[0], f[1], f[2]), vec3(f[3], f[4], f[5]));
+}
+
 static render_context_t make_context(const Scene& scene, size_t cameraId, size_t W, size_t H, random_generator_t& gen) {
   // Technique::render, Technique.cpp:37-45
   auto& cameras = scene.cameras();
@@ -146,6 +163,7 @@ template <class T> static void write_vec(const string& path, const std::vector<T
   f.write((const char*)v.data(), v.size() * sizeof(T));
 }
 
+#ifndef B2PT_STOCK_TIMING  // everything that needs the counter-based engine of rng_shim.h
 // UPGBase::_preprocess + _scatter (UPG.cpp:177-186, 599-672) with ONE stream per photon path instead of one
 // sequential generator: photon j of pass `sample` draws from stream (seed, domain 2, j, sample).  Everything the
 // photon does — _traceLight, the vertex records, the v3::HashGrid3D build — is the reference's own code; only the
@@ -189,6 +207,8 @@ static bool photon_pass(Technique& T, random_generator_t& gen, uint32_t seed, ui
   return upg_photon_pass<UPG0>(T, gen, seed, sample, dump) || upg_photon_pass<UPG1>(T, gen, seed, sample, dump) ||
          upg_photon_pass<UPG2>(T, gen, seed, sample, dump) || upg_photon_pass<UPGb>(T, gen, seed, sample, dump);
 }
+
+#endif  // B2PT_STOCK_TIMING
 
 // ---------------------------------------------------------------- sub-commands
 static int cmd_dump(int argc, char** argv) {
@@ -239,6 +259,7 @@ static int cmd_rays(int argc, char** argv) {
   return 0;
 }
 
+#ifndef B2PT_STOCK_TIMING
 // Per-(pixel, sample) streams.  The harness owns only the pixel loop and the seeding; the jitter
 // draws, _traceEye, the splats and the commit are the reference's (Technique.cpp:194-352).
 static int cmd_render(int argc, char** argv) {
@@ -252,6 +273,7 @@ static int cmd_render(int argc, char** argv) {
   string out = arg(a, "out", "/tmp/ref_render");
   shared<Technique> tech = make(scene, a, 1);
   Technique& T = *tech;
+  apply_sky(T, a);
 
   std::vector<dvec4> accum(W * H, dvec4(0.0));
   subimage_view_t view(accum.data(), W, H);
@@ -298,6 +320,8 @@ static int cmd_render(int argc, char** argv) {
   return 0;
 }
 
+#endif  // B2PT_STOCK_TIMING
+
 // The reference's own pass loop (Application::render -> Technique::render), as it ships:
 // num_threads pool threads, 32x32 tiles, per-tile std::random_device seeding when threads > 1.
 static int cmd_time(int argc, char** argv) {
@@ -310,6 +334,7 @@ static int cmd_time(int argc, char** argv) {
   size_t spp = argd(a, "num_samples", 1), warm = argd(a, "warmup", 0);
   double budget = argd(a, "seconds", 0.0);  // stop after this much time (0 = run all num_samples)
   shared<Technique> tech = make(scene, a, threads);
+  apply_sky(*tech, a);
   std::vector<dvec4> accum(W * H, dvec4(0.0));
   subimage_view_t view(accum.data(), W, H);
   random_generator_t gen(size_t(argd(a, "seed", 1234)));
@@ -373,6 +398,177 @@ static int cmd_grid(int argc, char** argv) {
   return 0;
 }
 
+
+#ifndef B2PT_STOCK_TIMING
+// BSDF::gathering_density (BSDF.cpp:42-66, 264-289, 393-434) + Intersector::intersectFast (Intersector.cpp:17-46) on explicit jobs.
+//   in:  u32 n, then n x { f32 ray_org[3], ray_dir[3], target[3], radius; u32 key }   (44 bytes)
+//        the surface of a job is the closest MESH hit of its ray (Scene::intersectMesh's RTCRay), omega = -ray_dir
+//   out: n x { u32 trials, f32 density, u32 bsdf_kind (0 none / not a lobe, 1 diffuse, 2 phong), f32 t }
+// The engine runs in trial mode (rng_shim.h) so that trial t of a loop sees the numbers the device gives trial t;
+// trials = engine draws / draws-per-trial, i.e. the N at which the reference's own loop returned.
+struct DensityJobIn { float org[3], dir[3], target[3], radius; uint32_t key; };
+struct DensityJobOut { uint32_t trials; float density; uint32_t kind; float t; };
+
+static int cmd_density(int argc, char** argv) {
+  if (argc < 5) return 2;
+  shared<Scene> scene = open_scene(argv[2]);
+  std::ifstream f(argv[3], std::ios::binary);
+  uint32_t n = 0;
+  f.read((char*)&n, 4);
+  std::vector<DensityJobIn> jobs(n);
+  f.read((char*)jobs.data(), size_t(n) * sizeof(DensityJobIn));
+  std::vector<DensityJobOut> out(n);
+  random_generator_t gen(size_t(0));
+  size_t rays0 = scene->numNormalRays();
+  auto t0 = std::chrono::steady_clock::now();
+  for (uint32_t i = 0; i < n; ++i) {
+    const DensityJobIn& j = jobs[i];
+    RayIsect r;
+    std::memcpy(r.org, j.org, 12);
+    std::memcpy(r.dir, j.dir, 12);
+    r.tnear = 0.f; r.tfar = INFINITY;
+    r.geomID = r.primID = r.instID = RTC_INVALID_GEOMETRY_ID;
+    r.mask = 1u << uint32_t(entity_type::mesh);
+    r.time = 0.f;
+    rtcIntersect(scene->rtcScene, r);
+    out[i] = DensityJobOut{0u, INFINITY, 0u, r.tfar};
+    if (!r.isPresent()) continue;
+    SurfacePoint surface = scene->querySurface(r);
+    const BSDF& bsdf = scene->queryBSDF(surface);
+    uint32_t draws = 0;
+    if (dynamic_cast<const DiffuseBSDF*>(&bsdf)) { draws = 2; out[i].kind = 1; }
+    else if (dynamic_cast<const PhongBSDF*>(&bsdf)) { draws = 3; out[i].kind = 2; }
+    else continue;  // delta lobes never reach the estimate; BSDF::sample_bounded would assert
+    gen.seed(j.key);
+    gen.engine.trial_draws = draws;
+    bounding_sphere_t target = {vec3(j.target[0], j.target[1], j.target[2]), j.radius};
+    vec3 omega = -vec3(j.dir[0], j.dir[1], j.dir[2]);
+    out[i].density = bsdf.gathering_density(gen, scene.get(), surface, target, omega);
+    out[i].trials = gen.engine.ctr / draws;
+    gen.engine.trial_draws = 0;
+  }
+  double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  write_vec(argv[4], out);
+  printf("{\"jobs\": %u, \"seconds\": %.6f, \"rays\": %zu}\n", n, s, scene->numNormalRays() - rays0);
+  return 0;
+}
+
+#endif  // B2PT_STOCK_TIMING
+
+// rms_abs_errors / rms_abs_errors_windowed (ImageView.cpp:60-117) — the reference's own functions — on a dvec4 film and a vec3 reference.
+static int cmd_errors(int argc, char** argv) {
+  if (argc < 6) return 2;
+  size_t W = atoi(argv[4]), H = atoi(argv[5]);
+  std::vector<dvec4> a(W * H);
+  std::vector<vec3> b(W * H);
+  { std::ifstream f(argv[2], std::ios::binary); f.read((char*)a.data(), W * H * sizeof(dvec4)); if (!f) throw std::runtime_error("short accum file"); }
+  { std::ifstream f(argv[3], std::ios::binary); f.read((char*)b.data(), W * H * sizeof(vec3)); if (!f) throw std::runtime_error("short reference file"); }
+  float rms = 0, abs = 0;
+  if (argc >= 9) rms_abs_errors_windowed(rms, abs, image_view_t<dvec4>(a, W, H), image_view_t<vec3>(b, W, H), ivec2(atoi(argv[6]), atoi(argv[7])), atoi(argv[8]));
+  else rms_abs_errors(rms, abs, image_view_t<dvec4>(a, W, H), image_view_t<vec3>(b, W, H));
+  printf("{\"rms\": %.9g, \"abs\": %.9g}\n", rms, abs);
+  return 0;
+}
+
+#ifndef B2PT_STOCK_TIMING
+// A technique that only records the primary ray _for_each_ray hands to _traceEye (Technique.cpp:321-338).
+struct ProbeTechnique : Technique {
+  ProbeTechnique(const shared<const Scene>& scene) : Technique(scene, 1) {}
+  Ray last;
+  vec3 _traceEye(render_context_t& context, Ray ray) override { last = ray; return vec3(0.0f); }
+};
+
+// What the parity contract rests on but the C++ standard leaves open (SURVEY.md §7 "hard parts"): the order in which the two
+// draws of `vec2(x + g.sample(), y + g.sample())` (Technique.cpp:322) and `vec2(g.sample(), g.sample())` (AreaLights.cpp:224)
+// are evaluated in THIS build of the reference, plus libstdc++'s float / piecewise draws from the engine.
+static int cmd_pinning(int argc, char** argv) {
+  if (argc < 3) return 2;
+  Args a = parse_kv(argc, argv, 3);
+  shared<Scene> scene = open_scene(argv[2]);
+  size_t W = argd(a, "width", 64), H = argd(a, "height", 48), cam = argd(a, "camera", 0);
+  uint32_t seed = argd(a, "seed", 1234), count = argd(a, "count", 16);
+  random_generator_t gen(size_t(0));
+  printf("{\"width\": %zu, \"height\": %zu, \"seed\": %u", W, H, seed);
+  uint32_t key = std::b2pt_counter_engine::stream_key(seed, 0, 7, 3);
+  printf(", \"key\": %u, \"raw\": [", key);
+  gen.seed(key);
+  for (int i = 0; i < 8; ++i) printf("%s%u", i ? ", " : "", (unsigned)gen());
+  printf("], \"floats\": [");
+  gen.seed(key);
+  for (int i = 0; i < 8; ++i) printf("%s%.9g", i ? ", " : "", gen.sample());
+  // piecewise_sampler_t over three weights (Sample.inl:233-247): one double per pick = two engine calls
+  const float weights[3] = {0.2f, 0.5f, 0.3f};
+  piecewise_sampler_t sampler(weights, weights + 3);
+  printf("], \"piecewise_weights\": [0.2, 0.5, 0.3], \"piecewise\": [");
+  gen.seed(key);
+  for (int i = 0; i < 8; ++i) printf("%s%.9g", i ? ", " : "", sampler.sample(gen));
+  printf("], \"piecewise_draws_used\": %u", gen.engine.ctr);
+  // primary rays: pixel p = (x, y), sample s, through the reference's own _for_each_ray
+  ProbeTechnique probe(scene);
+  std::vector<dvec4> accum(W * H, dvec4(0.0));
+  subimage_view_t view(accum.data(), W, H);
+  render_context_t context = make_context(*scene, cam, W, H, gen);
+  probe._adjust_helper_image(view);
+  printf(", \"focal_length_y\": %.9g, \"primary\": [", context.focal_length_y);
+  for (uint32_t i = 0; i < count; ++i) {
+    uint32_t pixel = (i * 2654435761u) % uint32_t(W * H), sample = i % 5;
+    gen.seed(std::b2pt_counter_engine::stream_key(seed, 0, pixel, sample));
+    subimage_view_t px = view;
+    px._xOffset = pixel % W; px._xWindow = 1; px._yOffset = pixel / W; px._yWindow = 1;
+    probe._for_each_ray(px, context);
+    printf("%s{\"pixel\": %u, \"sample\": %u, \"origin\": [%.9g, %.9g, %.9g], \"direction\": [%.9g, %.9g, %.9g]}", i ? ", " : "", pixel, sample,
+           probe.last.origin.x, probe.last.origin.y, probe.last.origin.z, probe.last.direction.x, probe.last.direction.y, probe.last.direction.z);
+  }
+  // light samples: AreaLights::sample (AreaLights.cpp:121-140) with a known stream
+  printf("], \"lights\": [");
+  for (uint32_t i = 0; i < count; ++i) {
+    uint32_t k = std::b2pt_counter_engine::stream_key(seed, 3, i, 0);
+    gen.seed(k);
+    LightSample ls = scene->lights.sample(gen);
+    printf("%s{\"key\": %u, \"position\": [%.9g, %.9g, %.9g], \"material_id\": %u, \"draws\": %u}", i ? ", " : "", k, ls.surface.position().x,
+           ls.surface.position().y, ls.surface.position().z, (unsigned)ls.surface.material_id, gen.engine.ctr);
+  }
+  printf("]}\n");
+  return 0;
+}
+
+#endif  // B2PT_STOCK_TIMING
+
+// The known answers the reference keeps in its own (never compiled) unittest() blocks and stale gtest file:
+// Cameras.cpp:164-189, Technique.cpp:118-152, unit_tests/Cameras.test.cpp:38-47 — evaluated by the reference's functions.
+static int cmd_camera(int, char**) {
+  auto v3 = [](const char* name, vec3 v) { printf("\"%s\": [%.9g, %.9g, %.9g], ", name, v.x, v.y, v.z); };
+  printf("{");
+  {  // Cameras.cpp:164-173: ray_direction <-> pixel_position round trip
+    vec2 resolution(800.0f, 600.0f);
+    float fov_y = half_pi<float>();
+    vec3 d = ray_direction(vec2(123.4f, 345.0f), resolution, fov_y);
+    vec2 p = pixel_position(d, resolution, fov_y);
+    v3("roundtrip_direction", d);
+    printf("\"roundtrip_pixel\": [%.9g, %.9g], \"flength_90\": %.9g, ", p.x, p.y, normalized_flength_y(fov_y));
+    // unit_tests/Cameras.test.cpp:38-47: directions at the image centre and corners, 800 x 600, fov 90 degrees
+    v3("dir_400_300", ray_direction(vec2(400.0f, 300.0f), resolution, fov_y));
+    v3("dir_0_0", ray_direction(vec2(0.0f, 0.0f), resolution, fov_y));
+    v3("dir_800_600", ray_direction(vec2(800.0f, 600.0f), resolution, fov_y));
+  }
+  {  // Cameras.cpp:175-189
+    mat4 view = glm::lookAt(vec3(1.f, 3.f, 2.f), vec3(1.f, 3.f, 2.f) + vec3(0.0f, 0.0f, -1.0f), vec3(0.0f, 1.0f, 0.0f));
+    v3("lookat_position", camera_position(view));
+    mat3 t = camera_tangent_space(view);
+    v3("lookat_tangent0", t[0]); v3("lookat_tangent1", t[1]); v3("lookat_tangent2", t[2]);
+  }
+  {  // Technique.cpp:118-152
+    vec3 position(1.f, 3.f, 2.f), direction(1.0f, 0.0f, 10.0f), up(0.0f, 1.0f, 0.0f);
+    mat3 view_to_world = inverse(glm::lookAt(position, position + direction, up));
+    v3("frame_tangent0", view_to_world[1]); v3("frame_tangent1", view_to_world[2]); v3("frame_tangent2", view_to_world[0]);
+    v3("frame_expected1", -normalize(direction)); v3("frame_expected2", normalize(cross(direction, up)));
+    mat3 v2 = inverse(glm::lookAt(vec3(1.f), vec3(1.f) + vec3(1.0f, 2.0f, 3.0f), up));
+    v3("frame2_col2", v2[2]); v3("frame2_expected", -normalize(vec3(1.0f, 2.0f, 3.0f)));
+  }
+  printf("\"ok\": true}\n");
+  return 0;
+}
+
 int main(int argc, char** argv) {
   _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);          // main.cpp:70-71
   _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
@@ -380,10 +576,16 @@ int main(int argc, char** argv) {
     string c = argc > 1 ? argv[1] : "";
     if (c == "dump") return cmd_dump(argc, argv);
     if (c == "rays") return cmd_rays(argc, argv);
-    if (c == "render") return cmd_render(argc, argv);
     if (c == "time") return cmd_time(argc, argv);
     if (c == "grid") return cmd_grid(argc, argv);
-    fprintf(stderr, "usage: ref_harness dump|rays|render|time ...\n");
+    if (c == "errors") return cmd_errors(argc, argv);
+    if (c == "camera") return cmd_camera(argc, argv);
+#ifndef B2PT_STOCK_TIMING
+    if (c == "render") return cmd_render(argc, argv);
+    if (c == "density") return cmd_density(argc, argv);
+    if (c == "pinning") return cmd_pinning(argc, argv);
+#endif
+    fprintf(stderr, "usage: ref_harness dump|rays|render|time|grid|density|errors|pinning|camera ...\n");
     return 2;
   } catch (const std::exception& e) {
     fprintf(stderr, "ref_harness: %s\n", e.what());

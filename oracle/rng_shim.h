@@ -10,14 +10,23 @@
 // The engine's contract towards libstdc++ is unchanged: a 32-bit URBG with
 // min() = 0, max() = 2^32-1.  std::uniform_real_distribution<float> then yields
 // min(float(u) * 2^-32, 0x1.fffffep-1f) and std::piecewise_constant_distribution
-// draws one double from two engine calls — both restated in oracle/b2pt_oracle.cpp
-// and in master_b200/csrc/rng.cuh.
+// draws one double from two engine calls — both restated in master_b200/csrc/rng.cuh and
+// pinned by tests/test_oracle_pinning.py (numpy restatement vs `ref_harness pinning`).
 //
 // Stream definition (shared by the three implementations; see DESIGN.md "RNG"):
 //   mix32(x):  x ^= x>>16; x *= 0x7feb352d; x ^= x>>15; x *= 0x846ca68b; x ^= x>>16
 //   key(seed, domain, index, sample) =
 //       mix32( mix32( mix32(seed + 0x9E3779B9*(domain+1)) ^ index ) + 0x85EBCA6B*sample )
 //   draw(key, ctr) = mix32( key ^ mix32(ctr*0x9E3779B9 + 0x7F4A7C15) ),  ctr = 0, 1, 2, ...
+//
+// Trial mode (trial_draws = k > 0), used only by `ref_harness density`: BSDF::gathering_density
+// (BSDF.cpp:42-66,264-289,393-434) is a rejection loop that makes exactly k draws per trial
+// (DiffuseBSDF 2, PhongBSDF 3) from ONE generator.  The GPU runs the trials of one loop on
+// many lanes at once, so it keys trial t (1, 2, ...) by its number:
+//   trial_key(key, t) = mix32( key ^ mix32(t*0x9E3779B9 + 0x85EBCA6B) ),  draw j of trial t = draw(trial_key, j).
+// In trial mode the engine hands the reference's sequential loop exactly those numbers
+// (draw number c belongs to trial c / k + 1, position c % k), so the trial count N of a loop
+// can be compared with the device's for equality.
 #pragma once
 #include <cstddef>
 #include <cstdint>
@@ -29,6 +38,7 @@ struct b2pt_counter_engine {
   typedef uint32_t result_type;
   uint32_t key = 0;
   uint32_t ctr = 0;
+  uint32_t trial_draws = 0;  // 0 = one sequential stream (everything except `ref_harness density`)
 
   static constexpr result_type min() { return 0u; }
   static constexpr result_type max() { return 0xFFFFFFFFu; }
@@ -49,7 +59,12 @@ struct b2pt_counter_engine {
   // the harness passes a ready-made stream key; low 32 bits are the key
   void seed(size_t s) { key = uint32_t(s); ctr = 0; }
   result_type operator()() {
-    uint32_t r = mix32(key ^ mix32(ctr * 0x9E3779B9U + 0x7F4A7C15U));
+    uint32_t k = key, c = ctr;
+    if (trial_draws) {
+      k = mix32(key ^ mix32((ctr / trial_draws + 1U) * 0x9E3779B9U + 0x85EBCA6BU));
+      c = ctr % trial_draws;
+    }
+    uint32_t r = mix32(k ^ mix32(c * 0x9E3779B9U + 0x7F4A7C15U));
     ++ctr;
     return r;
   }

@@ -182,20 +182,52 @@ def main():
         ("CornellBoxDiffuse", "UPG", 32, 32, 16, dict(beta=2, radius=0.1, per_path=0, from_light=0)),
         ("TestCaseFurnace", "UPG", 24, 24, 16, dict(beta=2, radius=0.1, per_path=0, from_light=0)),
     ]
+    # option branches of the reference that the ABI carries: same scenes, the oracle with other options.
+    # (name, technique, width, height, spp, options, variant) -> render_<name>_<tag>_<variant>.npz; the options are stored in the file.
+    SKY = "0.5,0.6,0.7,0.1,0.2,0.9"
+    variants = [
+        ("CornellBoxDiffuse", "BPT", 32, 32, 2, dict(beta=0), "beta0"),        # FixedBeta<0> (Beta.hpp:24-27)
+        ("CornellBoxDiffuse", "BPT", 32, 32, 2, dict(beta=1.5), "beta1.5"),    # VariableBeta: pow (Beta.hpp:38-42)
+        ("CornellBoxSpecular", "BPT", 32, 32, 2, dict(beta=1), "beta1"),       # FixedBeta<1>
+        ("CornellBoxDiffuse", "VCM", 32, 32, 2, dict(beta=0, radius=0.1), "beta0"),
+        ("CornellBoxDiffuse", "VCM", 32, 32, 2, dict(beta=1.5, radius=0.1), "beta1.5"),
+        ("CornellBoxDiffuse", "VCM", 32, 32, 2, dict(beta=2, radius=0.1, enable_vc=0), "novc"),   # --no-vc (UPG.cpp:67,129,142,156)
+        ("CornellBoxDiffuse", "VCM", 32, 32, 2, dict(beta=2, radius=0.1, enable_vm=0), "novm"),   # --no-vm (UPG.cpp:386-399,510)
+        ("CornellBoxSpecular", "VCM", 32, 32, 2, dict(beta=2, radius=0.1, enable_vm=0), "novm"),
+        ("CornellBoxDiffuse", "VCM", 32, 32, 2, dict(beta=2, radius=0.1, num_photons=2048), "photons2x"),  # num_photons = 2 W H
+        ("CornellBoxDiffuse", "PT", 32, 32, 4, dict(beta=1, lights=0.5), "lights0.5"),            # PT.cpp:23-26
+        ("CornellBoxDiffuse", "PT", 32, 32, 4, dict(beta=1, max_path=3), "maxpath3"),             # PT.cpp:27-40
+        ("CornellBoxDiffuse", "PT", 32, 32, 4, dict(beta=1, max_path=1), "maxpath1"),
+        ("CornellBoxDiffuse", "PT", 32, 32, 2, dict(beta=2), "beta2"),                             # pow(x, beta) (PT.cpp:72,112)
+        ("MetalRings", "BPT", 32, 32, 2, dict(beta=2, sky=SKY), "sky"),                            # misses see the gradient (BPT.cpp:50, Technique.cpp:87-93)
+        ("MetalRings", "VCM", 32, 32, 2, dict(beta=2, radius=0.05, sky=SKY), "sky"),               # UPG.cpp:76
+        ("CornellBoxDiffuse", "UPG", 32, 32, 16, dict(beta=2, radius=0.1, per_path=0, enable_vc=0), "novc"),
+        ("CornellBoxDiffuse", "UPG", 32, 32, 16, dict(beta=2, radius=0.1, per_path=0, enable_vm=0), "novm"),
+        # larger windows: 16 k pixel-samples per case instead of 2-9 k
+        ("CornellBoxDiffuse", "PT", 128, 128, 2, dict(beta=1), "128"),
+        ("CornellBoxDiffuse", "BPT", 128, 128, 2, dict(beta=2), "128"),
+        ("MetalRings", "BPT", 96, 96, 2, dict(beta=2), "96"),
+        # equal-spp UPG images for a relative-RMSE bound (a localised error must not hide behind the image mean)
+        ("CornellBoxDiffuse", "UPG", 32, 32, 256, dict(beta=2, radius=0.1, per_path=0), "256spp"),
+        ("CornellBoxSpecular", "UPG", 32, 32, 256, dict(beta=2, radius=0.1, per_path=0), "256spp"),
+        ("TestCaseFurnace", "UPG", 24, 24, 256, dict(beta=2, radius=0.1, per_path=0), "256spp"),
+    ]
     tag = lambda r: r[1] + ("c" if r[5].get("from_light", 1) == 0 else "")
     only = [a for a in sys.argv[1:] if not a.startswith("-")]
+    renders = [r + ("",) for r in renders] + variants
     if only:
-        renders = [r for r in renders if tag(r) in only or r[0] in only]
+        renders = [r for r in renders if tag(r) in only or r[0] in only or r[6] in only or ("variants" in only and r[6])]
     for name in SUN_SCENES:
         dst = os.path.join(HERE, "scenes", name + ".b2s")
         if not os.path.exists(dst):
             print(name, run("dump", os.path.join(REF, "models", name + ".blend"), dst))
-    for name, tech, w, h, spp, kw in renders:
+    for name, tech, w, h, spp, kw, variant in renders:
         scene = os.path.join(HERE, "scenes", name + ".b2s")
         out = ref_render(scene, tech, w, h, spp, seed=1234, **kw)
         extra = {k: v for k, v in kw.items() if k in ("radius", "beta", "from_light")}
-        np.savez_compressed(os.path.join(HERE, "render_%s_%s.npz" % (name, tag((name, tech, w, h, spp, kw)))), width=w, height=h, seed=1234, spp=spp, **extra, **out)
-        print(name, tech, out["info"])
+        fname = "render_%s_%s%s.npz" % (name, tag((name, tech, w, h, spp, kw)), "_" + variant if variant else "")
+        np.savez_compressed(os.path.join(HERE, fname), width=w, height=h, seed=1234, spp=spp, options=json.dumps(kw), **extra, **out)
+        print(fname, out["info"])
 
 
 if __name__ == "__main__":

@@ -11,6 +11,7 @@ import pytest
 from conftest import ROOT, golden_path
 
 HEADER = os.path.join(ROOT, "include", "b2pt.h")
+DEBUG_HEADER = os.path.join(ROOT, "include", "b2pt_debug.h")
 
 
 @pytest.fixture(scope="module")
@@ -20,8 +21,8 @@ def lib():
     return api.load_library()
 
 
-def declared_functions():
-    src = open(HEADER).read()
+def declared_functions(header=HEADER):
+    src = open(header).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(b2pt_[a-z_]+)\s*\(", src)))
 
@@ -32,7 +33,13 @@ def test_every_declared_symbol_is_exported(lib):
     assert sorted(api.EXPORTS) == names
     for n in names:
         assert getattr(lib, n) is not None
-    assert lib.b2pt_abi_version() == 2
+    assert lib.b2pt_abi_version() == 3
+    # the parity probes are a separate header: same rule, every declared symbol is exported
+    debug = declared_functions(DEBUG_HEADER)
+    assert sorted(api.DEBUG_EXPORTS) == debug
+    for n in debug:
+        assert getattr(lib, n) is not None
+    assert sorted(os.listdir(os.path.join(ROOT, "include"))) == ["b2pt.h", "b2pt_debug.h"]
 
 
 def test_struct_sizes_match_the_header(tmp_path):

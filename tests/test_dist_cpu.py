@@ -55,3 +55,22 @@ def test_sample_split_rejects_bad_rank():
     with pytest.raises(ValueError):
         sample_split(2, 2, 0, 1)
     assert sample_split(1, 8, 3, 4) == (3 * 4 * 8 + 1, 8)
+
+
+def test_technique_sample_indices_are_disjoint_across_ranks_and_calls():
+    """GpuTechnique(first_sample=g, sample_stride=G): consecutive calls on G ranks cover every global sample exactly once."""
+    from master_b200.technique import GpuTechnique
+    world, calls, passes = 4, 5, 3
+    seen = []
+    for rank in range(world):
+        t = GpuTechnique(None, "PT", first_sample=rank, sample_stride=world)
+        for _ in range(calls):
+            first, stride = t.sample_indices(passes)
+            assert stride == world
+            seen += [first + j * stride for j in range(passes)]
+            t.statistics["num_samples"] += passes  # what _account does after a render
+    assert sorted(seen) == list(range(world * calls * passes))
+    t = GpuTechnique(None, "BPT")  # the single-GPU default: pass k of the run is sample k
+    assert t.sample_indices(2) == (0, 1)
+    t.statistics["num_samples"] = 7
+    assert t.sample_indices(1) == (7, 1)

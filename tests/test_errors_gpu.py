@@ -5,10 +5,50 @@ The checker is a numpy restatement of the reference loop: per pixel d = |vec3(a.
 abs += d.x + d.y + d.z and rms += dot(d, d) added in FLOAT in row order (np.cumsum is sequential), then
 sqrt(rms / num), abs / num.  The device sums the same per-pixel terms in double, so it must agree with the double sum of
 those terms to float rounding (1e-6) and with the reference's float loop to that loop's own summation error (1e-3)."""
+import json
+import os
+import subprocess
+
 import numpy as np
 import pytest
 
+from conftest import REF_HARNESS
+
 pytestmark = pytest.mark.gpu
+
+
+def reference_errors(film, ref, tmp_path, window=None):
+    """rms_abs_errors / rms_abs_errors_windowed as COMPILED FROM THE REFERENCE (ImageView.cpp:60-117 inside oracle/_ref/ref_harness)."""
+    h, w = film.shape[:2]
+    a, b = str(tmp_path / "film.f64"), str(tmp_path / "ref.f32")
+    np.ascontiguousarray(film, dtype=np.float64).tofile(a)
+    np.ascontiguousarray(ref, dtype=np.float32).tofile(b)
+    cmd = [REF_HARNESS, "errors", a, b, str(w), str(h)] + ([str(x) for x in window] if window else [])
+    r = json.loads(subprocess.run(cmd, check=True, capture_output=True, text=True).stdout.strip().splitlines()[-1])
+    return r["rms"], r["abs"]
+
+
+needs_harness = pytest.mark.skipif(not os.path.exists(REF_HARNESS), reason="oracle/_ref/ref_harness not built")
+
+
+@needs_harness
+@pytest.mark.parametrize("width,height,window", [(37, 21, None), (512, 512, None), (37, 21, (10, 10, 4)), (37, 21, (0, 0, 3)), (37, 21, (36, 20, 5)),
+                                                 (37, 21, (18, 10, 100)), (1024, 1024, (512, 100, 16))])
+def test_against_the_references_compiled_function(width, height, window, tmp_path):
+    """b2pt_film_errors vs the reference's own rms_abs_errors(_windowed): the per-pixel terms are the reference's arithmetic, the
+    device adds them in double where the reference adds in float — agreement to the float loop's summation error."""
+    import torch
+    from master_b200.technique import film_errors_device
+    film, ref = make(width, height, width * 3 + height)
+    f, r = torch.from_numpy(film).cuda(), torch.from_numpy(ref).cuda()
+    rms, ab = film_errors_device(f.data_ptr(), r.data_ptr(), width, height, window=window)
+    want_rms, want_abs = reference_errors(film, ref, tmp_path, window)
+    tol = 1e-3 if window is None else 2e-5
+    assert rms == pytest.approx(want_rms, rel=tol) and ab == pytest.approx(want_abs, rel=tol)
+    # and the numpy restatement used by the other tests IS the reference loop, to the bit
+    if window is None:
+        sq, a = per_pixel_terms(film, ref)
+        assert reference_loop(sq, a, width * height * 3) == (pytest.approx(want_rms, rel=1e-7), pytest.approx(want_abs, rel=1e-7))
 
 
 def per_pixel_terms(film, ref):
