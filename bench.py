@@ -1,29 +1,32 @@
 #!/usr/bin/env python
 """bench.py — the hot path's headline metric on N B200s of one node.
 
-  python bench.py --gpus N --steps K --warmup W [--technique PT|BPT] [--impl reference]
+  python bench.py --gpus N --steps K --warmup W [--config 1|2|3|3b|4|5a|5b] [--technique PT|BPT|VCM|UPG] [--impl reference]
+                  [--scaling weak|strong]
   (N > 1: python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...)
 
-Workload (BASELINE.json configs[3], "CrytekSponza BPT cam0 ... 1/2/4/8-GPU sample-split scaling"):
-models/CrytekSponza.blend is stripped from the reference mount, so the large-mesh stand-in of SURVEY.md
-§8(d) is used: the reference's own models/LivingRoom.blend (567 304 triangles after one area light is added
-the way loader.cpp:434-456 adds lights; tests/golden/make_large_scene.py), camera 0, 1024 x 1024 (the thesis
-resolution, GenerateResults.psm1:22), roulette 0.9, beta 2 (BPT) / 1 (PT).
+Default workload = BASELINE.json configs[3] ("CrytekSponza BPT cam0 ... 1/2/4/8-GPU sample-split scaling"):
+models/CrytekSponza.blend is stripped from the reference mount, so the large-mesh stand-in of SURVEY.md §8(d) is used: the
+reference's own models/LivingRoom.blend (567 304 triangles after one area light is added the way loader.cpp:434-456 adds lights;
+tests/golden/make_large_scene.py), camera 0, 1024 x 1024 (the thesis resolution, GenerateResults.psm1:22), roulette 0.9,
+beta 2 (BPT) / 1 (PT).  --config selects the stand-ins SURVEY.md §8(d) gives for the other BASELINE.json configs (CONFIGS below).
 
-A STEP is `--spp` passes (default 16) of one sample per pixel over the whole window, i.e. one
-Technique::render call per pass in the reference's terms.  Scaling is weak: every rank renders `--spp`
-passes per step of ITS OWN sample indices (rank g of N takes samples g, g+N, ...) over a replicated scene;
-after the K timed steps the float64 accumulators are summed with ONE all-reduce over NCCL, inside the timed
-region — the exact analogue of `master merge` (Options.cpp:1340-1409).
+A STEP is `--spp` passes of one sample per pixel over the whole window, i.e. `spp` Technique::render calls in the reference's
+terms.  Scaling is weak by default: every rank renders `--spp` passes per step of ITS OWN sample indices (rank g of N takes
+samples g, g+N, ...) over a replicated scene; after the K timed steps the float64 accumulators are summed with ONE all-reduce
+over NCCL, inside the timed region — the exact analogue of `master merge` (Options.cpp:1340-1409).  --scaling strong keeps the
+TOTAL at `--spp` passes per step and gives each rank spp / N of them (a fixed sample budget split over the GPUs).
 
-value  = pixel-samples of all ranks / device time (CUDA events on the launching stream, max over ranks),
-         scene + BVH already resident in HBM.
-e2e    = the same through the host-buffer entry point b2pt_render_host (what GpuTechnique::render calls):
-         per step the parameters go host->device and the dvec4 view comes device->host and is added into
-         the caller's host buffer, all inside the timed region (wall clock around synchronous calls).
+value     = pixel-samples of all ranks / device time (CUDA events on the launching stream, max over ranks),
+            scene + BVH already resident in HBM.
+e2e       = the same through the host-buffer entry point b2pt_render_host (what GpuTechnique::render calls), one call per step:
+            parameters go host->device, the dvec4 film comes device->host and is added into the caller's host buffer, all
+            inside the timed region (wall clock around synchronous calls); at N > 1 the per-rank host views are merged.
+e2e_1pass = the same at the REFERENCE'S contract: one pass per render() call (Application.cpp:66), spp x K calls.
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -36,16 +39,35 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 LARGE = os.path.join(ROOT, "scenes", "_large", "LivingRoom.b2s.xz")
-FALLBACK = os.path.join(ROOT, "tests", "golden", "scenes", "MetalRings.b2s")
-HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+GOLDEN_SCENES = os.path.join(ROOT, "tests", "golden", "scenes")
+HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")              # parity build: RNG shim, Embree capped at AVX
+HARNESS_STOCK = os.path.join(ROOT, "oracle", "_ref", "ref_harness_stock")  # as the reference ships: std::mt19937, -O2 AVX2+FMA, Embree AVX2
 RAY_BYTES_CLOSEST = 48  # 32 B ray in + 16 B hit out
 RAY_BYTES_SHADOW = 36   # 32 B ray in + 4 B visibility out
 
+# BASELINE.json configs and the stand-ins SURVEY.md §8(d) gives for the scenes stripped from the mount.
+# oracle_mean: image mean (r, g, b) of the reference's own CPU render of the scene (BASELINE.md §2 / tests/golden/oracle_means.json),
+# the bench's correctness guard: a film whose mean is off is not a measurement.
+CONFIGS = {
+    "1": dict(scene="CornellBoxDiffuse", technique="PT", res=512, spp=64, what="BASELINE config 1: CornellBoxDiffuse PT"),
+    "2": dict(scene="CornellBoxDiffuse", technique="BPT", res=512, spp=32, what="BASELINE config 2: CornellBoxDiffuse BPT"),
+    "3": dict(scene="MetalRings", technique="BPT", res=512, spp=32,
+              what="BASELINE config 3 stand-in (Bearings.blend is stripped): MetalRings BPT, Phong gold + 2 lights"),
+    "3b": dict(scene="CornellBoxSpecular", technique="BPT", res=512, spp=32,
+               what="BASELINE config 3 stand-in (Bearings.blend is stripped): CornellBoxSpecular BPT, mirror / glass"),
+    "4": dict(scene="LivingRoom", technique="BPT", res=1024, spp=16,
+              what="BASELINE config 4 stand-in (CrytekSponza.blend is stripped): LivingRoom + one area light, 567304 triangles, cam0"),
+    "5a": dict(scene="CornellBoxDiffuse", technique="UPG", res=512, spp=8, radius=0.01,
+               what="BASELINE config 5 stand-in (BreakfastRoom1.blend is stripped): CornellBoxDiffuse UPG r = 0.010"),
+    "5b": dict(scene="CornellBoxDiffuse", technique="VCM", res=512, spp=8, radius=0.025,
+               what="BASELINE config 5 stand-in (BreakfastRoom1.blend is stripped): CornellBoxDiffuse VCM r = 0.025, alpha 0.75"),
+}
 
-def workload():
-    if os.path.exists(LARGE):
-        return LARGE, "LivingRoom+arealight (567304 tris; stand-in for the stripped CrytekSponza.blend), cam0"
-    return FALLBACK, "MetalRings (30558 tris) — FALLBACK: scenes/_large/LivingRoom.b2s.xz absent"
+
+def scene_file(name):
+    if name == "LivingRoom":
+        return LARGE
+    return os.path.join(GOLDEN_SCENES, name + ".b2s")
 
 
 def plain_scene_file(path):
@@ -61,14 +83,42 @@ def plain_scene_file(path):
     return out
 
 
-def run_reference(scene_file, technique, width, height, passes, seconds, threads=0, radius=None):
-    """The reference's own Technique::render loop (oracle/_ref/ref_harness time) on the host cores."""
+def host_has_avx2():
+    try:
+        flags = open("/proc/cpuinfo").read()
+        return all((" " + f + " ") in flags for f in ("avx2", "fma", "bmi2"))
+    except Exception:
+        return False
+
+
+def timing_harness():
+    """(binary, description) of the reference build that is timed: the stock-ISA build when this host can run it."""
+    if os.path.exists(HARNESS_STOCK) and host_has_avx2():
+        return HARNESS_STOCK, "stock build (std::mt19937, g++ -O2 -march=x86-64-v3, Embree 2.12 with EMBREE_MAX_ISA=AVX2 as Makefile:30-37 links it)"
+    return HARNESS, "parity build (counter-based RNG shim, g++ -O2 -msse4.2, Embree 2.12 capped at the AVX ISA)"
+
+
+def run_reference(scene_path, technique, width, height, passes, seconds, threads=0, radius=None):
+    """The reference's own Technique::render loop (ref_harness time) on the host cores."""
+    binary, build = timing_harness()
     extra = ["radius=%g" % radius] if radius is not None else []
-    cmd = [HARNESS, "time", scene_file, "technique=" + technique, "width=%d" % width, "height=%d" % height] + extra + [
+    cmd = [binary, "time", scene_path, "technique=" + technique, "width=%d" % width, "height=%d" % height] + extra + [
         "num_samples=%d" % passes, "seconds=%g" % seconds, "threads=%d" % threads,
         "beta=%d" % (1 if technique == "PT" else 2)]
     out = subprocess.run(cmd, check=True, capture_output=True, text=True).stdout
-    return json.loads(out.strip().splitlines()[-1])
+    r = json.loads(out.strip().splitlines()[-1])
+    r["build"] = build
+    return r
+
+
+def kernel_source_hash():
+    """Hash of the traversal + builder sources: profiler-only figures (DRAM traffic, warp instructions per ray) come from a committed
+    capture and are only quoted while the kernels they were captured from are the ones that run."""
+    h = hashlib.sha1()
+    for f in ("trace.cuh", "bvh8.cuh", "scene.cu", "scene.cuh"):
+        with open(os.path.join(ROOT, "master_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
 
 
 class ClockSampler(threading.Thread):
@@ -140,17 +190,28 @@ def emit(line):
         os.write(_STDOUT_FD, data)
 
 
+def oracle_mean(scene, technique):
+    try:
+        m = json.load(open(os.path.join(ROOT, "tests", "golden", "oracle_means.json")))
+        e = m.get("%s/%s" % (scene, technique)) or m.get(scene)
+        return e
+    except Exception:
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--technique", default=os.environ.get("B2PT_BENCH_TECHNIQUE", "BPT"), choices=["PT", "BPT", "VCM", "UPG"])
-    ap.add_argument("--width", type=int, default=1024)
-    ap.add_argument("--height", type=int, default=1024)
-    ap.add_argument("--spp", type=int, default=16, help="passes (samples per pixel) per step")
+    ap.add_argument("--config", default=os.environ.get("B2PT_BENCH_CONFIG", "4"), choices=sorted(CONFIGS))
+    ap.add_argument("--technique", default=os.environ.get("B2PT_BENCH_TECHNIQUE"), choices=["PT", "BPT", "VCM", "UPG"])
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--spp", type=int, default=None, help="passes (samples per pixel) per step")
     ap.add_argument("--radius", type=float, default=None, help="VCM / UPG merge radius (thesis values: UPG 0.01, VCM 0.025)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
@@ -158,16 +219,32 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    scene_path, scene_name = workload()
-    W, H = a.width, a.height
-    config = {"workload": "%s, %s %dx%d, %d spp/step, roulette 0.9, beta %d" %
-                          (scene_name, a.technique, W, H, a.spp, 1 if a.technique == "PT" else 2),
-              "technique": a.technique, "resolution": [W, H], "spp_per_step": a.spp,
+    cfg = dict(CONFIGS[a.config])
+    technique = a.technique or cfg["technique"]
+    W = a.width or cfg["res"]
+    H = a.height or cfg["res"]
+    spp = a.spp or cfg["spp"]
+    if a.technique in ("VCM", "UPG") and "radius" not in cfg:
+        cfg["radius"] = 0.01 if a.technique == "UPG" else 0.025
+    radius = a.radius if a.radius is not None else cfg.get("radius")
+    scene_name = cfg["scene"]
+    scene_path = scene_file(scene_name)
+    if not os.path.exists(scene_path):
+        scene_name, scene_path = "MetalRings", scene_file("MetalRings")
+        cfg["what"] += " — FALLBACK to MetalRings (30558 tris): %s absent" % os.path.relpath(scene_file(cfg["scene"]), ROOT)
+    N = world
+    strong = a.scaling == "strong"
+    if strong and spp % N:
+        raise SystemExit("bench.py: --scaling strong needs --spp divisible by the number of GPUs")
+    rank_spp = spp // N if strong else spp  # passes per step this rank renders
+    config = {"workload": "%s; %s %dx%d, %d spp/step%s, roulette 0.9, beta %d" %
+                          (cfg["what"], technique, W, H, spp, " in total" if strong else " per GPU", 1 if technique == "PT" else 2),
+              "config": a.config, "scene": scene_name, "technique": technique, "resolution": [W, H], "spp_per_step": spp,
               "parallelism": "sample-split x%d over a replicated scene, one all-reduce of the dvec4 film" % a.gpus}
+    if radius is not None and technique in ("VCM", "UPG"):
+        config["radius"] = radius
+    ref_radius = radius if technique in ("VCM", "UPG") else None
 
-    ref_radius = None
-    if a.technique in ("VCM", "UPG"):
-        ref_radius = a.radius if a.radius is not None else (0.01 if a.technique == "UPG" else 0.025)
     # ------------------------------------------------------------ reference arm: the reference's CPU code
     if a.impl == "reference":
         if rank != 0:
@@ -175,14 +252,14 @@ def main():
         cores = os.cpu_count()
         plain = plain_scene_file(scene_path)
         # a step = ONE pass of the same window (bounded sample of the b200 arm's step of `spp` passes)
-        run_reference(plain, a.technique, W, H, max(a.warmup, 1), 0, cores, radius=ref_radius) if a.warmup else None
-        r = run_reference(plain, a.technique, W, H, a.steps, 0, cores, radius=ref_radius)
+        run_reference(plain, technique, W, H, max(a.warmup, 1), 0, cores, radius=ref_radius) if a.warmup else None
+        r = run_reference(plain, technique, W, H, a.steps, 0, cores, radius=ref_radius)
         val = r["msamples_per_s"]
-        sample = "%d passes of 1 spp at %dx%d, %d host threads, Embree 2.12 + the reference's Technique::render" % (
-            r["num_samples"], W, H, r["threads"])
+        sample = "%d passes of 1 spp at %dx%d, %d host threads, the reference's Technique::render; %s" % (
+            r["num_samples"], W, H, r["threads"], r["build"])
         line = {"impl": "reference", "metric": "Msamples/s", "value": val, "unit": "Msamples/s", "n_gpus": a.gpus,
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": r["seconds"] / max(r["num_samples"], 1) * 1e3,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "higher_is_better": True, "scaling": a.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": config, "mrays_per_s": r["mrays_per_s"],
                 "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": r["threads"], "kind": "reference", "sample": sample},
                 "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -210,17 +287,18 @@ def main():
     scene = api.DeviceSceneHandle(flat)
     info = scene.info()
     tech_options = {}
-    if a.technique in ("VCM", "UPG"):
-        tech_options["radius"] = a.radius if a.radius is not None else (0.01 if a.technique == "UPG" else 0.025)
-        config["radius"] = tech_options["radius"]
-    tech = GpuTechnique(scene, a.technique, **tech_options)
+    if technique in ("VCM", "UPG"):
+        tech_options["radius"] = radius
+    tech = GpuTechnique(scene, technique, **tech_options)
     accum = torch.zeros(H * W, 4, dtype=torch.float64, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
-    N = world
+
+    def split(i, passes):
+        return sample_split(rank, N, i, passes)  # global sample (i * passes + j) * N + rank for pass j
 
     def step(i):
-        first, stride = sample_split(rank, N, i, a.spp)  # global sample (i * spp + j) * N + rank for pass j
-        return tech.render_device(accum.data_ptr(), W, H, passes=a.spp, stream=stream, first_sample=first, sample_stride=stride)
+        first, stride = split(i, rank_spp)
+        return tech.render_device(accum.data_ptr(), W, H, passes=rank_spp, stream=stream, first_sample=first, sample_stride=stride)
 
     def barrier():
         if world > 1:
@@ -255,32 +333,60 @@ def main():
         dist.all_reduce(elapsed_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(counts)
     t_ms = float(elapsed_ms.item())
-    samples = float(W) * H * a.spp * a.steps * N
+    samples = float(W) * H * rank_spp * a.steps * N
     value = samples / (t_ms * 1e-3) * 1e-6
     mrays = float(counts[0] + counts[1]) / (t_ms * 1e-3) * 1e-6
-    # every pixel-sample of every rank landed in the film (minus the non-finite ones the reference also drops)
+    # ---- correctness guard: every pixel-sample of every rank landed in the film (minus the non-finite ones the reference also drops),
+    # and the film's mean is the scene's mean as the REFERENCE renders it (a black or wrongly weighted film is not a measurement)
     dropped = torch.tensor([tot["numeric_errors"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(dropped)
-    film_ok = bool(torch.isfinite(accum).all().item()) and float(accum[:, 3].sum().item()) == samples - float(dropped.item())
+    counted = float(accum[:, 3].sum().item())
+    film_mean = (accum[:, :3].sum(dim=0) / max(counted, 1.0)).tolist()
+    want_mean = oracle_mean(scene_name, technique)
+    film_check = {"finite": bool(torch.isfinite(accum).all().item()), "samples_committed": counted == samples - float(dropped.item()),
+                  "mean": film_mean, "oracle_mean": want_mean["mean"] if want_mean else None,
+                  "oracle": want_mean["source"] if want_mean else "no oracle mean committed for this scene"}
+    tol = 0.03 if technique in ("VCM",) else 0.02  # VCM is biased by design (0.5 % at r = 0.025 on Cornell)
+    film_check["mean_within_tol"] = (bool(np.allclose(film_mean, want_mean["mean"], rtol=tol)) if want_mean else None)
+    film_check["rtol"] = tol
+    film_ok = film_check["finite"] and film_check["samples_committed"] and film_check["mean_within_tol"] is not False
 
     # ------------------------------------------------------------ end to end through host buffers
-    e2e = None
-    if not a.no_e2e:
+    def host_loop(passes_per_call, calls_per_step):
+        """K steps through b2pt_render_host; the per-rank host views are merged at N > 1 (the reduce of the e2e arm)."""
         view = np.zeros((H, W, 4), dtype=np.float64)
-        tech.render(view, passes=a.spp, first_sample=rank, sample_stride=N)  # warm the host path
+        tech.render(view, passes=passes_per_call, first_sample=rank, sample_stride=N)  # warm the host path
         view[:] = 0
         barrier()
         t0 = time.perf_counter()
         for i in range(a.steps):
-            tech.render(view, passes=a.spp, first_sample=(a.warmup + i) * a.spp * N + rank, sample_stride=N)
+            for c in range(calls_per_step):
+                first, stride = split((a.warmup + i) * calls_per_step + c, passes_per_call)
+                tech.render(view, passes=passes_per_call, first_sample=first, sample_stride=stride)
+        if world > 1:
+            dv = torch.from_numpy(view).cuda()
+            reduce_film(dv)
+            if rank == 0:
+                view[:] = dv.cpu().numpy()
         torch.cuda.synchronize()
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": samples / float(dt.item()) * 1e-6, "unit": "Msamples/s",
-               "h2d_bytes_per_step": C.sizeof(api.RenderParams), "d2h_bytes_per_step": W * H * 32,
-               "note": "b2pt_render_host: parameters in, dvec4 film out to pageable host memory and added into the caller's view"}
+        ok = bool(np.isfinite(view).all()) and (rank != 0 or abs(float(view[:, :, 3].sum()) - samples) <= 64)
+        return samples / float(dt.item()) * 1e-6, ok
+
+    e2e = e2e_1pass = None
+    if not a.no_e2e:
+        v, ok = host_loop(rank_spp, 1)
+        e2e = {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": C.sizeof(api.RenderParams), "d2h_bytes_per_step": W * H * 32, "film_ok": ok,
+               "note": "b2pt_render_host, one call of %d passes per step: parameters in, dvec4 film out to host memory and added into "
+                       "the caller's view" % rank_spp}
+        v1, ok1 = host_loop(1, rank_spp)
+        e2e_1pass = {"value": v1, "unit": "Msamples/s", "h2d_bytes_per_step": C.sizeof(api.RenderParams) * rank_spp,
+                     "d2h_bytes_per_step": W * H * 32 * rank_spp, "calls_per_step": rank_spp, "film_ok": ok1,
+                     "note": "the reference's contract: ONE pass per Technique::render call (Application.cpp:66); every call returns "
+                             "with its pass added into the caller's host view"}
 
     if rank != 0:
         if world > 1:
@@ -308,45 +414,57 @@ def main():
                            "grays_per_s_in_kernel": tot["num_shadow_rays"] / (ms["shadow_ms"] * 1e-3) * 1e-9 if ms["shadow_ms"] > 0 else None},
                 "note": "traversal is issue bound by design (SURVEY.md §8(d)): the HBM fraction is small because the scene is served from "
                         "L2/L1; the `issue` object is the roof that binds; see profiles/"}
-    # figures that only a profiler sees (DRAM traffic, warp instructions per ray) come from the committed ncu capture
+    # figures that only a profiler sees (DRAM traffic, warp instructions per ray) come from a committed ncu capture of THESE kernels:
+    # the capture carries the hash of the traversal + builder sources it was taken from and is refused when they have changed since
     try:
-        cap = json.load(open(os.path.join(ROOT, "profiles", "r01_roofline_inputs.json")))
-        per_ray = (cap["dram_bytes_read"] + cap["dram_bytes_written"]) / cap["rays_in_launch"]
-        roofline["traffic"] = per_ray * roofline["rays_per_launch"]  # bytes per launch, scaled to this run's mean launch size
-        roofline["traffic_note"] = "%.0f B/ray of DRAM traffic in the capture (%s) vs %d B/ray algorithmic: the excess is BVH nodes and " \
-                                   "triangles that missed the L2" % (per_ray, cap["capture"], RAY_BYTES_CLOSEST)
-        clk = sampler.summary()["sm_mhz"] or 1965
-        wi = cap["warp_instructions"] / cap["rays_in_launch"]
-        peak_issue = 148 * 4 * clk * 1e6 * 1e-9  # Gwarp-instr/s: 148 SMs x 4 schedulers x 1 instruction per cycle
-        ach_issue = wi * roofline["grays_per_s_in_kernel"] if roofline["grays_per_s_in_kernel"] else None
-        roofline["issue"] = {"bound": "issue", "achieved": ach_issue, "peak": peak_issue, "unit": "Gwarp-instr/s",
-                             "frac": ach_issue / peak_issue if ach_issue else None, "warp_instr_per_ray": wi,
-                             "active_lanes_per_instr": cap["active_lanes_per_instruction"],
-                             "note": "closest-hit stage while it shares the GPU with the other batch's kernels; warp instructions per ray "
-                                     "from the capture, rays/s from this run's CUDA events"}
+        cap = json.load(open(os.path.join(ROOT, "profiles", "roofline_inputs.json")))
+        now = kernel_source_hash()
+        if a.config != "4" or technique != "BPT":
+            roofline["traffic_note"] = "the committed ncu capture is of config 4 / BPT; not quoted for this workload"
+        elif cap.get("kernel_source_hash") != now:
+            roofline["traffic_note"] = "STALE capture refused: %s was taken from kernel sources %s, the sources are now %s — re-capture " \
+                                       "(tools/gpu_session.sh full) and regenerate profiles/roofline_inputs.json" % (
+                                           cap.get("capture"), cap.get("kernel_source_hash"), now)
+        else:
+            per_ray = (cap["dram_bytes_read"] + cap["dram_bytes_written"]) / cap["rays_in_launch"]
+            roofline["traffic"] = per_ray * roofline["rays_per_launch"]  # bytes per launch, scaled to this run's mean launch size
+            roofline["traffic_source"] = "static capture %s @ kernel sources %s" % (cap["capture"], cap["kernel_source_hash"])
+            roofline["traffic_note"] = "%.0f B/ray of DRAM traffic in the capture vs %d B/ray algorithmic; L2 hit rate %.0f %%" % (
+                per_ray, RAY_BYTES_CLOSEST, cap.get("l2_hit_pct", float("nan")))
+            clk = sampler.summary()["sm_mhz"] or 1965
+            wi = cap["warp_instructions"] / cap["rays_in_launch"]
+            peak_issue = 148 * 4 * clk * 1e6 * 1e-9  # Gwarp-instr/s: 148 SMs x 4 schedulers x 1 instruction per cycle
+            ach_issue = wi * roofline["grays_per_s_in_kernel"] if roofline["grays_per_s_in_kernel"] else None
+            roofline["issue"] = {"bound": "issue", "achieved": ach_issue, "peak": peak_issue, "unit": "Gwarp-instr/s",
+                                 "frac": ach_issue / peak_issue if ach_issue else None, "warp_instr_per_ray": wi,
+                                 "active_lanes_per_instr": cap["active_lanes_per_instruction"],
+                                 "source": roofline["traffic_source"],
+                                 "note": "closest-hit stage while it shares the GPU with the other batch's kernels; warp instructions per ray "
+                                         "from the capture, rays/s from this run's CUDA events"}
     except Exception as e:  # pragma: no cover
-        roofline["traffic_note"] = "profiles/r01_roofline_inputs.json unreadable: %s" % e
+        roofline["traffic_note"] = "profiles/roofline_inputs.json unreadable: %s" % e
 
     cpu = None
     if not a.no_cpu_baseline and os.path.exists(HARNESS):
         try:
-            r = run_reference(plain_scene_file(scene_path), a.technique, W, H, 1000, 15.0, os.cpu_count(), radius=ref_radius)
+            r = run_reference(plain_scene_file(scene_path), technique, W, H, 1000, 15.0, os.cpu_count(), radius=ref_radius)
             cpu = {"value": r["msamples_per_s"], "unit": "Msamples/s", "cores": r["threads"], "kind": "reference",
                    "mrays_per_s": r["mrays_per_s"],
                    "sample": "%d passes of 1 spp at %dx%d in %.1f s: the unmodified reference (Embree 2.12 + Technique::render) "
-                             "on %d host threads" % (r["num_samples"], W, H, r["seconds"], r["threads"])}
+                             "on %d host threads; %s" % (r["num_samples"], W, H, r["seconds"], r["threads"], r["build"])}
         except Exception as e:  # pragma: no cover
             cpu = {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "failed: %s" % e}
 
     line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": N, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": t_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": t_ms / a.steps, "higher_is_better": True, "scaling": a.scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": config, "mrays_per_s": mrays,
             "rays_per_sample": float(counts[0] + counts[1]) / samples,
-            "gpu_launches": int(counts[2].item()), "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
-            "clocks": sampler.summary(), "film_ok": film_ok,
-            "l2_policy": "inputs larger than L2: scene %.0f MB (BVH %.0f MB + shading frames) + path pool > 126 MB" % (
-                (info["bvh_bytes"] + info["triangles"] * 112) / 1e6, info["bvh_bytes"] / 1e6),
-            "scene": info, "numeric_errors": tot["numeric_errors"], "capacity_events": tot["capacity_events"]}
+            "gpu_launches": int(counts[2].item()), "e2e": e2e, "e2e_1pass": e2e_1pass, "roofline": roofline, "cpu_baseline": cpu,
+            "clocks": sampler.summary(), "film_ok": film_ok, "film_check": film_check,
+            "l2_policy": "inputs larger than L2: scene %.0f MB (BVH %.0f MB + shading frames) + path pools > 126 MB; the BVH block is "
+                         "pinned in persisting L2 (cudaAccessPolicyWindow), pools stream through the rest" % (
+                             (info["bvh_bytes"] + info["triangles"] * 112) / 1e6, info["bvh_bytes"] / 1e6),
+            "scene_info": info, "numeric_errors": tot["numeric_errors"], "capacity_events": tot["capacity_events"]}
     emit(line)
     if world > 1:
         dist.destroy_process_group()

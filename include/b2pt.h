@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define B2PT_ABI_VERSION 2
+#define B2PT_ABI_VERSION 3
 
 enum {
   B2PT_OK = 0,

@@ -27,6 +27,8 @@
 #include <algorithm>
 #include <memory>
 
+#include <cub/cub.cuh>
+
 #include "render_common.cuh"
 
 #ifndef B2PT_LOGIC_MIN_BLOCKS
@@ -92,6 +94,9 @@ struct BptPool {
   uint32_t* lv_link; // previous vertex of the same path
   uint32_t* lp_idx;  // the first kLpTable vertices of every light path by position: lp_idx[slot * kLpTable + k], one 128-byte line per path
   uint32_t* trace_q[2];  // live slots = the slots with an extension ray in flight; written by the logic stage of iteration i into [i & 1]
+  // ray sorting (B2PT_SORT_RAYS): the logic stage writes the live queue unsorted into sort_q with one key per entry and counts the
+  // keys; a scan and a scatter then lay the queue out in key order in trace_q, each end on its own
+  uint32_t* sort_q; uint32_t* key_q; uint32_t* hist; uint32_t* offs;
   uint2* pair_q;
   float4* shadow_q;  // 3 float4 per entry
   float4* dir_q;     // connections to sun lights, 4 float4 per entry (render_common.cuh: directional_kernel)
@@ -221,12 +226,48 @@ __device__ __forceinline__ unsigned warp_reserve(unsigned* counter, unsigned n) 
   return base + incl - n;
 }
 
+
+// ---------------------------------------------------------------- ray sorting
+// After two or three bounces the rays of neighbouring pixels start from nearby points but leave in every direction: a warp of the
+// traversal stage then walks 32 different parts of the tree (11.7 of 32 lanes per instruction, profiles/r01_bpt_trace_full_v7).  Rays
+// that start in the same cell of a 32^3 grid over the scene and travel into the same octant visit the same upper nodes in the same
+// order (the 8-wide tree orders its children by octant), so the live queue is put in the order of
+//   key = octant << 15 | morton(cell)                                              (18 bits, one counting sort per iteration)
+// before the traversal stage reads it.  The paths do not change, only which lanes run beside which.
+constexpr uint32_t kSortBins = 1u << 18;
+__device__ __forceinline__ uint32_t spread5(uint32_t v) {  // 5 bits -> every third bit
+  v = (v | (v << 8)) & 0x0000100Fu;
+  v = (v | (v << 4)) & 0x000010C3u;
+  v = (v | (v << 2)) & 0x00001249u;
+  return v;
+}
+__device__ __forceinline__ uint32_t ray_sort_key(const DeviceScene& sc, float3 O, float3 D) {
+  const uint32_t cx = uint32_t(fminf(fmaxf((O.x - sc.bounds_lo[0]) * sc.bounds_inv_ext[0] * 32.0f, 0.0f), 31.0f));
+  const uint32_t cy = uint32_t(fminf(fmaxf((O.y - sc.bounds_lo[1]) * sc.bounds_inv_ext[1] * 32.0f, 0.0f), 31.0f));
+  const uint32_t cz = uint32_t(fminf(fmaxf((O.z - sc.bounds_lo[2]) * sc.bounds_inv_ext[2] * 32.0f, 0.0f), 31.0f));
+  const uint32_t oct = (D.x >= 0.0f ? 1u : 0u) | (D.y >= 0.0f ? 2u : 0u) | (D.z >= 0.0f ? 4u : 0u);
+  return (oct << 15) | (spread5(cx) << 2) | (spread5(cy) << 1) | spread5(cz);
+}
+
+// sort_q (two-ended, unsorted) -> trace_q[parity] (two-ended, each end in key order); offs = exclusive scan of the key counts,
+// eye-end keys first.  Clears nothing: the host zeroes hist after the scan.
+__global__ void __launch_bounds__(256) bpt_sort_scatter_kernel(BptPool pool, BptCounters* cnt, int parity) {
+  const uint32_t n_eye = cnt->trace_count[parity], n_light = cnt->light_count[parity];
+  uint32_t* out = pool.trace_q[parity];
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_eye + n_light; i += gridDim.x * blockDim.x) {
+    const uint32_t idx = i < n_eye ? i : pool.size - 1u - (i - n_eye);
+    const uint32_t key = pool.key_q[idx] + (i < n_eye ? 0u : kSortBins);
+    const uint32_t pos = atomicAdd(&pool.offs[key], 1u);
+    out[pos < n_eye ? pos : pool.size - 1u - (pos - n_eye)] = pool.sort_q[idx];
+  }
+}
+
 // The stage runs over the LIVE paths only: after every iteration a path is either done or waiting for the hit of its
 // extension ray, so the trace queue the previous iteration wrote is exactly the list of live slots (`first` = iteration 0
 // of a batch walks every slot instead).  A pool-order loop would leave a warp with as many busy lanes as the pool has
 // live paths — 4 of 32 halfway through a batch (ncu, profiles/).
 __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
-                                                                               int first) {
+                                                                               int first, int sort) {
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     // trace_count[parity ^ 1] is this launch's input; the closest-hit stage clears it afterwards
@@ -246,7 +287,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
   const uint32_t n_eye_round = (n_eye + 31u) & ~31u;
   const uint32_t n_round = n_eye_round + ((n_light + 31u) & ~31u);
   const uint32_t* live_q = pool.trace_q[parity ^ 1];
-  uint32_t* next_q = pool.trace_q[parity];
+  uint32_t* next_q = sort ? pool.sort_q : pool.trace_q[parity];
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
     const bool eye_end = i < n_eye_round;
     const uint32_t j = eye_end ? i : i - n_eye_round;
@@ -500,7 +541,15 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
     const bool to_eye_end = want_trace && st == kEyeWait;
     const unsigned tq = warp_append(&cnt->trace_count[parity], to_eye_end);
     const unsigned lq = warp_append(&cnt->light_count[parity], want_trace && !to_eye_end);
-    if (want_trace) next_q[to_eye_end ? tq : pool.size - 1u - lq] = slot;
+    if (want_trace) {
+      const uint32_t at = to_eye_end ? tq : pool.size - 1u - lq;
+      next_q[at] = slot;
+      if (sort) {
+        const uint32_t key = ray_sort_key(sc, O, bs.omega);
+        pool.key_q[at] = key;
+        atomicAdd(&pool.hist[key + (to_eye_end ? 0u : kSortBins)], 1u);
+      }
+    }
     unsigned pq = warp_reserve(&cnt->pair_count[parity], emit_n);
     if (emit_n) {
       if (pq + emit_n > pool.q_capacity) {
@@ -711,6 +760,7 @@ __global__ void __launch_bounds__(256) bpt_commit_kernel(RenderConfig cfg, BptPo
 // so its kernels are small and end in long single-ray tails; the other lane's kernels fill the machine meanwhile.
 constexpr int kMaxLanes = 8;
 constexpr int kDefaultLanes = 2;
+constexpr int kSortRaysDefault = 0;
 inline int bpt_lanes() {  // B2PT_BPT_LANES overrides the number of concurrent batches for A/B runs
   const char* e = getenv("B2PT_BPT_LANES");
   const int v = e ? atoi(e) : kDefaultLanes;
@@ -729,6 +779,7 @@ struct BptLane {
 struct BptWorkspace {
   BptLane lane[kMaxLanes];
   uint32_t size = 0, per_path = 0;
+  char* scan_tmp = nullptr; size_t scan_bytes = 0;  // cub scratch of the ray sort, one slice per lane
   cudaEvent_t fork = nullptr;
   std::vector<void*> blocks;
 };
@@ -777,6 +828,18 @@ int bpt_workspace(b2pt_scene_s* scene, uint32_t size, uint32_t per_path, int lan
     if ((rc = ws_alloc(w, &p.lp_idx, size_t(size) * kLpTable))) return rc;
     if ((rc = ws_alloc(w, &p.trace_q[0], size))) return rc;
     if ((rc = ws_alloc(w, &p.trace_q[1], size))) return rc;
+    if ((rc = ws_alloc(w, &p.sort_q, size))) return rc;
+    if ((rc = ws_alloc(w, &p.key_q, size))) return rc;
+    if ((rc = ws_alloc(w, &p.hist, 2 * kSortBins))) return rc;
+    if ((rc = ws_alloc(w, &p.offs, 2 * kSortBins))) return rc;
+    B2_CUDA(cudaMemset(p.hist, 0, size_t(2 * kSortBins) * 4));
+    if (!w->scan_tmp) {
+      B2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, w->scan_bytes, p.hist, p.offs, int(2 * kSortBins)));
+      w->scan_bytes = (w->scan_bytes + 255) & ~size_t(255);
+      char* t = nullptr;
+      if ((rc = ws_alloc(w, &t, w->scan_bytes * kMaxLanes))) return rc;
+      w->scan_tmp = t;
+    }
     if ((rc = ws_alloc(w, &p.pair_q, p.q_capacity))) return rc;
     if ((rc = ws_alloc(w, &p.shadow_q, size_t(p.q_capacity) * 3))) return rc;
     if ((rc = ws_alloc(w, &p.dir_q, size_t(size) * 4))) return rc;
@@ -784,7 +847,7 @@ int bpt_workspace(b2pt_scene_s* scene, uint32_t size, uint32_t per_path, int lan
     B2_CUDA(cudaMallocHost((void**)&l.host_counters, sizeof(BptCounters)));
     B2_CUDA(cudaMemset(p.splat, 0, size_t(size) * 3 * sizeof(double)));
     B2_CUDA(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
-    if (k > 0) B2_CUDA(cudaStreamCreateWithFlags(&l.own_stream, cudaStreamNonBlocking));
+    if (k > 0) { B2_CUDA(cudaStreamCreateWithFlags(&l.own_stream, cudaStreamNonBlocking)); scene_l2_window(scene, l.own_stream); }
   }
   *out = w;
   return B2PT_OK;
@@ -825,6 +888,9 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   const char* sv = getenv("B2PT_SHADOW_STREAM");
   const int stream_trace = tv ? (tv[0] == '1' ? 1 : tv[0] == '0' ? 0 : 2) : 2;
   const int stream_shadow = sv ? (sv[0] == '1' ? 1 : sv[0] == '0' ? 0 : 2) : stream_trace;
+  // ray sorting of the closest-hit queue (see ray_sort_key): B2PT_SORT_RAYS=0/1
+  int sort_rays = kSortRaysDefault;
+  { const char* e = getenv("B2PT_SORT_RAYS"); if (e) sort_rays = e[0] == '1' ? 1 : 0; }
   unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
   const int kBatchIters = 8;
 
@@ -866,12 +932,20 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       StageTimer& timer = *timers[k];
       for (int j = 0; j < kBatchIters; ++j, ++g.it) {
         const int parity = g.it & 1;
-        timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0); timer.end();
+        timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays); timer.end();
         timer.begin(kStageShade); bpt_connect_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);
           directional_kernel<<<grid, block, 0, l.stream>>>(cfg.scene, g.pool.dir_q, &l.counters->dir_count[parity], g.pool.size,
                                                           DirectionalParams{cfg.params.beta, 1.0f, 0.0f, 0.0f}, g.pool.rec + kRecRad, uint32_t(kRecFloat4s), &l.counters->basic_rays);
+          timer.end();
+        }
+        if (sort_rays) {
+          timer.begin(kStageShade);
+          size_t bytes = w->scan_bytes;
+          B2_CUDA(cub::DeviceScan::ExclusiveSum(w->scan_tmp + w->scan_bytes * k, bytes, g.pool.hist, g.pool.offs, int(2 * kSortBins), l.stream));
+          bpt_sort_scatter_kernel<<<grid, block, 0, l.stream>>>(g.pool, l.counters, parity);
+          B2_CUDA(cudaMemsetAsync(g.pool.hist, 0, size_t(2 * kSortBins) * 4, l.stream));
           timer.end();
         }
         timer.begin(kStageTrace);

@@ -466,7 +466,7 @@ int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream
     }
   }
   if (lanes == 1) return render_pt_lane(cfg[0], w[0], stream, stats);
-  for (int k = 1; k < lanes; ++k) if (!set->stream[k]) B2_CUDA(cudaStreamCreateWithFlags(&set->stream[k], cudaStreamNonBlocking));
+  for (int k = 1; k < lanes; ++k) if (!set->stream[k]) { B2_CUDA(cudaStreamCreateWithFlags(&set->stream[k], cudaStreamNonBlocking)); scene_l2_window(scene, set->stream[k]); }
   if (!set->fork) B2_CUDA(cudaEventCreateWithFlags(&set->fork, cudaEventDisableTiming));
   int device = 0;
   B2_CUDA(cudaGetDevice(&device));

@@ -87,6 +87,7 @@ int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accu
   if (int rc = make_config(scene, params, accum_dev, path_radiance_dev, &cfg)) return rc;
   B2ptStats local{};
   if (params->num_samples == 0) { if (stats) *stats = local; return B2PT_OK; }
+  scene_l2_window(scene, stream);  // BVH block -> persisting L2 for the kernels of this stream (scene.cu)
   // a stack overflow of an earlier call must not fail this one: the flag is per call
   B2_CUDA(cudaMemsetAsync(scene->dev.error_flags, 0, 4, stream));
   if (!scene->ev[0]) { B2_CUDA(cudaEventCreate(&scene->ev[0])); }

@@ -14,6 +14,7 @@
 // The result is a different tree from Embree's; parity is defined on what the tree returns
 // (closest triangle id, t, u, v), not on the tree.
 #include <cub/cub.cuh>
+#include <algorithm>
 #include <float.h>
 #include <math.h>
 #include <stdlib.h>
@@ -84,7 +85,7 @@ __global__ void bounds_kernel(BuildInput in, float4* tri_lo, float4* tri_hi, uin
     lo = f3(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)));
     hi = f3(fmaxf(a.x, fmaxf(b.x, c.x)), fmaxf(a.y, fmaxf(b.y, c.y)), fmaxf(a.z, fmaxf(b.z, c.z)));
     tri_lo[t] = make_float4(lo.x, lo.y, lo.z, __uint_as_float(m));
-    tri_hi[t] = make_float4(hi.x, hi.y, hi.z, 0.f);
+    tri_hi[t] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(t));  // w: the source triangle of this reference (split_refs_kernel)
   }
   // warp reduce, then one atomic per warp and component
   for (int o = 16; o > 0; o >>= 1) {
@@ -103,6 +104,154 @@ __global__ void bounds_kernel(BuildInput in, float4* tri_lo, float4* tri_hi, uin
     atomicMax(&scene_bounds[4], float_to_ordered(hi.y));
     atomicMax(&scene_bounds[5], float_to_ordered(hi.z));
   }
+}
+
+
+// ---------------------------------------------------------------- triangle pre-splitting (the builder's stand-in for Embree's spatial splits)
+// Embree builds this scene with RTC_SCENE_HIGH_QUALITY = SAH + spatial splits (kernels/common/scene.cpp:100-124): a large or slanted
+// triangle is referenced from several leaves, each with the part of its box that lies in that leaf.  A bottom-up clustering build
+// cannot split while it builds, so the triangles are split BEFORE it, after Karras & Aila, "Fast Parallel Construction of High-Quality
+// Bounding Volume Hierarchies" (HPG 2013, section 4.1), restated from the paper: every triangle gets a priority
+//   (2^-level * (area(box) - area_ideal))^(1/3)     level = that of the coarsest scene-grid plane that cuts the box
+// a budget of `budget * triangles` extra references is handed out in proportion to it, and a triangle's box is cut recursively at the
+// coarsest grid plane that crosses it, each side shrunk to the bounds of the clipped triangle.  A reference is (box, triangle): the
+// leaf test still tests the WHOLE triangle with Embree's arithmetic, so what a ray hits, and its t, u, v, do not change — only how many
+// boxes and triangles it has to look at.
+constexpr int kSplitGridBits = 20;
+constexpr int kMaxRefsPerTri = 64;
+
+struct SceneGrid { float3 lo, ext; };
+
+__device__ __forceinline__ float comp(float3 v, int a) { return a == 0 ? v.x : a == 1 ? v.y : v.z; }
+__device__ __forceinline__ void set_comp(float3& v, int a, float x) { if (a == 0) v.x = x; else if (a == 1) v.y = x; else v.z = x; }
+
+// coarsest grid plane strictly inside (lo, hi) along the best axis; returns the bit of that plane (-1: the box is not cut by any plane)
+__device__ __forceinline__ int split_plane(const SceneGrid& g, float3 lo, float3 hi, int& axis, float& pos) {
+  int best_bit = -1; float best_ext = -1.f;
+  axis = 0; pos = 0.f;
+  const float scale = float(1u << kSplitGridBits);
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const float l = comp(lo, a), h = comp(hi, a), o = comp(g.lo, a), e = comp(g.ext, a);
+    const uint32_t il = uint32_t(fminf(fmaxf((l - o) / e * scale, 0.f), scale - 1.f));
+    const uint32_t ih = uint32_t(fminf(fmaxf((h - o) / e * scale, 0.f), scale - 1.f));
+    if (il == ih) continue;
+    const int bit = 31 - __clz(int(il ^ ih));
+    const float p = o + e * (float((ih >> bit) << bit) / scale);
+    if (!(p > l && p < h)) continue;  // rounding put the plane on the border: nothing to gain
+    if (bit > best_bit || (bit == best_bit && h - l > best_ext)) { best_bit = bit; best_ext = h - l; axis = a; pos = p; }
+  }
+  return best_bit;
+}
+
+__device__ __forceinline__ float box_half_area(float3 lo, float3 hi) {
+  const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+  return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void split_priority_kernel(BuildInput in, SceneGrid g, const float4* tri_lo, const float4* tri_hi, float* priority, double* sum) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  float p = 0.f;
+  if (t < in.num_tris) {
+    const float4 lo4 = tri_lo[t], hi4 = tri_hi[t];
+    const float3 lo = f3(lo4.x, lo4.y, lo4.z), hi = f3(hi4.x, hi4.y, hi4.z);
+    int axis; float pos;
+    const int bit = split_plane(g, lo, hi, axis, pos);
+    if (bit >= 0) {
+      const uint32_t m = __float_as_uint(lo4.w);
+      const float3 a = load_vertex(in, m, t * 3 + 0), b = load_vertex(in, m, t * 3 + 1), c = load_vertex(in, m, t * 3 + 2);
+      const float3 n = cross(b - a, c - a);
+      const float ideal = fabsf(n.x) + fabsf(n.y) + fabsf(n.z);        // twice the sum of the three projected areas
+      const float excess = 2.0f * box_half_area(lo, hi) - ideal;
+      const float root = 2.0f * box_half_area(f3(0.f), g.ext);
+      const int level = kSplitGridBits - bit;                           // 1 = the plane that halves the scene
+      if (excess > 0.f && root > 0.f) p = cbrtf(exp2f(-float(level)) * excess / root);
+    }
+    priority[t] = p;
+  }
+  for (int o = 16; o > 0; o >>= 1) p += __shfl_xor_sync(0xFFFFFFFFu, p, o);
+  if ((threadIdx.x & 31) == 0 && p > 0.f) atomicAdd(sum, double(p));
+}
+
+// total[0] += sum over triangles of min(floor(scale * priority), kMaxRefsPerTri - 1): the splits a scale would hand out
+__global__ void split_budget_kernel(uint32_t n, const float* priority, float scale, unsigned long long* total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned c = t < n ? unsigned(fminf(floorf(scale * priority[t]), float(kMaxRefsPerTri - 1))) : 0u;
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(total, (unsigned long long)c);
+}
+
+// One thread per triangle walks its split tree depth first.  kEmit = false: counts[t] = references produced;
+// kEmit = true: writes them at offsets[t].  Both passes run the same arithmetic, so the counts are exact.
+template <bool kEmit>
+__global__ void split_refs_kernel(BuildInput in, SceneGrid g, const float4* tri_lo, const float4* tri_hi, const float* priority, float scale,
+                                  uint32_t* counts, const uint32_t* offsets, float4* ref_lo, float4* ref_hi) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= in.num_tris) return;
+  const float4 lo4 = tri_lo[t], hi4 = tri_hi[t];
+  const int splits = int(fminf(floorf(scale * priority[t]), float(kMaxRefsPerTri - 1)));
+  uint32_t produced = 0;
+  const uint32_t base = kEmit ? offsets[t] : 0u;
+  auto emit = [&](float3 lo, float3 hi) {
+    if (kEmit) {
+      ref_lo[base + produced] = make_float4(lo.x, lo.y, lo.z, lo4.w);
+      ref_hi[base + produced] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(t));
+    }
+    ++produced;
+  };
+  if (splits <= 0) {
+    emit(f3(lo4.x, lo4.y, lo4.z), f3(hi4.x, hi4.y, hi4.z));
+  } else {
+    const uint32_t m = __float_as_uint(lo4.w);
+    const float3 v[3] = {load_vertex(in, m, t * 3 + 0), load_vertex(in, m, t * 3 + 1), load_vertex(in, m, t * 3 + 2)};
+    struct Task { float3 lo, hi; int splits; };
+    Task stack[kMaxRefsPerTri];
+    int sp = 0;
+    stack[sp++] = Task{f3(lo4.x, lo4.y, lo4.z), f3(hi4.x, hi4.y, hi4.z), splits};
+    while (sp > 0) {
+      const Task k = stack[--sp];
+      int axis; float pos;
+      if (k.splits <= 0 || split_plane(g, k.lo, k.hi, axis, pos) < 0) { emit(k.lo, k.hi); continue; }
+      // bounds of the triangle on either side of the plane (Sutherland-Hodgman against one plane, kept as boxes)
+      float3 llo = f3(INFINITY), lhi = f3(-INFINITY), rlo = f3(INFINITY), rhi = f3(-INFINITY);
+      auto grow = [](float3& lo, float3& hi, float3 p) {
+        lo = f3(fminf(lo.x, p.x), fminf(lo.y, p.y), fminf(lo.z, p.z)); hi = f3(fmaxf(hi.x, p.x), fmaxf(hi.y, p.y), fmaxf(hi.z, p.z));
+      };
+#pragma unroll
+      for (int e = 0; e < 3; ++e) {
+        const float3 p0 = v[e], p1 = v[(e + 1) % 3];
+        const float c0 = comp(p0, axis), c1 = comp(p1, axis);
+        if (c0 <= pos) grow(llo, lhi, p0);
+        if (c0 >= pos) grow(rlo, rhi, p0);
+        if ((c0 < pos && c1 > pos) || (c0 > pos && c1 < pos)) {
+          const float w = fminf(fmaxf((pos - c0) / (c1 - c0), 0.f), 1.f);
+          float3 q = p0 + (p1 - p0) * w;
+          set_comp(q, axis, pos);
+          grow(llo, lhi, q); grow(rlo, rhi, q);
+        }
+      }
+      // each side stays inside the parent box and on its side of the plane
+      float3 plo = k.lo, phi = k.hi;
+      float3 cl_hi = phi; set_comp(cl_hi, axis, pos);
+      float3 cr_lo = plo; set_comp(cr_lo, axis, pos);
+      llo = f3(fmaxf(llo.x, plo.x), fmaxf(llo.y, plo.y), fmaxf(llo.z, plo.z)); lhi = f3(fminf(lhi.x, cl_hi.x), fminf(lhi.y, cl_hi.y), fminf(lhi.z, cl_hi.z));
+      rlo = f3(fmaxf(rlo.x, cr_lo.x), fmaxf(rlo.y, cr_lo.y), fmaxf(rlo.z, cr_lo.z)); rhi = f3(fminf(rhi.x, phi.x), fminf(rhi.y, phi.y), fminf(rhi.z, phi.z));
+      const bool l_ok = llo.x <= lhi.x && llo.y <= lhi.y && llo.z <= lhi.z, r_ok = rlo.x <= rhi.x && rlo.y <= rhi.y && rlo.z <= rhi.z;
+      if (!l_ok || !r_ok) {  // the triangle's part in this box lies on one side only: keep the box that is not empty, with its splits
+        if (l_ok) stack[sp++] = Task{llo, lhi, k.splits - 1};
+        else if (r_ok) stack[sp++] = Task{rlo, rhi, k.splits - 1};
+        else emit(k.lo, k.hi);
+        continue;
+      }
+      const float wl = fmaxf(fmaxf(lhi.x - llo.x, lhi.y - llo.y), lhi.z - llo.z), wr = fmaxf(fmaxf(rhi.x - rlo.x, rhi.y - rlo.y), rhi.z - rlo.z);
+      const int rest = k.splits - 1;
+      int sl = wl + wr > 0.f ? int(float(rest) * wl / (wl + wr) + 0.5f) : rest / 2;
+      sl = sl < 0 ? 0 : sl > rest ? rest : sl;
+      stack[sp++] = Task{rlo, rhi, rest - sl};   // sp stays below kMaxRefsPerTri: a task with s splits yields at most s + 1 references
+      stack[sp++] = Task{llo, lhi, sl};
+    }
+  }
+  if (!kEmit) counts[t] = produced;
 }
 
 __device__ __forceinline__ uint32_t expand_bits10(uint32_t v) {
@@ -196,7 +345,7 @@ __global__ void fit_kernel(int n, const uint64_t* keys, const float4* tri_lo, co
 // kPlocRadius neighbours to either side for the partner that minimises the surface area of the union; mutual
 // nearest neighbours merge; the survivors are compacted and the search repeats until one cluster is left.
 // Cluster ids: [0, n) are the sorted triangles, [n, 2n-1) inner nodes in order of creation.
-constexpr int kPlocRadius = 16;
+constexpr int kPlocRadiusDefault = 16;  // B2PT_PLOC_RADIUS overrides (A/B runs)
 
 __global__ void ploc_init_kernel(uint32_t n, const uint64_t* keys, const float4* tri_lo, const float4* tri_hi, uint32_t* cid,
                                  float4* clo, float4* chi, float4* node_lo, float4* node_hi, uint32_t* size, uint32_t* parent) {
@@ -210,13 +359,13 @@ __global__ void ploc_init_kernel(uint32_t n, const uint64_t* keys, const float4*
   parent[i] = kInvalid;
 }
 
-__global__ void ploc_nearest_kernel(uint32_t m, const float4* clo, const float4* chi, uint32_t* nn) {
+__global__ void ploc_nearest_kernel(uint32_t m, int radius, const float4* clo, const float4* chi, uint32_t* nn) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
   const float4 lo = clo[i], hi = chi[i];
   float best = INFINITY; uint32_t bj = kInvalid;
-  const int j0 = int(i) - kPlocRadius < 0 ? 0 : int(i) - kPlocRadius;
-  const int j1 = int(i) + kPlocRadius >= int(m) ? int(m) - 1 : int(i) + kPlocRadius;
+  const int j0 = int(i) - radius < 0 ? 0 : int(i) - radius;
+  const int j1 = int(i) + radius >= int(m) ? int(m) - 1 : int(i) + radius;
   for (int j = j0; j <= j1; ++j) {
     if (j == int(i)) continue;
     const float4 l2 = clo[j], h2 = chi[j];
@@ -487,21 +636,23 @@ __global__ void collapse8_kernel(uint32_t count, const CollapseItem* items, cons
   out[4] = make_float4(__uint_as_float(pack4(q[4])), __uint_as_float(pack4(q[4] + 4)), __uint_as_float(pack4(q[5])), __uint_as_float(pack4(q[5] + 4)));
 }
 
-// Triangle + shading records in leaf (sorted) order.
-__global__ void pack_kernel(BuildInput in, const uint64_t* keys, const float4* tri_lo, float4* v0o, float4* e1o, float4* e2o,
-                            float4* frames) {
+// Triangle + shading records in leaf (sorted) order, one per REFERENCE (a split triangle is stored once per leaf that holds a
+// part of it: the leaf test reads the record next to its siblings instead of chasing an index).
+__global__ void pack_kernel(BuildInput in, uint32_t num_refs, const uint64_t* keys, const float4* ref_lo, const float4* ref_hi, float4* tris, float4* frames) {
   uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
-  if (pos >= in.num_tris) return;
-  uint32_t t = uint32_t(keys[pos]);
-  uint32_t m = __float_as_uint(tri_lo[t].w);
+  if (pos >= num_refs) return;
+  const uint32_t r = uint32_t(keys[pos]);
+  const uint32_t t = __float_as_uint(ref_hi[r].w);
+  uint32_t m = __float_as_uint(ref_lo[r].w);
   uint32_t prim = t - in.mesh_index_offset[m] / 3u;
   float3 a = load_vertex(in, m, t * 3 + 0), b = load_vertex(in, m, t * 3 + 1), c = load_vertex(in, m, t * 3 + 2);
   float3 e1 = a - b, e2 = c - a;  // Embree: e1 = v0 - v1, e2 = v2 - v0
   uint32_t material = in.mesh_material_id[m];
   uint32_t mask = 1u << (material & 3u);  // rtcSetMask, Scene.cpp:47
-  v0o[pos] = make_float4(a.x, a.y, a.z, __uint_as_float(m));
-  e1o[pos] = make_float4(e1.x, e1.y, e1.z, __uint_as_float(prim));
-  e2o[pos] = make_float4(e2.x, e2.y, e2.z, __uint_as_float(mask));
+  float4* tr = tris + size_t(pos) * kTriFloat4s;
+  tr[0] = make_float4(a.x, a.y, a.z, __uint_as_float(m));
+  tr[1] = make_float4(e1.x, e1.y, e1.z, __uint_as_float(prim));
+  tr[2] = make_float4(e2.x, e2.y, e2.z, __uint_as_float(mask));
   float fr[28];
   for (int k = 0; k < 3; ++k) {
     uint32_t v = in.mesh_vertex_offset[m] + uint32_t(in.indices[t * 3 + k]);
@@ -525,9 +676,10 @@ static int dev_alloc(b2pt_scene_s* s, T** p, size_t count, bool keep) {
 static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
   const uint32_t M = d->num_meshes;
   const uint32_t nv = d->mesh_vertex_offset[M], ni = d->mesh_index_offset[M];
-  const uint32_t n = ni / 3;
-  B2_CHECK(n >= 1, B2PT_ERR_INVALID, "scene has no triangles");
-  B2_CHECK(n < (1u << 28), B2PT_ERR_CAPACITY, "more than 2^28 triangles");
+  const uint32_t nt = ni / 3;  // source triangles
+  uint32_t n = nt;             // references = leaves of the tree (> nt once triangles are pre-split)
+  B2_CHECK(nt >= 1, B2PT_ERR_INVALID, "scene has no triangles");
+  B2_CHECK(nt < (1u << 27), B2PT_ERR_CAPACITY, "more than 2^27 triangles");
   for (uint32_t m = 0; m < M; ++m)
     B2_CHECK(d->mesh_index_offset[m] % 3 == 0, B2PT_ERR_INVALID, "mesh index count not a multiple of 3");
 
@@ -540,7 +692,7 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
 
   // ---- upload (inputs are temporaries except the small tables)
   BuildInput in;
-  in.num_meshes = M; in.num_tris = n;
+  in.num_meshes = M; in.num_tris = nt;
   uint32_t* d_mat = (uint32_t*)tmp(M * 4); uint32_t* d_voff = (uint32_t*)tmp((M + 1) * 4); uint32_t* d_ioff = (uint32_t*)tmp((M + 1) * 4);
   float* d_vert = (float*)tmp(size_t(nv) * 12); float* d_tan = (float*)tmp(size_t(nv) * 36); int32_t* d_idx = (int32_t*)tmp(size_t(ni) * 4);
   B2_CHECK(d_mat && d_voff && d_ioff && d_vert && d_tan && d_idx, B2PT_ERR_CUDA, "cudaMalloc failed for scene upload");
@@ -555,14 +707,73 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
 
   B2_CUDA(cudaEventRecord(ev0));
   const int B = 256;
-  const uint32_t G = (n + B - 1) / B;
-  float4* tri_lo = (float4*)tmp(size_t(n) * 16); float4* tri_hi = (float4*)tmp(size_t(n) * 16);
+  uint32_t G = (nt + B - 1) / B;
+  float4* tri_lo = (float4*)tmp(size_t(nt) * 16); float4* tri_hi = (float4*)tmp(size_t(nt) * 16);
   uint32_t* bounds = (uint32_t*)tmp(6 * 4);
-  uint64_t* keys_in = (uint64_t*)tmp(size_t(n) * 8); uint64_t* keys = (uint64_t*)tmp(size_t(n) * 8);
-  B2_CHECK(tri_lo && tri_hi && bounds && keys_in && keys, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
+  B2_CHECK(tri_lo && tri_hi && bounds, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
   uint32_t init_bounds[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
   B2_CUDA(cudaMemcpy(bounds, init_bounds, sizeof init_bounds, cudaMemcpyHostToDevice));
   bounds_kernel<<<G, B>>>(in, tri_lo, tri_hi, bounds);
+  uint32_t h_bounds[6];
+  B2_CUDA(cudaMemcpy(h_bounds, bounds, sizeof h_bounds, cudaMemcpyDeviceToHost));
+  float ext = 0.f;
+  SceneGrid grid;
+  {
+    float lo[3], ex[3];
+    for (int a = 0; a < 3; ++a) { lo[a] = ordered_to_float(h_bounds[a]); ex[a] = fmaxf(ordered_to_float(h_bounds[3 + a]) - lo[a], 1e-30f); ext = fmaxf(ext, ex[a]); }
+    grid.lo = f3(lo[0], lo[1], lo[2]);
+    grid.ext = f3(ext, ext, ext);  // one cubic grid: its planes are what the Morton order of the build splits at
+    for (int a = 0; a < 3; ++a) { s->dev.bounds_lo[a] = lo[a]; s->dev.bounds_inv_ext[a] = 1.0f / ex[a]; }
+  }
+
+  // ---- triangle pre-splitting: budget * triangles extra references (B2PT_SPLIT_BUDGET, default kSplitBudgetDefault; 0 = off)
+  float split_budget = kSplitBudgetDefault;
+  { const char* e = getenv("B2PT_SPLIT_BUDGET"); if (e) split_budget = float(atof(e)); }
+  if (split_budget > 0.f && nt > 3) {
+    float* priority = (float*)tmp(size_t(nt) * 4);
+    double* psum = (double*)tmp(16);
+    unsigned long long* total = (unsigned long long*)tmp(16);
+    uint32_t* counts = (uint32_t*)tmp(size_t(nt) * 4); uint32_t* offsets = (uint32_t*)tmp(size_t(nt) * 4);
+    B2_CHECK(priority && psum && total && counts && offsets, B2PT_ERR_CUDA, "cudaMalloc failed for triangle splitting");
+    B2_CUDA(cudaMemset(psum, 0, 8));
+    split_priority_kernel<<<G, B>>>(in, grid, tri_lo, tri_hi, priority, psum);
+    double h_psum = 0.0;
+    B2_CUDA(cudaMemcpy(&h_psum, psum, 8, cudaMemcpyDeviceToHost));
+    if (h_psum > 0.0) {
+      // the scale that hands out the budget: floor() and the per-triangle cap lose some, so bisect upwards from budget / sum
+      const double want = double(split_budget) * nt;
+      double lo_s = want / h_psum, hi_s = lo_s * 16.0;
+      float scale = float(lo_s);
+      for (int it = 0; it < 8; ++it) {
+        const double mid = 0.5 * (lo_s + hi_s);
+        B2_CUDA(cudaMemset(total, 0, 8));
+        split_budget_kernel<<<G, B>>>(nt, priority, float(mid), total);
+        unsigned long long h_total = 0;
+        B2_CUDA(cudaMemcpy(&h_total, total, 8, cudaMemcpyDeviceToHost));
+        if (double(h_total) > want) hi_s = mid; else { lo_s = mid; scale = float(mid); }
+      }
+      split_refs_kernel<false><<<G, B>>>(in, grid, tri_lo, tri_hi, priority, scale, counts, nullptr, nullptr, nullptr);
+      size_t scan_bytes = 0;
+      B2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, counts, offsets, int(nt)));
+      void* scan_tmp = tmp(scan_bytes);
+      B2_CHECK(scan_tmp, B2PT_ERR_CUDA, "cudaMalloc failed for scan");
+      B2_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, counts, offsets, int(nt)));
+      uint32_t tail[2];
+      B2_CUDA(cudaMemcpy(&tail[0], offsets + (nt - 1), 4, cudaMemcpyDeviceToHost));
+      B2_CUDA(cudaMemcpy(&tail[1], counts + (nt - 1), 4, cudaMemcpyDeviceToHost));
+      const uint32_t refs = tail[0] + tail[1];
+      B2_CHECK(refs >= nt && refs < (1u << 28), B2PT_ERR_CAPACITY, "more than 2^28 triangle references after splitting");
+      float4* ref_lo = (float4*)tmp(size_t(refs) * 16); float4* ref_hi = (float4*)tmp(size_t(refs) * 16);
+      B2_CHECK(ref_lo && ref_hi, B2PT_ERR_CUDA, "cudaMalloc failed for triangle splitting");
+      split_refs_kernel<true><<<G, B>>>(in, grid, tri_lo, tri_hi, priority, scale, counts, offsets, ref_lo, ref_hi);
+      tri_lo = ref_lo; tri_hi = ref_hi;
+      n = refs;
+      G = (n + B - 1) / B;
+    }
+  }
+
+  uint64_t* keys_in = (uint64_t*)tmp(size_t(n) * 8); uint64_t* keys = (uint64_t*)tmp(size_t(n) * 8);
+  B2_CHECK(keys_in && keys, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
   morton_kernel<<<G, B>>>(n, tri_lo, tri_hi, bounds, keys_in);
   size_t sort_bytes = 0;
   B2_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, keys_in, keys, int(n)));
@@ -572,10 +783,6 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
 
   float4* nodes = nullptr;
   uint32_t num_wide = 1;
-  uint32_t h_bounds[6];
-  B2_CUDA(cudaMemcpy(h_bounds, bounds, sizeof h_bounds, cudaMemcpyDeviceToHost));
-  float ext = 0.f;
-  for (int a = 0; a < 3; ++a) ext = fmaxf(ext, ordered_to_float(h_bounds[3 + a]) - ordered_to_float(h_bounds[a]));
   const float pad = ext * 1e-6f;  // conservative slack on every child box (see trace.cuh)
 
   const char* bvh_env = getenv("B2PT_BVH");
@@ -611,6 +818,8 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
     B2_CHECK(bin && parent_inner && parent_leaf && box_lo && box_hi && visit && items_a && items_b && counters, B2PT_ERR_CUDA,
              "cudaMalloc failed for BVH build");
     uint32_t root_bin = 0;
+    int ploc_radius = kPlocRadiusDefault;
+    { const char* e = getenv("B2PT_PLOC_RADIUS"); if (e) { const int v = atoi(e); if (v >= 1 && v <= 256) ploc_radius = v; } }
     const char* builder = getenv("B2PT_BUILDER");
     if (builder && !strcmp(builder, "lbvh")) {
       B2_CUDA(cudaMemset(visit, 0, size_t(n) * 4));
@@ -642,7 +851,7 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
       int guard = 0;
       while (m > 1) {
         const uint32_t g = (m + B - 1) / B;
-        ploc_nearest_kernel<<<g, B>>>(m, clo_a, chi_a, nn);
+        ploc_nearest_kernel<<<g, B>>>(m, ploc_radius, clo_a, chi_a, nn);
         ploc_merge_kernel<<<g, B>>>(m, n, nn, cid_a, clo_a, chi_a, cid_b, clo_b, chi_b, valid, next_node, left, right, node_lo, node_hi,
                                     size, parent);
         B2_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, valid, offset, int(m)));
@@ -664,7 +873,8 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
     { const char* e = getenv("B2PT_LEAF_MAX"); if (e && e[0] >= '1' && e[0] <= '3') leaf_max = uint32_t(e[0] - '0'); }
     if (wide8 && n > 3) {
       // compressed 8-wide tree (bvh8.cuh); a wide inner node has at least two children, so n nodes is a safe bound
-      if (int rc = dev_alloc(s, &nodes8, size_t(n) * 5, true)) return rc;
+      nodes8 = (float4*)tmp(size_t(n) * 5 * 16);  // built here, then copied at its real size into the BVH block below
+      B2_CHECK(nodes8, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
       tri_map = (uint64_t*)tmp(size_t(n) * 8);
       uint32_t* counters8 = (uint32_t*)tmp(16);  // [0] num_wide, [1] next_count, [2] triangles placed
       B2_CHECK(tri_map && counters8, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
@@ -705,7 +915,8 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
   }
   if (wide8 && n <= 3) {
     // a root with one leaf child that holds every triangle
-    if (int rc = dev_alloc(s, &nodes8, 5, true)) return rc;
+    nodes8 = (float4*)tmp(5 * 16);
+    B2_CHECK(nodes8, B2PT_ERR_CUDA, "cudaMalloc failed for BVH build");
     tri_map = (uint64_t*)tmp(size_t(n) * 8);
     CollapseItem* item = (CollapseItem*)tmp(sizeof(CollapseItem));
     uint32_t* counters8 = (uint32_t*)tmp(16);
@@ -720,12 +931,19 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
     num_wide = 1;
   }
 
-  float4 *v0o, *e1o, *e2o, *frames;
-  if (int rc = dev_alloc(s, &v0o, n, true)) return rc;
-  if (int rc = dev_alloc(s, &e1o, n, true)) return rc;
-  if (int rc = dev_alloc(s, &e2o, n, true)) return rc;
+  // ---- the BVH block: [8-wide nodes | triangle records], ONE allocation so that a single access-policy window covers what every
+  // ray reads again and again (b2pt_scene_l2_window below); the shading frames are read once per hit and stay outside
+  float4 *tris = nullptr, *frames = nullptr, *bvh_block = nullptr;
+  const size_t node_f4 = nodes8 ? size_t(num_wide) * 5 : 0;  // kNode8Float4s (bvh8.cuh)
+  if (int rc = dev_alloc(s, &bvh_block, node_f4 + size_t(n) * kTriFloat4s, true)) return rc;
+  if (nodes8) {
+    B2_CUDA(cudaMemcpy(bvh_block, nodes8, node_f4 * 16, cudaMemcpyDeviceToDevice));
+    nodes8 = bvh_block;
+  }
+  tris = bvh_block + node_f4;
+  s->bvh_block = bvh_block; s->bvh_block_bytes = (node_f4 + size_t(n) * kTriFloat4s) * 16;
   if (int rc = dev_alloc(s, &frames, size_t(n) * kFrameFloat4s, true)) return rc;
-  pack_kernel<<<G, B>>>(in, keys, tri_lo, v0o, e1o, e2o, frames);
+  pack_kernel<<<G, B>>>(in, n, keys, tri_lo, tri_hi, tris, frames);
   B2_CUDA(cudaEventRecord(ev1));
   B2_CUDA(cudaEventSynchronize(ev1));
   B2_CUDA(cudaGetLastError());
@@ -767,15 +985,44 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
   B2_CUDA(cudaMemset(d_flags, 0, 16));
 
   DeviceScene& ds = s->dev;
-  ds.num_tris = n; ds.num_nodes = num_wide; ds.num_materials = d->num_materials; ds.num_lights = L;
-  ds.tri_v0 = v0o; ds.tri_e1 = e1o; ds.tri_e2 = e2o; ds.tri_frames = frames; ds.nodes = nodes; ds.nodes8 = nodes8;
+  ds.num_tris = n; ds.num_source_tris = nt; ds.num_nodes = num_wide; ds.num_materials = d->num_materials; ds.num_lights = L;
+  ds.tris = tris; ds.tri_frames = frames; ds.nodes = nodes; ds.nodes8 = nodes8;
   ds.materials = d_materials; ds.lights = d_lights; ds.light_cp = d_cp; ds.light_den = d_den; ds.light_int = d_int;
   ds.error_flags = d_flags;
   { const char* e = getenv("B2PT_DYN_FETCH"); if (e) ds.dyn_fetch_lanes = atoi(e); }
   { const char* e = getenv("B2PT_DYN_TRI"); if (e) ds.dyn_tri_lanes = atoi(e); }
   for (uint32_t k = 0; k < L; ++k) if (d->lights[k].diffuse == 0.0f) ds.has_directional = 1u;
   s->bvh_bytes = uint64_t(num_wide) * (nodes8 ? 5 : kNodeFloat4s) * 16 + uint64_t(n) * 48;
+  // ---- L2 residency (north_star: "top BVH levels staged in shared memory / L2"): set aside as much persisting L2 as the device
+  // allows for the BVH block; render streams attach the window (b2pt_scene_l2_window).  B2PT_L2_PERSIST=0 turns it off (A/B runs).
+  {
+    const char* e = getenv("B2PT_L2_PERSIST");
+    int dev = 0; cudaDeviceProp prop{};
+    if (!(e && e[0] == '0') && cudaGetDevice(&dev) == cudaSuccess && cudaGetDeviceProperties(&prop, dev) == cudaSuccess &&
+        prop.persistingL2CacheMaxSize > 0 && prop.accessPolicyMaxWindowSize > 0) {
+      const size_t want = std::min<size_t>(s->bvh_block_bytes, size_t(prop.persistingL2CacheMaxSize));
+      if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+        s->l2_window_bytes = std::min<size_t>(s->bvh_block_bytes, size_t(prop.accessPolicyMaxWindowSize));
+        s->l2_hit_ratio = float(std::min(1.0, double(want) / double(s->l2_window_bytes)));
+      } else {
+        cudaGetLastError();
+      }
+    }
+  }
   return B2PT_OK;
+}
+
+// Attaches the scene's persisting-L2 window to a stream: loads of the BVH block (nodes + triangle records) are kept in the set-aside
+// part of the L2 with probability hit_ratio, everything else the stream touches (path pools, queues) is streamed through the rest.
+void scene_l2_window(const b2pt_scene_s* s, cudaStream_t stream) {
+  if (!s->l2_window_bytes) return;
+  cudaStreamAttrValue attr{};
+  attr.accessPolicyWindow.base_ptr = s->bvh_block;
+  attr.accessPolicyWindow.num_bytes = s->l2_window_bytes;
+  attr.accessPolicyWindow.hitRatio = s->l2_hit_ratio;
+  attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+  attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  if (cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
 }
 
 }  // namespace b2pt

@@ -1,10 +1,12 @@
 // scene.cuh — the scene as it lives in HBM.
 //
 // Replaces what haste::Scene + Embree hold on the host (Scene.hpp:28-76, Scene.cpp:20-73):
-//   * triangles in BVH-leaf order as three float4 streams (128-bit loads):
-//       tri_v0 = (v0.xyz, bits geomID)   tri_e1 = (v0-v1, bits primID)   tri_e2 = (v2-v0, bits mask)
+//   * triangle references in BVH-leaf order, one 48-byte record each (three 128-bit loads from two or three adjacent sectors;
+//     the up-to-three triangles of a leaf are contiguous):
+//       (v0.xyz, bits geomID)   (v0-v1, bits primID)   (v2-v0, bits mask)
 //     — Embree's Triangle4 convention e1 = v0-v1, e2 = v2-v0 (kernels/geometry/triangle.h:54), so the
-//     Möller–Trumbore arithmetic can follow triangle_intersector_moeller.h:78-111 operation by operation;
+//     Möller–Trumbore arithmetic can follow triangle_intersector_moeller.h:78-111 operation by operation.  A triangle the builder
+//     split (scene.cu: split_refs_kernel) has one record per leaf that holds a part of it;
 //   * the per-triangle shading record in the same order: the three vertex tangent frames
 //     (Mesh::tangents, AreaLights.hpp:14-20) + material id, 7 float4 = 112 B, so querySurface
 //     (Scene.cpp:80-126) is one contiguous read instead of index + 3 gathers;
@@ -19,6 +21,8 @@ namespace b2pt {
 constexpr uint32_t kInvalid = 0xFFFFFFFFu;
 constexpr int kNodeFloat4s = 8;    // 128-byte BVH4 node
 constexpr int kFrameFloat4s = 7;   // 112-byte shading record per triangle
+constexpr int kTriFloat4s = 3;     // 48-byte triangle record
+constexpr float kSplitBudgetDefault = 0.5f;  // extra triangle references the builder may create, as a fraction of the triangles
 constexpr int kMaxLeafTris = 4;
 
 // Child link encoding in node float4 #6:
@@ -33,15 +37,15 @@ __host__ __device__ __forceinline__ uint32_t make_leaf(uint32_t first, uint32_t 
 }
 
 struct DeviceScene {
-  uint32_t num_tris = 0;
+  uint32_t num_tris = 0;         // triangle REFERENCES = records in `tris` / `tri_frames`
+  uint32_t num_source_tris = 0;  // triangles of the scene
   uint32_t num_nodes = 0;
   uint32_t num_materials = 0;
   uint32_t num_lights = 0;
   uint32_t has_directional = 0;  // some light is a sun (AreaLight::diffuse == false): the integrators run the directional stage
-  const float4* tri_v0 = nullptr;
-  const float4* tri_e1 = nullptr;
-  const float4* tri_e2 = nullptr;
+  const float4* tris = nullptr;        // [num_tris * kTriFloat4s]
   const float4* tri_frames = nullptr;  // [num_tris * kFrameFloat4s]
+  float bounds_lo[3] = {0.f, 0.f, 0.f}, bounds_inv_ext[3] = {1.f, 1.f, 1.f};  // scene box: the cells of the ray-sorting key (bpt.cu)
   const float4* nodes = nullptr;       // 4-wide tree: [num_nodes * kNodeFloat4s], root = node 0 (null when the 8-wide tree is built)
   const float4* nodes8 = nullptr;      // compressed 8-wide tree (bvh8.cuh): [num_nodes * 5], root = node 0
   const B2ptMaterial* materials = nullptr;
@@ -73,4 +77,9 @@ struct b2pt_scene_s {
   double* film_host = nullptr;
   size_t film_doubles = 0;
   cudaEvent_t ev[2] = {nullptr, nullptr};  // timing pair of b2pt_render
+  // nodes + triangle records in one allocation, and the persisting-L2 window over it (scene.cu: scene_l2_window)
+  void* bvh_block = nullptr;
+  size_t bvh_block_bytes = 0, l2_window_bytes = 0;
+  float l2_hit_ratio = 0.f;
 };
+namespace b2pt { void scene_l2_window(const b2pt_scene_s* s, cudaStream_t stream); }

@@ -85,7 +85,7 @@ __device__ __forceinline__ Surface query_surface(const DeviceScene& sc, uint32_t
   t2 = normalize(t2);
   p.tan.c0 = t0; p.tan.c1 = t1; p.tan.c2 = t2;
   // RayIsect::gnormal() = normalize(-Ng) with Embree's Ng = cross(e1, e2) (triangle.h:54)
-  const float4 q1 = __ldg(&sc.tri_e1[tri]), q2 = __ldg(&sc.tri_e2[tri]);
+  const float4 q1 = __ldg(sc.tris + size_t(tri) * kTriFloat4s + 1), q2 = __ldg(sc.tris + size_t(tri) * kTriFloat4s + 2);
   const float3 e1 = f3(q1.x, q1.y, q1.z), e2 = f3(q2.x, q2.y, q2.z);
   const float3 Ng = f3(e1.y * e2.z - e1.z * e2.y, e1.z * e2.x - e1.x * e2.z, e1.x * e2.y - e1.y * e2.x);
   float3 gn = normalize(-Ng);

@@ -58,9 +58,10 @@ __device__ __forceinline__ float rcp_embree(float a) {  // a > 0
 // ray_mask: RTCRay::mask — 0xFFFFFFFF (Scene::intersect) or 1 << entity_type::mesh (intersectMesh / occluded).
 __device__ __forceinline__ bool intersect_triangle(const DeviceScene& sc, uint32_t pos, float3 O, float3 D, float tnear,
                                                    float& tfar, float& u, float& v, uint32_t ray_mask) {
-  const float4 q0 = __ldg(&sc.tri_v0[pos]);
-  const float4 q1 = __ldg(&sc.tri_e1[pos]);
-  const float4 q2 = __ldg(&sc.tri_e2[pos]);
+  const float4* tr = sc.tris + size_t(pos) * kTriFloat4s;
+  const float4 q0 = __ldg(tr + 0);
+  const float4 q1 = __ldg(tr + 1);
+  const float4 q2 = __ldg(tr + 2);
   // geometry mask = 1 << (material_id & 3) (rtcSetMask, Scene.cpp:47); Embree skips the triangle when (mask & ray.mask) == 0
   if ((__float_as_uint(q2.w) & ray_mask) == 0u) return false;
   const float3 v0 = f3(q0.x, q0.y, q0.z), e1 = f3(q1.x, q1.y, q1.z), e2 = f3(q2.x, q2.y, q2.z);
@@ -484,7 +485,7 @@ inline int persistent_grid(size_t n, int block) {
 }
 
 // geomID / primID of a triangle in leaf order
-__device__ __forceinline__ uint32_t tri_geom(const DeviceScene& sc, uint32_t pos) { return __float_as_uint(__ldg(&sc.tri_v0[pos]).w); }
-__device__ __forceinline__ uint32_t tri_prim(const DeviceScene& sc, uint32_t pos) { return __float_as_uint(__ldg(&sc.tri_e1[pos]).w); }
+__device__ __forceinline__ uint32_t tri_geom(const DeviceScene& sc, uint32_t pos) { return __float_as_uint(__ldg(sc.tris + size_t(pos) * kTriFloat4s).w); }
+__device__ __forceinline__ uint32_t tri_prim(const DeviceScene& sc, uint32_t pos) { return __float_as_uint(__ldg(sc.tris + size_t(pos) * kTriFloat4s + 1).w); }
 
 }  // namespace b2pt

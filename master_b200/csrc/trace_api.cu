@@ -67,6 +67,7 @@ int launch_trace(b2pt_scene_s* scene, const B2ptRay* rays, size_t n, unsigned mo
   B2_CHECK(n < (size_t(1) << 31), B2PT_ERR_CAPACITY, "b2pt_trace: more than 2^31 rays in one call");
   B2_CHECK(mode <= B2PT_TRACE_OCCLUDED_MESH, B2PT_ERR_INVALID, "b2pt_trace: unknown mode");
   const int block = 256;
+  scene_l2_window(scene, stream);
   const float4* r = reinterpret_cast<const float4*>(rays);
   const char* stream_env = getenv("B2PT_TRACE_STREAM");  // 1: persistent warp-synchronous traversal (wins on >= 4 M incoherent rays)
   if (!(stream_env && (stream_env[0] == '1' || stream_env[0] == '2')) || !sc.nodes8) {

@@ -1298,7 +1298,7 @@ int vcm_workspace(b2pt_scene_s* scene, uint32_t pixels, uint32_t photons, uint32
     }
   }
   *lanes_io = lanes;
-  for (int k = 1; k < lanes; ++k) if (!set->stream[k]) B2_CUDA(cudaStreamCreateWithFlags(&set->stream[k], cudaStreamNonBlocking));
+  for (int k = 1; k < lanes; ++k) if (!set->stream[k]) { B2_CUDA(cudaStreamCreateWithFlags(&set->stream[k], cudaStreamNonBlocking)); scene_l2_window(scene, set->stream[k]); }
   if (lanes > 1 && !set->fork) B2_CUDA(cudaEventCreateWithFlags(&set->fork, cudaEventDisableTiming));
   *out = set;
   return B2PT_OK;

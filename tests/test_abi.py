@@ -89,6 +89,10 @@ def test_product_does_not_touch_the_oracle():
                     s = line.strip()
                     if s.startswith(("#include", "import ", "from ")) or "subprocess" in s or "dlopen" in s or "CDLL" in s:
                         assert "oracle" not in s, (f, s)
+            if f.endswith(".sh"):  # build recipes: no include path, library path or source under oracle/
+                for line in open(os.path.join(dirpath, f), errors="replace").read().splitlines():
+                    if not line.strip().startswith("#"):
+                        assert "oracle" not in line, (f, line)
 
 
 def test_b2s_round_trip(tmp_path, flat_scenes):

@@ -1,0 +1,86 @@
+"""Parity on the workload that is benchmarked: scenes/_large/LivingRoom.b2s.xz (567 304 triangles; the stand-in for the stripped
+CrytekSponza.blend; built from the reference's models/ by tests/golden/make_large_scene.py).
+
+* ray level: >= 1 M rays per class (camera / cosine bounce / shadow) against Embree itself, run on this host by the shipped
+  oracle/_ref/ref_harness — ids >= 99.99 %, t / u / v bit-exact on the same triangle (Scene.cpp:151-226);
+* per path: PT and BPT at 128 x 128 x 2 spp against goldens the oracle rendered from the same scene file with the same streams."""
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import REF_HARNESS, ROOT, golden_path
+from test_pt_gpu import gpu_render, image_rel_rmse, path_agreement
+from test_trace_gpu import compare_closest
+
+pytestmark = pytest.mark.gpu
+
+LARGE = os.path.join(ROOT, "scenes", "_large", "LivingRoom.b2s.xz")
+needs_scene = pytest.mark.skipif(not os.path.exists(LARGE), reason="scenes/_large/LivingRoom.b2s.xz absent (built from the reference's models/)")
+
+
+@pytest.fixture(scope="module")
+def large():
+    from master_b200 import api
+    from master_b200.scene import load_b2s
+    flat = load_b2s(LARGE)
+    scene = api.DeviceSceneHandle(flat)
+    yield flat, scene
+    scene.close()
+
+
+@needs_scene
+@pytest.mark.skipif(not os.path.exists(REF_HARNESS), reason="oracle/_ref/ref_harness not built")
+def test_livingroom_live_embree_parity_1m(large, tmp_path):
+    sys.path.insert(0, golden_path())
+    sys.path.insert(0, ROOT)
+    import bench
+    import make_golden as mg
+    from master_b200 import api
+    flat, scene = large
+    mg.TMP = str(tmp_path)
+    plain = bench.plain_scene_file(LARGE)
+    sets = mg.make_ray_sets(flat, plain, 1024, 1024, seed=11)
+    assert len(sets["camera_rays"]) >= 1 << 20 and len(sets["bounce_rays"]) >= 1000000 and len(sets["shadow_rays"]) >= 1000000
+    compare_closest(scene.trace(sets["camera_rays"], api.TRACE_CLOSEST_ALL), sets["camera_hits"], "LivingRoom 1M camera")
+    compare_closest(scene.trace(sets["bounce_rays"], api.TRACE_CLOSEST_ALL), sets["bounce_hits"], "LivingRoom 1M bounce/all")
+    compare_closest(scene.trace(sets["bounce_rays"], api.TRACE_CLOSEST_MESH), sets["bounce_mesh_hits"], "LivingRoom 1M bounce/mesh")
+    occ = scene.trace(sets["shadow_rays"], api.TRACE_OCCLUDED_MESH)
+    agree = (occ["geom"] == sets["shadow_hits"]["geom"]).mean()
+    print(json.dumps(dict(what="LivingRoom 1M shadow", rays=len(occ), agree=float(agree))))
+    assert agree >= 0.9999
+    # the persistent traversal the integrators use (trace_dyn8) returns the same hits as one ray per thread
+    os.environ["B2PT_TRACE_STREAM"] = "2"
+    try:
+        compare_closest(scene.trace(sets["bounce_rays"], api.TRACE_CLOSEST_ALL), sets["bounce_hits"], "LivingRoom 1M bounce/all dyn8")
+    finally:
+        del os.environ["B2PT_TRACE_STREAM"]
+
+
+@needs_scene
+@pytest.mark.parametrize("tech", ["PT", "BPT"])
+def test_livingroom_per_path(tech, large):
+    flat, scene = large
+    g = np.load(golden_path("render_LivingRoom_%s.npz" % tech))
+    w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
+    info = json.loads(str(g["info"]))
+    accum, paths, stats = gpu_render(scene, flat, tech, w, h, spp, int(g["seed"]), beta=float(g["beta"]))
+    frac, err = path_agreement(paths, g["paths"])
+    mean_ref, mean_ours = g["accum"][:, :3].mean(axis=0), accum[:, :3].mean(axis=0)
+    out = dict(scene="LivingRoom", tech=tech, paths=int(err.size), within_1e4=frac, flips=int((err > 1e-4).sum()),
+               rays=[stats["num_basic_rays"], stats["num_shadow_rays"]], ref_rays=[info["basic_rays"], info["shadow_rays"]],
+               mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist(), rel_rmse=image_rel_rmse(accum, g["accum"]))
+    if tech == "BPT":
+        light_ours = accum[:, :3] - paths.astype(np.float64).sum(axis=0)
+        scale = max(np.abs(g["light"]).max(), 1e-6)
+        out["light_pixels_off"] = float((np.abs(light_ours - g["light"]).max(axis=1) > 1e-4 * scale + 1e-4 * np.abs(g["light"]).max(axis=1)).mean())
+    print(json.dumps(out))
+    assert frac >= 0.999
+    assert np.array_equal(accum[:, 3], g["accum"][:, 3])
+    np.testing.assert_allclose(mean_ours, mean_ref, rtol=5e-3, atol=1e-6)
+    if tech == "BPT":
+        assert out["light_pixels_off"] <= 0.01
+    else:
+        assert stats["num_basic_rays"] == pytest.approx(info["basic_rays"], rel=0.01)
