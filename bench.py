@@ -356,7 +356,8 @@ def main():
     def host_loop(passes_per_call, calls_per_step):
         """K steps through b2pt_render_host; the per-rank host views are merged at N > 1 (the reduce of the e2e arm)."""
         view = np.zeros((H, W, 4), dtype=np.float64)
-        tech.render(view, passes=passes_per_call, first_sample=rank, sample_stride=N)  # warm the host path
+        tech.render(view, passes=passes_per_call, first_sample=rank, sample_stride=N)  # warm the host path (buffers, threads)
+        tech.render(view, passes=0)  # flush: nothing rendered ahead of the timed region survives into it
         view[:] = 0
         barrier()
         t0 = time.perf_counter()
@@ -464,7 +465,7 @@ def main():
             "l2_policy": "inputs larger than L2: scene %.0f MB (BVH %.0f MB + shading frames) + path pools > 126 MB; the BVH block is "
                          "pinned in persisting L2 (cudaAccessPolicyWindow), pools stream through the rest" % (
                              (info["bvh_bytes"] + info["triangles"] * 112) / 1e6, info["bvh_bytes"] / 1e6),
-            "scene_info": info, "numeric_errors": tot["numeric_errors"], "capacity_events": tot["capacity_events"]}
+            "scene_info": info, "l2_window": scene.l2_window(), "numeric_errors": tot["numeric_errors"], "capacity_events": tot["capacity_events"]}
     emit(line)
     if world > 1:
         dist.destroy_process_group()

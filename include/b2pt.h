@@ -209,8 +209,13 @@ int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accu
                 float* path_radiance_dev, void* stream, B2ptStats* stats);
 
 /*
- * Same, through HOST memory: view_host (width*height dvec4) += the passes.  This is
- * what GpuTechnique::render calls; the device->host copy is inside.
+ * Same, through HOST memory: view_host (width*height dvec4) += the passes.  This is what
+ * GpuTechnique::render calls — one pass per call in the reference (Application.cpp:66); the
+ * device->host copy is inside.  Passes are pure functions of (seed, sample index), so the
+ * library renders AHEAD of a caller that asks for consecutive sample indices with otherwise
+ * unchanged parameters (csrc/host_pipeline.cu): what a call adds is exactly the passes it names.
+ * num_samples = 0 waits for passes being rendered ahead and drops them (a flush);
+ * B2PT_HOST_LOOKAHEAD=0 in the environment turns rendering ahead off.
  */
 int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* params, double* view_host,
                      B2ptStats* stats);

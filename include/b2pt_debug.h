@@ -63,6 +63,11 @@ int b2pt_debug_tree_stats(b2pt_scene_t scene, double* stats6);
 /* rays in HOST memory; counts: n * 2 uint32 (node visits, triangle tests) of the one-ray-per-thread traversal */
 int b2pt_debug_trace_counts(b2pt_scene_t scene, const B2ptRay* rays, size_t n, unsigned mode, uint32_t* counts);
 
+/* The persisting-L2 window over the BVH block (csrc/scene.cu): out[0] = bytes of the BVH block (nodes + triangle records),
+   out[1] = window bytes attached to the render streams (0: off), out[2] = hit ratio, out[3] = the device's
+   persistingL2CacheMaxSize, out[4] = its accessPolicyMaxWindowSize, out[5] = its l2CacheSize. */
+int b2pt_debug_l2_window(b2pt_scene_t scene, double* out6);
+
 #ifdef __cplusplus
 }
 #endif

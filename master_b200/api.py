@@ -112,7 +112,7 @@ EXPORTS = [
 # parity probes of include/b2pt_debug.h (not part of the drop-in boundary)
 DEBUG_EXPORTS = [
     "b2pt_debug_density", "b2pt_debug_primary", "b2pt_debug_camera", "b2pt_debug_light_samples", "b2pt_debug_draws",
-    "b2pt_debug_tree_stats", "b2pt_debug_trace_counts",
+    "b2pt_debug_tree_stats", "b2pt_debug_trace_counts", "b2pt_debug_l2_window",
 ]
 DENSITY_JOB_DTYPE = np.dtype([("org", "<f4", 3), ("dir", "<f4", 3), ("target", "<f4", 3), ("radius", "<f4"), ("key", "<u4")])
 DENSITY_RESULT_DTYPE = np.dtype([("trials", "<u4"), ("density", "<f4"), ("kind", "<u4"), ("t", "<f4")])
@@ -155,6 +155,7 @@ def load_library():
     lib.b2pt_debug_draws.argtypes = [C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.b2pt_debug_tree_stats.argtypes = [C.c_void_p, C.c_void_p]
     lib.b2pt_debug_trace_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint, C.c_void_p]
+    lib.b2pt_debug_l2_window.argtypes = [C.c_void_p, C.c_void_p]
     _lib = lib
     return lib
 
@@ -230,6 +231,12 @@ class DeviceSceneHandle:
         check(load_library().b2pt_debug_tree_stats(self.handle, _ptr(s)))
         return {"sah_cost": s[0], "inner_nodes": int(s[1]), "leaf_children": int(s[2]), "triangle_refs": int(s[3]),
                 "expected_triangle_tests": s[4], "expected_node_visits": s[5]}
+
+    def l2_window(self):
+        s = np.zeros(6, dtype=np.float64)
+        check(load_library().b2pt_debug_l2_window(self.handle, _ptr(s)))
+        return {"bvh_block_bytes": int(s[0]), "window_bytes": int(s[1]), "hit_ratio": float(s[2]), "persisting_l2_max": int(s[3]),
+                "window_max": int(s[4]), "l2_bytes": int(s[5])}
 
     def trace_counts(self, rays, mode):
         rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)

@@ -94,8 +94,9 @@ struct BptPool {
   uint32_t* lv_link; // previous vertex of the same path
   uint32_t* lp_idx;  // the first kLpTable vertices of every light path by position: lp_idx[slot * kLpTable + k], one 128-byte line per path
   uint32_t* trace_q[2];  // live slots = the slots with an extension ray in flight; written by the logic stage of iteration i into [i & 1]
-  // ray sorting (B2PT_SORT_RAYS): the logic stage writes the live queue unsorted into sort_q with one key per entry and counts the
-  // keys; a scan and a scatter then lay the queue out in key order in trace_q, each end on its own
+  // ray sorting (B2PT_SORT_RAYS): the logic stage writes one key per entry of the live queue and counts the keys; a scan and a scatter
+  // then lay the queue out in key order in sort_q, each end on its own, for the TRAVERSAL stage only — the next logic stage keeps
+  // walking trace_q, whose order follows the path pool (slots that are neighbours in the queue are neighbours in HBM)
   uint32_t* sort_q; uint32_t* key_q; uint32_t* hist; uint32_t* offs;
   uint2* pair_q;
   float4* shadow_q;  // 3 float4 per entry
@@ -249,16 +250,16 @@ __device__ __forceinline__ uint32_t ray_sort_key(const DeviceScene& sc, float3 O
   return (oct << 15) | (spread5(cx) << 2) | (spread5(cy) << 1) | spread5(cz);
 }
 
-// sort_q (two-ended, unsorted) -> trace_q[parity] (two-ended, each end in key order); offs = exclusive scan of the key counts,
+// trace_q[parity] (two-ended, pool order) -> sort_q (two-ended, each end in key order); offs = exclusive scan of the key counts,
 // eye-end keys first.  Clears nothing: the host zeroes hist after the scan.
 __global__ void __launch_bounds__(256) bpt_sort_scatter_kernel(BptPool pool, BptCounters* cnt, int parity) {
   const uint32_t n_eye = cnt->trace_count[parity], n_light = cnt->light_count[parity];
-  uint32_t* out = pool.trace_q[parity];
+  const uint32_t* in = pool.trace_q[parity];
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_eye + n_light; i += gridDim.x * blockDim.x) {
     const uint32_t idx = i < n_eye ? i : pool.size - 1u - (i - n_eye);
     const uint32_t key = pool.key_q[idx] + (i < n_eye ? 0u : kSortBins);
     const uint32_t pos = atomicAdd(&pool.offs[key], 1u);
-    out[pos < n_eye ? pos : pool.size - 1u - (pos - n_eye)] = pool.sort_q[idx];
+    pool.sort_q[pos < n_eye ? pos : pool.size - 1u - (pos - n_eye)] = in[idx];
   }
 }
 
@@ -287,7 +288,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
   const uint32_t n_eye_round = (n_eye + 31u) & ~31u;
   const uint32_t n_round = n_eye_round + ((n_light + 31u) & ~31u);
   const uint32_t* live_q = pool.trace_q[parity ^ 1];
-  uint32_t* next_q = sort ? pool.sort_q : pool.trace_q[parity];
+  uint32_t* next_q = pool.trace_q[parity];
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
     const bool eye_end = i < n_eye_round;
     const uint32_t j = eye_end ? i : i - n_eye_round;
@@ -696,7 +697,7 @@ struct BptShadowIo {
 };
 
 template <int kStream>
-__global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+__global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, int sorted) {
   const uint32_t n_eye = cnt->trace_count[parity];
   const uint32_t n = n_eye + cnt->light_count[parity];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -704,7 +705,7 @@ __global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(R
     cnt->trace_count[parity ^ 1] = 0;  // consumed by this iteration's logic stage; the next one appends to it
     cnt->light_count[parity ^ 1] = 0;
   }
-  BptTraceIo io{&pool, pool.trace_q[parity], n_eye};
+  BptTraceIo io{&pool, sorted ? pool.sort_q : pool.trace_q[parity], n_eye};
   if (kStream == 2) { trace_dyn8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   if (kStream == 1) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -744,12 +745,18 @@ __global__ void __launch_bounds__(256) bpt_commit_kernel(RenderConfig cfg, BptPo
         float* o = cfg.path_radiance + (size_t(batch_pass0 + k) * cfg.pixels + pixel) * 3;
         o[0] = e.x; o[1] = e.y; o[2] = e.z;
       }
-      if (isfinite(fabs(r) + fabs(g) + fabs(b))) {
+      const bool ok = isfinite(fabs(r) + fabs(g) + fabs(b));
+      if (!ok) atomicAdd(&cnt->numeric_errors, 1ull);
+      if (cfg.accum_pass_stride) {  // per-pass films (host pipeline): this pass owns its film
+        if (ok) {
+          double* a = cfg.accum + size_t(batch_pass0 + k) * cfg.accum_pass_stride + size_t(pixel) * 4;
+          a[0] += r; a[1] += g; a[2] += b; a[3] += 1.0;
+        }
+      } else if (ok) {
         sum[0] += r; sum[1] += g; sum[2] += b; sum[3] += 1.0;
-      } else {
-        atomicAdd(&cnt->numeric_errors, 1ull);
       }
     }
+    if (cfg.accum_pass_stride) continue;
     // two batches (lanes) may commit at the same time: red.global.add.f64
     double* a = cfg.accum + size_t(pixel) * 4;
     atomicAdd(a + 0, sum[0]); atomicAdd(a + 1, sum[1]); atomicAdd(a + 2, sum[2]); atomicAdd(a + 3, sum[3]);
@@ -949,9 +956,9 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
           timer.end();
         }
         timer.begin(kStageTrace);
-        if (stream_trace == 2) bpt_trace_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
-        else if (stream_trace == 1) bpt_trace_kernel<1><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
-        else bpt_trace_kernel<0><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        if (stream_trace == 2) bpt_trace_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, sort_rays);
+        else if (stream_trace == 1) bpt_trace_kernel<1><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, sort_rays);
+        else bpt_trace_kernel<0><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, sort_rays);
         timer.end();
         timer.begin(kStageShadow);
         if (stream_shadow == 2) bpt_shadow_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);

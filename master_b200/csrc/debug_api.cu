@@ -203,6 +203,17 @@ int b2pt_debug_tree_stats(b2pt_scene_t scene, double* stats6) {
   return B2PT_OK;
 }
 
+int b2pt_debug_l2_window(b2pt_scene_t scene, double* out6) {
+  using namespace b2pt;
+  B2_CHECK(scene && out6, B2PT_ERR_INVALID, "b2pt_debug_l2_window: null argument");
+  int dev = 0; cudaDeviceProp prop{};
+  B2_CUDA(cudaGetDevice(&dev));
+  B2_CUDA(cudaGetDeviceProperties(&prop, dev));
+  out6[0] = double(scene->bvh_block_bytes); out6[1] = double(scene->l2_window_bytes); out6[2] = scene->l2_hit_ratio;
+  out6[3] = double(prop.persistingL2CacheMaxSize); out6[4] = double(prop.accessPolicyMaxWindowSize); out6[5] = double(prop.l2CacheSize);
+  return B2PT_OK;
+}
+
 int b2pt_debug_trace_counts(b2pt_scene_t scene, const B2ptRay* rays, size_t n, unsigned mode, uint32_t* counts) {
   using namespace b2pt;
   B2_CHECK(scene && (n == 0 || (rays && counts)), B2PT_ERR_INVALID, "b2pt_debug_trace_counts: null argument");

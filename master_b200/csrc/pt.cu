@@ -456,11 +456,12 @@ int render_pt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t stream
       cfg[k].params.sample_stride = stride * uint32_t(lanes);
       cfg[k].params.num_samples = (rp.num_samples - uint32_t(k) + uint32_t(lanes) - 1u) / uint32_t(lanes);
       cfg[k].total_work = (unsigned long long)base.pixels * cfg[k].params.num_samples;
+      cfg[k].pass_index0 = uint32_t(k); cfg[k].pass_index_step = uint32_t(lanes);
     }
     if (int rc = pt_workspace(scene, k, pt_pool_size(cfg[k]), &set, &w[k])) {
       if (k == 0) return rc;
       cudaGetLastError();  // no memory for a second pool: one lane
-      lanes = 1; cfg[0] = base;
+      lanes = 1; cfg[0] = base;  // (pass_index0 = 0, pass_index_step = 1)
       if (int rc0 = pt_workspace(scene, 0, pt_pool_size(cfg[0]), &set, &w[0])) return rc0;
       break;
     }

@@ -3,7 +3,6 @@
 // Builds the render_context_t equivalent (Technique.cpp:37-45), dispatches to the wavefront
 // integrator the Options select (make_technique.cpp:112-170) and fills the statistics_t fields a
 // device technique can know (Technique.cpp:52-76).
-#include <thread>
 #include <vector>
 
 #include "render_common.cuh"
@@ -69,6 +68,7 @@ static int make_config(b2pt_scene_s* scene, const B2ptRenderParams* p, double* a
   cfg->total_work = (unsigned long long)cfg->pixels * p->num_samples;
   cfg->pool_size = 0;
   cfg->accum = accum;
+  cfg->accum_pass_stride = 0; cfg->pass_index0 = 0; cfg->pass_index_step = 1;
   cfg->path_radiance = path_radiance;
   cfg->counters = nullptr;
   return B2PT_OK;
@@ -76,15 +76,15 @@ static int make_config(b2pt_scene_s* scene, const B2ptRenderParams* p, double* a
 
 }  // namespace b2pt
 
-extern "C" {
+namespace b2pt {
 
-int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accum_dev, float* path_radiance_dev, void* stream_,
-                B2ptStats* stats) {
-  using namespace b2pt;
-  B2_CHECK(scene && params && accum_dev, B2PT_ERR_INVALID, "b2pt_render: null argument");
-  cudaStream_t stream = (cudaStream_t)stream_;
+// b2pt_render with the film layout made explicit: pass_stride = 0 adds every pass into the one film at accum_dev (b2pt_render);
+// pass_stride = width * height * 4 gives every pass of the call its own film (the host pipeline renders ahead of its caller).
+int render_passes(b2pt_scene_s* scene, const B2ptRenderParams* params, double* accum_dev, size_t pass_stride, float* path_radiance_dev,
+                  cudaStream_t stream, B2ptStats* stats) {
   RenderConfig cfg;
   if (int rc = make_config(scene, params, accum_dev, path_radiance_dev, &cfg)) return rc;
+  cfg.accum_pass_stride = pass_stride;
   B2ptStats local{};
   if (params->num_samples == 0) { if (stats) *stats = local; return B2PT_OK; }
   scene_l2_window(scene, stream);  // BVH block -> persisting L2 for the kernels of this stream (scene.cu)
@@ -114,6 +114,19 @@ int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accu
   local.num_paths = cfg.total_work;
   if (stats) *stats = local;
   return B2PT_OK;
+}
+
+}  // namespace b2pt
+
+extern "C" {
+
+int b2pt_render(b2pt_scene_t scene, const B2ptRenderParams* params, double* accum_dev, float* path_radiance_dev, void* stream_,
+                B2ptStats* stats) {
+  using namespace b2pt;
+  B2_CHECK(scene && params && accum_dev, B2PT_ERR_INVALID, "b2pt_render: null argument");
+  // one render at a time per scene handle: passes the host pipeline is still rendering ahead for b2pt_render_host finish first
+  if (scene->pipeline_quiesce) scene->pipeline_quiesce(scene);
+  return render_passes(scene, params, accum_dev, 0, path_radiance_dev, (cudaStream_t)stream_, stats);
 }
 
 int b2pt_film_errors(const double* accum_dev, const float* reference_dev, uint32_t width, uint32_t height, const int32_t* window, float* out,
@@ -146,34 +159,6 @@ int b2pt_film_errors(const double* accum_dev, const float* reference_dev, uint32
   const float num = window ? float(sums[2]) : float(size_t(width) * height * 3);
   out[0] = sqrtf(float(sums[0]) / num);
   out[1] = float(sums[1]) / num;
-  return B2PT_OK;
-}
-
-int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* params, double* view_host, B2ptStats* stats) {
-  using namespace b2pt;
-  B2_CHECK(scene && params && view_host, B2PT_ERR_INVALID, "b2pt_render_host: null argument");
-  const size_t n = size_t(params->width) * params->height * 4;
-  if (scene->film_doubles != n) {  // staging buffers live with the scene: one allocation per resolution, not per pass
-    if (scene->film_dev) cudaFree(scene->film_dev);
-    if (scene->film_host) cudaFreeHost(scene->film_host);
-    scene->film_dev = nullptr; scene->film_host = nullptr; scene->film_doubles = 0;
-    B2_CUDA(cudaMalloc(&scene->film_dev, n * sizeof(double)));
-    B2_CUDA(cudaMallocHost((void**)&scene->film_host, n * sizeof(double)));
-    scene->film_doubles = n;
-  }
-  B2_CUDA(cudaMemsetAsync(scene->film_dev, 0, n * sizeof(double), nullptr));
-  int rc = b2pt_render(scene, params, scene->film_dev, nullptr, nullptr, stats);
-  if (rc != B2PT_OK) return rc;
-  // view += pass sums (Technique::_commit_images adds into the caller's dvec4 buffer)
-  B2_CUDA(cudaMemcpy(scene->film_host, scene->film_dev, n * sizeof(double), cudaMemcpyDeviceToHost));
-  const double* h = scene->film_host;
-  // a 1024^2 film is 32 MB: four host threads add it in a quarter of the time one takes (the add is memory-bound)
-  const int parts = n >= (size_t(1) << 20) ? 4 : 1;
-  auto add = [&](int k) { for (size_t i = n * k / parts, e = n * (k + 1) / parts; i < e; ++i) view_host[i] += h[i]; };
-  std::vector<std::thread> helpers;
-  for (int k = 1; k < parts; ++k) helpers.emplace_back(add, k);
-  add(0);
-  for (auto& t : helpers) t.join();
   return B2PT_OK;
 }
 

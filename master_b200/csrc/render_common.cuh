@@ -29,6 +29,11 @@ struct RenderConfig {
   uint32_t pixels;          // width * height
   uint32_t pool_size;
   double* accum;            // dvec4 per pixel
+  // Per-pass films (the host pipeline of render.cu renders ahead of the caller): pass p of the call (0-based, in the call's own
+  // numbering) commits into accum + p * accum_pass_stride doubles; 0 = every pass into the one film.  A lane that renders every
+  // lanes-th pass sees its local pass l as call pass pass_index0 + l * pass_index_step.
+  size_t accum_pass_stride;
+  uint32_t pass_index0, pass_index_step;
   float* path_radiance;     // nullable
   RenderCounters* counters;
 };
@@ -43,7 +48,7 @@ __device__ __forceinline__ void commit_sample(const RenderConfig& cfg, unsigned 
     float* o = cfg.path_radiance + work * 3ull;
     o[0] = radiance.x; o[1] = radiance.y; o[2] = radiance.z;
   }
-  double* a = cfg.accum + size_t(pixel) * 4;
+  double* a = cfg.accum + size_t(pixel) * 4 + size_t(cfg.pass_index0 + uint32_t(work / cfg.pixels) * cfg.pass_index_step) * cfg.accum_pass_stride;
   if (isfinite(l1norm(radiance))) {
     atomicAdd(a + 0, double(radiance.x));
     atomicAdd(a + 1, double(radiance.y));

@@ -1055,10 +1055,9 @@ int b2pt_scene_create(const B2ptSceneDesc* desc, b2pt_scene_t* out) {
 
 void b2pt_scene_destroy(b2pt_scene_t s) {
   if (!s) return;
+  if (s->pipeline && s->pipeline_free) s->pipeline_free(s->pipeline);  // joins the worker before the pools go away
   if (s->workspace && s->workspace_free) s->workspace_free(s->workspace);
   for (int i = 0; i < s->num_allocations; ++i) cudaFree(s->allocations[i]);
-  if (s->film_dev) cudaFree(s->film_dev);
-  if (s->film_host) cudaFreeHost(s->film_host);
   for (cudaEvent_t e : s->ev) if (e) cudaEventDestroy(e);
   delete s;
 }

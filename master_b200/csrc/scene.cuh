@@ -72,10 +72,10 @@ struct b2pt_scene_s {
   // per-scene render workspace (path pool, queues), created lazily by render.cu
   void* workspace = nullptr;
   void (*workspace_free)(void*) = nullptr;
-  // film staging of b2pt_render_host, kept between calls (device dvec4 + pinned host copy)
-  double* film_dev = nullptr;
-  double* film_host = nullptr;
-  size_t film_doubles = 0;
+  // b2pt_render_host's pipeline (host_pipeline.cu): per-pass films rendered ahead of the caller, staging buffers, worker threads
+  void* pipeline = nullptr;
+  void (*pipeline_free)(void*) = nullptr;
+  void (*pipeline_quiesce)(b2pt_scene_s*) = nullptr;  // waits for passes still being rendered ahead
   cudaEvent_t ev[2] = {nullptr, nullptr};  // timing pair of b2pt_render
   // nodes + triangle records in one allocation, and the persisting-L2 window over it (scene.cu: scene_l2_window)
   void* bvh_block = nullptr;

@@ -1211,7 +1211,7 @@ __global__ void __launch_bounds__(256) vcm_commit_kernel(RenderConfig cfg, VcmPo
       float* o = cfg.path_radiance + (size_t(pass) * cfg.pixels + pixel) * 3;
       o[0] = e.x; o[1] = e.y; o[2] = e.z;
     }
-    double* a = cfg.accum + size_t(pixel) * 4;
+    double* a = cfg.accum + size_t(pixel) * 4 + size_t(pass) * cfg.accum_pass_stride;
     if (isfinite(fabs(r) + fabs(g) + fabs(b))) {
       // passes in different lanes may commit the same pixel at the same time (render_vcm)
       atomicAdd(a + 0, r); atomicAdd(a + 1, g); atomicAdd(a + 2, b); atomicAdd(a + 3, 1.0);

