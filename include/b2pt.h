@@ -18,6 +18,9 @@
  *                             like Technique::_commit_images (Technique.cpp:194-244).
  *   b2pt_film_*            <- subimage_view_t's dvec4 buffer (ImageView.hpp:10-46),
  *                             kept resident on the device between passes.
+ *   b2pt_comm_* /
+ *   b2pt_reduce_accum      <- merge_exr (Options.cpp:1340-1409): the sum of independently
+ *                             rendered accumulators, as ONE NCCL reduce of the device films.
  *   b2pt_grid_*            <- v3::HashGrid3D<T>::build / rQuery (HashGrid3D.hpp:181-325).
  *   b2pt_last_error        <- the C++ exceptions the reference throws
  *                             (runtime_assert.cpp:7-11, Scene.cpp:55-57).
@@ -181,6 +184,11 @@ const char* b2pt_last_error(void);
 int b2pt_abi_version(void);
 /* number of visible CUDA devices, 0 if none */
 int b2pt_device_count(void);
+/* makes `device` current for the CALLING host thread (cudaSetDevice): a multi-GPU host uses one thread per device, and every
+   handle (scene, film, communicator) belongs to the device that was current when it was created */
+int b2pt_set_device(int device);
+/* waits for everything queued on the current device */
+int b2pt_device_synchronize(void);
 
 int b2pt_scene_create(const B2ptSceneDesc* desc, b2pt_scene_t* out);
 void b2pt_scene_destroy(b2pt_scene_t scene);
@@ -232,6 +240,32 @@ int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* params, double*
  */
 int b2pt_film_errors(const double* accum_dev, const float* reference_dev, uint32_t width, uint32_t height,
                      const int32_t* window, float* out, void* stream);
+
+/* ---- the film on the device: subimage_view_t's dvec4 accumulator (ImageView.hpp:10-46), width*height*(sum r, sum g, sum b, sum 1),
+ * resident in HBM between passes; it crosses PCIe only when the host asks. ---- */
+typedef struct b2pt_film_s* b2pt_film_t;
+int b2pt_film_create(uint32_t width, uint32_t height, b2pt_film_t* out); /* zeroed, on the current CUDA device */
+void b2pt_film_destroy(b2pt_film_t film);
+double* b2pt_film_data(b2pt_film_t film);                /* the DEVICE pointer b2pt_render / b2pt_reduce_accum / b2pt_film_errors take */
+int b2pt_film_clear(b2pt_film_t film, void* stream);
+/* device -> host: view_host = film (add == 0) or view_host += film (add != 0); synchronises `stream` */
+int b2pt_film_read(b2pt_film_t film, double* view_host, int add, void* stream);
+
+/* ---- multi-GPU: samples split over a replicated scene, ONE reduce of the films.
+ * merge_exr (Options.cpp:1340-1409) adds the RGBA accumulators of independently rendered images, count channel included;
+ * b2pt_reduce_accum is that sum over the ranks of a communicator, on the device, over NVLink (ncclAllReduce / ncclReduce, float64).
+ * Rank g of G renders the sample indices g, g + G, ... (B2ptRenderParams::first_sample = g, sample_stride = G).
+ * NCCL is loaded at run time (libnccl.so.2, or the file named by B2PT_NCCL_LIB); nranks == 1 needs no NCCL at all. ---- */
+typedef struct b2pt_comm_s* b2pt_comm_t;
+#define B2PT_COMM_ID_BYTES 128
+/* rank 0 makes the id (ncclGetUniqueId) and hands the 128 bytes to the other ranks by any means (file, socket, launcher) */
+int b2pt_comm_unique_id(void* id);
+/* one communicator per rank, on the CURRENT CUDA device; collective: returns when all nranks ranks have called it */
+int b2pt_comm_init(int nranks, int rank, const void* id, b2pt_comm_t* out);
+/* accum_dev (num_doubles float64, device) = sum over ranks, in place; root = -1: every rank gets the sum, else only `root`.
+   Asynchronous on `stream`. */
+int b2pt_reduce_accum(b2pt_comm_t comm, double* accum_dev, size_t num_doubles, int root, void* stream);
+void b2pt_comm_destroy(b2pt_comm_t comm);
 
 /* ---- photon index: v3::HashGrid3D<T>::build / rQuery (HashGrid3D.hpp:181-325) ---- */
 typedef struct b2pt_grid_s* b2pt_grid_t;

@@ -105,9 +105,10 @@ class Stats(C.Structure):
 
 # every symbol include/b2pt.h declares; tests/test_abi.py checks the list against the header
 EXPORTS = [
-    "b2pt_last_error", "b2pt_abi_version", "b2pt_device_count", "b2pt_scene_create", "b2pt_scene_destroy",
+    "b2pt_last_error", "b2pt_abi_version", "b2pt_device_count", "b2pt_set_device", "b2pt_device_synchronize", "b2pt_scene_create", "b2pt_scene_destroy",
     "b2pt_scene_info", "b2pt_trace", "b2pt_trace_device", "b2pt_render", "b2pt_render_host", "b2pt_grid_build",
-    "b2pt_grid_destroy", "b2pt_grid_query", "b2pt_film_errors",
+    "b2pt_grid_destroy", "b2pt_grid_query", "b2pt_film_errors", "b2pt_film_create", "b2pt_film_destroy", "b2pt_film_data",
+    "b2pt_film_clear", "b2pt_film_read", "b2pt_comm_unique_id", "b2pt_comm_init", "b2pt_reduce_accum", "b2pt_comm_destroy",
 ]
 # parity probes of include/b2pt_debug.h (not part of the drop-in boundary)
 DEBUG_EXPORTS = [
@@ -148,6 +149,18 @@ def load_library():
     lib.b2pt_grid_destroy.restype = None
     lib.b2pt_grid_query.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p, C.c_void_p]
     lib.b2pt_film_errors.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_float), C.c_void_p]
+    lib.b2pt_film_create.argtypes = [C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p)]
+    lib.b2pt_film_destroy.argtypes = [C.c_void_p]
+    lib.b2pt_film_destroy.restype = None
+    lib.b2pt_film_data.argtypes = [C.c_void_p]
+    lib.b2pt_film_data.restype = C.c_void_p
+    lib.b2pt_film_clear.argtypes = [C.c_void_p, C.c_void_p]
+    lib.b2pt_film_read.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    lib.b2pt_comm_unique_id.argtypes = [C.c_void_p]
+    lib.b2pt_comm_init.argtypes = [C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+    lib.b2pt_reduce_accum.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+    lib.b2pt_comm_destroy.argtypes = [C.c_void_p]
+    lib.b2pt_comm_destroy.restype = None
     lib.b2pt_debug_density.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.b2pt_debug_primary.argtypes = [C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.b2pt_debug_camera.argtypes = [C.POINTER(RenderParams), C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
@@ -328,3 +341,27 @@ def debug_draws(key, n):
     raw, fl, db = np.zeros(n, dtype=np.uint32), np.zeros(n, dtype=np.float32), np.zeros(n, dtype=np.float64)
     check(load_library().b2pt_debug_draws(C.c_uint32(key), n, _ptr(raw), _ptr(fl), _ptr(db)))
     return raw, fl, db
+
+
+class Comm:
+    """b2pt_comm_*: the communicator of the film reduce (NCCL behind the C ABI).  `id_bytes` comes from Comm.unique_id() on rank 0."""
+
+    def __init__(self, nranks, rank, id_bytes=None):
+        h = C.c_void_p()
+        buf = C.create_string_buffer(bytes(id_bytes), 128) if id_bytes is not None else None
+        check(load_library().b2pt_comm_init(nranks, rank, buf, C.byref(h)))
+        self.handle, self.nranks, self.rank = h, nranks, rank
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        check(load_library().b2pt_comm_unique_id(buf))
+        return buf.raw
+
+    def reduce_accum(self, accum_ptr, num_doubles, root=-1, stream=0):
+        check(load_library().b2pt_reduce_accum(self.handle, C.c_void_p(accum_ptr), num_doubles, root, C.c_void_p(stream)))
+
+    def close(self):
+        if getattr(self, "handle", None):
+            load_library().b2pt_comm_destroy(self.handle)
+            self.handle = None

@@ -77,7 +77,7 @@ def build_library(force=False, verbose=False, variant=None, extra_flags=()):
     if failed:
         raise RuntimeError("nvcc compilation failed")
     if procs or not os.path.exists(LIB):
-        cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"]
+        cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart", "-ldl"]
         subprocess.check_call(cmd)
     return LIB
 

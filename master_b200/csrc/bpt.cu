@@ -65,6 +65,7 @@ struct BptCounters {
   unsigned int light_count[2];  // the live queue has two ends: eye-phase paths from the front (trace_count), light-phase paths from the back
   unsigned int dir_count[2];
   unsigned int ticket[2];  // dynamic ray fetch of the traversal stages (trace, shadow), zeroed by the logic stage
+  unsigned int oct_count[2][8];  // B2PT_SORT_RAYS=2: rays per direction octant, [iteration parity][octant]
 };
 
 // LightVertex / EyeVertex (BPT.hpp:13-27): w0 = a or c, w1 = A or C
@@ -98,6 +99,9 @@ struct BptPool {
   // then lay the queue out in key order in sort_q, each end on its own, for the TRAVERSAL stage only — the next logic stage keeps
   // walking trace_q, whose order follows the path pool (slots that are neighbours in the queue are neighbours in HBM)
   uint32_t* sort_q; uint32_t* key_q; uint32_t* hist; uint32_t* offs;
+  // B2PT_SORT_RAYS=2: one queue per direction octant (8 x size entries), appended by the logic stage next to trace_q; the traversal
+  // stage walks them one after the other — direction coherence without a sorting pass
+  uint32_t* oct_q;
   uint2* pair_q;
   float4* shadow_q;  // 3 float4 per entry
   float4* dir_q;     // connections to sun lights, 4 float4 per entry (render_common.cuh: directional_kernel)
@@ -276,6 +280,8 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
     cnt->shadow_count[parity ^ 1] = 0;
     cnt->ticket[0] = 0; cnt->ticket[1] = 0;
     cnt->dir_count[parity ^ 1] = 0;
+#pragma unroll
+    for (int o = 0; o < 8; ++o) cnt->oct_count[parity ^ 1][o] = 0;
   }
   const float beta = cfg.params.beta;
   const float roulette = cfg.params.roulette;
@@ -545,10 +551,23 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
     if (want_trace) {
       const uint32_t at = to_eye_end ? tq : pool.size - 1u - lq;
       next_q[at] = slot;
-      if (sort) {
+      if (sort == 1) {
         const uint32_t key = ray_sort_key(sc, O, bs.omega);
         pool.key_q[at] = key;
         atomicAdd(&pool.hist[key + (to_eye_end ? 0u : kSortBins)], 1u);
+      }
+    }
+    if (sort == 2) {  // every lane of the warp is here: one atomic per octant present in the warp
+      const uint32_t oct = (bs.omega.x >= 0.0f ? 1u : 0u) | (bs.omega.y >= 0.0f ? 2u : 0u) | (bs.omega.z >= 0.0f ? 4u : 0u);
+      const unsigned active = __ballot_sync(0xFFFFFFFFu, want_trace);
+      if (want_trace) {
+        const unsigned peers = __match_any_sync(active, oct);
+        const unsigned lane = threadIdx.x & 31u;
+        const int leader = __ffs(int(peers)) - 1;
+        unsigned base = 0;
+        if (lane == unsigned(leader)) base = atomicAdd(&cnt->oct_count[parity][oct], unsigned(__popc(peers)));
+        base = __shfl_sync(peers, base, leader);
+        pool.oct_q[size_t(oct) * pool.size + base + __popc(peers & ((1u << lane) - 1u))] = slot;
       }
     }
     unsigned pq = warp_reserve(&cnt->pair_count[parity], emit_n);
@@ -660,8 +679,17 @@ struct BptTraceIo {
   const BptPool* pool;
   const uint32_t* q;
   uint32_t n_eye;  // entries [0, n_eye) from the front of the queue, the rest from its back
+  const unsigned* oct_count;  // non-null: q is the array of eight octant queues and ray i is found through the prefix of the counts
   __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
-    const uint32_t slot = q[i < n_eye ? i : pool->size - 1u - (i - n_eye)];
+    uint32_t slot;
+    if (oct_count) {
+      uint32_t o = 0, j = i;
+#pragma unroll
+      for (int k = 0; k < 7; ++k) { const uint32_t c = oct_count[k]; if (o == uint32_t(k) && j >= c) { j -= c; ++o; } }
+      slot = q[size_t(o) * pool->size + j];
+    } else {
+      slot = q[i < n_eye ? i : pool->size - 1u - (i - n_eye)];
+    }
     const float4* rec = pool->rec + size_t(slot) * kRecFloat4s;
     const float4 o = rec[kRecRayO], d = rec[kRecOmega];
     O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY;
@@ -705,7 +733,7 @@ __global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(R
     cnt->trace_count[parity ^ 1] = 0;  // consumed by this iteration's logic stage; the next one appends to it
     cnt->light_count[parity ^ 1] = 0;
   }
-  BptTraceIo io{&pool, sorted ? pool.sort_q : pool.trace_q[parity], n_eye};
+  BptTraceIo io{&pool, sorted == 2 ? pool.oct_q : sorted == 1 ? pool.sort_q : pool.trace_q[parity], n_eye, sorted == 2 ? cnt->oct_count[parity] : nullptr};
   if (kStream == 2) { trace_dyn8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   if (kStream == 1) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -768,6 +796,11 @@ __global__ void __launch_bounds__(256) bpt_commit_kernel(RenderConfig cfg, BptPo
 constexpr int kMaxLanes = 8;
 constexpr int kDefaultLanes = 2;
 constexpr int kSortRaysDefault = 0;
+// ray ordering of the closest-hit queue: 0 = pool order, 1 = counting sort by (octant, cell) (ray_sort_key), 2 = one queue per octant
+inline int bpt_sort_mode() {
+  const char* e = getenv("B2PT_SORT_RAYS");
+  return e ? (e[0] == '1' ? 1 : e[0] == '2' ? 2 : 0) : kSortRaysDefault;
+}
 inline int bpt_lanes() {  // B2PT_BPT_LANES overrides the number of concurrent batches for A/B runs
   const char* e = getenv("B2PT_BPT_LANES");
   const int v = e ? atoi(e) : kDefaultLanes;
@@ -835,6 +868,7 @@ int bpt_workspace(b2pt_scene_s* scene, uint32_t size, uint32_t per_path, int lan
     if ((rc = ws_alloc(w, &p.lp_idx, size_t(size) * kLpTable))) return rc;
     if ((rc = ws_alloc(w, &p.trace_q[0], size))) return rc;
     if ((rc = ws_alloc(w, &p.trace_q[1], size))) return rc;
+    if (bpt_sort_mode() == 2) { if ((rc = ws_alloc(w, &p.oct_q, size_t(size) * 8))) return rc; }
     if ((rc = ws_alloc(w, &p.sort_q, size))) return rc;
     if ((rc = ws_alloc(w, &p.key_q, size))) return rc;
     if ((rc = ws_alloc(w, &p.hist, 2 * kSortBins))) return rc;
@@ -896,8 +930,8 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   const int stream_trace = tv ? (tv[0] == '1' ? 1 : tv[0] == '0' ? 0 : 2) : 2;
   const int stream_shadow = sv ? (sv[0] == '1' ? 1 : sv[0] == '0' ? 0 : 2) : stream_trace;
   // ray sorting of the closest-hit queue (see ray_sort_key): B2PT_SORT_RAYS=0/1
-  int sort_rays = kSortRaysDefault;
-  { const char* e = getenv("B2PT_SORT_RAYS"); if (e) sort_rays = e[0] == '1' ? 1 : 0; }
+  int sort_rays = bpt_sort_mode();
+  if (sort_rays == 2 && !w->lane[0].pool.oct_q) sort_rays = 0;  // the workspace was built before the mode was switched on
   unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
   const int kBatchIters = 8;
 
@@ -947,7 +981,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
                                                           DirectionalParams{cfg.params.beta, 1.0f, 0.0f, 0.0f}, g.pool.rec + kRecRad, uint32_t(kRecFloat4s), &l.counters->basic_rays);
           timer.end();
         }
-        if (sort_rays) {
+        if (sort_rays == 1) {
           timer.begin(kStageShade);
           size_t bytes = w->scan_bytes;
           B2_CUDA(cub::DeviceScan::ExclusiveSum(w->scan_tmp + w->scan_bytes * k, bytes, g.pool.hist, g.pool.offs, int(2 * kSortBins), l.stream));

@@ -1038,6 +1038,17 @@ int b2pt_device_count(void) {
   return n;
 }
 
+int b2pt_set_device(int device) {
+  B2_CHECK(device >= 0 && device < b2pt_device_count(), B2PT_ERR_INVALID, "b2pt_set_device: no such device");
+  B2_CUDA(cudaSetDevice(device));
+  return B2PT_OK;
+}
+
+int b2pt_device_synchronize(void) {
+  B2_CUDA(cudaDeviceSynchronize());
+  return B2PT_OK;
+}
+
 int b2pt_scene_create(const B2ptSceneDesc* desc, b2pt_scene_t* out) {
   B2_CHECK(desc && out, B2PT_ERR_INVALID, "b2pt_scene_create: null argument");
   B2_CHECK(desc->num_meshes > 0 && desc->mesh_material_id && desc->mesh_vertex_offset && desc->mesh_index_offset && desc->vertices &&

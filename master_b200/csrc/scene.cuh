@@ -22,7 +22,7 @@ constexpr uint32_t kInvalid = 0xFFFFFFFFu;
 constexpr int kNodeFloat4s = 8;    // 128-byte BVH4 node
 constexpr int kFrameFloat4s = 7;   // 112-byte shading record per triangle
 constexpr int kTriFloat4s = 3;     // 48-byte triangle record
-constexpr float kSplitBudgetDefault = 0.5f;  // extra triangle references the builder may create, as a fraction of the triangles
+constexpr float kSplitBudgetDefault = 0.0f;  // extra triangle references the builder may create, as a fraction of the triangles (0 = no pre-splitting; measured in DESIGN.md §7)
 constexpr int kMaxLeafTris = 4;
 
 // Child link encoding in node float4 #6:

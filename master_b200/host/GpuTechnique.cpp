@@ -40,7 +40,77 @@ GpuTechnique::GpuTechnique(const shared<const Scene>& scene, const GpuOptions& o
   check(b2pt_scene_create(&desc, &_device_scene), "b2pt_scene_create");  // replaces Scene::buildAccelStructs
 }
 
-GpuTechnique::~GpuTechnique() { b2pt_scene_destroy(_device_scene); }
+GpuTechnique::~GpuTechnique() {
+  b2pt_film_destroy(_film);
+  b2pt_scene_destroy(_device_scene);
+}
+
+void GpuTechnique::fill_params(B2ptRenderParams& p, size_t width, size_t height, size_t cameraId, uint32_t passes) {
+  auto& cameras = _scene->cameras();
+  std::memset(&p, 0, sizeof p);
+  p.technique = _options.technique;
+  p.beta = _options.beta; p.roulette = _options.roulette; p.lights = _options.lights;
+  p.max_path = _options.max_path > 0xFFFFFFFFull ? 0u : uint32_t(_options.max_path);
+  p.radius = _options.radius; p.alpha = _options.alpha; p.num_photons = uint32_t(_options.num_photons);
+  p.unbiased = _options.technique == B2PT_TECHNIQUE_UPG;
+  p.enable_vc = _options.enable_vc; p.enable_vm = _options.enable_vm; p.from_light = _options.from_light;
+  p.width = uint32_t(width); p.height = uint32_t(height);
+  // render_context_t, Technique.cpp:37-45
+  const mat3 v2w = cameras.view_to_world_mat3(cameraId), w2v = cameras.world_to_view_mat3(cameraId);
+  const vec3 pos = cameras.position(cameraId);
+  std::memcpy(p.camera.view_to_world, &v2w, 36);
+  std::memcpy(p.camera.world_to_view, &w2v, 36);
+  std::memcpy(p.camera.position, &pos, 12);
+  p.camera.focal_length_y = cameras.focal_length_y(cameraId, float(width) / float(height));
+  p.seed = _seed;
+  p.first_sample = _options.first_sample + uint32_t(_statistics.num_samples) * _options.sample_stride;
+  p.sample_stride = _options.sample_stride;
+  p.num_samples = passes;
+  std::memcpy(p.sky_horizon, &_sky_horizon, 12);
+  std::memcpy(p.sky_zenith, &_sky_zenith, 12);
+}
+
+void GpuTechnique::account(double start_time, uint32_t passes) {
+  // statistics, Technique.cpp:52-76
+  const double current_time = high_resolution_time();
+  _statistics.num_samples += passes;
+  _statistics.num_basic_rays += _last.num_basic_rays;
+  _statistics.num_shadow_rays += _last.num_shadow_rays;
+  _statistics.total_time = current_time - _start_time;
+  statistics_t::record_t record;
+  record.sample_index = _statistics.num_samples - 1;
+  record.rms_error = 0.0f;
+  record.abs_error = 0.0f;
+  record.clock_time = float(_statistics.total_time);
+  record.frame_duration = float(current_time - start_time);
+  record.numeric_errors = _last.numeric_errors;
+  _statistics.records.push_back(record);
+}
+
+void GpuTechnique::render_resident(size_t width, size_t height, size_t cameraId, uint32_t passes) {
+  if (!_film || _film_width != width || _film_height != height) {
+    b2pt_film_destroy(_film); _film = nullptr;
+    check(b2pt_film_create(uint32_t(width), uint32_t(height), &_film), "b2pt_film_create");
+    _film_width = width; _film_height = height;
+  }
+  if (!std::isfinite(_start_time)) _start_time = high_resolution_time();
+  if (!_seeded) { _seed = _options.seed; _seeded = true; }  // ranks of a multi-GPU run share the seed: fixed, never drawn per rank
+  const double start_time = high_resolution_time();
+  B2ptRenderParams p;
+  fill_params(p, width, height, cameraId, passes);
+  check(b2pt_render(_device_scene, &p, b2pt_film_data(_film), nullptr, nullptr, &_last), "b2pt_render");
+  account(start_time, passes);
+}
+
+void GpuTechnique::reduce_film(b2pt_comm_t comm, int root) {
+  runtime_assert(_film != nullptr);
+  check(b2pt_reduce_accum(comm, b2pt_film_data(_film), _film_width * _film_height * 4, root, nullptr), "b2pt_reduce_accum");
+}
+
+void GpuTechnique::read_film(subimage_view_t& view) {
+  runtime_assert(_film != nullptr && view.width() == _film_width && view.height() == _film_height);
+  check(b2pt_film_read(_film, (double*)view.data(), 1, nullptr), "b2pt_film_read");
+}
 
 void GpuTechnique::render(subimage_view_t& view, RandomEngine& engine, size_t cameraId, const vector<vec3>& reference,
                           const vector<ivec3>& trace_points) {
@@ -58,27 +128,7 @@ void GpuTechnique::render(subimage_view_t& view, RandomEngine& engine, size_t ca
   const double start_time = high_resolution_time();
 
   B2ptRenderParams p;
-  std::memset(&p, 0, sizeof p);
-  p.technique = _options.technique;
-  p.beta = _options.beta; p.roulette = _options.roulette; p.lights = _options.lights;
-  p.max_path = _options.max_path > 0xFFFFFFFFull ? 0u : uint32_t(_options.max_path);
-  p.radius = _options.radius; p.alpha = _options.alpha; p.num_photons = uint32_t(_options.num_photons);
-  p.unbiased = _options.technique == B2PT_TECHNIQUE_UPG;
-  p.enable_vc = _options.enable_vc; p.enable_vm = _options.enable_vm; p.from_light = _options.from_light;
-  p.width = uint32_t(view.width()); p.height = uint32_t(view.height());
-  // render_context_t, Technique.cpp:37-45
-  const mat3 v2w = cameras.view_to_world_mat3(cameraId), w2v = cameras.world_to_view_mat3(cameraId);
-  const vec3 pos = cameras.position(cameraId);
-  std::memcpy(p.camera.view_to_world, &v2w, 36);
-  std::memcpy(p.camera.world_to_view, &w2v, 36);
-  std::memcpy(p.camera.position, &pos, 12);
-  p.camera.focal_length_y = cameras.focal_length_y(cameraId, float(view.width()) / float(view.height()));
-  p.seed = _seed;
-  p.first_sample = _options.first_sample + uint32_t(_statistics.num_samples) * _options.sample_stride;
-  p.sample_stride = _options.sample_stride;
-  p.num_samples = _options.passes_per_render;
-  std::memcpy(p.sky_horizon, &_sky_horizon, 12);
-  std::memcpy(p.sky_zenith, &_sky_zenith, 12);
+  fill_params(p, view.width(), view.height(), cameraId, _options.passes_per_render);
 
   check(b2pt_render_host(_device_scene, &p, (double*)view.data(), &_last), "b2pt_render_host");
 

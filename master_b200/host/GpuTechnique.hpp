@@ -46,7 +46,19 @@ class GpuTechnique : public haste::Technique {
 
   const B2ptStats& last_stats() const { return _last; }
 
+  // ---- the film kept on the device ("copies ... only when the host needs it"), and the multi-GPU reduce.
+  // render_resident adds `passes` passes of the next sample indices into a dvec4 film that stays in HBM (b2pt_film_*);
+  // reduce_film sums the films of all ranks of `comm` (b2pt_reduce_accum = ncclAllReduce / ncclReduce: merge_exr's a + b,
+  // Options.cpp:1340-1409); read_film adds the device film into a host view.  Statistics are kept like render() keeps them.
+  void render_resident(size_t width, size_t height, size_t cameraId, uint32_t passes);
+  void reduce_film(b2pt_comm_t comm, int root);
+  void read_film(haste::subimage_view_t& view);
+
  private:
+  void fill_params(B2ptRenderParams& p, size_t width, size_t height, size_t cameraId, uint32_t passes);
+  void account(double start_time, uint32_t passes);
+  b2pt_film_t _film = nullptr;
+  size_t _film_width = 0, _film_height = 0;
   GpuOptions _options;
   b2pt_scene_t _device_scene = nullptr;
   B2ptStats _last{};

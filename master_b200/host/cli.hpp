@@ -2,7 +2,7 @@
 //
 // parseArgs (Options.cpp:483-1033) restated for the options the sampling path reads: the same flags, the same defaults
 // (Options.hpp:26-55), the same sub-commands for the image tools that only need the checkpoint files
-// (main.cpp:80-107: average, errors, time, merge, strip, bake, continue).  `key=value` arguments (the form the tests
+// (main.cpp:90-92,108: merge, continue — the reference's other image tools are post-processing and out of this repo's scope).  `key=value` arguments (the form the tests
 // use) are accepted next to `--flag[=value]`.  Display options (--no-ui, --no-reload, --snapshot) are parsed and ignored:
 // there is no window on this box.
 #pragma once
@@ -15,11 +15,12 @@
 namespace b2pt_host {
 
 struct CliOptions {
-  std::string action = "render";  // render | continue | average | errors | time | merge | strip | bake
+  std::string action = "render";  // render | continue | merge
   std::vector<std::string> inputs;
   std::string technique = "PT";  // Options::technique = PT
   double beta = 1.0, roulette = 0.9, radius = 0.01, alpha = 0.75, lights = 1.0;
   size_t num_photons = 0, num_samples = 0, seed = 0, camera_id = 0, width = 512, height = 512, passes_per_render = 1;
+  size_t gpus = 1, max_path = 0;  // --gpus=N: devices of this node (sample split + one film reduce); --max-path (PT only, PT.cpp:23-40)
   double num_seconds = 0.0;
   bool enable_vc = true, enable_vm = true, from_light = true, enable_seed = false, quiet = false;
   std::string output, reference, raw_out;
@@ -82,6 +83,8 @@ inline CliOptions parse_cli(int argc, char** argv) {
     else if (key == "width") { need(true); o.width = size_t(atof(value.c_str())); }
     else if (key == "height") { need(true); o.height = size_t(atof(value.c_str())); }
     else if (key == "passes-per-render") { need(true); o.passes_per_render = size_t(atof(value.c_str())); }
+    else if (key == "gpus") { need(true); o.gpus = size_t(atof(value.c_str())); if (o.gpus < 1) throw std::runtime_error("Invalid value for --gpus."); }
+    else if (key == "max-path") { need(true); o.max_path = size_t(atof(value.c_str())); }
     else if (key == "resolution") {
       unsigned w = 0, h = 0;
       if (!has_value || sscanf(value.c_str(), "%ux%u", &w, &h) != 2 || !w || !h) throw std::runtime_error("Invalid value for --resolution.");
@@ -98,11 +101,11 @@ inline CliOptions parse_cli(int argc, char** argv) {
   if (num_techniques > 1) throw std::runtime_error("More than one technique specified.");
   if (num_from > 1) throw std::runtime_error("--from-light and --from-camera cannot be specified at the same time.");
   if (positional.empty()) throw std::runtime_error("Input file is required.");
-  static const char* actions[] = {"average", "errors", "time", "merge", "strip", "bake", "continue"};
+  static const char* actions[] = {"merge", "continue"};
   for (const char* act : actions)
     if (positional[0] == act && o.action == "render") { o.action = act; positional.erase(positional.begin()); break; }
   o.inputs = positional;
-  const size_t want = o.action == "merge" ? 3 : (o.action == "errors" || o.action == "strip" || o.action == "bake") ? 2 : 1;
+  const size_t want = o.action == "merge" ? 3 : 1;
   // `continue` takes the checkpoint; the scene comes from its options.input0 unless a second path overrides it
   if (o.inputs.size() != want && !(o.action == "continue" && o.inputs.size() == 2)) throw std::runtime_error("Input file is required.");
   return o;

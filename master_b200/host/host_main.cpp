@@ -3,7 +3,9 @@
 //   b2pt_master <scene.b2s> --BPT --beta=2 --resolution=1024x1024 --num-samples=64 --output=image.exr [--seed= --camera= ...]
 //   b2pt_master continue <image.exr> [<scene.b2s>] --num-samples=128        master continue (main.cpp:108-…)
 //   b2pt_master merge <out.exr> <fst.exr> <snd.exr>                         master merge    (Options.cpp:1340-1409)
-//   b2pt_master errors <fst.exr> <snd.exr> | average <in.exr> | time <in.exr> | strip <out> <in> | bake <out> <in>
+//   b2pt_master <scene.b2s> --BPT ... --gpus=N                              N GPUs of this node: one host thread per device, the
+//                                                                           samples split g, g + N, ..., films summed with ONE
+//                                                                           b2pt_reduce_accum (NCCL) — merge's a + b on the device
 //
 // Rendering is Framework::runBatch (framework.cpp:426-437) around GpuTechnique::render, the way Application::render drives
 // any Technique (Application.cpp:41-79): one pass (or passes_per_render of them) per call until num_samples / num_seconds.
@@ -13,10 +15,12 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstring>
 #include <fstream>
 #include <iomanip>
 #include <iostream>
 #include <map>
+#include <thread>
 
 #include <xmmintrin.h>
 #include <pmmintrin.h>
@@ -69,44 +73,8 @@ void options_from_dict(const Meta& m, CliOptions& o, std::string& scene_path) {
   if (!z.empty()) sscanf(z.c_str(), "%fx%fx%f", o.sky_zenith, o.sky_zenith + 1, o.sky_zenith + 2);
 }
 
-// ---- the image tools of main.cpp:80-107 that need nothing but the files
-int tool_average(const std::string& path) {  // exr_average (exr.cpp:300-335): mean of rgb / denom; sorted sums there, pairwise here
-  ExrImage img = read_exr(path);
-  double s[3] = {0, 0, 0};
-  const size_t n = img.width * img.height;
-  for (size_t i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) s[c] += double(img.rgbd[i * 4 + c] / img.rgbd[i * 4 + 3]);
-  std::cout << "[" << float(s[0] / n) << " " << float(s[1] / n) << " " << float(s[2] / n) << "]" << std::endl;
-  return 0;
-}
-
-int tool_errors(const std::string& fst, const std::string& snd) {  // compute_errors (main.cpp:216-275), whole-image part
-  ExrImage a = read_exr(fst), b = read_exr(snd);
-  if (a.width != b.width || a.height != b.height) throw std::runtime_error("Sizes of '" + fst + "' and '" + snd + "' doesn't match.");
-  double num = 0, abs_sum = 0, rms_sum = 0;
-  for (size_t i = 0; i < a.width * a.height; ++i) {
-    float d[3]; bool nan = false;
-    for (int c = 0; c < 3; ++c) {  // load_exr for vec3 data divides by denom (exr.cpp:150-157)
-      const float x = a.rgbd[i * 4 + c] / a.rgbd[i * 4 + 3], y = b.rgbd[i * 4 + c] / b.rgbd[i * 4 + 3];
-      nan = nan || std::isnan(x) || std::isnan(y);
-      d[c] = x - y;
-    }
-    if (nan) continue;
-    for (int c = 0; c < 3; ++c) { rms_sum += std::fabs(d[c] * d[c]); abs_sum += std::fabs(d[c]); }
-    num += 3.0;
-  }
-  std::cout << std::setprecision(10) << "ABS: " << abs_sum / num << "\n" << "RMS: " << std::sqrt(rms_sum / num) << "\n";
-  return 0;
-}
-
-int tool_time(const std::string& path) {  // query_time (exr.cpp:440-443) reads "total_time"; the files carry "statistics.total_time"
-  ExrImage img = read_exr(path);
-  auto i = img.metadata.find("total_time");
-  if (i == img.metadata.end()) i = img.metadata.find("statistics.total_time");
-  if (i == img.metadata.end()) throw std::runtime_error("no total_time attribute in " + path);
-  std::cout << i->second;
-  return 0;
-}
-
+// ---- `master merge` (main.cpp:90-92): the CPU analogue of the multi-GPU film reduce; the other image tools of main.cpp:80-107
+// (average, errors, time, strip, bake, gnuplot) are post-processing and stay with the reference's own binary
 int tool_merge(const std::string& dst, const std::string& fst, const std::string& snd) {  // merge_exr (Options.cpp:1340-1409)
   ExrImage a = read_exr(fst), b = read_exr(snd);
   if (a.width != b.width || a.height != b.height) throw std::runtime_error("Sizes of '" + fst + "' and '" + snd + "' doesn't match.");
@@ -134,25 +102,67 @@ int tool_merge(const std::string& dst, const std::string& fst, const std::string
   return 0;
 }
 
-int tool_strip(const std::string& dst, const std::string& src) {  // strip_exr (Options.cpp:1306-1338): one record, no measurements
-  ExrImage img = read_exr(src);
-  statistics_t st(img.metadata);
-  double duration = 0;
-  for (auto& r : st.records) duration += r.frame_duration;
-  if (!st.records.empty()) { st.records.erase(st.records.begin(), st.records.end() - 1); st.records.back().frame_duration = float(duration); }
-  st.measurements.clear();
-  Meta meta = st.to_dict();
-  for (auto& kv : img.metadata) if (kv.first.rfind("options.", 0) == 0) meta[kv.first] = kv.second;
-  meta["options.output"] = dst; meta["options.input1"] = src;
-  save_exr(dst, meta, img.width, img.height, img.rgbd.data(), 4);
-  return 0;
-}
 
-int tool_bake(const std::string& dst, const std::string& src) {  // bake (main.cpp:157-214): rgb / denom, three channels
-  ExrImage img = read_exr(src);
-  std::vector<float> rgb(img.width * img.height * 3);
-  for (size_t i = 0; i < img.width * img.height; ++i) for (int c = 0; c < 3; ++c) rgb[i * 3 + c] = img.rgbd[i * 4 + c] / img.rgbd[i * 4 + 3];
-  save_exr(dst, img.metadata, img.width, img.height, rgb.data(), 3);
+// --gpus=N: one host thread per device.  Thread g builds its own device scene (replicated BVH), renders the sample indices
+// g, g + N, ... into a film that stays on its GPU, then all films are added into rank 0's with one b2pt_reduce_accum and rank 0
+// brings the sum to the host once.  No other communication.
+int render_multi_gpu(const CliOptions& o, const GpuOptions& base, const shared<Scene>& scene, const std::string& scene_path) {
+  const int N = int(o.gpus);
+  if (b2pt_device_count() < N) throw std::runtime_error("--gpus=" + std::to_string(N) + ": only " + std::to_string(b2pt_device_count()) + " CUDA devices are visible");
+  if (o.num_samples == 0) throw std::runtime_error("--gpus needs --num-samples (the sample budget that is split over the GPUs)");
+  const size_t W = o.width, H = o.height;
+  char id[B2PT_COMM_ID_BYTES];
+  std::memset(id, 0, sizeof id);
+  if (N > 1 && b2pt_comm_unique_id(id) != B2PT_OK) throw std::runtime_error(std::string("b2pt_comm_unique_id: ") + b2pt_last_error());
+  std::vector<dvec4> accum(W * H, dvec4(0.0));
+  std::vector<std::string> errors(N);
+  std::vector<statistics_t> stats(N);
+  const auto t0 = std::chrono::steady_clock::now();
+  std::vector<std::thread> threads;
+  for (int r = 0; r < N; ++r) threads.emplace_back([&, r] {
+    try {
+      if (b2pt_set_device(r) != B2PT_OK) throw std::runtime_error(std::string("b2pt_set_device: ") + b2pt_last_error());
+      GpuOptions g = base;
+      g.first_sample = uint32_t(r); g.sample_stride = uint32_t(N);
+      GpuTechnique technique(scene, g);
+      technique.set_sky_gradient(vec3(o.sky_horizon[0], o.sky_horizon[1], o.sky_horizon[2]), vec3(o.sky_zenith[0], o.sky_zenith[1], o.sky_zenith[2]));
+      b2pt_comm_t comm = nullptr;
+      if (b2pt_comm_init(N, r, id, &comm) != B2PT_OK) throw std::runtime_error(std::string("b2pt_comm_init: ") + b2pt_last_error());
+      const size_t mine = (o.num_samples - size_t(r) + size_t(N) - 1) / size_t(N);  // passes r, r + N, ... below num_samples
+      const size_t chunk = o.passes_per_render > 1 ? o.passes_per_render : 16;
+      for (size_t done = 0; done < mine; done += chunk)
+        technique.render_resident(W, H, o.camera_id, uint32_t(std::min(chunk, mine - done)));
+      if (mine == 0) technique.render_resident(W, H, o.camera_id, 0);  // creates the (empty) film this rank contributes
+      technique.reduce_film(comm, 0);
+      if (r == 0) { subimage_view_t view(accum.data(), W, H); technique.read_film(view); }
+      else b2pt_device_synchronize();
+      stats[r] = technique.statistics();
+      b2pt_comm_destroy(comm);
+    } catch (const std::exception& e) { errors[r] = e.what(); }
+  });
+  for (auto& t : threads) t.join();
+  for (int r = 0; r < N; ++r) if (!errors[r].empty()) throw std::runtime_error("rank " + std::to_string(r) + ": " + errors[r]);
+  const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  statistics_t total = stats[0];
+  for (int r = 1; r < N; ++r) { total.num_samples += stats[r].num_samples; total.num_basic_rays += stats[r].num_basic_rays; total.num_shadow_rays += stats[r].num_shadow_rays; }
+  total.total_time = sec;
+  if (!o.raw_out.empty()) {
+    std::ofstream f(o.raw_out, std::ios::binary);
+    f.write((const char*)accum.data(), accum.size() * sizeof(dvec4));
+  }
+  if (!o.output.empty()) {
+    Meta meta = total.to_dict();
+    const Meta opts = options_to_dict(o, scene_path);
+    meta.insert(opts.begin(), opts.end());
+    std::vector<float> rgbd(W * H * 4);
+    for (size_t i = 0; i < W * H; ++i) { rgbd[i * 4] = float(accum[i].x); rgbd[i * 4 + 1] = float(accum[i].y); rgbd[i * 4 + 2] = float(accum[i].z); rgbd[i * 4 + 3] = float(accum[i].w); }
+    save_exr(o.output, meta, W, H, rgbd.data(), 4);
+  }
+  if (!o.quiet)
+    printf("{\"width\": %zu, \"height\": %zu, \"num_samples\": %zu, \"gpus\": %d, \"seconds\": %.6f, \"basic_rays\": %zu, \"shadow_rays\": %zu, "
+           "\"msamples_per_s\": %.6f, \"mrays_per_s\": %.6f}\n",
+           W, H, size_t(total.num_samples), N, sec, size_t(total.num_basic_rays), size_t(total.num_shadow_rays),
+           W * H * double(total.num_samples) / sec * 1e-6, double(total.num_basic_rays + total.num_shadow_rays) / sec * 1e-6);
   return 0;
 }
 
@@ -164,12 +174,7 @@ int main(int argc, char** argv) {
   try {
     if (argc < 2) { fprintf(stderr, "usage: b2pt_master <scene.b2s> [--PT|--BPT|--VCM|--UPG] [options]   (the reference's `master` command line)\n"); return 2; }
     CliOptions o = parse_cli(argc, argv);
-    if (o.action == "average") return tool_average(o.inputs[0]);
-    if (o.action == "errors") return tool_errors(o.inputs[0], o.inputs[1]);
-    if (o.action == "time") return tool_time(o.inputs[0]);
     if (o.action == "merge") return tool_merge(o.inputs[0], o.inputs[1], o.inputs[2]);
-    if (o.action == "strip") return tool_strip(o.inputs[0], o.inputs[1]);
-    if (o.action == "bake") return tool_bake(o.inputs[0], o.inputs[1]);
 
     std::string scene_path = o.inputs[0];
     std::vector<dvec4> accum;
@@ -200,8 +205,11 @@ int main(int argc, char** argv) {
     g.radius = float(o.radius); g.alpha = float(o.alpha); g.num_photons = o.num_photons;
     g.enable_vc = o.enable_vc; g.enable_vm = o.enable_vm; g.from_light = o.from_light;
     g.passes_per_render = uint32_t(o.passes_per_render ? o.passes_per_render : 1);
+    g.max_path = o.max_path;
     g.fixed_seed = true; g.seed = uint32_t(o.seed);
     const size_t W = o.width, H = o.height;
+    // B2PT_FORCE_MULTI=1 takes the multi-GPU path with one rank too (tests of the resident film + reduce on a single-GPU box)
+    if (o.gpus > 1 || (getenv("B2PT_FORCE_MULTI") && o.action == "render")) return render_multi_gpu(o, g, scene, scene_path);
     shared<Technique> technique = std::make_shared<GpuTechnique>(scene, g);  // makeTechnique's --gpu case
     technique->set_sky_gradient(vec3(o.sky_horizon[0], o.sky_horizon[1], o.sky_horizon[2]), vec3(o.sky_zenith[0], o.sky_zenith[1], o.sky_zenith[2]));
     if (resumed) technique->set_statistics(restored);

@@ -35,6 +35,13 @@ g++ -o "$OUT/ref_harness" $OBJS -L"$DEPS/lib" -lassimp -lembree -lembree_avx -le
   -lz -lpthread -ldl
 echo "built $OUT/ref_harness"
 
+# ---- the same objects on a correctly rounded float libm (oracle/cr_libm.cpp interposes sinf, cosf, powf, ...): a diagnostic
+# oracle that tells how much of a per-path disagreement is the last bit of the host's libm (tests/test_large_scene_gpu.py)
+g++ -O2 -msse4.2 -fno-builtin -c "$HERE/cr_libm.cpp" -o "$OUT/obj/cr_libm.o"
+g++ -o "$OUT/ref_harness_crlibm" "$OUT/obj/cr_libm.o" $OBJS -L"$DEPS/lib" -lassimp -lembree -lembree_avx -lembree_sse42 -lsimd -llexers -lsys \
+  -lz -lpthread -ldl
+echo "built $OUT/ref_harness_crlibm"
+
 # ---- timing-only build, as the stock reference compiles (Makefile:27,30-37): no RNG shim (std::mt19937), -O2 with AVX2 + FMA
 # (-march=x86-64-v3 instead of -march=native so that the binary runs on any AVX2 host: the GPU box is not this machine), linked
 # with the AVX2 Embree.  bench.py uses it for cpu_baseline / --impl reference when the host CPU has AVX2, and says which build ran.

@@ -3,7 +3,14 @@ CrytekSponza.blend; built from the refer
 
 * ray level: >= 1 M rays per class (camera / cosine bounce / shadow) against Embree itself, run on this host by the shipped
   oracle/_ref/ref_harness — ids >= 99.99 %, t / u / v bit-exact on the same triangle (Scene.cpp:151-226);
-* per path: PT and BPT at 128 x 128 x 2 spp against goldens the oracle rendered from the same scene file with the same streams."""
+* per path: PT and BPT at 128 x 128 x 2 spp against goldens the oracle rendered from the same scene file with the same streams.
+
+On this scene (Phong materials everywhere, 567 k triangles) the reference's OWN per-path result depends on the last bit of the host's
+float libm: the unmodified reference linked against glibc and the same objects linked against a correctly rounded float libm
+(oracle/cr_libm.cpp -> ref_harness_crlibm; sinf, cosf, powf, asinf, atan2f evaluated in double and rounded once) disagree on 48 of
+32 768 PT paths and 82 BPT paths — a 1-ulp difference in a sampled direction picks another triangle or falls on the other side of
+a roulette threshold.  The device rounds those functions correctly (csrc/common.cuh: cr_*), so it is held to >= 99.99 % against
+the correctly rounded oracle and to the oracle-vs-oracle level (>= 99.7 %) against the glibc one."""
 import json
 import os
 import sys
@@ -60,16 +67,19 @@ def test_livingroom_live_embree_parity_1m(large, tmp_path):
 
 
 @needs_scene
-@pytest.mark.parametrize("tech", ["PT", "BPT"])
-def test_livingroom_per_path(tech, large):
+@pytest.mark.parametrize("tech,libm", [("PT", "crlibm"), ("BPT", "crlibm"), ("PT", "glibc"), ("BPT", "glibc")])
+def test_livingroom_per_path(tech, libm, large):
     flat, scene = large
-    g = np.load(golden_path("render_LivingRoom_%s.npz" % tech))
+    g = np.load(golden_path("render_LivingRoom_%s%s.npz" % (tech, "_crlibm" if libm == "crlibm" else "")))
+    other = np.load(golden_path("render_LivingRoom_%s%s.npz" % (tech, "" if libm == "crlibm" else "_crlibm")))
     w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
     info = json.loads(str(g["info"]))
     accum, paths, stats = gpu_render(scene, flat, tech, w, h, spp, int(g["seed"]), beta=float(g["beta"]))
     frac, err = path_agreement(paths, g["paths"])
     mean_ref, mean_ours = g["accum"][:, :3].mean(axis=0), accum[:, :3].mean(axis=0)
-    out = dict(scene="LivingRoom", tech=tech, paths=int(err.size), within_1e4=frac, flips=int((err > 1e-4).sum()),
+    oracle_vs_oracle, _ = path_agreement(other["paths"], g["paths"])
+    out = dict(scene="LivingRoom", tech=tech, oracle_libm=libm, paths=int(err.size), within_1e4=frac, flips=int((err > 1e-4).sum()),
+               glibc_oracle_vs_crlibm_oracle=oracle_vs_oracle,
                rays=[stats["num_basic_rays"], stats["num_shadow_rays"]], ref_rays=[info["basic_rays"], info["shadow_rays"]],
                mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist(), rel_rmse=image_rel_rmse(accum, g["accum"]))
     if tech == "BPT":
@@ -77,7 +87,10 @@ def test_livingroom_per_path(tech, large):
         scale = max(np.abs(g["light"]).max(), 1e-6)
         out["light_pixels_off"] = float((np.abs(light_ours - g["light"]).max(axis=1) > 1e-4 * scale + 1e-4 * np.abs(g["light"]).max(axis=1)).mean())
     print(json.dumps(out))
-    assert frac >= 0.999
+    if libm == "crlibm":
+        assert int((err > 1e-4).sum()) <= 3  # >= 99.99 %: every path takes the decisions of the reference on a correctly rounded libm
+    else:
+        assert frac >= 0.997 and frac >= oracle_vs_oracle - 5e-4  # no worse than the reference against itself on another libm
     assert np.array_equal(accum[:, 3], g["accum"][:, 3])
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=5e-3, atol=1e-6)
     if tech == "BPT":

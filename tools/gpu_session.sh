@@ -13,6 +13,7 @@ for w in $what; do
   case $w in
     tests) timeout 1800 python -m pytest tests -m gpu -q -rA --durations=15 > gpurun_out/${tag}_tests.log 2>&1; echo "tests rc=$?"; tail -5 gpurun_out/${tag}_tests.log ;;
     tests_nosplit) B2PT_SPLIT_BUDGET=0 timeout 900 python -m pytest tests/test_trace_gpu.py tests/test_pt_gpu.py tests/test_bpt_gpu.py -m gpu -q -rA > gpurun_out/${tag}_tests_nosplit.log 2>&1; echo "tests_nosplit rc=$?"; tail -3 gpurun_out/${tag}_tests_nosplit.log ;;
+    large_nosplit) B2PT_SPLIT_BUDGET=0 timeout 900 python -m pytest tests/test_large_scene_gpu.py -m gpu -q -rA > gpurun_out/${tag}_large_nosplit.log 2>&1; echo "large_nosplit rc=$?"; grep "^{" gpurun_out/${tag}_large_nosplit.log ;;
     smoke) timeout 300 python __graft_entry__.py --smoke > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/${tag}_smoke.log ;;
     bpt) timeout 900 python bench.py --steps 6 --warmup 3 > gpurun_out/${tag}_bpt_bench.json 2> gpurun_out/${tag}_bpt_bench.err; echo "bpt rc=$?"; cat gpurun_out/${tag}_bpt_bench.json ;;
     pt) timeout 900 python bench.py --steps 6 --warmup 3 --technique PT > gpurun_out/${tag}_pt_bench.json 2> gpurun_out/${tag}_pt_bench.err; echo "pt rc=$?"; cat gpurun_out/${tag}_pt_bench.json ;;
