@@ -279,6 +279,11 @@ void b2pt_grid_destroy(b2pt_grid_t grid);
  */
 int b2pt_grid_query(b2pt_grid_t grid, const float* queries, size_t nq, uint32_t max_per_query,
                     uint32_t* counts, uint32_t* indices);
+/* the same with queries / counts / indices already in DEVICE memory; asynchronous on `stream` */
+int b2pt_grid_query_device(b2pt_grid_t grid, const float* queries_dev, size_t nq, uint32_t max_per_query,
+                           uint32_t* counts_dev, uint32_t* indices_dev, void* stream);
+/* points indexed (light-origin vertices left out, HashGrid3D.hpp:253), cell size, device milliseconds of the build */
+int b2pt_grid_info(b2pt_grid_t grid, uint64_t* num_points, float* radius, float* build_ms);
 
 #ifdef __cplusplus
 }

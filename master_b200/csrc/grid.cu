@@ -131,6 +131,7 @@ __global__ void grid_pack_kernel(uint32_t n, const float* __restrict__ xyz, floa
 
 struct b2pt_grid_s {
   b2pt::GridStorage storage;
+  float build_ms = 0.f;  // device time of the build (keys, radix sort, gather, table inserts), points already in HBM
 };
 
 extern "C" {
@@ -152,8 +153,14 @@ int b2pt_grid_build(const float* points, size_t n, float radius, b2pt_grid_t* ou
     if (e == cudaSuccess) e = cudaMemcpy(d_xyz, points, n * 12, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
       grid_pack_kernel<<<unsigned((n + 255) / 256), 256>>>(uint32_t(n), d_xyz, d_pts);
+      cudaEvent_t e0 = nullptr, e1 = nullptr;
+      cudaEventCreate(&e0); cudaEventCreate(&e1);
+      cudaEventRecord(e0, nullptr);
       rc = grid_build_device(g->storage, d_pts, uint32_t(n), radius, nullptr);
+      cudaEventRecord(e1, nullptr);
       if (rc == B2PT_OK) e = cudaDeviceSynchronize();
+      if (rc == B2PT_OK && e == cudaSuccess) cudaEventElapsedTime(&g->build_ms, e0, e1);
+      cudaEventDestroy(e0); cudaEventDestroy(e1);
     }
     cudaFree(d_xyz); cudaFree(d_pts);
     if (e != cudaSuccess) rc = cuda_fail(e, "b2pt_grid_build", __FILE__, __LINE__);
@@ -169,6 +176,25 @@ void b2pt_grid_destroy(b2pt_grid_t grid) {
   if (!grid) return;
   grid->storage.release();
   delete grid;
+}
+
+int b2pt_grid_info(b2pt_grid_t grid, uint64_t* num_points, float* radius, float* build_ms) {
+  B2_CHECK(grid, B2PT_ERR_INVALID, "b2pt_grid_info: null grid");
+  if (num_points) *num_points = grid->storage.dev.num_points;
+  if (radius) *radius = grid->storage.dev.radius;
+  if (build_ms) *build_ms = grid->build_ms;
+  return B2PT_OK;
+}
+
+int b2pt_grid_query_device(b2pt_grid_t grid, const float* queries_dev, size_t nq, uint32_t max_per_query, uint32_t* counts_dev,
+                           uint32_t* indices_dev, void* stream) {
+  using namespace b2pt;
+  B2_CHECK(grid && (nq == 0 || (queries_dev && counts_dev)) && (max_per_query == 0 || indices_dev), B2PT_ERR_INVALID, "b2pt_grid_query_device: null argument");
+  if (nq == 0) return B2PT_OK;
+  B2_CHECK(nq < 0xFFFFFFFFull, B2PT_ERR_CAPACITY, "b2pt_grid_query_device: too many queries");
+  grid_query_kernel<<<unsigned((nq + 127) / 128), 128, 0, (cudaStream_t)stream>>>(grid->storage.dev, queries_dev, uint32_t(nq), max_per_query, counts_dev, indices_dev);
+  B2_CUDA(cudaGetLastError());
+  return B2PT_OK;
 }
 
 int b2pt_grid_query(b2pt_grid_t grid, const float* queries, size_t nq, uint32_t max_per_query, uint32_t* counts, uint32_t* indices) {

@@ -994,11 +994,13 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
   for (uint32_t k = 0; k < L; ++k) if (d->lights[k].diffuse == 0.0f) ds.has_directional = 1u;
   s->bvh_bytes = uint64_t(num_wide) * (nodes8 ? 5 : kNodeFloat4s) * 16 + uint64_t(n) * 48;
   // ---- L2 residency (north_star: "top BVH levels staged in shared memory / L2"): set aside as much persisting L2 as the device
-  // allows for the BVH block; render streams attach the window (b2pt_scene_l2_window).  B2PT_L2_PERSIST=0 turns it off (A/B runs).
+  // allows for the BVH block; render streams attach the window (scene_l2_window).  OFF by default — measured on B200: with
+  // the window the closest-hit stage is unchanged (the BVH block is L2-resident anyway) and the shading stages, which lose the set-aside
+  // part of the L2 for their pools, slow down by 9 %: 77.7 Msamples/s with it, 79.4 without.  B2PT_L2_PERSIST=1 turns it on.
   {
     const char* e = getenv("B2PT_L2_PERSIST");
     int dev = 0; cudaDeviceProp prop{};
-    if (!(e && e[0] == '0') && cudaGetDevice(&dev) == cudaSuccess && cudaGetDeviceProperties(&prop, dev) == cudaSuccess &&
+    if ((e && e[0] == '1') && cudaGetDevice(&dev) == cudaSuccess && cudaGetDeviceProperties(&prop, dev) == cudaSuccess &&
         prop.persistingL2CacheMaxSize > 0 && prop.accessPolicyMaxWindowSize > 0) {
       const size_t want = std::min<size_t>(s->bvh_block_bytes, size_t(prop.persistingL2CacheMaxSize));
       if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {

@@ -95,5 +95,5 @@ def test_livingroom_per_path(tech, libm, large):
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=5e-3, atol=1e-6)
     if tech == "BPT":
         assert out["light_pixels_off"] <= 0.01
-    else:
-        assert stats["num_basic_rays"] == pytest.approx(info["basic_rays"], rel=0.01)
+    else:  # a ray whose sampled BSDF throughput is already zero (a Phong sample below the surface) is not shot here: fewer rays, same paths
+        assert 0.85 * info["basic_rays"] <= stats["num_basic_rays"] <= info["basic_rays"]
