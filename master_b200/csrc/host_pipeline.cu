@@ -7,7 +7,8 @@
 // caller:
 //
 //   * a call for pass j of a sequence (same parameters, consecutive sample indices) is served from a batch of per-pass films
-//     [j, j + L) rendered in one go (L = 2^24 / pixels passes: the batch size the integrators are efficient at);
+//     [j, j + L) rendered in one go; L starts at a quarter of 2^24 / pixels passes (or what the call asks for, if that is more) and
+//     doubles per batch up to 2^24 / pixels — the batch size the integrators are efficient at — so a short run wastes little;
 //   * while the caller consumes batch A — device->host copy in chunks on a copy stream, each chunk added into the view by a pool of
 //     persistent host threads as it lands — a worker thread already renders batch B = [j + L, j + 2L) on its own streams;
 //   * a call whose parameters do not continue the sequence drops what was rendered ahead and starts a new sequence.
@@ -117,6 +118,8 @@ struct HostPipeline {
   size_t film_doubles = 0;
   uint32_t capacity = 0;   // films per batch
   uint32_t lookahead = 0;  // passes per batch rendered ahead (0 = off)
+  uint32_t last_batch = 0; // size of the batch launched last in this sequence: batches double from what the caller asks for up to `lookahead`,
+                           // so a short run wastes at most about as many passes as it consumed
   PassBatch batch[2];
   double* stage_dev = nullptr;
   double* pinned = nullptr;
@@ -272,7 +275,7 @@ extern "C" int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* para
   if (!continues) {
     h->quiesce();
     for (auto& b : h->batch) b.state = PassBatch::kEmpty;
-    h->key = *params; h->has_key = true; h->cursor = 0;
+    h->key = *params; h->has_key = true; h->cursor = 0; h->last_batch = 0;
   }
 
   // ---- gather the n passes [cursor, cursor + n) into `src` (a single film is read in place, several are summed on the device)
@@ -292,7 +295,9 @@ extern "C" int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* para
       h->quiesce();
       int slot = h->batch[0].state == PassBatch::kEmpty ? 0 : 1;
       if (h->batch[slot].state != PassBatch::kEmpty) { h->batch[0].state = PassBatch::kEmpty; h->batch[1].state = PassBatch::kEmpty; slot = 0; }
-      pipeline_launch(h, slot, h->cursor, std::max(per_batch, left));
+      const uint32_t size = std::min(per_batch, std::max(std::max(left, (look + 3u) / 4u), 2u * h->last_batch));
+      h->last_batch = size;
+      pipeline_launch(h, slot, h->cursor, size);
       continue;
     }
     PassBatch& pb = h->batch[b];
@@ -311,7 +316,11 @@ extern "C" int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* para
         const bool other_done = other.state == PassBatch::kEmpty || (other.state == PassBatch::kReady && other.start + other.passes <= h->cursor);
         go = h->job < 0 && other_done;
       }
-      if (go) pipeline_launch(h, b ^ 1, pb.start + pb.passes, per_batch);
+      if (go) {
+        const uint32_t size = std::min(per_batch, std::max(n, 2u * h->last_batch));
+        h->last_batch = size;
+        pipeline_launch(h, b ^ 1, pb.start + pb.passes, size);
+      }
     }
     const uint32_t take = std::min(left, pb.start + pb.passes - h->cursor);
     const double* first = pb.films + size_t(h->cursor - pb.start) * fd;

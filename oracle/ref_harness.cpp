@@ -19,6 +19,7 @@
 //   errors <accum.f64> <ref.f32> W H [cx cy r]   rms_abs_errors / rms_abs_errors_windowed (ImageView.cpp:60-117)
 //   pinning <scene> key=value ...  raw draws, float / piecewise draws, primary rays of _for_each_ray, light samples
 //   camera                         ray_direction / pixel_position / lookAt frames at the in-source unittest() inputs
+//   rawdump <scene.blend> <out.b2i>  what the Assimp fork hands to loadScene (loader.cpp:458-487), before the loader's own math
 // <scene> is a .blend (needs the reference's models/) or a .b2s written by `dump`.
 //
 // -DB2PT_STOCK_TIMING (oracle/build_ref.sh, second binary oracle/_ref/ref_harness_stock): the same driver WITHOUT the RNG shim
@@ -35,6 +36,10 @@
 
 #include <xmmintrin.h>
 #include <pmmintrin.h>
+
+#include <assimp/postprocess.h>
+#include <assimp/scene.h>
+#include <assimp/Importer.hpp>
 
 #include <BPT.hpp>
 #include <PT.hpp>
@@ -569,6 +574,63 @@ static int cmd_camera(int, char**) {
   return 0;
 }
 
+// The importer's output as loadScene sees it (loader.cpp:458-487: same flags), written before any of the loader's own arithmetic:
+// cameras, material properties, per-mesh positions / normals / optional tangents / faces, area lights.  Format: raw_import.hpp.
+static int cmd_rawdump(int argc, char** argv) {
+  if (argc < 4) return 2;
+  Assimp::Importer importer;
+  auto flags = aiProcess_Triangulate | aiProcess_GenNormals | aiProcess_JoinIdenticalVertices | aiProcess_PreTransformVertices;
+  const aiScene* scene = importer.ReadFile(argv[2], flags);
+  if (!scene) throw std::runtime_error(string("Cannot load \"") + argv[2] + "\" scene.");
+  std::ofstream f(argv[3], std::ios::binary);
+  auto u32 = [&](uint32_t v) { f.write((const char*)&v, 4); };
+  auto f32 = [&](float v) { f.write((const char*)&v, 4); };
+  auto str = [&](const char* s) { u32(uint32_t(strlen(s))); f.write(s, strlen(s)); };
+  auto v3 = [&](const aiVector3D& v) { f32(v.x); f32(v.y); f32(v.z); };
+  auto c3 = [&](const aiColor3D& v) { f32(v.r); f32(v.g); f32(v.b); };
+  f.write("B2IMPORT", 8);
+  uint32_t area_lights = 0;
+  for (unsigned i = 0; i < scene->mNumLights; ++i) area_lights += scene->mLights[i]->mType == aiLightSource_AREA;
+  u32(scene->mNumCameras); u32(scene->mNumMaterials); u32(scene->mNumMeshes); u32(scene->mNumLights);
+  for (unsigned i = 0; i < scene->mNumCameras; ++i) {
+    auto c = scene->mCameras[i];
+    str(c->mName.C_Str()); v3(c->mPosition); v3(c->mLookAt); v3(c->mUp); f32(c->mHorizontalFOV); f32(c->mClipPlaneNear); f32(c->mClipPlaneFar);
+  }
+  for (unsigned i = 0; i < scene->mNumMaterials; ++i) {
+    const aiMaterial* m = scene->mMaterials[i];
+    aiString name; m->Get(AI_MATKEY_NAME, name);
+    int transparency = 0, mirror = 0; float ior = 0, shin = 0;
+    m->Get("$mat.blend.transparency.use", 0, 0, transparency); m->Get("$mat.blend.transparency.ior", 0, 0, ior);
+    m->Get("$mat.blend.mirror.use", 0, 0, mirror); m->Get(AI_MATKEY_SHININESS, shin);
+    aiColor3D diffuse, specular;
+    m->Get(AI_MATKEY_COLOR_DIFFUSE, diffuse); m->Get(AI_MATKEY_COLOR_SPECULAR, specular);
+    str(name.C_Str()); u32(transparency != 0); f32(ior); u32(mirror != 0); c3(diffuse); c3(specular); f32(shin);
+  }
+  for (unsigned i = 0; i < scene->mNumMeshes; ++i) {
+    const aiMesh* m = scene->mMeshes[i];
+    const bool has_tangents = m->mBitangents != nullptr && m->mTangents != nullptr;
+    str(m->mName.C_Str()); u32(m->mMaterialIndex); u32(m->mNumVertices); u32(m->mNumFaces); u32(has_tangents);
+    for (unsigned j = 0; j < m->mNumVertices; ++j) v3(m->mVertices[j]);
+    for (unsigned j = 0; j < m->mNumVertices; ++j) v3(m->mNormals[j]);
+    if (has_tangents) {
+      for (unsigned j = 0; j < m->mNumVertices; ++j) v3(m->mTangents[j]);
+      for (unsigned j = 0; j < m->mNumVertices; ++j) v3(m->mBitangents[j]);
+    }
+    for (unsigned j = 0; j < m->mNumFaces; ++j) {
+      if (m->mFaces[j].mNumIndices != 3) throw std::runtime_error("non-triangle face after aiProcess_Triangulate");
+      for (int k = 0; k < 3; ++k) u32(m->mFaces[j].mIndices[k]);
+    }
+  }
+  for (unsigned i = 0; i < scene->mNumLights; ++i) {
+    const aiLight* l = scene->mLights[i];
+    str(l->mName.C_Str()); u32(l->mType == aiLightSource_AREA); v3(l->mPosition); v3(l->mDirection); v3(l->mUp); c3(l->mColorDiffuse);
+    f32(l->mSize.x); f32(l->mSize.y); u32(l->mDiffuse ? 1u : 0u);
+  }
+  printf("{\"cameras\": %u, \"materials\": %u, \"meshes\": %u, \"lights\": %u, \"area_lights\": %u}\n", scene->mNumCameras, scene->mNumMaterials,
+         scene->mNumMeshes, scene->mNumLights, area_lights);
+  return 0;
+}
+
 int main(int argc, char** argv) {
   _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);          // main.cpp:70-71
   _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
@@ -580,6 +642,7 @@ int main(int argc, char** argv) {
     if (c == "grid") return cmd_grid(argc, argv);
     if (c == "errors") return cmd_errors(argc, argv);
     if (c == "camera") return cmd_camera(argc, argv);
+    if (c == "rawdump") return cmd_rawdump(argc, argv);
 #ifndef B2PT_STOCK_TIMING
     if (c == "render") return cmd_render(argc, argv);
     if (c == "density") return cmd_density(argc, argv);
