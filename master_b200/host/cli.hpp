@@ -15,7 +15,7 @@
 namespace b2pt_host {
 
 struct CliOptions {
-  std::string action = "render";  // render | continue | merge
+  std::string action = "render";  // render | continue | merge | import
   std::vector<std::string> inputs;
   std::string technique = "PT";  // Options::technique = PT
   double beta = 1.0, roulette = 0.9, radius = 0.01, alpha = 0.75, lights = 1.0;
@@ -101,11 +101,11 @@ inline CliOptions parse_cli(int argc, char** argv) {
   if (num_techniques > 1) throw std::runtime_error("More than one technique specified.");
   if (num_from > 1) throw std::runtime_error("--from-light and --from-camera cannot be specified at the same time.");
   if (positional.empty()) throw std::runtime_error("Input file is required.");
-  static const char* actions[] = {"merge", "continue"};
+  static const char* actions[] = {"merge", "continue", "import"};
   for (const char* act : actions)
     if (positional[0] == act && o.action == "render") { o.action = act; positional.erase(positional.begin()); break; }
   o.inputs = positional;
-  const size_t want = o.action == "merge" ? 3 : 1;
+  const size_t want = o.action == "merge" ? 3 : o.action == "import" ? 2 : 1;
   // `continue` takes the checkpoint; the scene comes from its options.input0 unless a second path overrides it
   if (o.inputs.size() != want && !(o.action == "continue" && o.inputs.size() == 2)) throw std::runtime_error("Input file is required.");
   return o;

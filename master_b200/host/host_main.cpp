@@ -3,6 +3,7 @@
 //   b2pt_master <scene.b2s> --BPT --beta=2 --resolution=1024x1024 --num-samples=64 --output=image.exr [--seed= --camera= ...]
 //   b2pt_master continue <image.exr> [<scene.b2s>] --num-samples=128        master continue (main.cpp:108-…)
 //   b2pt_master merge <out.exr> <fst.exr> <snd.exr>                         master merge    (Options.cpp:1340-1409)
+//   b2pt_master import <scene.b2i> <scene.b2s>                              the loader's own math without Assimp (raw_import.hpp)
 //   b2pt_master <scene.b2s> --BPT ... --gpus=N                              N GPUs of this node: one host thread per device, the
 //                                                                           samples split g, g + N, ..., films summed with ONE
 //                                                                           b2pt_reduce_accum (NCCL) — merge's a + b on the device
@@ -29,6 +30,7 @@
 #include "b2s_io.hpp"
 #include "cli.hpp"
 #include "exr_io.hpp"
+#include "raw_import.hpp"
 
 using namespace haste;
 using namespace b2pt_host;
@@ -175,6 +177,15 @@ int main(int argc, char** argv) {
     if (argc < 2) { fprintf(stderr, "usage: b2pt_master <scene.b2s> [--PT|--BPT|--VCM|--UPG] [options]   (the reference's `master` command line)\n"); return 2; }
     CliOptions o = parse_cli(argc, argv);
     if (o.action == "merge") return tool_merge(o.inputs[0], o.inputs[1], o.inputs[2]);
+    if (o.action == "import") {  // .b2i (what an importer hands over) -> .b2s (what the device scene is built from): loader.cpp:293-456 on the host
+      shared<Scene> imported = scene_from_import(read_b2i(o.inputs[0]));
+      write_b2s(*imported, o.inputs[1]);
+      size_t tris = 0;
+      for (auto& m : imported->meshes) tris += m.indices.size() / 3;
+      printf("{\"meshes\": %zu, \"triangles\": %zu, \"materials\": %zu, \"lights\": %zu, \"cameras\": %zu}\n", imported->meshes.size(), tris,
+             imported->materials.bsdfs.size(), imported->lights.num_lights(), imported->cameras().numCameras());
+      return 0;
+    }
 
     std::string scene_path = o.inputs[0];
     std::vector<dvec4> accum;

@@ -142,7 +142,23 @@ def ref_render(scene_path, technique, width, height, num_samples, **kw):
                 light=np.fromfile(TMP + "/r.light.f64", dtype=np.float64).reshape(n, 3))
 
 
+def make_import_records():
+    """tests/golden/import/*.b2i: what the Assimp fork hands to loadScene (ref_harness rawdump), the input of tests/test_import.py."""
+    import lzma
+    out = os.path.join(HERE, "import")
+    os.makedirs(out, exist_ok=True)
+    for name in ["CornellBoxDiffuse", "CornellBoxSpecular", "TestCaseFurnace", "TestCase12", "MetalRings"]:
+        dst = os.path.join(out, name + ".b2i")
+        print(name, run("rawdump", os.path.join(REF, "models", name + ".blend"), dst))
+        if os.path.getsize(dst) > (1 << 18):
+            with open(dst, "rb") as f, lzma.open(dst + ".xz", "wb", preset=9) as g:
+                g.write(f.read())
+            os.remove(dst)
+
+
 def main():
+    if "import" in sys.argv[1:]:
+        return make_import_records()
     os.makedirs(os.path.join(HERE, "scenes"), exist_ok=True)
     for name in ([] if [a for a in sys.argv[1:] if not a.startswith("-")] else SMALL_SCENES):
         dst = os.path.join(HERE, "scenes", name + ".b2s")
