@@ -74,6 +74,7 @@ struct Vertex {
   float3 omega, thr;
   float w0, w1;
   uint32_t finite;
+  float ladj;  // light_lobe_adjust of the surface if it is a point on an area emitter (computed once, when the vertex is made), else -1
 };
 
 struct BptPool {
@@ -112,7 +113,7 @@ __device__ __forceinline__ void pack_vertex(const Vertex& v, float4* q) {
   q[1] = make_float4(v.s.gnormal.x, v.s.gnormal.y, v.s.gnormal.z, __uint_as_float(v.finite));
   q[2] = make_float4(v.s.tan.c0.x, v.s.tan.c0.y, v.s.tan.c0.z, v.w0);
   q[3] = make_float4(v.s.tan.c1.x, v.s.tan.c1.y, v.s.tan.c1.z, v.w1);
-  q[4] = make_float4(v.s.tan.c2.x, v.s.tan.c2.y, v.s.tan.c2.z, 0.f);
+  q[4] = make_float4(v.s.tan.c2.x, v.s.tan.c2.y, v.s.tan.c2.z, v.ladj);
   q[5] = make_float4(v.omega.x, v.omega.y, v.omega.z, 0.f);
   q[6] = make_float4(v.thr.x, v.thr.y, v.thr.z, 0.f);
 }
@@ -122,7 +123,7 @@ __device__ __forceinline__ Vertex unpack_vertex(const float4* q) {
   v.s.gnormal = f3(q[1].x, q[1].y, q[1].z); v.finite = __float_as_uint(q[1].w);
   v.s.tan.c0 = f3(q[2].x, q[2].y, q[2].z); v.w0 = q[2].w;
   v.s.tan.c1 = f3(q[3].x, q[3].y, q[3].z); v.w1 = q[3].w;
-  v.s.tan.c2 = f3(q[4].x, q[4].y, q[4].z);
+  v.s.tan.c2 = f3(q[4].x, q[4].y, q[4].z); v.ladj = q[4].w;
   v.omega = f3(q[5].x, q[5].y, q[5].z);
   v.thr = f3(q[6].x, q[6].y, q[6].z);
   return v;
@@ -155,8 +156,9 @@ __device__ __forceinline__ Vertex load_pool_vertex(const BptPool& p, uint32_t id
 }
 
 // BPTBase::_sample_to_vertex (BPT.cpp:103-114)
-__device__ __forceinline__ Vertex sample_to_vertex(const LightSample& sample, float roulette_inv, float beta) {
+__device__ __forceinline__ Vertex sample_to_vertex(const LightSample& sample, float roulette_inv, float beta, float ladj) {
   Vertex v;
+  v.ladj = ladj;
   v.s = sample.surface;
   v.omega = v.s.normal();
   v.thr = sample.radiance / sample.combined_density() * roulette_inv;
@@ -186,7 +188,7 @@ __device__ __forceinline__ LightSample light_sample_at(const DeviceScene& sc, ui
 // BPTBase::_connect(light, eye) without the visibility factor (BPT.cpp:194-223)
 __device__ __forceinline__ float3 connect_vertices(const DeviceScene& sc, const Vertex& light, const Vertex& eye, float beta) {
   const float3 omega = normalize(eye.s.pos - light.s.pos);
-  const BsdfQuery lb = bsdf_query(sc, light.s, light.omega, omega);
+  const BsdfQuery lb = bsdf_query(sc, light.s, light.omega, omega, light.ladj);
   const BsdfQuery eb = bsdf_query(sc, eye.s, -omega, eye.omega);
   const Edge edge(light.s.pos, light.s.normal(), eye.s.pos, eye.s.normal(), omega);
   const float Ap = (light.w1 * beta_fn(lb.density_rev, beta) + light.w0 * float(light.finite)) * beta_fn(edge.b_geometry * eb.density_rev, beta);
@@ -335,7 +337,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
           st = kEyeStart;
         } else {
           const LightSample ls = sample_light(sc, rng);
-          cur = sample_to_vertex(ls, roulette_inv, beta);
+          cur = sample_to_vertex(ls, roulette_inv, beta, light_lobe_adjust(sc, ls.surface));
           const unsigned idx = warp_append(&cnt->lv_count, true);
           if (idx >= pool.lv_capacity) {
             atomicAdd(&cnt->capacity_events, 1ull);
@@ -372,6 +374,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
           st = kLightFinal;
         } else {
           Vertex nv;
+          nv.ladj = -1.0f;
           nv.s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, bs.omega);
           nv.omega = -bs.omega;
           const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
@@ -437,6 +440,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
         Rng first; first.key = rng.key; first.ctr = 0;  // the two jitter draws open the stream (Technique.cpp:322)
         const float3 dir = shoot_primary(cfg, first, slot % cfg.pixels);
         cur.s = cfg.camera;
+        cur.ladj = -1.0f;
         cur.omega = -dir;
         cur.thr = f3(1.0f) * roulette_inv;
         cur.finite = 1; cur.w0 = 0.0f; cur.w1 = 0.0f;
@@ -460,6 +464,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
           finished = true;
         } else {
           Vertex nv;
+          nv.ladj = -1.0f;
           nv.s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, bs.omega);
           nv.omega = -bs.omega;
           const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
@@ -492,6 +497,9 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
                     emit_nee = true;
                     const uint32_t light_id = sc.materials[ls.surface.material_index()].light_id;
                     rec[kRecNee] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
+                    // the emitter's lobe restriction at this point: computed here, where every lane of the warp samples a light, instead of
+                    // in the connect stage, where one pair in six needs it and the other lanes of its warp would wait for it
+                    rec[kRecState].y = light_lobe_adjust(sc, ls.surface);
                   } else {
                     // _connect_directional (BPT.cpp:245-269): queued for the directional stage
                     const float3 n = ls.surface.normal();
@@ -545,9 +553,30 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
       const unsigned mask = __ballot_sync(0xFFFFFFFFu, finished);
       if (mask && (threadIdx.x & 31u) == 0) atomicAdd(&cnt->done, unsigned(__popc(mask)));
     }
+    // The three reservations of the iteration — the eye end and the light end of the live queue, the pair queue — are made by lane 0 with
+    // three atomics issued back to back and broadcast afterwards: one round trip to the L2 per warp and iteration instead of three in a
+    // row (the shuffles that wait for them were 15 % of the stage's warp-state samples, profiles/r02_bpt_logic_full_summary.md).
     const bool to_eye_end = want_trace && st == kEyeWait;
-    const unsigned tq = warp_append(&cnt->trace_count[parity], to_eye_end);
-    const unsigned lq = warp_append(&cnt->light_count[parity], want_trace && !to_eye_end);
+    const unsigned lane_id = threadIdx.x & 31u;
+    const unsigned m_eye = __ballot_sync(0xFFFFFFFFu, to_eye_end), m_light = __ballot_sync(0xFFFFFFFFu, want_trace && !to_eye_end);
+    unsigned pair_incl = emit_n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t = __shfl_up_sync(0xFFFFFFFFu, pair_incl, o);
+      if (lane_id >= unsigned(o)) pair_incl += t;
+    }
+    const unsigned pair_total = __shfl_sync(0xFFFFFFFFu, pair_incl, 31);
+    unsigned base_eye = 0, base_light = 0, base_pair = 0;
+    if (lane_id == 0) {
+      if (m_eye) base_eye = atomicAdd(&cnt->trace_count[parity], unsigned(__popc(m_eye)));
+      if (m_light) base_light = atomicAdd(&cnt->light_count[parity], unsigned(__popc(m_light)));
+      if (pair_total) base_pair = atomicAdd(&cnt->pair_count[parity], pair_total);
+    }
+    base_eye = __shfl_sync(0xFFFFFFFFu, base_eye, 0);
+    base_light = __shfl_sync(0xFFFFFFFFu, base_light, 0);
+    base_pair = __shfl_sync(0xFFFFFFFFu, base_pair, 0);
+    const unsigned tq = base_eye + __popc(m_eye & ((1u << lane_id) - 1u));
+    const unsigned lq = base_light + __popc(m_light & ((1u << lane_id) - 1u));
     if (want_trace) {
       const uint32_t at = to_eye_end ? tq : pool.size - 1u - lq;
       next_q[at] = slot;
@@ -570,7 +599,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
         pool.oct_q[size_t(oct) * pool.size + base + __popc(peers & ((1u << lane) - 1u))] = slot;
       }
     }
-    unsigned pq = warp_reserve(&cnt->pair_count[parity], emit_n);
+    unsigned pq = base_pair + pair_incl - emit_n;
     if (emit_n) {
       if (pq + emit_n > pool.q_capacity) {
         atomicAdd(&cnt->capacity_events, 1ull);
@@ -615,7 +644,8 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel
       Vertex light;
       if (desc.y == kNeeVertex) {
         const float4 nr = pool.rec[size_t(slot) * kRecFloat4s + kRecNee];
-        light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), roulette_inv, beta);
+        light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), roulette_inv, beta,
+                                 pool.rec[size_t(slot) * kRecFloat4s + kRecState].y);
       } else {
         light = load_pool_vertex(pool, desc.y);
       }
@@ -934,6 +964,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   if (sort_rays == 2 && !w->lane[0].pool.oct_q) sort_rays = 0;  // the workspace was built before the mode was switched on
   unsigned long long basic = 0, shadow = 0, numeric = 0, capacity = 0;
   const int kBatchIters = 8;
+  const bool log_iterations = getenv("B2PT_LOG_ITER") != nullptr;
 
   // per-lane progress
   struct Progress { bool active = false; uint32_t pass0 = 0, passes = 0; int it = 0; BptPool pool; };
@@ -999,6 +1030,13 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         else if (stream_shadow == 1) bpt_shadow_kernel<1><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         else bpt_shadow_kernel<0><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         timer.end();
+        if (log_iterations) {  // B2PT_LOG_ITER=1: queue lengths of every iteration (synchronises: for matching an ncu launch with its ray count)
+          B2_CUDA(cudaMemcpyAsync(l.host_counters, l.counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, l.stream));
+          B2_CUDA(cudaStreamSynchronize(l.stream));
+          fprintf(stderr, "b2pt_iter lane %d pass0 %u it %d closest %u shadow %u pairs %u\n", k, g.pass0, g.it,
+                  l.host_counters->trace_count[parity] + l.host_counters->light_count[parity],
+                  min(l.host_counters->shadow_count[parity], g.pool.q_capacity), l.host_counters->pair_count[parity]);
+        }
       }
       B2_CUDA(cudaMemcpyAsync(l.host_counters, l.counters, sizeof(BptCounters), cudaMemcpyDeviceToHost, l.stream));
     }

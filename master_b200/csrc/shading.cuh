@@ -253,8 +253,20 @@ __device__ __forceinline__ BsdfQuery phong_query(const B2ptMaterial& m, float3 i
   return q;
 }
 
+// The restriction factor of an emitter's lobe, lambert_adjust(sphere in the emitter's frame) (LightBSDF::query, BSDF.cpp:93-114): it
+// depends on the point of the emitter only, not on the directions of a query, and it is the expensive part of the query (two asin,
+// one atan2, four cos, all correctly rounded).  A stage that queries the same emitter point many times computes it once and hands it
+// to bsdf_query; -1 = not an area emitter / not computed.
+__device__ __forceinline__ float light_lobe_adjust(const DeviceScene& sc, const Surface& s) {
+  const B2ptMaterial& m = sc.materials[s.material_index()];
+  if (m.type != B2PT_BSDF_LIGHT) return -1.0f;
+  const float3 center = s.to_surface(f3(m.sphere[0], m.sphere[1], m.sphere[2]) - s.pos);
+  return lambert_adjust(center, m.sphere[3]);
+}
+
 // Scene::queryBSDF(surface, incident, outgoing) (Scene.cpp:142-149) -> BSDF::query of the surface's material
-__device__ __forceinline__ BsdfQuery bsdf_query(const DeviceScene& sc, const Surface& s, float3 incident, float3 outgoing) {
+// light_adjust >= 0: light_lobe_adjust(sc, s) computed earlier for this surface (same function, same inputs: same bits)
+__device__ __forceinline__ BsdfQuery bsdf_query(const DeviceScene& sc, const Surface& s, float3 incident, float3 outgoing, float light_adjust = -1.0f) {
   const B2ptMaterial& m = sc.materials[s.material_index()];
   BsdfQuery q;
   switch (m.type) {
@@ -265,10 +277,10 @@ __device__ __forceinline__ BsdfQuery bsdf_query(const DeviceScene& sc, const Sur
       return phong_query(m, s.to_surface(incident), s.to_surface(outgoing), same_side);
     }
     case B2PT_BSDF_LIGHT: {  // LightBSDF::query (BSDF.cpp:93-114)
-      const float3 center = s.to_surface(f3(m.sphere[0], m.sphere[1], m.sphere[2]) - s.pos);
       const float3 local_outgoing = s.to_surface(outgoing);
+      const float adjust = light_adjust >= 0.0f ? light_adjust : lambert_adjust(s.to_surface(f3(m.sphere[0], m.sphere[1], m.sphere[2]) - s.pos), m.sphere[3]);
       q.throughput = local_outgoing.y > 0.0f ? f3(1.0f) : f3(0.0f);
-      q.density = (local_outgoing.y > 0.0f ? 1.0f : 0.0f) * local_outgoing.y * kOneOverPi / lambert_adjust(center, m.sphere[3]);
+      q.density = (local_outgoing.y > 0.0f ? 1.0f : 0.0f) * local_outgoing.y * kOneOverPi / adjust;
       q.density_rev = 0.0f;
       q.finite = 1;
       return q;
