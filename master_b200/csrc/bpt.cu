@@ -877,7 +877,8 @@ int ws_alloc(BptWorkspace* w, T** p, size_t count) {
 
 int bpt_workspace(b2pt_scene_s* scene, uint32_t size, uint32_t per_path, int lanes, BptWorkspace** out) {
   BptWorkspace* w = (BptWorkspace*)scene->workspace;
-  if (w && scene->workspace_free == bpt_workspace_free && w->size == size && w->per_path == per_path && w->lane[lanes - 1].counters) { *out = w; return B2PT_OK; }
+  // a workspace that is large enough is reused (b2pt_render_host ramps its batch sizes; start_batch sets the size a batch really uses)
+  if (w && scene->workspace_free == bpt_workspace_free && w->size >= size && w->per_path == per_path && w->lane[lanes - 1].counters) { *out = w; return B2PT_OK; }
   if (scene->workspace && scene->workspace_free) scene->workspace_free(scene->workspace);
   scene->workspace = nullptr;
   w = new BptWorkspace();

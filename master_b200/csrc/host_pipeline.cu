@@ -7,7 +7,7 @@
 // caller:
 //
 //   * a call for pass j of a sequence (same parameters, consecutive sample indices) is served from a batch of per-pass films
-//     [j, j + L) rendered in one go; L starts at a quarter of 2^24 / pixels passes (or what the call asks for, if that is more) and
+//     [j, j + L) rendered in one go; L starts at half of 2^24 / pixels passes (or what the call asks for, if that is more) and
 //     doubles per batch up to 2^24 / pixels — the batch size the integrators are efficient at — so a short run wastes little;
 //   * while the caller consumes batch A — device->host copy in chunks on a copy stream, each chunk added into the view by a pool of
 //     persistent host threads as it lands — a worker thread already renders batch B = [j + L, j + 2L) on its own streams;
@@ -295,7 +295,7 @@ extern "C" int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* para
       h->quiesce();
       int slot = h->batch[0].state == PassBatch::kEmpty ? 0 : 1;
       if (h->batch[slot].state != PassBatch::kEmpty) { h->batch[0].state = PassBatch::kEmpty; h->batch[1].state = PassBatch::kEmpty; slot = 0; }
-      const uint32_t size = std::min(per_batch, std::max(std::max(left, (look + 3u) / 4u), 2u * h->last_batch));
+      const uint32_t size = std::min(per_batch, std::max(std::max(left, (look + 1u) / 2u), 2u * h->last_batch));
       h->last_batch = size;
       pipeline_launch(h, slot, h->cursor, size);
       continue;

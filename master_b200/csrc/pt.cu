@@ -300,7 +300,8 @@ __global__ void __launch_bounds__(256) pt_shadow_kernel(RenderConfig cfg, PtPool
 // ---------------------------------------------------------------- host driver
 struct PtWorkspace {
   PtPool pool{};
-  uint32_t pool_size = 0;
+  uint32_t pool_size = 0;  // slots in use by the current call (<= capacity)
+  uint32_t capacity = 0;   // slots allocated: a call that needs no more reuses the pool (b2pt_render_host ramps its batch sizes)
   RenderCounters* counters = nullptr;
   RenderCounters* host_counters = nullptr;  // pinned
   void* blocks[24] = {nullptr};
@@ -351,7 +352,7 @@ static int pt_workspace(b2pt_scene_s* scene, int k, uint32_t pool_size, PtWorksp
     scene->workspace = set; scene->workspace_free = pt_workspace_set_free;
   }
   *out_set = set;
-  if (set->lane[k] && set->lane[k]->pool_size == pool_size) { *out = set->lane[k]; return B2PT_OK; }
+  if (set->lane[k] && set->lane[k]->capacity >= pool_size) { set->lane[k]->pool_size = pool_size; *out = set->lane[k]; return B2PT_OK; }
   if (set->lane[k]) { pt_workspace_free(set->lane[k]); set->lane[k] = nullptr; }
   set->lane[k] = new PtWorkspace();
   *out = set->lane[k];
@@ -359,7 +360,7 @@ static int pt_workspace(b2pt_scene_s* scene, int k, uint32_t pool_size, PtWorksp
 }
 
 static int pt_workspace_fill(PtWorkspace* w, uint32_t pool_size) {
-  w->pool_size = pool_size;
+  w->pool_size = pool_size; w->capacity = pool_size;
   int rc;
   if ((rc = ws_alloc(w, &w->pool.state, pool_size))) return rc;
   if ((rc = ws_alloc(w, &w->pool.ray_o, pool_size))) return rc;

@@ -30,9 +30,10 @@ def test_bpt_per_path_radiance_and_light_image(name, device_scenes, flat_scenes)
                           ref_rays=[info["basic_rays"], info["shadow_rays"]], capacity_events=stats["capacity_events"],
                           mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist())))
     assert stats["capacity_events"] == 0
-    # hits are bit-identical to Embree's and the transcendentals correctly rounded: (almost) no decision flips
-    assert frac >= 0.999
-    assert light_bad <= 0.005
+    # hits are bit-identical to Embree's and the transcendentals correctly rounded: measured 100 % on all seven scenes; a counted
+    # handful (1 path in 5 000) is allowed for the last bit of the host's libm
+    assert int((err > 1e-4).sum()) <= max(1, err.size // 5000)
+    assert light_bad <= 0.002
     assert np.all(accum[:, 3] + 0 == g["accum"][:, 3])
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=2e-3, atol=1e-5)
     assert image_rel_rmse(accum, g["accum"]) <= 2e-2
@@ -52,3 +53,23 @@ def test_bpt_pass_split_is_exact(device_scenes, flat_scenes):
     a, _, _ = gpu_render(sc, fl, "BPT", 32, 32, 2, 99, per_path=False, beta=2.0, first_sample=0, sample_stride=2)
     b, _, _ = gpu_render(sc, fl, "BPT", 32, 32, 2, 99, per_path=False, beta=2.0, first_sample=1, sample_stride=2)
     np.testing.assert_allclose(a + b, whole, rtol=1e-5, atol=1e-7)
+
+
+def test_long_paths_do_not_overflow_the_vertex_pool(device_scenes, flat_scenes):
+    """roulette 0.98 in a closed furnace: 50 stored light vertices per path on average.  The pool is sized from the roulette
+    (render_common.cuh: lv_per_path) and exhausting it is B2PT_ERR_CAPACITY, never a silently truncated subpath:
+    the call succeeds, nothing was dropped, and the furnace still averages to its analytic answer 1."""
+    sc, fl = device_scenes("TestCaseFurnace"), flat_scenes("TestCaseFurnace")
+    accum, _, stats = gpu_render(sc, fl, "BPT", 32, 32, 8, 3, per_path=False, beta=2.0, roulette=0.98)
+    mean = float((accum[:, :3].sum(axis=0) / accum[:, 3].sum()).mean())
+    print(json.dumps(dict(mean=mean, capacity_events=stats["capacity_events"], rays=[stats["num_basic_rays"], stats["num_shadow_rays"]])))
+    assert stats["capacity_events"] == 0 and np.all(accum[:, 3] == 8)
+    assert abs(mean - 1.0) < 0.05
+
+
+def test_exhausted_vertex_pool_is_an_error_not_a_biased_film(device_scenes, flat_scenes, monkeypatch):
+    from master_b200 import api
+    monkeypatch.setenv("B2PT_LV_PER_PATH", "1")  # one stored vertex per path on a scene that stores ten
+    with pytest.raises(api.B2ptError) as e:
+        gpu_render(device_scenes("CornellBoxDiffuse"), flat_scenes("CornellBoxDiffuse"), "BPT", 96, 96, 2, 3, per_path=False, beta=2.0)
+    assert e.value.code == 4 and "B2PT_LV_PER_PATH" in str(e.value)

@@ -31,8 +31,8 @@ def test_gpu_technique_behind_the_reference_interface(name, tech, tmp_path):
     scale = np.maximum(np.abs(ref[:, :3]).max(axis=1), 1e-6)
     close = (np.abs(accum[:, :3] - ref[:, :3]).max(axis=1) / scale <= 1e-4).mean()
     print(json.dumps(dict(scene=name, technique=tech, pixels_within_1e4=float(close), info=info)))
-    assert close >= 0.98
-    np.testing.assert_allclose(accum[:, :3].mean(axis=0), ref[:, :3].mean(axis=0), rtol=3e-2)
+    assert close >= 0.999  # measured 100 %: the same paths as the golden, summed per pixel
+    np.testing.assert_allclose(accum[:, :3].mean(axis=0), ref[:, :3].mean(axis=0), rtol=2e-3)
 
 
 def test_missing_scene_is_an_exception_not_a_crash():

@@ -60,7 +60,8 @@ def test_option_variant_per_path(name, tech, variant, device_scenes, flat_scenes
                           light_pixels_off=light_bad, rays=[stats["num_basic_rays"], stats["num_shadow_rays"]],
                           ref_rays=[info["basic_rays"], info["shadow_rays"]], mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist())))
     assert stats["capacity_events"] == 0
-    assert frac >= (0.999 if tech != "VCM" else 0.99)
+    flips = int((err > 1e-4).sum())
+    assert flips <= max(1, err.size // 5000) if tech != "VCM" else frac >= 0.995  # measured: 0 or 1 flips (PT, BPT); VCM 99.8 - 100 %
     assert light_bad <= 0.01
     assert np.array_equal(accum[:, 3], g["accum"][:, 3])
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=2e-3, atol=1e-5)

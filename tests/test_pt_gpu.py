@@ -48,8 +48,11 @@ def test_pt_per_path_radiance(name, device_scenes, flat_scenes):
     print(json.dumps(dict(scene=name, paths=int(err.size), within_1e4=frac, rays=[stats["num_basic_rays"], stats["num_shadow_rays"]],
                           ref_rays=[info["basic_rays"], info["shadow_rays"]], mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist())))
     # hits are bit-identical to Embree's (rcp_embree, trace.cuh) and the float transcendentals are evaluated in double
-    # (common.cuh: libm parity), so essentially every path takes the reference's decisions
-    assert frac >= 0.999
+    # (common.cuh: libm parity), so every path takes the reference's decisions: measured 100 % on all six scenes.  The assert
+    # allows a counted handful (1 path in 5 000) for the last bit of the host's libm, so a regression cannot hide
+    flips = int((err > 1e-4).sum())
+    print(json.dumps(dict(scene=name, flips=flips)))
+    assert flips <= max(1, err.size // 5000)
     assert np.all(accum[:, 3] == spp)
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=2e-3, atol=1e-5)
     # image level, equal spp, same streams: the films agree to 1 % relative RMSE (a single flipped path would show)

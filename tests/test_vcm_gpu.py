@@ -38,15 +38,17 @@ def test_vcm_per_path_radiance_and_light_image(name, tag, device_scenes, flat_sc
                           rays=[stats["num_basic_rays"], stats["num_shadow_rays"]], ref_rays=[info["basic_rays"], info["shadow_rays"]],
                           capacity_events=stats["capacity_events"], mean_ref=mean_ref.tolist(), mean_ours=mean_ours.tolist())))
     assert stats["capacity_events"] == 0
-    assert frac >= 0.99
+    assert frac >= 0.995  # measured 99.6 - 100 %: one flipped photon path changes every eye path that merges with it
     assert light_bad <= 0.01
     assert np.all(accum[:, 3] == g["accum"][:, 3])
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=2e-3, atol=1e-5)
     assert image_rel_rmse(accum, g["accum"]) <= 5e-2
 
 
-@pytest.mark.parametrize("name,tol,tag", [("CornellBoxDiffuse", 0.08, "UPG"), ("TestCaseFurnace", 0.06, "UPG"),
-                                          ("CornellBoxDiffuse", 0.08, "UPGc"), ("TestCaseFurnace", 0.06, "UPGc")])
+# 16 spp on 24^2 - 32^2 windows: a quick check in distribution (measured agreement 0.2 - 0.3 %); the bound that would catch a wrong MIS
+# weight is the 256-spp equal-image test of tests/test_options_gpu.py and the pinned density loop of tests/test_density_gpu.py
+@pytest.mark.parametrize("name,tol,tag", [("CornellBoxDiffuse", 0.03, "UPG"), ("TestCaseFurnace", 0.03, "UPG"),
+                                          ("CornellBoxDiffuse", 0.03, "UPGc"), ("TestCaseFurnace", 0.03, "UPGc")])
 def test_upg_image_mean_matches_reference(name, tol, tag, device_scenes, flat_scenes):
     g = np.load(golden_path("render_%s_%s.npz" % (name, tag)))
     w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
@@ -58,7 +60,7 @@ def test_upg_image_mean_matches_reference(name, tol, tag, device_scenes, flat_sc
     assert np.isfinite(accum).all() and np.all(accum[:, 3] == spp)
     np.testing.assert_allclose(mean_ours, mean_ref, rtol=tol)
     if name == "TestCaseFurnace":  # analytic answer: every pixel converges to 1
-        assert abs(mean_ours.mean() - 1.0) < 0.06
+        assert abs(mean_ours.mean() - 1.0) < 0.03
 
 
 def test_vcm_rejects_what_is_not_built(device_scenes, flat_scenes):
