@@ -952,7 +952,17 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   RenderConfig cfg = base;
   cfg.pool_size = size;
   const int grid = grid_for(size, block);
-  const int grid_t = persistent_grid(size, block);  // traversal stages: persistent warps fetch rays from a ticket counter
+  int grid_t = persistent_grid(size, block);  // traversal stages: persistent warps fetch rays from a ticket counter
+  // Co-residency experiment (A/B): B2PT_TRACE_CTAS=n caps the persistent traversal grids at n CTAs per SM (4 fill the register file),
+  // B2PT_SHADE_BLOCK=128 launches the shading stages with 128-thread CTAs, so that a shading CTA of the OTHER lane fits beside the
+  // traversal CTAs and the latency-bound shading overlaps the issue-bound traversal on the same SM.
+  int shade_block = block, shade_grid = grid;
+  { const char* e = getenv("B2PT_TRACE_CTAS"); if (e) { const int v = atoi(e); if (v >= 1 && v <= 8) grid_t = std::min(grid_t, kNumSMs * v); } }
+  { const char* e = getenv("B2PT_SHADE_BLOCK"); if (e) { const int v = atoi(e); if (v == 64 || v == 128) {
+      shade_block = v;
+      const size_t want = (size_t(size) + v - 1) / v, cap = size_t(kNumSMs) * 8 * (block / v);  // the same number of threads in flight
+      shade_grid = int(std::min(want < 1 ? size_t(1) : want, cap));
+  } } }
   // traversal form per stage: 0 = one ray per thread, 1 = persistent warps with dynamic fetch, 2 = the same plus postponed triangle
   // groups (trace.cuh: trace_dyn8).  B2PT_TRACE_STREAM / B2PT_SHADOW_STREAM select them for A/B runs; measured on the LivingRoom
   // stand-in with 2^23-path batches: closest-hit 2 / any-hit 2 = 79.4 Msamples/s against 76.3 for 0 / 0.
@@ -1005,8 +1015,8 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       StageTimer& timer = *timers[k];
       for (int j = 0; j < kBatchIters; ++j, ++g.it) {
         const int parity = g.it & 1;
-        timer.begin(kStageShade); bpt_logic_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays); timer.end();
-        timer.begin(kStageShade); bpt_connect_kernel<<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
+        timer.begin(kStageShade); bpt_logic_kernel<<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays); timer.end();
+        timer.begin(kStageShade); bpt_connect_kernel<<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);
           directional_kernel<<<grid, block, 0, l.stream>>>(cfg.scene, g.pool.dir_q, &l.counters->dir_count[parity], g.pool.size,
