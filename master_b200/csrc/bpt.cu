@@ -764,6 +764,7 @@ __global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(R
     cnt->light_count[parity ^ 1] = 0;
   }
   BptTraceIo io{&pool, sorted == 2 ? pool.oct_q : sorted == 1 ? pool.sort_q : pool.trace_q[parity], n_eye, sorted == 2 ? cnt->oct_count[parity] : nullptr};
+  if (kStream == 3) { trace_queue8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   if (kStream == 2) { trace_dyn8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   if (kStream == 1) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -778,6 +779,7 @@ __global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_shadow_kernel(
   const uint32_t n = min(cnt->shadow_count[parity], pool.q_capacity);
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->shadow_rays, (unsigned long long)n);
   BptShadowIo io{&pool};
+  if (kStream == 3) { trace_queue8<true>(cfg.scene, n, &cnt->ticket[1], io); return; }
   if (kStream == 2) { trace_dyn8<true>(cfg.scene, n, &cnt->ticket[1], io); return; }
   if (kStream == 1) { trace_stream8<true>(cfg.scene, n, &cnt->ticket[1], io); return; }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -964,12 +966,14 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       shade_grid = int(std::min(want < 1 ? size_t(1) : want, cap));
   } } }
   // traversal form per stage: 0 = one ray per thread, 1 = persistent warps with dynamic fetch, 2 = the same plus postponed triangle
-  // groups (trace.cuh: trace_dyn8).  B2PT_TRACE_STREAM / B2PT_SHADOW_STREAM select them for A/B runs; measured on the LivingRoom
-  // stand-in with 2^23-path batches: closest-hit 2 / any-hit 2 = 79.4 Msamples/s against 76.3 for 0 / 0.
+  // groups (trace.cuh: trace_dyn8), 3 = warp-synchronous rounds with a shared triangle queue (trace_queue8, the default).
+  // B2PT_TRACE_STREAM / B2PT_SHADOW_STREAM select them for A/B runs; measured on the LivingRoom stand-in with 2^23-path batches:
+  // 0 / 0 76.3, 2 / 2 79.8, 3 / 2 87.4, 2 / 3 83.2, 3 / 3 92.8 Msamples/s (closest-hit / any-hit stage).
   const char* tv = getenv("B2PT_TRACE_STREAM");
   const char* sv = getenv("B2PT_SHADOW_STREAM");
-  const int stream_trace = tv ? (tv[0] == '1' ? 1 : tv[0] == '0' ? 0 : 2) : 2;
-  const int stream_shadow = sv ? (sv[0] == '1' ? 1 : sv[0] == '0' ? 0 : 2) : stream_trace;
+  const bool queue_ok = cfg.scene.num_tris < (1u << 27);  // trace_queue8 packs (lane, triangle) into 32 bits
+  const int stream_trace = tv ? (tv[0] == '1' ? 1 : tv[0] == '0' ? 0 : tv[0] == '2' || !queue_ok ? 2 : 3) : (queue_ok ? 3 : 2);
+  const int stream_shadow = sv ? (sv[0] == '1' ? 1 : sv[0] == '0' ? 0 : sv[0] == '3' && queue_ok ? 3 : 2) : stream_trace;
   // ray sorting of the closest-hit queue (see ray_sort_key): B2PT_SORT_RAYS=0/1
   int sort_rays = bpt_sort_mode();
   if (sort_rays == 2 && !w->lane[0].pool.oct_q) sort_rays = 0;  // the workspace was built before the mode was switched on
@@ -1032,12 +1036,14 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
           timer.end();
         }
         timer.begin(kStageTrace);
-        if (stream_trace == 2) bpt_trace_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, sort_rays);
+        if (stream_trace == 3) bpt_trace_kernel<3><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, sort_rays);
+        else if (stream_trace == 2) bpt_trace_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, sort_rays);
         else if (stream_trace == 1) bpt_trace_kernel<1><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, sort_rays);
         else bpt_trace_kernel<0><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, sort_rays);
         timer.end();
         timer.begin(kStageShadow);
-        if (stream_shadow == 2) bpt_shadow_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        if (stream_shadow == 3) bpt_shadow_kernel<3><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else if (stream_shadow == 2) bpt_shadow_kernel<2><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         else if (stream_shadow == 1) bpt_shadow_kernel<1><<<grid_t, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         else bpt_shadow_kernel<0><<<grid, block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         timer.end();

@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
     // [parity ^ 1][trace / free] are this launch's inputs; the trace stage clears them afterwards
     cnt->queue_count[parity ^ 1][kQueueShadow] = 0;
     cnt->queue_count[parity][kQueueTicket] = 0;
+    cnt->shadow_ticket[parity] = 0;
   }
   const float beta = cfg.params.beta;
   const uint32_t max_path = cfg.params.max_path ? cfg.params.max_path : 0xFFFFFFFFu;
@@ -259,6 +260,18 @@ __global__ void __launch_bounds__(256, 4) pt_trace_dyn_kernel(RenderConfig cfg, 
   trace_dyn8<false>(cfg.scene, n, &cfg.counters->queue_count[parity][kQueueTicket], io);
 }
 
+// the same stage with a shared triangle queue per warp (trace.cuh: trace_queue8), the default
+__global__ void __launch_bounds__(256, 4) pt_trace_queue_kernel(RenderConfig cfg, PtPool pool, int parity) {
+  const uint32_t n = cfg.counters->queue_count[parity][kQueueTrace];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(&cfg.counters->basic_rays, (unsigned long long)n);
+    cfg.counters->queue_count[parity ^ 1][kQueueTrace] = 0;
+    cfg.counters->queue_count[parity ^ 1][kQueueFree] = 0;
+  }
+  PtTraceIo io{&pool, pool.trace_q[parity]};
+  trace_queue8<false>(cfg.scene, n, &cfg.counters->queue_count[parity][kQueueTicket], io);
+}
+
 __global__ void __launch_bounds__(256) pt_trace_kernel(RenderConfig cfg, PtPool pool, int parity) {
   const uint32_t n = cfg.counters->queue_count[parity][kQueueTrace];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -295,6 +308,45 @@ __global__ void __launch_bounds__(256) pt_shadow_kernel(RenderConfig cfg, PtPool
       pool.free_q[parity][warp_append(&cfg.counters->queue_count[parity][kQueueFree], true)] = slot;
     }
   }
+}
+
+// The any-hit stage through trace_queue8: entry i of the shadow queue is ray i; what the one-ray-per-thread kernel does after the
+// query (add the contribution if visible, commit the sample and free the slot if this was the path's last query) happens in store(),
+// whichever lanes of the warp finish in that round (warp_append works on the active lanes).
+struct PtShadowIo {
+  const RenderConfig* cfg;
+  const PtPool* pool;
+  int parity;
+  __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
+    const float4* e = pool->shadow_q + size_t(i) * 3;
+    const float4 o = e[0], d = e[1];
+    O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = 1.0f; mask = kMaskMesh;  // Scene::occluded (Scene.cpp:162-176)
+    return i;
+  }
+  __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
+    const float4* e = pool->shadow_q + size_t(i) * 3;
+    const uint32_t slot = __float_as_uint(e[0].w), flags = __float_as_uint(e[1].w);
+    const float4 c = e[2];
+    float4 r = pool->rad[slot];
+    if (h.tri == kInvalid) {
+      r.x += c.x; r.y += c.y; r.z += c.z;
+      if (!(flags & kShadowCommit)) pool->rad[slot] = r;
+    }
+    const bool commit = (flags & kShadowCommit) != 0u;
+    if (commit) {
+      commit_sample(*cfg, pool->work[slot], f3(r.x, r.y, r.z));
+      pool->state[slot] = kFree;
+    }
+    const unsigned fq = warp_append(&cfg->counters->queue_count[parity][kQueueFree], commit);
+    if (commit) pool->free_q[parity][fq] = slot;
+  }
+};
+
+__global__ void __launch_bounds__(256, 4) pt_shadow_queue_kernel(RenderConfig cfg, PtPool pool, int parity) {
+  const uint32_t n = cfg.counters->queue_count[parity][kQueueShadow];
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cfg.counters->shadow_rays, (unsigned long long)n);
+  PtShadowIo io{&cfg, &pool, parity};
+  trace_queue8<true>(cfg.scene, n, &cfg.counters->shadow_ticket[parity], io);
 }
 
 // ---------------------------------------------------------------- host driver
@@ -406,6 +458,8 @@ static int render_pt_lane(const RenderConfig& base, PtWorkspace* w, cudaStream_t
   // stand-in); B2PT_TRACE_STREAM=0 selects one ray per thread for A/B runs
   const char* tv = getenv("B2PT_TRACE_STREAM");
   const bool dyn_trace = !(tv && tv[0] == '0') && cfg.scene.nodes8;
+  // 3 (default) = shared triangle queue (trace_queue8) for both stages, 2 = trace_dyn8 for the closest-hit stage, 0 = one ray per thread
+  const bool queue_trace = dyn_trace && !(tv && tv[0] == '2') && cfg.scene.num_tris < (1u << 27);
   StageTimer timer(stream);
   const int kBatch = 8;  // stage iterations between two looks at the device counters
   for (int it = 0;; ) {
@@ -413,10 +467,14 @@ static int render_pt_lane(const RenderConfig& base, PtWorkspace* w, cudaStream_t
       const int parity = it & 1;
       timer.begin(kStageShade); pt_logic_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity, it == 0 ? 1 : 0); timer.end();
       timer.begin(kStageTrace);
-      if (dyn_trace) pt_trace_dyn_kernel<<<persistent_grid(cfg.pool_size, block), block, 0, stream>>>(cfg, w->pool, parity);
+      if (queue_trace) pt_trace_queue_kernel<<<persistent_grid(cfg.pool_size, block), block, 0, stream>>>(cfg, w->pool, parity);
+      else if (dyn_trace) pt_trace_dyn_kernel<<<persistent_grid(cfg.pool_size, block), block, 0, stream>>>(cfg, w->pool, parity);
       else pt_trace_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity);
       timer.end();
-      timer.begin(kStageShadow); pt_shadow_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity); timer.end();
+      timer.begin(kStageShadow);
+      if (queue_trace) pt_shadow_queue_kernel<<<persistent_grid(cfg.pool_size, block), block, 0, stream>>>(cfg, w->pool, parity);
+      else pt_shadow_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity);
+      timer.end();
     }
     B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(RenderCounters), cudaMemcpyDeviceToHost, stream));
     B2_CUDA(cudaStreamSynchronize(stream));

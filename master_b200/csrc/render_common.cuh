@@ -17,6 +17,7 @@ struct RenderCounters {
   unsigned long long capacity_events;
   unsigned int live_paths;            // paths in flight
   unsigned int queue_count[2][4];     // [iteration parity][queue id]
+  unsigned int shadow_ticket[2];      // ray ticket of the persistent any-hit stage, [iteration parity]
 };
 
 // Everything a stage kernel needs to know about the render call. Passed by value.

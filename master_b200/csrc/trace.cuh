@@ -456,6 +456,163 @@ __device__ __forceinline__ void trace_dyn8(const DeviceScene& sc, uint32_t n, un
   }
 }
 
+// ---------------------------------------------------------------- persistent warps, warp-synchronous rounds, a shared triangle queue
+//
+// In trace_dyn8 the leaf test — Embree's arithmetic, 28 % of the stage's warp instructions — runs with 6 of 32 lanes: at any moment
+// few lanes of a warp hold a triangle.  trace_queue8 separates WHO FINDS a triangle from WHO TESTS it.  Every round each lane with
+// node work advances one node (as in trace_stream8); the triangles its node test finds are not tested by the lane but appended as
+// (owner lane, triangle) items to a ring in shared memory, and whenever the ring holds 32 items the warp tests 32 of them at once,
+// lane i taking item i: the owner's ray is read from shared memory, a hit is merged into the owner's best hit with a 64-bit
+// atomicMin on (t bits, triangle).  A lane whose triangles are still queued goes on with its other nodes; its culling distance
+// lags by the queue's latency (a round or two), which costs a few node visits and never a hit.  The ring is drained to fewer than
+// 32 items before every node phase and a lane appends at most kEnqueuePerRound triangles per round, so it cannot overflow; when no
+// lane can advance a node the remainder is tested as a partial chunk.  The tests are the same ones in another order: a closest hit can
+// differ from trace_ray8's only where two triangles are hit at exactly the same distance (the smaller triangle index wins here).
+// Needs 256-thread CTAs (one WarpQueue per warp) and fewer than 2^27 triangle references.
+constexpr int kQueueItems = 512;
+constexpr int kEnqueuePerRound = 8;
+struct WarpQueue {
+  uint32_t items[kQueueItems];   // owner lane << 27 | triangle
+  float ray[8][32];              // Ox Oy Oz tnear Dx Dy Dz bits(mask), [field][owner lane]
+  unsigned long long best[32];   // bits(t) << 32 | triangle; low word kInvalid = no hit yet (t = the ray's tfar)
+  float2 uv[32];
+};
+
+template <bool kAnyHit, class Io>
+__device__ __forceinline__ void trace_queue8(const DeviceScene& sc, uint32_t n, unsigned* ticket, Io& io) {
+  __shared__ WarpQueue s_wq[8];
+  WarpQueue& q = s_wq[(threadIdx.x >> 5) & 7u];
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned lane_lt = (1u << lane) - 1u;
+  uint2 stack[kStack8];
+  int sp = 0;
+  uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
+  uint32_t tag = kInvalid, oct = 0u;
+  bool has_ray = false, exhausted = false;
+  float3 O = f3(0.f), idir = f3(0.f);
+  float tnear = 0.f;
+  uint32_t head = 0u, tail = 0u;  // items tested / appended so far (the same in every lane)
+  uint32_t my_last = 0u;          // tail after this lane's last append: its items are all tested once head >= my_last
+  for (;;) {
+    // ---- refill
+    const unsigned idle = __ballot_sync(kFullMask, !has_ray);
+    if (!exhausted && __popc(idle) >= kFetchMin8) {
+      const unsigned cnt = __popc(idle);
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(ticket, cnt);
+      base = __shfl_sync(kFullMask, base, 0);
+      exhausted = base + cnt >= n;
+      if (!has_ray) {
+        const uint32_t i = base + __popc(idle & lane_lt);
+        if (i < n) {
+          float tfar; float3 D; uint32_t ray_mask;
+          tag = io.load(i, O, D, tnear, tfar, ray_mask);
+          const float kHuge = 1e24f;  // node8_step adds 2^15 grid steps to the plane offsets: keep that finite
+          idir = f3(fabsf(D.x) > 1e-24f ? 1.0f / D.x : copysignf(kHuge, D.x),
+                    fabsf(D.y) > 1e-24f ? 1.0f / D.y : copysignf(kHuge, D.y),
+                    fabsf(D.z) > 1e-24f ? 1.0f / D.z : copysignf(kHuge, D.z));
+          oct = (idir.x >= 0.0f ? 1u : 0u) | (idir.y >= 0.0f ? 2u : 0u) | (idir.z >= 0.0f ? 4u : 0u);
+          sp = 0;
+          G = make_uint2(0u, (1u << (24u + oct)) | 1u);
+          T = make_uint2(0u, 0u);
+          q.ray[0][lane] = O.x; q.ray[1][lane] = O.y; q.ray[2][lane] = O.z; q.ray[3][lane] = tnear;
+          q.ray[4][lane] = D.x; q.ray[5][lane] = D.y; q.ray[6][lane] = D.z; q.ray[7][lane] = __uint_as_float(ray_mask);
+          q.best[lane] = ((unsigned long long)__float_as_uint(tfar) << 32) | 0xFFFFFFFFull;
+          q.uv[lane] = make_float2(0.f, 0.f);
+          my_last = head;
+          has_ray = true;
+        }
+      }
+    }
+    __syncwarp();
+    if (__ballot_sync(kFullMask, has_ray) == 0u) {
+      if (exhausted) break;
+      continue;
+    }
+    // ---- node phase: one node per lane; its triangles go to the ring
+    bool advanced = false;
+    unsigned want = 0;
+    if (has_ray) {
+      const unsigned long long b = q.best[lane];
+      if (kAnyHit && uint32_t(b) != kInvalid) { G.y = 0u; T.y = 0u; sp = 0; }  // occluded: nothing left to look at
+      else {
+        if (T.y == 0u) {
+          if (!(G.y & 0xFF000000u) && sp > 0) G = stack[--sp];
+          if (G.y & 0xFF000000u) {
+            const int pos = 31 - __clz(int(G.y));
+            G.y &= ~(1u << pos);
+            const uint32_t slot = uint32_t(pos - 24) ^ oct;
+            const uint32_t child = G.x + __popc(G.y & 0xFFu & ((1u << slot) - 1u));
+            if (G.y & 0xFF000000u) { if (sp < kStack8) stack[sp++] = G; else atomicOr(sc.error_flags, 1u); }
+            node8_step(sc, child, O, idir, oct, tnear, __uint_as_float(uint32_t(b >> 32)), G, T);
+            advanced = true;
+          }
+        }
+        want = min(unsigned(__popc(T.y)), unsigned(kEnqueuePerRound));
+      }
+    }
+    unsigned incl = want;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t = __shfl_up_sync(kFullMask, incl, o);
+      if (lane >= unsigned(o)) incl += t;
+    }
+    const unsigned total = __shfl_sync(kFullMask, incl, 31);
+    if (want) {
+      uint32_t at = tail + incl - want;
+      for (unsigned k = 0; k < want; ++k, ++at) {
+        const uint32_t j = uint32_t(__ffs(int(T.y)) - 1);
+        T.y &= T.y - 1u;
+        q.items[at & uint32_t(kQueueItems - 1)] = (lane << 27) | (T.x + j);
+      }
+      my_last = at;
+    }
+    tail += total;
+    const unsigned any_advanced = __ballot_sync(kFullMask, advanced);
+    __syncwarp();
+    // ---- triangle phase: 32 items at a time; what is left when no lane could advance a node
+    // (a partial chunk also when so few lanes advanced a node that waiting for 32 items would leave the warp mostly idle)
+    while (tail - head >= 32u || (tail != head && __popc(any_advanced) < sc.queue_drain_lanes)) {
+      const uint32_t m = min(32u, tail - head);
+      bool hit = false;
+      unsigned long long key = 0ull;
+      uint32_t owner = 0u;
+      float u = 0.f, v = 0.f;
+      if (lane < m) {
+        const uint32_t item = q.items[(head + lane) & uint32_t(kQueueItems - 1)];
+        owner = item >> 27;
+        const uint32_t tri = item & 0x07FFFFFFu;
+        const unsigned long long b = q.best[owner];
+        if (!(kAnyHit && uint32_t(b) != kInvalid)) {
+          const float3 Oo = f3(q.ray[0][owner], q.ray[1][owner], q.ray[2][owner]);
+          const float3 Do = f3(q.ray[4][owner], q.ray[5][owner], q.ray[6][owner]);
+          float t = __uint_as_float(uint32_t(b >> 32));
+          if (intersect_triangle(sc, tri, Oo, Do, q.ray[3][owner], t, u, v, __float_as_uint(q.ray[7][owner]))) {
+            hit = true;
+            key = ((unsigned long long)__float_as_uint(t) << 32) | tri;
+            atomicMin(&q.best[owner], key);
+          }
+        }
+      }
+      __syncwarp();
+      if (hit && q.best[owner] == key) q.uv[owner] = make_float2(u, v);
+      head += m;
+      __syncwarp();
+      if (m < 32u) break;
+    }
+    // ---- a ray with nothing left, and all of its items tested, hands its hit over
+    if (has_ray && T.y == 0u && !(G.y & 0xFF000000u) && sp == 0 && int(head - my_last) >= 0) {
+      const unsigned long long b = q.best[lane];
+      Hit h;
+      h.t = __uint_as_float(uint32_t(b >> 32)); h.tri = uint32_t(b);
+      const float2 uv = q.uv[lane];
+      h.u = uv.x; h.v = uv.y;
+      io.store(tag, h);
+      has_ray = false;
+    }
+  }
+}
+
 template <bool kAnyHit>
 __device__ __forceinline__ Hit trace_any_bvh(const DeviceScene& sc, float3 O, float3 D, float tnear, float tfar, uint32_t ray_mask) {
 #ifdef B2PT_EXPERIMENTS

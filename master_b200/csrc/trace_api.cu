@@ -49,6 +49,14 @@ __global__ void __launch_bounds__(256, 4) trace_dyn8_kernel(DeviceScene sc, cons
   trace_dyn8<kAnyHit>(sc, n, ticket, io);
 }
 
+// persistent warps, warp-synchronous rounds, shared triangle queue (trace.cuh: trace_queue8); B2PT_TRACE_STREAM=3
+template <bool kAnyHit, bool kMeshOnly>
+__global__ void __launch_bounds__(256, 4) trace_queue8_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
+                                                              B2ptHit* __restrict__ hits, unsigned* ticket) {
+  ApiIo<kAnyHit, kMeshOnly> io{&sc, rays, hits};
+  trace_queue8<kAnyHit>(sc, n, ticket, io);
+}
+
 // one ray per thread, run to completion (trace.cuh: trace_ray8): the default
 template <bool kAnyHit, bool kMeshOnly>
 __global__ void __launch_bounds__(256, 5) trace_rays_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
@@ -70,14 +78,23 @@ int launch_trace(b2pt_scene_s* scene, const B2ptRay* rays, size_t n, unsigned mo
   scene_l2_window(scene, stream);
   const float4* r = reinterpret_cast<const float4*>(rays);
   const char* stream_env = getenv("B2PT_TRACE_STREAM");  // 1: persistent warp-synchronous traversal (wins on >= 4 M incoherent rays)
-  if (!(stream_env && (stream_env[0] == '1' || stream_env[0] == '2')) || !sc.nodes8) {
+  if (!(stream_env && (stream_env[0] == '1' || stream_env[0] == '2' || stream_env[0] == '3')) || !sc.nodes8) {
     const int grid = grid_for_trace(n, block);
     switch (mode) {
       case B2PT_TRACE_CLOSEST_ALL: trace_rays_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
       case B2PT_TRACE_CLOSEST_MESH: trace_rays_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
       default: trace_rays_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
     }
-  } else if (stream_env[0] == '2') {
+  } else if (stream_env[0] == '3' && sc.num_tris < (1u << 27)) {
+    unsigned* ticket = scene->dev.error_flags + 1;
+    B2_CUDA(cudaMemsetAsync(ticket, 0, 4, stream));
+    const int grid = persistent_grid(n, block);
+    switch (mode) {
+      case B2PT_TRACE_CLOSEST_ALL: trace_queue8_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+      case B2PT_TRACE_CLOSEST_MESH: trace_queue8_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+      default: trace_queue8_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits, ticket); break;
+    }
+  } else if (stream_env[0] == '2' || stream_env[0] == '3') {
     unsigned* ticket = scene->dev.error_flags + 1;
     B2_CUDA(cudaMemsetAsync(ticket, 0, 4, stream));
     const int grid = persistent_grid(n, block);
