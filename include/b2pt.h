@@ -198,7 +198,10 @@ int b2pt_scene_info(b2pt_scene_t scene, uint64_t* num_triangles, uint64_t* num_n
 
 /* rays / hits in HOST memory; copies both ways */
 int b2pt_trace(b2pt_scene_t scene, const B2ptRay* rays, size_t n, unsigned mode, B2ptHit* hits);
-/* rays / hits already in DEVICE memory; asynchronous on `stream` (a cudaStream_t, may be NULL) */
+/* rays / hits already in DEVICE memory; asynchronous on `stream` (a cudaStream_t, may be NULL).  Batches of >= 2^18 rays run
+   as persistent warps that fetch rays through ONE counter owned by the scene: calls on the same scene must be ordered with
+   each other (same stream, or events between streams).  When two triangles are hit at exactly the same distance such a batch
+   reports the one with the smaller position in the scene's leaf order; a small batch reports the one traversal met first. */
 int b2pt_trace_device(b2pt_scene_t scene, const B2ptRay* rays_dev, size_t n, unsigned mode,
                       B2ptHit* hits_dev, void* stream);
 

@@ -992,6 +992,8 @@ static int build_scene(const B2ptSceneDesc* d, b2pt_scene_s* s) {
   { const char* e = getenv("B2PT_DYN_FETCH"); if (e) ds.dyn_fetch_lanes = atoi(e); }
   { const char* e = getenv("B2PT_DYN_TRI"); if (e) ds.dyn_tri_lanes = atoi(e); }
   { const char* e = getenv("B2PT_QUEUE_DRAIN"); if (e) ds.queue_drain_lanes = atoi(e); }
+  { const char* e = getenv("B2PT_QUEUE_CHUNK"); if (e && atoi(e) >= 32) ds.queue_chunk = atoi(e); }
+  { const char* e = getenv("B2PT_QUEUE_FETCH"); if (e && atoi(e) >= 1 && atoi(e) <= 32) ds.queue_fetch_lanes = atoi(e); }
   for (uint32_t k = 0; k < L; ++k) if (d->lights[k].diffuse == 0.0f) ds.has_directional = 1u;
   s->bvh_bytes = uint64_t(num_wide) * (nodes8 ? 5 : kNodeFloat4s) * 16 + uint64_t(n) * kTriFloat4s * 16;
   // ---- L2 residency (north_star: "top BVH levels staged in shared memory / L2"): set aside as much persisting L2 as the device

@@ -59,6 +59,8 @@ struct DeviceScene {
   // scheduling thresholds of trace_dyn8 (trace.cuh); B2PT_DYN_FETCH / B2PT_DYN_TRI override them for A/B runs
   int dyn_fetch_lanes = 20;
   int dyn_tri_lanes = 8;
+  int queue_fetch_lanes = 8;   // trace_queue8: idle lanes of a warp that trigger a refill (B2PT_QUEUE_FETCH)
+  int queue_chunk = 128;       // trace_queue8: tickets a warp reserves per atomic (B2PT_QUEUE_CHUNK)
   int queue_drain_lanes = 12;  // trace_queue8: a partial chunk of the triangle ring is tested when fewer lanes than this advanced a node (B2PT_QUEUE_DRAIN)
 };
 

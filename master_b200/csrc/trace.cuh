@@ -56,12 +56,16 @@ __device__ __forceinline__ float rcp_embree(float a) {  // a > 0
 
 // Returns true and updates (tfar, u, v) when triangle `pos` is hit inside (tnear, tfar).
 // ray_mask: RTCRay::mask — 0xFFFFFFFF (Scene::intersect) or 1 << entity_type::mesh (intersectMesh / occluded).
-__device__ __forceinline__ bool intersect_triangle(const DeviceScene& sc, uint32_t pos, float3 O, float3 D, float tnear,
-                                                   float& tfar, float& u, float& v, uint32_t ray_mask) {
+struct TriData { float4 q0, q1, q2; };
+__device__ __forceinline__ TriData tri_load(const DeviceScene& sc, uint32_t pos) {
   const float4* tr = sc.tris + size_t(pos) * kTriFloat4s;
-  const float4 q0 = __ldg(tr + 0);
-  const float4 q1 = __ldg(tr + 1);
-  const float4 q2 = __ldg(tr + 2);
+  TriData d;
+  d.q0 = __ldg(tr + 0); d.q1 = __ldg(tr + 1); d.q2 = __ldg(tr + 2);
+  return d;
+}
+__device__ __forceinline__ bool intersect_triangle_data(const TriData& d, float3 O, float3 D, float tnear,
+                                                        float& tfar, float& u, float& v, uint32_t ray_mask) {
+  const float4 q0 = d.q0, q1 = d.q1, q2 = d.q2;
   // geometry mask = 1 << (material_id & 3) (rtcSetMask, Scene.cpp:47); Embree skips the triangle when (mask & ray.mask) == 0
   if ((__float_as_uint(q2.w) & ray_mask) == 0u) return false;
   const float3 v0 = f3(q0.x, q0.y, q0.z), e1 = f3(q1.x, q1.y, q1.z), e2 = f3(q2.x, q2.y, q2.z);
@@ -81,6 +85,11 @@ __device__ __forceinline__ bool intersect_triangle(const DeviceScene& sc, uint32
   u = __fmul_rn(U, rcpAbsDen);
   v = __fmul_rn(V, rcpAbsDen);
   return true;
+}
+__device__ __forceinline__ bool intersect_triangle(const DeviceScene& sc, uint32_t pos, float3 O, float3 D, float tnear,
+                                                   float& tfar, float& u, float& v, uint32_t ray_mask) {
+  const TriData d = tri_load(sc, pos);
+  return intersect_triangle_data(d, O, D, tnear, tfar, u, v, ray_mask);
 }
 
 __device__ __forceinline__ void cswap(float& ta, uint32_t& ca, float& tb, uint32_t& cb) {
@@ -155,11 +164,16 @@ __device__ __forceinline__ Hit trace_ray_masked(const DeviceScene& sc, float3 O,
 // ---------------------------------------------------------------- compressed 8-wide BVH (layout: bvh8.cuh)
 // One node of the compressed 8-wide tree against one ray: five 128-bit loads, eight quantised slab tests, and the
 // hit children split into a node group G (inner children, priority-ordered hit bits | imask) and a triangle group T.
-__device__ __forceinline__ void node8_step(const DeviceScene& sc, uint32_t child, float3 O, float3 idir, uint32_t oct, float tnear, float tmax,
-                                           uint2& G, uint2& T) {
-  struct { float t; } hit = {tmax};
+struct Node8Data { float4 n0, n1, n2, n3, n4; };
+__device__ __forceinline__ Node8Data node8_load(const DeviceScene& sc, uint32_t child) {
   const float4* nd = sc.nodes8 + size_t(child) * kNode8Float4s;
-  const float4 n0 = __ldg(nd + 0), n1 = __ldg(nd + 1), n2 = __ldg(nd + 2), n3 = __ldg(nd + 3), n4 = __ldg(nd + 4);
+  Node8Data d;
+  d.n0 = __ldg(nd + 0); d.n1 = __ldg(nd + 1); d.n2 = __ldg(nd + 2); d.n3 = __ldg(nd + 3); d.n4 = __ldg(nd + 4);
+  return d;
+}
+__device__ __forceinline__ void node8_test(const Node8Data& d, float3 O, float3 idir, uint32_t oct, float tnear, float tmax, uint2& G, uint2& T) {
+  struct { float t; } hit = {tmax};
+  const float4 n0 = d.n0, n1 = d.n1, n2 = d.n2, n3 = d.n3, n4 = d.n4;
   const uint32_t hdr = __float_as_uint(n0.w);
   const uint32_t imask = hdr >> 24;
   // grid step 2^e per axis (biased exponents), folded into the reciprocal direction; origin of the grid relative to the ray
@@ -207,6 +221,11 @@ __device__ __forceinline__ void node8_step(const DeviceScene& sc, uint32_t child
   const uint32_t ghits = hits & 0xFF000000u, tmask = hits & 0x00FFFFFFu;
   G = make_uint2(__float_as_uint(n1.x), ghits | imask);
   T = make_uint2(__float_as_uint(n1.y), tmask);
+}
+__device__ __forceinline__ void node8_step(const DeviceScene& sc, uint32_t child, float3 O, float3 idir, uint32_t oct, float tnear, float tmax,
+                                           uint2& G, uint2& T) {
+  const Node8Data d = node8_load(sc, child);
+  node8_test(d, O, idir, oct, tnear, tmax, G, T);
 }
 
 // kCount (b2pt_debug_trace_counts): counts->x += node steps, counts->y += triangle tests of this ray
@@ -488,23 +507,38 @@ __device__ __forceinline__ void trace_queue8(const DeviceScene& sc, uint32_t n, 
   int sp = 0;
   uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
   uint32_t tag = kInvalid, oct = 0u;
-  bool has_ray = false, exhausted = false;
+  bool has_ray = false, exhausted = false;  // exhausted: the global counter has passed n (this warp may still hold tickets)
   float3 O = f3(0.f), idir = f3(0.f);
   float tnear = 0.f;
   uint32_t head = 0u, tail = 0u;  // items tested / appended so far (the same in every lane)
   uint32_t my_last = 0u;          // tail after this lane's last append: its items are all tested once head >= my_last
+  // Tickets are reserved `chunk` at a time and handed out from the warp's own range [next, end): one atomic per refill on ONE address
+  // was the any-hit stage's largest stall (28 % of its warp samples, ncu r02 s17) — 3.5 M short rays per ms are ~350 refills per us.
+  uint32_t next = 0u, end = 0u;
+  const unsigned chunk = max(32u, min(unsigned(sc.queue_chunk), n / (gridDim.x * 32u)));
   for (;;) {
     // ---- refill
     const unsigned idle = __ballot_sync(kFullMask, !has_ray);
-    if (!exhausted && __popc(idle) >= kFetchMin8) {
-      const unsigned cnt = __popc(idle);
-      unsigned base = 0;
-      if (lane == 0) base = atomicAdd(ticket, cnt);
-      base = __shfl_sync(kFullMask, base, 0);
-      exhausted = base + cnt >= n;
-      if (!has_ray) {
-        const uint32_t i = base + __popc(idle & lane_lt);
-        if (i < n) {
+    const unsigned cnt = __popc(idle);
+    if (cnt >= unsigned(sc.queue_fetch_lanes) && (!exhausted || next != end)) {
+      const unsigned avail = end - next;
+      const unsigned r = __popc(idle & lane_lt);
+      uint32_t i = next + r;
+      bool mine = !has_ray && r < avail;
+      if (avail < cnt && !exhausted) {
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(ticket, chunk);
+        base = __shfl_sync(kFullMask, base, 0);
+        if (r >= avail) { i = base + (r - avail); mine = !has_ray && i < n; }
+        exhausted = base + chunk >= n;
+        end = min(base + chunk, n);
+        next = min(base + (cnt - avail), end);
+        if (base >= n) next = end = 0u;
+      } else {
+        next += min(cnt, avail);
+      }
+      if (mine) {
+        {
           float tfar; float3 D; uint32_t ray_mask;
           tag = io.load(i, O, D, tnear, tfar, ray_mask);
           const float kHuge = 1e24f;  // node8_step adds 2^15 grid steps to the plane offsets: keep that finite
@@ -526,7 +560,7 @@ __device__ __forceinline__ void trace_queue8(const DeviceScene& sc, uint32_t n, 
     }
     __syncwarp();
     if (__ballot_sync(kFullMask, has_ray) == 0u) {
-      if (exhausted) break;
+      if (exhausted && next == end) break;
       continue;
     }
     // ---- node phase: one node per lane; its triangles go to the ring

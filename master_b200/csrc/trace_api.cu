@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(256, 4) trace_queue8_kernel(DeviceScene sc, co
   trace_queue8<kAnyHit>(sc, n, ticket, io);
 }
 
-// one ray per thread, run to completion (trace.cuh: trace_ray8): the default
+// one ray per thread, run to completion (trace.cuh: trace_ray8): small batches
 template <bool kAnyHit, bool kMeshOnly>
 __global__ void __launch_bounds__(256, 5) trace_rays_kernel(DeviceScene sc, const float4* __restrict__ rays, uint32_t n,
                                                             B2ptHit* __restrict__ hits) {
@@ -77,15 +77,21 @@ int launch_trace(b2pt_scene_s* scene, const B2ptRay* rays, size_t n, unsigned mo
   const int block = 256;
   scene_l2_window(scene, stream);
   const float4* r = reinterpret_cast<const float4*>(rays);
-  const char* stream_env = getenv("B2PT_TRACE_STREAM");  // 1: persistent warp-synchronous traversal (wins on >= 4 M incoherent rays)
-  if (!(stream_env && (stream_env[0] == '1' || stream_env[0] == '2' || stream_env[0] == '3')) || !sc.nodes8) {
+  // The default is trace_queue8 for batches that fill the persistent grid a few times over, one ray per thread below that;
+  // B2PT_TRACE_STREAM = 0 | 1 | 2 | 3 forces one form (A/B: tools/trace_bench.py)
+  const char* env = getenv("B2PT_TRACE_STREAM");
+  const bool queue_ok = sc.nodes8 && sc.num_tris < (1u << 27);
+  char form[2] = {env ? env[0] : (queue_ok && n >= (size_t(1) << 18) ? '3' : '0'), 0};
+  if (form[0] == '3' && !queue_ok) form[0] = '2';
+  const char* stream_env = form;
+  if (!(stream_env[0] == '1' || stream_env[0] == '2' || stream_env[0] == '3') || !sc.nodes8) {
     const int grid = grid_for_trace(n, block);
     switch (mode) {
       case B2PT_TRACE_CLOSEST_ALL: trace_rays_kernel<false, false><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
       case B2PT_TRACE_CLOSEST_MESH: trace_rays_kernel<false, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
       default: trace_rays_kernel<true, true><<<grid, block, 0, stream>>>(sc, r, uint32_t(n), hits); break;
     }
-  } else if (stream_env[0] == '3' && sc.num_tris < (1u << 27)) {
+  } else if (stream_env[0] == '3') {
     unsigned* ticket = scene->dev.error_flags + 1;
     B2_CUDA(cudaMemsetAsync(ticket, 0, 4, stream));
     const int grid = persistent_grid(n, block);

@@ -52,6 +52,7 @@ struct VcmCounters {
   unsigned int wide_count;               // UPG: density loops handed to the whole grid (upg_density_wide_kernel)
   unsigned int job_count, job_ticket;  // UPG: merges whose density is still to be estimated, and the fetch counter of the stage that does it
   unsigned int ray_ticket;             // ray fetch counter of the persistent closest-hit stages, zeroed by the logic stage before them
+  unsigned int shadow_ticket;          // the same of the persistent any-hit stage, zeroed by the eye stage
 };
 
 // the per-pass constants of UPGBase (UPG.hpp:119-137)
@@ -411,8 +412,9 @@ struct VcmTraceIo {
   }
   __device__ __forceinline__ void store(uint32_t slot, const Hit& h) const { hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri)); }
 };
-// kPhoton: light subpaths (Scene::intersectMesh), else eye subpaths (Scene::intersect); persistent warps, dynamic fetch
-template <bool kPhoton>
+// kPhoton: light subpaths (Scene::intersectMesh), else eye subpaths (Scene::intersect); persistent warps, dynamic fetch;
+// kQueue: trace_queue8 (the default), else trace_dyn8
+template <bool kPhoton, bool kQueue>
 __global__ void __launch_bounds__(256, 4) vcm_trace_dyn_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
   const uint32_t n = cnt->trace_count[parity];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -421,7 +423,8 @@ __global__ void __launch_bounds__(256, 4) vcm_trace_dyn_kernel(RenderConfig cfg,
   }
   VcmTraceIo io{pool.trace_q[parity], kPhoton ? pool.p_ray_o : pool.ray_o, kPhoton ? pool.p_bs_omega : pool.bs_omega,
                 kPhoton ? pool.p_hit : pool.hit, kPhoton ? kMaskMesh : kMaskAll};
-  trace_dyn8<false>(cfg.scene, n, &cnt->ray_ticket, io);
+  if (kQueue) trace_queue8<false>(cfg.scene, n, &cnt->ray_ticket, io);
+  else trace_dyn8<false>(cfg.scene, n, &cnt->ray_ticket, io);
 }
 
 __global__ void __launch_bounds__(256) vcm_photon_trace_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
@@ -466,7 +469,7 @@ __global__ void __launch_bounds__(256) vcm_eye_kernel(RenderConfig cfg, VcmParam
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     cnt->pair_count[parity ^ 1] = 0; cnt->merge_count = 0; cnt->job_count = 0; cnt->job_ticket = 0; cnt->long_count = 0; cnt->long_ticket = 0; cnt->wide_count = 0;
     cnt->shadow_count[parity ^ 1] = 0; cnt->gather_count[parity ^ 1] = 0; cnt->dir_count[parity ^ 1] = 0;
-    cnt->ray_ticket = 0;
+    cnt->ray_ticket = 0; cnt->shadow_ticket = 0;
   }
   const float beta = P.beta;
   const uint32_t n_live = first ? pool.pixels_pad : cnt->trace_count[parity ^ 1];
@@ -757,6 +760,37 @@ __global__ void __launch_bounds__(256) vcm_shadow_kernel(RenderConfig cfg, VcmPo
       }
     }
   }
+}
+
+// the any-hit stage through trace_queue8: entry i of the shadow queue is ray i, an unoccluded one adds its contribution
+struct VcmShadowIo {
+  const float4* shadow_q;
+  double* splat; float4* rad;
+  __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& m) const {
+    const float4* e = shadow_q + size_t(i) * 3;
+    const float4 o = e[0], d = e[1];
+    O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = 1.0f; m = kMaskMesh;
+    return i;
+  }
+  __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
+    if (h.tri != kInvalid) return;
+    const float4* e = shadow_q + size_t(i) * 3;
+    const float4 c = e[2];
+    const uint32_t target = __float_as_uint(e[0].w), flags = __float_as_uint(e[1].w);
+    if (flags & kShadowSplat) {
+      double* s = splat + size_t(target) * 3;
+      atomicAdd(s + 0, double(c.x)); atomicAdd(s + 1, double(c.y)); atomicAdd(s + 2, double(c.z));
+    } else {
+      float* r = &rad[target].x;
+      atomicAdd(r + 0, c.x); atomicAdd(r + 1, c.y); atomicAdd(r + 2, c.z);
+    }
+  }
+};
+__global__ void __launch_bounds__(256, 4) vcm_shadow_queue_kernel(RenderConfig cfg, VcmPool pool, VcmCounters* cnt, int parity) {
+  const uint32_t n = min(cnt->shadow_count[parity], pool.q_capacity);
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->shadow_rays, (unsigned long long)n);
+  VcmShadowIo io{pool.shadow_q, pool.splat, pool.rad};
+  trace_queue8<true>(cfg.scene, n, &cnt->shadow_ticket, io);
 }
 
 // ---------------------------------------------------------------- merging stage
@@ -1415,8 +1449,10 @@ static int vcm_run_passes(const RenderConfig& base, VcmWorkspace* w, cudaStream_
   const int kBatchIters = 8;
   const uint32_t stride = rp.sample_stride ? rp.sample_stride : 1u;
   const int grid_p = grid_for(pool.photons, block), grid_e = grid_for(pool.pixels_pad, block);
-  // closest-hit stages through trace_dyn8 when B2PT_TRACE_STREAM=2 (A/B)
+  // traversal stages: trace_queue8 (persistent warps, shared triangle queue; the default), B2PT_TRACE_STREAM=2 closest-hit stages
+  // through trace_dyn8, =0 one ray per thread (A/B)
   const char* tv = getenv("B2PT_TRACE_STREAM");
+  const bool queue_trace = cfg.scene.nodes8 && cfg.scene.num_tris < (1u << 27) && !(tv && (tv[0] == '0' || tv[0] == '2'));
   const bool dyn_trace = tv && tv[0] == '2' && cfg.scene.nodes8;
   for (uint32_t pass = first; pass < rp.num_samples; pass += step) {
     const uint32_t sample = rp.first_sample + pass * stride;
@@ -1441,7 +1477,8 @@ static int vcm_run_passes(const RenderConfig& base, VcmWorkspace* w, cudaStream_
         const int parity = it & 1;
         timer.begin(kStageShade); vcm_photon_kernel<<<grid_p, block, 0, stream>>>(cfg, P, pool, w->counters, parity, sample, it == 0 ? 1 : 0); timer.end();
         timer.begin(kStageTrace);
-        if (dyn_trace) vcm_trace_dyn_kernel<true><<<persistent_grid(pool.photons, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
+        if (queue_trace) vcm_trace_dyn_kernel<true, true><<<persistent_grid(pool.photons, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
+        else if (dyn_trace) vcm_trace_dyn_kernel<true, false><<<persistent_grid(pool.photons, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
         else vcm_photon_trace_kernel<<<grid_p, block, 0, stream>>>(cfg, pool, w->counters, parity);
         timer.end();
       }
@@ -1482,10 +1519,14 @@ static int vcm_run_passes(const RenderConfig& base, VcmWorkspace* w, cudaStream_
           timer.end();
         }
         timer.begin(kStageTrace);
-        if (dyn_trace) vcm_trace_dyn_kernel<false><<<persistent_grid(pool.pixels_pad, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
+        if (queue_trace) vcm_trace_dyn_kernel<false, true><<<persistent_grid(pool.pixels_pad, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
+        else if (dyn_trace) vcm_trace_dyn_kernel<false, false><<<persistent_grid(pool.pixels_pad, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
         else vcm_trace_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity);
         timer.end();
-        timer.begin(kStageShadow); vcm_shadow_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity); timer.end();
+        timer.begin(kStageShadow);
+        if (queue_trace) vcm_shadow_queue_kernel<<<persistent_grid(pool.q_capacity, block), block, 0, stream>>>(cfg, pool, w->counters, parity);
+        else vcm_shadow_kernel<<<grid_e, block, 0, stream>>>(cfg, pool, w->counters, parity);
+        timer.end();
       }
       B2_CUDA(cudaMemcpyAsync(w->host_counters, w->counters, sizeof(VcmCounters), cudaMemcpyDeviceToHost, stream));
       B2_CUDA(cudaStreamSynchronize(stream));

@@ -58,10 +58,11 @@ def test_livingroom_live_embree_parity_1m(large, tmp_path):
     agree = (occ["geom"] == sets["shadow_hits"]["geom"]).mean()
     print(json.dumps(dict(what="LivingRoom 1M shadow", rays=len(occ), agree=float(agree))))
     assert agree >= 0.9999
-    # the persistent traversal the integrators use (trace_dyn8) returns the same hits as one ray per thread
-    os.environ["B2PT_TRACE_STREAM"] = "2"
+    # batches of this size run through trace_queue8 (the integrators' traversal); one ray per thread and trace_dyn8 return the same hits
     try:
-        compare_closest(scene.trace(sets["bounce_rays"], api.TRACE_CLOSEST_ALL), sets["bounce_hits"], "LivingRoom 1M bounce/all dyn8")
+        for form, label in (("0", "one ray per thread"), ("2", "dyn8")):
+            os.environ["B2PT_TRACE_STREAM"] = form
+            compare_closest(scene.trace(sets["bounce_rays"], api.TRACE_CLOSEST_ALL), sets["bounce_hits"], "LivingRoom 1M bounce/all " + label)
     finally:
         del os.environ["B2PT_TRACE_STREAM"]
 
