@@ -47,10 +47,10 @@ __device__ __forceinline__ float3 cross_embree(float3 a, float3 b) {
 static __device__ const uint32_t kRcpTable[2048] = {
 #include "rcp_table.inc"
 };
-__device__ __forceinline__ float rcp_embree(float a) {  // a > 0
+__device__ __forceinline__ float rcp_embree(float a, const uint32_t* table = kRcpTable) {  // a > 0; table: kRcpTable or a copy in shared memory
   const uint32_t b = __float_as_uint(a), e = b >> 23;
   if (e < 2u || e > 252u) return __frcp_rn(a);  // results near the ends of the exponent range: not table territory
-  const float r = __uint_as_float(kRcpTable[(b >> 12) & 0x7FFu] - ((e - 127u) << 23));
+  const float r = __uint_as_float(table[(b >> 12) & 0x7FFu] - ((e - 127u) << 23));
   return __fmul_rn(r, __fsub_rn(2.0f, __fmul_rn(r, a)));
 }
 
@@ -64,7 +64,7 @@ __device__ __forceinline__ TriData tri_load(const DeviceScene& sc, uint32_t pos)
   return d;
 }
 __device__ __forceinline__ bool intersect_triangle_data(const TriData& d, float3 O, float3 D, float tnear,
-                                                        float& tfar, float& u, float& v, uint32_t ray_mask) {
+                                                        float& tfar, float& u, float& v, uint32_t ray_mask, const uint32_t* rcp_table = kRcpTable) {
   const float4 q0 = d.q0, q1 = d.q1, q2 = d.q2;
   // geometry mask = 1 << (material_id & 3) (rtcSetMask, Scene.cpp:47); Embree skips the triangle when (mask & ray.mask) == 0
   if ((__float_as_uint(q2.w) & ray_mask) == 0u) return false;
@@ -80,7 +80,7 @@ __device__ __forceinline__ bool intersect_triangle_data(const TriData& d, float3
   if (!((den != 0.0f) & (U >= 0.0f) & (V >= 0.0f) & (__fadd_rn(U, V) <= absDen))) return false;
   const float T = xor_sign(dot_embree(Ng, C), sgnDen);
   if (!((T > __fmul_rn(absDen, tnear)) & (T < __fmul_rn(absDen, tfar)))) return false;
-  const float rcpAbsDen = rcp_embree(absDen);
+  const float rcpAbsDen = rcp_embree(absDen, rcp_table);
   tfar = __fmul_rn(T, rcpAbsDen);
   u = __fmul_rn(U, rcpAbsDen);
   v = __fmul_rn(V, rcpAbsDen);
@@ -488,8 +488,18 @@ __device__ __forceinline__ void trace_dyn8(const DeviceScene& sc, uint32_t n, un
 // lane can advance a node the remainder is tested as a partial chunk.  The tests are the same ones in another order: a closest hit can
 // differ from trace_ray8's only where two triangles are hit at exactly the same distance (the smaller triangle index wins here).
 // Needs 256-thread CTAs (one WarpQueue per warp) and fewer than 2^27 triangle references.
-constexpr int kQueueItems = 512;
-constexpr int kEnqueuePerRound = 8;
+#ifndef B2PT_Q_SMEMRCP
+#define B2PT_Q_SMEMRCP 0
+#endif
+#ifndef B2PT_Q_UNROLL2
+#define B2PT_Q_UNROLL2 1
+#endif
+#ifndef B2PT_Q_ENQ
+#define B2PT_Q_ENQ 8
+#endif
+constexpr int kEnqueuePerRound = B2PT_Q_ENQ;
+constexpr int kQueueItems = kEnqueuePerRound <= 15 ? 512 : 1024;  // a power of two >= 32 * kEnqueuePerRound + 31
+static_assert(kQueueItems >= 32 * kEnqueuePerRound + 31 && kEnqueuePerRound <= 24, "triangle ring too small");
 struct WarpQueue {
   uint32_t items[kQueueItems];   // owner lane << 27 | triangle
   float ray[8][32];              // Ox Oy Oz tnear Dx Dy Dz bits(mask), [field][owner lane]
@@ -501,6 +511,14 @@ template <bool kAnyHit, class Io>
 __device__ __forceinline__ void trace_queue8(const DeviceScene& sc, uint32_t n, unsigned* ticket, Io& io) {
   __shared__ WarpQueue s_wq[8];
   WarpQueue& q = s_wq[(threadIdx.x >> 5) & 7u];
+#if B2PT_Q_SMEMRCP
+  __shared__ uint32_t s_rcp[2048];  // the RCPPS table next to the queue: a hit's lookup is a shared-memory load
+  for (unsigned i = threadIdx.x; i < 2048u; i += blockDim.x) s_rcp[i] = kRcpTable[i];
+  __syncthreads();
+  const uint32_t* rcp_table = s_rcp;
+#else
+  const uint32_t* rcp_table = kRcpTable;
+#endif
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lane_lt = (1u << lane) - 1u;
   uint2 stack[kStack8];
@@ -594,12 +612,27 @@ __device__ __forceinline__ void trace_queue8(const DeviceScene& sc, uint32_t n, 
     const unsigned total = __shfl_sync(kFullMask, incl, 31);
     if (want) {
       uint32_t at = tail + incl - want;
+#if B2PT_Q_UNROLL2
+      const uint32_t owner_base = (lane << 27) | T.x;  // T.x + j < 2^27: the sum never carries into the lane bits
+      for (unsigned k = 0; k < want; k += 2u, at += 2u) {
+        const uint32_t j0 = uint32_t(__ffs(int(T.y)) - 1);
+        T.y &= T.y - 1u;
+        q.items[at & uint32_t(kQueueItems - 1)] = owner_base + j0;
+        if (k + 1u < want) {
+          const uint32_t j1 = uint32_t(__ffs(int(T.y)) - 1);
+          T.y &= T.y - 1u;
+          q.items[(at + 1u) & uint32_t(kQueueItems - 1)] = owner_base + j1;
+        }
+      }
+      my_last = tail + incl;
+#else
       for (unsigned k = 0; k < want; ++k, ++at) {
         const uint32_t j = uint32_t(__ffs(int(T.y)) - 1);
         T.y &= T.y - 1u;
         q.items[at & uint32_t(kQueueItems - 1)] = (lane << 27) | (T.x + j);
       }
       my_last = at;
+#endif
     }
     tail += total;
     const unsigned any_advanced = __ballot_sync(kFullMask, advanced);
@@ -621,7 +654,8 @@ __device__ __forceinline__ void trace_queue8(const DeviceScene& sc, uint32_t n, 
           const float3 Oo = f3(q.ray[0][owner], q.ray[1][owner], q.ray[2][owner]);
           const float3 Do = f3(q.ray[4][owner], q.ray[5][owner], q.ray[6][owner]);
           float t = __uint_as_float(uint32_t(b >> 32));
-          if (intersect_triangle(sc, tri, Oo, Do, q.ray[3][owner], t, u, v, __float_as_uint(q.ray[7][owner]))) {
+          const TriData td = tri_load(sc, tri);
+          if (intersect_triangle_data(td, Oo, Do, q.ray[3][owner], t, u, v, __float_as_uint(q.ray[7][owner]), rcp_table)) {
             hit = true;
             key = ((unsigned long long)__float_as_uint(t) << 32) | tri;
             atomicMin(&q.best[owner], key);
