@@ -29,7 +29,7 @@ for w in $what; do
     iterlog) B2PT_LOG_ITER=1 timeout 600 python bench.py --steps 1 --warmup 0 --spp 8 --no-cpu-baseline --no-e2e > gpurun_out/${tag}_iter_bench.json 2> gpurun_out/${tag}_iter.log; echo "iterlog rc=$?"; grep -c b2pt_iter gpurun_out/${tag}_iter.log ;;
     fulllogic) timeout 900 ncu --set full --clock-control none --import-source on -k regex:'bpt_(logic|connect)_kernel' -s 24 -c 4 -f -o gpurun_out/${tag}_bpt_logic_full \
         python bench.py --steps 1 --warmup 0 --spp 8 --no-cpu-baseline --no-e2e > gpurun_out/${tag}_ncu_fulllogic.log 2>&1; echo "fulllogic rc=$?" ;;
-    tracebench) timeout 900 python tools/trace_bench.py --builds "${TB_BUILDS:-default:}" --variants ${TB_VARIANTS:-0,2} > gpurun_out/${tag}_tracebench.json 2> gpurun_out/${tag}_tracebench.err; echo "tracebench rc=$?"; python - gpurun_out/${tag}_tracebench.json <<'PY'
+    tracebench) timeout 900 python tools/trace_bench.py --builds "${TB_BUILDS:-default:}" --variants ${TB_VARIANTS:-0,2,3} > gpurun_out/${tag}_tracebench.json 2> gpurun_out/${tag}_tracebench.err; echo "tracebench rc=$?"; python - gpurun_out/${tag}_tracebench.json <<'PY'
 import json, sys
 try:
     d = json.load(open(sys.argv[1]))
