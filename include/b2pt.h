@@ -244,6 +244,24 @@ int b2pt_render_host(b2pt_scene_t scene, const B2ptRenderParams* params, double*
 int b2pt_film_errors(const double* accum_dev, const float* reference_dev, uint32_t width, uint32_t height,
                      const int32_t* window, float* out, void* stream);
 
+/*
+ * b2pt_film_errors for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  It has no counterpart in the reference.  Same per-pixel
+ * arithmetic and the same (rms, abs) as b2pt_film_errors, with three differences:
+ *   - it calls no cudaMalloc / cudaFree / allocating routine and never synchronises: one cudaMemsetAsync of 256 bytes and one kernel on
+ *     `stream`; out_dev is a DEVICE buffer of two floats (out_dev[0] = rms, out_dev[1] = abs), valid once the stream reaches that point;
+ *   - its scratch (one partial sum per 4096-pixel tile) is a file-scope __device__ array of 98 560 bytes inside libb2pt.so: every GPU
+ *     that loads the library holds it until the process exits.  The number of pixels SUMMED (the window's, else width * height) must not
+ *     exceed B2PT_FILM_ERRORS_STATIC_MAX_PIXELS; beyond it the call fails with B2PT_ERR_CAPACITY and launches nothing;
+ *   - every call on a device shares that array: calls that overlap on the GPU (different streams with no event between them) race.
+ *     Calls ordered on one stream, or by events, are safe; what must start at zero is cleared by every call.
+ * The partial sums are added in a fixed order, so the result is deterministic; it agrees with b2pt_film_errors to the rounding of
+ * a double sum (1e-6 relative in the float results is the tests' bound).
+ */
+#define B2PT_FILM_ERRORS_STATIC_MAX_PIXELS (1u << 24)
+int b2pt_film_errors_static(const double* accum_dev, const float* reference_dev, uint32_t width, uint32_t height,
+                            const int32_t* window, float* out_dev, void* stream);
+
 /* ---- the film on the device: subimage_view_t's dvec4 accumulator (ImageView.hpp:10-46), width*height*(sum r, sum g, sum b, sum 1),
  * resident in HBM between passes; it crosses PCIe only when the host asks. ---- */
 typedef struct b2pt_film_s* b2pt_film_t;

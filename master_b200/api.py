@@ -107,7 +107,7 @@ class Stats(C.Structure):
 EXPORTS = [
     "b2pt_last_error", "b2pt_abi_version", "b2pt_device_count", "b2pt_set_device", "b2pt_device_synchronize", "b2pt_scene_create", "b2pt_scene_destroy",
     "b2pt_scene_info", "b2pt_trace", "b2pt_trace_device", "b2pt_render", "b2pt_render_host", "b2pt_grid_build",
-    "b2pt_grid_destroy", "b2pt_grid_query", "b2pt_grid_query_device", "b2pt_grid_info", "b2pt_film_errors", "b2pt_film_create", "b2pt_film_destroy", "b2pt_film_data",
+    "b2pt_grid_destroy", "b2pt_grid_query", "b2pt_grid_query_device", "b2pt_grid_info", "b2pt_film_errors", "b2pt_film_errors_static", "b2pt_film_create", "b2pt_film_destroy", "b2pt_film_data",
     "b2pt_film_clear", "b2pt_film_read", "b2pt_comm_unique_id", "b2pt_comm_init", "b2pt_reduce_accum", "b2pt_comm_destroy",
 ]
 # parity probes of include/b2pt_debug.h (not part of the drop-in boundary)
@@ -151,6 +151,7 @@ def load_library():
     lib.b2pt_grid_query_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.b2pt_grid_info.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.b2pt_film_errors.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_float), C.c_void_p]
+    lib.b2pt_film_errors_static.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.b2pt_film_create.argtypes = [C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p)]
     lib.b2pt_film_destroy.argtypes = [C.c_void_p]
     lib.b2pt_film_destroy.restype = None
