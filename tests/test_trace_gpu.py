@@ -87,3 +87,48 @@ def test_live_embree_parity_1m(name, device_scenes, flat_scenes, tmp_path):
     agree = (occ["geom"] == sets["shadow_hits"]["geom"]).mean()
     print(json.dumps(dict(what=name + " 1M shadow", rays=len(occ), agree=float(agree))))
     assert agree >= 0.9999
+
+
+@pytest.fixture
+def forced_form():
+    """sets B2PT_TRACE_STREAM for one call: 0 one ray per thread, 1 trace_stream8, 2 trace_dyn8, 3 trace_queue8 (csrc/trace_api.cu)"""
+    saved = os.environ.get("B2PT_TRACE_STREAM")
+
+    def use(form):
+        if form is None:
+            os.environ.pop("B2PT_TRACE_STREAM", None)
+        else:
+            os.environ["B2PT_TRACE_STREAM"] = str(form)
+    yield use
+    if saved is None:
+        os.environ.pop("B2PT_TRACE_STREAM", None)
+    else:
+        os.environ["B2PT_TRACE_STREAM"] = saved
+
+
+@pytest.mark.parametrize("name", ["CornellBoxSpecular", "MetalRings", "TestCase9"])
+def test_every_traversal_form_returns_the_same_hits(name, device_scenes, forced_form):
+    """The persistent forms (the integrators use trace_queue8) against one ray per thread on the golden ray sets, at batch sizes that
+    exercise the ticket ranges of trace_queue8 (fewer rays than one warp, than one chunk, than one grid), and twice in a row: the
+    shared-memory triangle ring is warp-synchronous code, a race in it would show as a run-to-run difference."""
+    from master_b200 import api
+    g = np.load(golden_path("rays_%s.npz" % name))
+    scene = device_scenes(name)
+    rays = np.concatenate([g["bounce_rays"], g["camera_rays"]])
+    for n in (1, 7, 32, 33, 100, 1000, 4097, len(rays)):
+        sub = np.ascontiguousarray(rays[:n])
+        for mode in (api.TRACE_CLOSEST_ALL, api.TRACE_CLOSEST_MESH, api.TRACE_OCCLUDED_MESH):
+            forced_form(0)
+            want = scene.trace(sub, mode)
+            for form in (1, 2, 3, 3):
+                forced_form(form)
+                got = scene.trace(sub, mode)
+                if mode == api.TRACE_OCCLUDED_MESH:
+                    assert np.array_equal(got["geom"] == MISS, want["geom"] == MISS), (name, n, mode, form)
+                    continue
+                same = (got["geom"] == want["geom"]) & (got["prim"] == want["prim"])
+                # a different triangle only as an exact tie in t (the queue keeps the smaller leaf-order index, a stack the first met)
+                assert np.array_equal(got["t"][~same].view(np.uint32), want["t"][~same].view(np.uint32)), (name, n, mode, form)
+                assert (~same).mean() <= 1e-3, (name, n, mode, form, int((~same).sum()))
+                for k in ("t", "u", "v"):
+                    assert np.array_equal(got[k][same].view(np.uint32), want[k][same].view(np.uint32)), (name, n, mode, form, k)
