@@ -51,7 +51,7 @@ constexpr uint32_t kNeeVertex = 0xFFFFFFFFu;   // descriptor.y: the freshly samp
 constexpr uint32_t kShadowSplat = 1u;
 constexpr int kVertexFloat4s = 7;
 constexpr int kRecFloat4s = 16;
-enum { kRecThr = 7, kRecOmega = 8, kRecRayO = 9, kRecHit = 10, kRecRad = 11, kRecCtl = 12, kRecNee = 13, kRecState = 14 };
+enum { kRecThr = 7, kRecOmega = 8, kRecRayO = 9, kRecHit = 10, kRecRad = 11, kRecCtl = 12, kRecNee = 14, kRecLadj = 15 };
 // Expanding a path's connections into pair descriptors by walking its vertex chain is a string of dependent loads
 // (one L2 / HBM round trip per vertex); the first kLpTable vertex indices are therefore also kept by position, so the
 // expansion reads them independently.  Longer paths (3 % at roulette 0.9) walk the chain for the rest.
@@ -89,7 +89,9 @@ struct BptPool {
   //   8  pending BSDF sample: omega.xyz, density           9  extension ray origin, w = bits(bsdf.finite | ray mask selector << 1)
   //   10 hit: t, u, v, bits(triangle)                      11 eye-path radiance (float atomics from the shadow stage)
   //   12 bits(rng key, rng counter, light path head, light path count)
-  //   13 next-event sample: position, bits(light id)       14 bits(state), -, -, -
+  //   14 next-event sample: position, bits(light id)       15 its emitter's lobe restriction (light_lobe_adjust), -, -, -
+  // (14 and 15 share one 32-byte sector and are written together.)  The state of a live path is not stored: it waits for the hit of
+  // its extension ray, and the end of the live queue it sits at says for which subpath.
   float4* rec;
   double* splat;     // light image of the pass the path belongs to: 3 doubles per slot (= per pixel of that pass)
   float4* lv;        // light vertex pool, AoS: 7 float4 per vertex
@@ -269,12 +271,37 @@ __global__ void __launch_bounds__(256) bpt_sort_scatter_kernel(BptPool pool, Bpt
   }
 }
 
+// ---------------------------------------------------------------- staging of gathered records through shared memory
+// The shading stages reach their records through queues, i.e. as gathers: every item costs one or two dependent round trips to HBM
+// before any arithmetic can start (56 % / 47 % of the warp-state samples of the logic / connect stage were long-scoreboard stalls,
+// profiles/r02_bpt_logic_full_v4_summary.md), and asking for the next item's words early in registers spills (128 registers, measured
+// slower).  cp.async (LDGSTS) moves 16-byte words from global to shared memory without a destination register: a thread asks for the
+// NEXT item's words right after it has read the current item's out of its own staging column, and the copy lands while it computes.
+// Every thread owns one column [word][threadIdx.x] (conflict-free 128-bit accesses) and reads only what it copied itself, so the only
+// synchronisation is the thread's own cp.async.wait_all.
+__device__ __forceinline__ void cp_async16(float4* smem_dst, const float4* gmem_src) {
+  const uint32_t d = uint32_t(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+
 // The stage runs over the LIVE paths only: after every iteration a path is either done or waiting for the hit of its
 // extension ray, so the trace queue the previous iteration wrote is exactly the list of live slots (`first` = iteration 0
 // of a batch walks every slot instead).  A pool-order loop would leave a warp with as many busy lanes as the pool has
 // live paths — 4 of 32 halfway through a batch (ncu, profiles/).
+// kStaged (never with `first`): the path record of a thread's NEXT item is copied to shared memory while the current one is worked
+// on (cp.async, above).  Two buffers: the words of the current item are read out of shared memory where they are used — the buffer
+// serves as an extension of the register file (holding a whole record in registers next to the prefetch state spilled 300 bytes) —
+// while the copy of the next item lands in the other one.  The launch is one wave of resident CTAs and needs kLogicStageBytes of
+// dynamic shared memory.
+constexpr int kLogicStageWords = 12;  // words 0..10 of the record (vertex, pending sample, ray origin, hit) and the control word
+constexpr size_t kLogicStageBytes = size_t(2 * kLogicStageWords) * 256 * sizeof(float4);
+__host__ __device__ constexpr int logic_stage_index(int word) { return word == kRecCtl ? 11 : word; }
+template <bool kStaged>
 __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
                                                                                int first, int sort) {
+  extern __shared__ float4 s_stage[];
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     // trace_count[parity ^ 1] is this launch's input; the closest-hit stage clears it afterwards
@@ -297,21 +324,62 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
   const uint32_t n_round = n_eye_round + ((n_light + 31u) & ~31u);
   const uint32_t* live_q = pool.trace_q[parity ^ 1];
   uint32_t* next_q = pool.trace_q[parity];
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
-    const bool eye_end = i < n_eye_round;
-    const uint32_t j = eye_end ? i : i - n_eye_round;
-    const bool lane_on = j < (eye_end ? n_eye : n_light);
-    const uint32_t slot = lane_on ? (first ? j : live_q[eye_end ? j : pool.size - 1u - j]) : 0u;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  // which slot entry i of the two-ended queue names (eye end first, each end rounded up to whole warps)
+  auto item = [&](uint32_t i, bool& on, bool& eye) -> uint32_t {
+    eye = i < n_eye_round;
+    const uint32_t j = eye ? i : i - n_eye_round;
+    on = j < (eye ? n_eye : n_light);
+    return on ? (first ? j : live_q[eye ? j : pool.size - 1u - j]) : 0u;
+  };
+  float4* mine = s_stage + threadIdx.x;
+  auto stage = [&](uint32_t slot, uint32_t buf) {
+    const float4* src = pool.rec + size_t(slot) * kRecFloat4s;
+    float4* dst = mine + buf * (kLogicStageWords * 256);
+#pragma unroll
+    for (int k = 0; k <= kRecHit; ++k) cp_async16(dst + k * 256, src + k);
+    cp_async16(dst + logic_stage_index(kRecCtl) * 256, src + kRecCtl);
+  };
+  uint32_t pre_slot = 0, pre2_slot = 0, sbuf = 0;
+  bool pre_on = false, pre_eye = false, pre2_on = false, pre2_eye = false;
+  if (kStaged) {
+    const uint32_t i0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i0 < n_round) { pre_slot = item(i0, pre_on, pre_eye); if (pre_on) stage(pre_slot, 0u); }
+    cp_async_commit();
+    if (i0 + stride < n_round) pre2_slot = item(i0 + stride, pre2_on, pre2_eye);
+  }
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    bool eye_end, lane_on;
+    uint32_t slot;
+    const float4* staged_rec = mine + sbuf * (kLogicStageWords * 256);
+    if (kStaged) {
+      eye_end = pre_eye; lane_on = pre_on; slot = pre_slot;
+      cp_async_wait_all();
+      // ask for the next item's record (into the other buffer), and for the queue entry after that
+      sbuf ^= 1u;
+      pre_slot = pre2_slot; pre_on = pre2_on; pre_eye = pre2_eye;
+      if (i + stride < n_round && pre_on) stage(pre_slot, sbuf);
+      cp_async_commit();
+      pre2_on = false;
+      if (i + stride < n_round && i + 2u * stride < n_round) pre2_slot = item(i + 2u * stride, pre2_on, pre2_eye);
+    } else {
+      slot = item(i, lane_on, eye_end);
+    }
     float4* rec = pool.rec + size_t(slot) * kRecFloat4s;
-    // iteration 0 of a batch never reads the records: every slot is born kNew
-    const uint32_t st0 = lane_on ? (first ? uint32_t(kNew) : __float_as_uint(rec[kRecState].x)) : uint32_t(kDone);
+#define B2PT_REC(k) (kStaged ? staged_rec[logic_stage_index(k) * 256] : rec[k])
+    // iteration 0 of a batch never reads the records: every slot is born kNew.  Afterwards a live path waits for the hit of its
+    // extension ray, and which end of the queue it sits at says for which subpath: the state is not stored.
+    const uint32_t st0 = lane_on ? (first ? uint32_t(kNew) : eye_end ? uint32_t(kEyeWait) : uint32_t(kLightWait)) : uint32_t(kDone);
     uint32_t st = st0;
     bool want_trace = false, finished = false;
     uint32_t emit_n = 0, emit_flags = 0;  // pair descriptors to write after the branches
     bool emit_nee = false, emit_skip_first = false;
     uint32_t head = kInvalid, count = 0;
     uint32_t ray_mesh_only = 0;
-    float3 O = f3(0.f), rad = f3(0.f);
+    int sample_kind = 0;  // the BSDF sample this item needs, taken at ONE place below: 1 = light subpath goes on, 2 = its last vertex, 3 = eye subpath
+    float3 O = f3(0.f), rad = f3(0.f);  // rad: what this iteration adds to the path's radiance (emission through a light, the sky)
+    bool rad_add = false;
+    float4 hv = make_float4(0.f, 0.f, 0.f, 0.f);
     Rng rng; rng.key = 0; rng.ctr = 0;
     Vertex cur;
     BsdfSample bs;
@@ -353,22 +421,26 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
           }
         }
       } else {
-        const float4 ctl = rec[kRecCtl];
+        const float4 ctl = B2PT_REC(kRecCtl);
         rng.key = __float_as_uint(ctl.x); rng.ctr = __float_as_uint(ctl.y);
         head = __float_as_uint(ctl.z); count = __float_as_uint(ctl.w);
-        const float4 rv = rec[kRecRad];
-        rad = f3(rv.x, rv.y, rv.z);
-        cur = load_slot_vertex(pool, slot);
-        const float4 bo = rec[kRecOmega], bt = rec[kRecThr], ro = rec[kRecRayO];
+        {
+          float4 q[kVertexFloat4s];
+#pragma unroll
+          for (int k = 0; k < kVertexFloat4s; ++k) q[k] = B2PT_REC(k);
+          cur = unpack_vertex(q);
+        }
+        const float4 bo = B2PT_REC(kRecOmega), bt = B2PT_REC(kRecThr), ro = B2PT_REC(kRecRayO);
         bs.omega = f3(bo.x, bo.y, bo.z); bs.density = bo.w;
         bs.throughput = f3(bt.x, bt.y, bt.z); bs.density_rev = bt.w;
         bs.finite = __float_as_uint(ro.w) & 1u;
         O = f3(ro.x, ro.y, ro.z);
+        hv = B2PT_REC(kRecHit);
       }
+#undef B2PT_REC
 
       if (st == kLightWait) {
         // ---- _traceLight loop body after intersectMesh (BPT.cpp:139-176)
-        const float4 hv = rec[kRecHit];
         const uint32_t tri = __float_as_uint(hv.w);
         if (tri == kInvalid) {
           st = kLightFinal;
@@ -414,52 +486,20 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
       }
 
       if (st == kLightLoop) {
-        if (roulette < rng.sample()) {  // while (!_russian_roulette(generator))
-          st = kLightFinal;
-        } else {
-          bs = bsdf_sample(sc, rng, cur.s, cur.omega);
-          O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);  // Scene::intersectMesh (Scene.cpp:204-208)
-          ray_mesh_only = 1;
-          want_trace = true;
-          st = kLightWait;
-        }
+        if (roulette < rng.sample()) st = kLightFinal;  // while (!_russian_roulette(generator))
+        else sample_kind = 1;
       }
+      if (st == kLightFinal) sample_kind = 2;  // BPT.cpp:184-191: one more BSDF sample at the last vertex
 
-      if (st == kLightFinal) {
-        // BPT.cpp:184-191: one more BSDF sample at the last vertex; a delta vertex cannot be connected
-        const BsdfSample last = bsdf_sample(sc, rng, cur.s, cur.omega);
-        if (last.finite == 0) {
-          head = pool.lv_link[head];
-          --count;
-        }
-        st = kEyeStart;
-      }
-
-      if (st == kEyeStart) {
-        // ---- BPT.cpp:26-34: the camera vertex
-        Rng first; first.key = rng.key; first.ctr = 0;  // the two jitter draws open the stream (Technique.cpp:322)
-        const float3 dir = shoot_primary(cfg, first, slot % cfg.pixels);
-        cur.s = cfg.camera;
-        cur.ladj = -1.0f;
-        cur.omega = -dir;
-        cur.thr = f3(1.0f) * roulette_inv;
-        cur.finite = 1; cur.w0 = 0.0f; cur.w1 = 0.0f;
-        cur_dirty = true;
-        emit_n = count; emit_flags = kPairCamera;  // _connect_eye: every light vertex, no next-event sample
-        bs = bsdf_sample(sc, rng, cur.s, cur.omega);  // CameraBSDF::sample: no draws
-        O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);
-        ray_mesh_only = 0;
-        want_trace = true;
-        st = kEyeWait;
-      } else if (st0 == kEyeWait) {
+      if (st0 == kEyeWait) {
         // ---- BPT.cpp:45-97: consume the closest hit of the extension ray
-        const float4 hv = rec[kRecHit];
         const uint32_t tri = __float_as_uint(hv.w);
         if (tri == kInvalid) {
           if (cur.s.is_camera()) {  // sky_gradient(bsdf.omega) *= _roulette_inv  (Technique.cpp:87-89)
             const float3 h = f3(cfg.params.sky_horizon[0], cfg.params.sky_horizon[1], cfg.params.sky_horizon[2]);
             const float3 z = f3(cfg.params.sky_zenith[0], cfg.params.sky_zenith[1], cfg.params.sky_zenith[2]);
-            rad = (h * (1 - bs.omega.z) + z * bs.omega.z) * roulette_inv;
+            rad = (h * (1 - bs.omega.z) + z * bs.omega.z) * roulette_inv;  // nothing was added to a camera ray's radiance before
+            rad_add = true;
           }
           finished = true;
         } else {
@@ -478,7 +518,8 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
             nv.w0 = 1.0f / beta_fn(edge.f_geometry * bs.density, beta);
             nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + cur.w0 * float(cur.finite)) * beta_fn(edge.b_geometry, beta) * nv.w0;
             if (nv.s.is_light()) {
-              rad += connect_light(sc, nv, beta);
+              rad = connect_light(sc, nv, beta);
+              rad_add = true;
               // surface = _scene->intersect(surface, bsdf.omega): on through the light, eye[prv] stays
               O = offset_origin(nv.s.pos, nv.s.gnormal, bs.omega);
               cur_dirty = true;  // eye[prv].finite
@@ -499,7 +540,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
                     rec[kRecNee] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
                     // the emitter's lobe restriction at this point: computed here, where every lane of the warp samples a light, instead of
                     // in the connect stage, where one pair in six needs it and the other lanes of its warp would wait for it
-                    rec[kRecState].y = light_lobe_adjust(sc, ls.surface);
+                    rec[kRecLadj] = make_float4(light_lobe_adjust(sc, ls.surface), 0.f, 0.f, 0.f);
                   } else {
                     // _connect_directional (BPT.cpp:245-269): queued for the directional stage
                     const float3 n = ls.surface.normal();
@@ -522,30 +563,68 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
                 }
                 emit_n = (count > 0 ? count - 1u : 0u) + (emit_nee ? 1u : 0u);  // light vertices 1 .. n-1 (+ the fresh sample)
                 emit_skip_first = true;
-                bs = bsdf_sample(sc, rng, cur.s, cur.omega);
-                O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);
-                ray_mesh_only = 0;
-                want_trace = true;
+                sample_kind = 3;
               }
             }
           }
         }
       }
 
+      // ---- the BSDF sample of the iteration, for whichever branch asked for it.  A lane takes at most one per iteration, and taking
+      // it HERE lets the lanes of a warp run Scene::sampleBSDF together: at the light end of the queue nearly every warp holds both
+      // paths that go on (kind 1) and paths at their last vertex (kind 2), and two call sites ran the whole function twice per warp.
+      if (sample_kind) {
+        const BsdfSample smp = bsdf_sample(sc, rng, cur.s, cur.omega);
+        if (sample_kind == 2) {
+          if (smp.finite == 0) {  // a delta vertex cannot be connected
+            head = pool.lv_link[head];
+            --count;
+          }
+          st = kEyeStart;
+        } else {
+          bs = smp;
+          O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);  // Scene::intersectMesh (Scene.cpp:204-208) / Scene::intersect
+          ray_mesh_only = sample_kind == 1 ? 1u : 0u;
+          want_trace = true;
+          if (sample_kind == 1) st = kLightWait;
+        }
+      }
+
+      if (st == kEyeStart) {
+        // ---- BPT.cpp:26-34: the camera vertex
+        Rng first; first.key = rng.key; first.ctr = 0;  // the two jitter draws open the stream (Technique.cpp:322)
+        const float3 dir = shoot_primary(cfg, first, slot % cfg.pixels);
+        cur.s = cfg.camera;
+        cur.ladj = -1.0f;
+        cur.omega = -dir;
+        cur.thr = f3(1.0f) * roulette_inv;
+        cur.finite = 1; cur.w0 = 0.0f; cur.w1 = 0.0f;
+        cur_dirty = true;
+        emit_n = count; emit_flags = kPairCamera;  // _connect_eye: every light vertex, no next-event sample
+        bs = camera_sample(cur.s, cur.omega);  // CameraBSDF::sample: no draws
+        O = offset_origin(cur.s.pos, cur.s.gnormal, bs.omega);
+        ray_mesh_only = 0;
+        want_trace = true;
+        st = kEyeWait;
+      }
+
+      // the path's radiance lives in its record only: the any-hit stage adds the visible connections with float atomics, this stage
+      // adds its own terms the same way (the same IEEE additions a load, add and store would make; nothing else touches the word now)
+      if (rad_add) {
+        float* r = &rec[kRecRad].x;
+        atomicAdd(r + 0, rad.x); atomicAdd(r + 1, rad.y); atomicAdd(r + 2, rad.z);
+      }
       if (finished) {
-        rec[kRecRad] = make_float4(rad.x, rad.y, rad.z, 0.f);
         st = kDone;
       } else {
         if (cur_dirty) store_slot_vertex(pool, slot, cur);
         rec[kRecCtl] = make_float4(__uint_as_float(rng.key), __uint_as_float(rng.ctr), __uint_as_float(head), __uint_as_float(count));
-        if (st0 == kEyeWait) rec[kRecRad] = make_float4(rad.x, rad.y, rad.z, 0.f);
         if (want_trace) {
           rec[kRecOmega] = make_float4(bs.omega.x, bs.omega.y, bs.omega.z, bs.density);
           rec[kRecThr] = make_float4(bs.throughput.x, bs.throughput.y, bs.throughput.z, bs.density_rev);
           rec[kRecRayO] = make_float4(O.x, O.y, O.z, __uint_as_float((bs.finite & 1u) | (ray_mesh_only << 1)));
         }
       }
-      rec[kRecState].x = __uint_as_float(st);
     }
 
     // ---- converged: queue appends
@@ -625,82 +704,152 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
   }
 }
 
+// one (eye vertex, light vertex) pair: BPTBase::_connect / _connect_eye without the visibility test; fills the shadow-queue entry
+struct PairOut {
+  bool want;
+  float3 a, d, c;
+  uint32_t target, flags;
+};
+__device__ __forceinline__ void connect_pair(const RenderConfig& cfg, const BptPool& pool, uint32_t slot, bool camera, const Vertex& eye,
+                                             const Vertex& light, float beta, PairOut& o) {
+  const DeviceScene& sc = cfg.scene;
+  o.want = false; o.a = f3(0.f); o.d = f3(0.f); o.c = f3(0.f); o.target = 0; o.flags = 0;
+  bool inside = true;
+  if (camera) {
+    // Technique::_accumulate (Technique.cpp:276-305): which pixel the light vertex projects to
+    const float3 omega = normalize(light.s.pos - eye.s.pos);
+    mat3 w2v;
+    const float* m = cfg.params.camera.world_to_view;
+    w2v.c0 = f3(m[0], m[1], m[2]); w2v.c1 = f3(m[3], m[4], m[5]); w2v.c2 = f3(m[6], m[7], m[8]);
+    const float3 vd = mul(w2v, omega);
+    const float2 pp = pixel_position(vd, cfg.width_f, cfg.height_f, cfg.res_y_inv, cfg.params.camera.focal_length_y);
+    inside = (0 <= pp.x) && (pp.x < cfg.width_f) && (0 <= pp.y) && (pp.y < cfg.height_f);
+    if (inside) {
+      const uint32_t pixel = uint32_t(int(pp.y)) * cfg.params.width + uint32_t(int(pp.x));
+      o.target = (slot / cfg.pixels) * cfg.pixels + pixel;  // same pass, other pixel
+      o.flags = kShadowSplat;
+      const float cc = camera_coefficient(light.omega, light.s.gnormal, light.s.normal(), omega, eye.s.normal());
+      o.c = connect_vertices(sc, light, eye, beta) * cfg.focal_factor_y * cc;
+    }
+  } else {
+    o.target = slot;
+    o.c = connect_vertices(sc, light, eye, beta);
+  }
+  if (inside) {
+    const float l1 = l1norm(o.c);
+    if (!isfinite(l1)) {
+      // the reference multiplies by occluded() first: 0 * inf = NaN, so a non-finite connection poisons the
+      // sample whether or not it is visible, and _commit_images drops it (Technique.cpp:224-230)
+      if (o.flags & kShadowSplat) {
+        atomicAdd(pool.splat + size_t(o.target) * 3, double(NAN));
+      } else {
+        atomicAdd(&pool.rec[size_t(o.target) * kRecFloat4s + kRecRad].x, NAN);
+      }
+    } else if (l1 != 0.0f) {
+      // Scene::occluded(eye.surface, light.surface) (Scene.cpp:151-171)
+      const float3 direction = normalize(light.s.pos - eye.s.pos);
+      o.a = eye.s.pos + (dot(eye.s.gnormal, direction) > 0.0f ? 1.0f : -1.0f) * eye.s.gnormal * 0.0001f;
+      const float3 b = light.s.pos + (dot(light.s.gnormal, direction) < 0.0f ? 1.0f : -1.0f) * light.s.gnormal * 0.0001f;
+      o.d = b - o.a;
+      o.want = true;
+    }
+  }
+}
+__device__ __forceinline__ void connect_emit(const BptPool& pool, BptCounters* cnt, int parity, const PairOut& o) {
+  const unsigned sq = warp_append(&cnt->shadow_count[parity], o.want);
+  if (o.want) {
+    if (sq < pool.q_capacity) {
+      float4* e = pool.shadow_q + size_t(sq) * 3;
+      e[0] = make_float4(o.a.x, o.a.y, o.a.z, __uint_as_float(o.target));
+      e[1] = make_float4(o.d.x, o.d.y, o.d.z, __uint_as_float(o.flags));
+      e[2] = make_float4(o.c.x, o.c.y, o.c.z, 0.f);
+    } else {
+      atomicAdd(&cnt->capacity_events, 1ull);
+    }
+  }
+}
+
+// kStaged: the two vertices of the NEXT pair of a thread are copied to shared memory while it evaluates the current one (above);
+// the launch is then one wave of resident CTAs (148 x B2PT_LOGIC_MIN_BLOCKS) and needs kConnectStageBytes of dynamic shared memory
+constexpr int kConnectStageWords = 2 * kVertexFloat4s;
+constexpr size_t kConnectStageBytes = size_t(kConnectStageWords) * 256 * sizeof(float4);
+template <bool kStaged>
 __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+  extern __shared__ float4 s_stage[];
   const DeviceScene& sc = cfg.scene;
   const uint32_t n = min(cnt->pair_count[parity], pool.q_capacity);
   const float beta = cfg.params.beta;
   const float roulette_inv = 1.0f / cfg.params.roulette;
-  const uint32_t rounds = (n + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
-  for (uint32_t r = 0; r < rounds; ++r) {
-    const uint32_t i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
-    bool want = false;
-    float3 a = f3(0.f), d = f3(0.f), c = f3(0.f);
-    uint32_t target = 0, flags = 0;
-    if (i < n) {
-      const uint2 desc = pool.pair_q[i];
-      const uint32_t slot = desc.x & ~kPairCamera;
-      const bool camera = (desc.x & kPairCamera) != 0u;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const uint32_t rounds = (n + stride - 1) / stride;
+  float4* mine = s_stage + threadIdx.x;
+  // copy the words of pair `desc` into this thread's column: eye vertex 0..6, then the light vertex — or, for the next-event sample,
+  // the two words of the path record it is rebuilt from
+  auto stage = [&](uint2 desc) {
+    const float4* rec = pool.rec + size_t(desc.x & ~kPairCamera) * kRecFloat4s;
+#pragma unroll
+    for (int k = 0; k < kVertexFloat4s; ++k) cp_async16(mine + k * 256, rec + k);
+    if (desc.y == kNeeVertex) {
+      cp_async16(mine + kVertexFloat4s * 256, rec + kRecNee);
+      cp_async16(mine + (kVertexFloat4s + 1) * 256, rec + kRecLadj);
+    } else {
+      const float4* lv = pool.lv + size_t(desc.y) * kVertexFloat4s;
+#pragma unroll
+      for (int k = 0; k < kVertexFloat4s; ++k) cp_async16(mine + (kVertexFloat4s + k) * 256, lv + k);
+    }
+  };
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  uint2 desc = make_uint2(0u, 0u), desc_next = make_uint2(0u, 0u);
+  if (kStaged) {
+    if (i < n) { desc = pool.pair_q[i]; stage(desc); }
+    cp_async_commit();
+    if (i + stride < n && i + stride >= i) desc_next = pool.pair_q[i + stride];
+  }
+  for (uint32_t r = 0; r < rounds; ++r, i += stride) {
+    PairOut o;
+    o.want = false; o.a = f3(0.f); o.d = f3(0.f); o.c = f3(0.f); o.target = 0; o.flags = 0;
+    if (kStaged) {
+      cp_async_wait_all();
+      const bool on = i < n;
+      const uint2 dcur = desc;
+      float4 q[kConnectStageWords];
+      if (on) {
+#pragma unroll
+        for (int k = 0; k < kConnectStageWords; ++k) q[k] = mine[k * 256];
+      }
+      // the column is free again: ask for the next pair's words, and for the descriptor after that
+      desc = desc_next;
+      if (i + stride < n) stage(desc);
+      cp_async_commit();
+      desc_next = make_uint2(0u, 0u);
+      if (r + 2 < rounds) { const uint32_t i2 = i + 2 * stride; if (i2 < n) desc_next = pool.pair_q[i2]; }
+      if (on) {
+        const uint32_t slot = dcur.x & ~kPairCamera;
+        const Vertex eye = unpack_vertex(q);
+        Vertex light;
+        if (dcur.y == kNeeVertex) {
+          const float4 nr = q[kVertexFloat4s];
+          light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), roulette_inv, beta, q[kVertexFloat4s + 1].x);
+        } else {
+          light = unpack_vertex(q + kVertexFloat4s);
+        }
+        connect_pair(cfg, pool, slot, (dcur.x & kPairCamera) != 0u, eye, light, beta, o);
+      }
+    } else if (i < n) {
+      const uint2 d = pool.pair_q[i];
+      const uint32_t slot = d.x & ~kPairCamera;
       const Vertex eye = load_slot_vertex(pool, slot);
       Vertex light;
-      if (desc.y == kNeeVertex) {
+      if (d.y == kNeeVertex) {
         const float4 nr = pool.rec[size_t(slot) * kRecFloat4s + kRecNee];
         light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), roulette_inv, beta,
-                                 pool.rec[size_t(slot) * kRecFloat4s + kRecState].y);
+                                 pool.rec[size_t(slot) * kRecFloat4s + kRecLadj].x);
       } else {
-        light = load_pool_vertex(pool, desc.y);
+        light = load_pool_vertex(pool, d.y);
       }
-      bool inside = true;
-      if (camera) {
-        // Technique::_accumulate (Technique.cpp:276-305): which pixel the light vertex projects to
-        const float3 omega = normalize(light.s.pos - eye.s.pos);
-        mat3 w2v;
-        const float* m = cfg.params.camera.world_to_view;
-        w2v.c0 = f3(m[0], m[1], m[2]); w2v.c1 = f3(m[3], m[4], m[5]); w2v.c2 = f3(m[6], m[7], m[8]);
-        const float3 vd = mul(w2v, omega);
-        const float2 pp = pixel_position(vd, cfg.width_f, cfg.height_f, cfg.res_y_inv, cfg.params.camera.focal_length_y);
-        inside = (0 <= pp.x) && (pp.x < cfg.width_f) && (0 <= pp.y) && (pp.y < cfg.height_f);
-        if (inside) {
-          const uint32_t pixel = uint32_t(int(pp.y)) * cfg.params.width + uint32_t(int(pp.x));
-          target = (slot / cfg.pixels) * cfg.pixels + pixel;  // same pass, other pixel
-          flags = kShadowSplat;
-          const float cc = camera_coefficient(light.omega, light.s.gnormal, light.s.normal(), omega, eye.s.normal());
-          c = connect_vertices(sc, light, eye, beta) * cfg.focal_factor_y * cc;
-        }
-      } else {
-        target = slot;
-        c = connect_vertices(sc, light, eye, beta);
-      }
-      if (inside) {
-        const float l1 = l1norm(c);
-        if (!isfinite(l1)) {
-          // the reference multiplies by occluded() first: 0 * inf = NaN, so a non-finite connection poisons the
-          // sample whether or not it is visible, and _commit_images drops it (Technique.cpp:224-230)
-          if (flags & kShadowSplat) {
-            atomicAdd(pool.splat + size_t(target) * 3, double(NAN));
-          } else {
-            atomicAdd(&pool.rec[size_t(target) * kRecFloat4s + kRecRad].x, NAN);
-          }
-        } else if (l1 != 0.0f) {
-          // Scene::occluded(eye.surface, light.surface) (Scene.cpp:151-171)
-          const float3 direction = normalize(light.s.pos - eye.s.pos);
-          a = eye.s.pos + (dot(eye.s.gnormal, direction) > 0.0f ? 1.0f : -1.0f) * eye.s.gnormal * 0.0001f;
-          const float3 b = light.s.pos + (dot(light.s.gnormal, direction) < 0.0f ? 1.0f : -1.0f) * light.s.gnormal * 0.0001f;
-          d = b - a;
-          want = true;
-        }
-      }
+      connect_pair(cfg, pool, slot, (d.x & kPairCamera) != 0u, eye, light, beta, o);
     }
-    const unsigned sq = warp_append(&cnt->shadow_count[parity], want);
-    if (want) {
-      if (sq < pool.q_capacity) {
-        float4* e = pool.shadow_q + size_t(sq) * 3;
-        e[0] = make_float4(a.x, a.y, a.z, __uint_as_float(target));
-        e[1] = make_float4(d.x, d.y, d.z, __uint_as_float(flags));
-        e[2] = make_float4(c.x, c.y, c.z, 0.f);
-      } else {
-        atomicAdd(&cnt->capacity_events, 1ull);
-      }
-    }
+    connect_emit(pool, cnt, parity, o);
   }
 }
 
@@ -965,6 +1114,22 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       const size_t want = (size_t(size) + v - 1) / v, cap = size_t(kNumSMs) * 8 * (block / v);  // the same number of threads in flight
       shade_grid = int(std::min(want < 1 ? size_t(1) : want, cap));
   } } }
+  // Shading stages with their gathers staged through shared memory (cp.async, see bpt_logic_kernel): one wave of resident CTAs.
+  // B2PT_STAGED=0 keeps the plain loads for A/B runs (2: connect stage only, 3: logic stage only).
+  bool staged_logic = false, staged_connect = false;
+  { const char* e = getenv("B2PT_STAGED"); if (e && shade_block == block) { staged_logic = e[0] == '1' || e[0] == '3'; staged_connect = e[0] == '1' || e[0] == '2'; } }
+  const bool staged = staged_logic || staged_connect;
+  int staged_grid = std::min(grid, kNumSMs * B2PT_LOGIC_MIN_BLOCKS);
+  { const char* e = getenv("B2PT_STAGED_GRID"); if (e) { const int v = atoi(e); if (v >= 1 && v <= 8) staged_grid = std::min(grid, kNumSMs * v); } }
+  if (staged) {
+    static bool configured = false;  // per process; the attribute is per function and device-independent in effect
+    if (!configured) {
+      B2_CUDA(cudaFuncSetAttribute(bpt_logic_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kLogicStageBytes)));
+      B2_CUDA(cudaFuncSetAttribute(bpt_logic_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, int(cudaSharedmemCarveoutMaxShared)));
+      B2_CUDA(cudaFuncSetAttribute(bpt_connect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kConnectStageBytes)));
+      configured = true;
+    }
+  }
   // traversal form per stage: 0 = one ray per thread, 1 = persistent warps with dynamic fetch, 2 = the same plus postponed triangle
   // groups (trace.cuh: trace_dyn8), 3 = warp-synchronous rounds with a shared triangle queue (trace_queue8, the default).
   // B2PT_TRACE_STREAM / B2PT_SHADOW_STREAM select them for A/B runs; measured on the LivingRoom stand-in with 2^23-path batches:
@@ -1019,8 +1184,14 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       StageTimer& timer = *timers[k];
       for (int j = 0; j < kBatchIters; ++j, ++g.it) {
         const int parity = g.it & 1;
-        timer.begin(kStageShade); bpt_logic_kernel<<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays); timer.end();
-        timer.begin(kStageShade); bpt_connect_kernel<<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity); timer.end();
+        timer.begin(kStageShade);
+        if (staged_logic && g.it > 0) bpt_logic_kernel<true><<<staged_grid, block, kLogicStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
+        else bpt_logic_kernel<false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays);
+        timer.end();
+        timer.begin(kStageShade);
+        if (staged_connect) bpt_connect_kernel<true><<<staged_grid, block, kConnectStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else bpt_connect_kernel<false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        timer.end();
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);
           directional_kernel<<<grid, block, 0, l.stream>>>(cfg.scene, g.pool.dir_q, &l.counters->dir_count[parity], g.pool.size,

@@ -97,9 +97,49 @@ __device__ __forceinline__ float cr_asinf(float x) { return float(asin(double(x)
 __device__ __forceinline__ float cr_atan2f(float y, float x) { return float(atan2(double(y), double(x))); }
 // pow for the arguments shading has (0 < x, finite): exp2(y log2 x) in double is ~2^-42 relative for the exponents used here — still
 // far inside half a float ulp — at a third of the instructions of double pow (which carries an extended-precision logarithm)
-__device__ B2PT_MATH_INLINE float cr_powf(float x, float y) {
+__device__ B2PT_MATH_INLINE float cr_powf_lib(float x, float y) {
   if (x > 0.0f && x < INFINITY) return float(exp2(double(y) * log2(double(x))));
   return float(pow(double(x), double(y)));
+}
+// The same value from two small tables in a quarter of the instructions (pow_core.h; tables: tools/make_pow_tables.py).
+// -DB2PT_POW_LIB=1 keeps the math-library form for A/B runs.
+#ifndef B2PT_POW_LIB
+#define B2PT_POW_LIB 0
+#endif
+#include "pow_tables.inc"
+static __device__ const uint64_t kPowLogTable[128][2] = {B2PT_POW_LOG_TABLE};
+static __device__ const uint64_t kPowExpTable[64] = {B2PT_POW_EXP_TABLE};
+static __constant__ uint64_t kPowLogCoeffs[6] = {B2PT_POW_LOG_COEFFS};
+static __constant__ uint64_t kPowExpCoeffs[5] = {B2PT_POW_EXP_COEFFS};
+#define B2PT_POW_QUAL __device__ __forceinline__
+#define B2PT_POW_LOG(i, w) b2pt_pow_log_word(i, w)
+#define B2PT_POW_EXP(j) __ldg(&kPowExpTable[j])
+#define B2PT_POW_LC(k) kPowLogCoeffs[k]
+#define B2PT_POW_EC(k) kPowExpCoeffs[k]
+__device__ __forceinline__ uint64_t b2pt_pow_log_word(uint32_t i, int w) {  // both words of an entry come with one 128-bit load
+  const ulonglong2 e = __ldg(reinterpret_cast<const ulonglong2*>(&kPowLogTable[i][0]));
+  return w ? e.y : e.x;
+}
+__device__ __forceinline__ double b2pt_pow_u2d(uint64_t u) { return __longlong_as_double((long long)u); }
+__device__ __forceinline__ uint64_t b2pt_pow_d2u(double d) { return (uint64_t)__double_as_longlong(d); }
+__device__ __forceinline__ uint32_t b2pt_pow_f2u(float f) { return __float_as_uint(f); }
+__device__ __forceinline__ float b2pt_pow_u2f(uint32_t u) { return __uint_as_float(u); }
+__device__ __forceinline__ double b2pt_pow_fma(double a, double b, double c) { return fma(a, b, c); }
+#include "pow_core.h"
+__device__ B2PT_MATH_INLINE float cr_powf_slow(float x, float y) {
+#if !B2PT_POW_LIB
+  float r;
+  if (b2pt_pow_core(x, y, &r)) return r;
+#endif
+  return cr_powf_lib(x, y);
+}
+// The Phong lobe clamps its cosine to [0, 1] and lands ON the ends for every direction outside the lobe's hemisphere (about half of
+// all BSDF queries of a connection): pow(+0, y > 0) = +0 and pow(1, y) = 1 exactly (C11 F.10.4.4), without the call — the general
+// double pow those arguments used to fall into was 6 % of the connect stage's warp instructions at 9 lanes.
+__device__ __forceinline__ float cr_powf(float x, float y) {
+  if (x == 1.0f) return 1.0f;
+  if (x == 0.0f && y > 0.0f && __float_as_uint(x) == 0u) return 0.0f;
+  return cr_powf_slow(x, y);
 }
 __device__ __forceinline__ float cr_cubef(float x) { const double d = double(x); return float(d * d * d); }  // powf(x, 3.0f)
 // sin and cos of one angle: one range reduction

@@ -132,11 +132,21 @@ __device__ __forceinline__ AngularBound angular_bound(float3 center, float radiu
 
 struct LambertRange { float theta_inf, theta_range, phi_inf, phi_range; };
 
+// cos of a bound of angular_bound.  An emitter INSIDE the scene's bounding sphere (the usual case) has the unrestricted bounds 0 and
+// pi/2 exactly, and every next-event sample evaluates this four times: the two known answers are constants —
+// float(cos(double(0x3FC90FDB))) = 0xB33BBD2E, nowhere near a rounding tie, and cos(0) = 1 — the rest goes through cr_cosf.
+__device__ __forceinline__ float cos_of_bound(float x) {
+  if (x == kHalfPi) return __uint_as_float(0xB33BBD2Eu);
+  if (x == 0.0f) return 1.0f;
+  return cr_cosf(x);
+}
+
 __device__ __forceinline__ LambertRange lambert_range(float3 center, float radius) {
   const AngularBound bound = angular_bound(center, radius);
   LambertRange r;
-  const float uniform_theta_inf = cr_cosf(bound.theta_sup) * cr_cosf(bound.theta_sup);
-  const float uniform_theta_sup = cr_cosf(bound.theta_inf) * cr_cosf(bound.theta_inf);
+  const float cos_sup = cos_of_bound(bound.theta_sup), cos_inf = cos_of_bound(bound.theta_inf);
+  const float uniform_theta_inf = cos_sup * cos_sup;
+  const float uniform_theta_sup = cos_inf * cos_inf;
   const float uniform_phi_inf = bound.phi_inf * kOneOverPi * 0.5f;
   const float uniform_phi_sup = bound.phi_sup * kOneOverPi * 0.5f;
   r.theta_inf = uniform_theta_inf;
@@ -300,6 +310,15 @@ __device__ __forceinline__ BsdfQuery bsdf_query(const DeviceScene& sc, const Sur
   }
 }
 
+// CameraBSDF::sample (BSDF.cpp:197-208): no draws
+__device__ __forceinline__ BsdfSample camera_sample(const Surface& s, float3 omega) {
+  BsdfSample r;
+  r.omega = -omega;
+  r.throughput = f3(1.0f) / fabsf(dot(s.normal(), omega));
+  r.density = 1.0f; r.density_rev = 0.0f; r.finite = 1;
+  return r;
+}
+
 // Scene::sampleBSDF (Scene.cpp:133-140) -> BSDF::sample of the surface's material
 __device__ __forceinline__ BsdfSample bsdf_sample(const DeviceScene& sc, Rng& rng, const Surface& s, float3 omega) {
   const B2ptMaterial& m = sc.materials[s.material_index()];
@@ -315,7 +334,16 @@ __device__ __forceinline__ BsdfSample bsdf_sample(const DeviceScene& sc, Rng& rn
     }
     case B2PT_BSDF_PHONG: {  // PhongBSDF::sample (BSDF.cpp:328-347)
       const float3 local_omega = s.to_surface(omega);
-      const float3 d = rng.sample() < m.diffuse_probability ? sample_lambert(rng, local_omega) : sample_phong(rng, local_omega, m.power);
+      // sample_lambert (Sample.inl:48-56) or sample_phong (Sample.inl:137-149): both draw (u1, u2), make a height y from u1 and turn
+      // (r, y, phi) into a direction — the same operations in the same order as the two functions above, but with ONE polar
+      // conversion after the branch, so the double-precision sincos runs once per warp instead of once per lobe
+      const bool diffuse_lobe = rng.sample() < m.diffuse_probability;
+      const float u1 = rng.sample();
+      const float y = diffuse_lobe ? sqrtf(u1) * sign_glm(local_omega.y) : cr_powf(u1, 1.0f / (m.power + 1.0f));
+      const float rr = sqrtf(1.0f - y * y);
+      const float phi = rng.sample() * 2.0f * kPi;
+      float3 d = cr_polar(rr, y, phi);
+      if (!diffuse_lobe) d = mul(reflection_to_surface(f3(-local_omega.x, local_omega.y, -local_omega.z)), d);
       r.omega = s.to_world(d);
       const float same_side = dot(omega, s.gnormal) * dot(r.omega, s.gnormal) > 0.0f ? 1.0f : 0.0f;
       const BsdfQuery q = phong_query(m, local_omega, d, same_side);
@@ -360,10 +388,7 @@ __device__ __forceinline__ BsdfSample bsdf_sample(const DeviceScene& sc, Rng& rn
       r.throughput = f3(1.0f); r.omega = omega; r.density = 1.0f; r.density_rev = 0.0f; r.finite = 1;
       return r;
     default:  // CameraBSDF::sample (BSDF.cpp:197-208)
-      r.omega = -omega;
-      r.throughput = f3(1.0f) / fabsf(dot(s.normal(), omega));
-      r.density = 1.0f; r.density_rev = 0.0f; r.finite = 1;
-      return r;
+      return camera_sample(s, omega);
   }
 }
 
