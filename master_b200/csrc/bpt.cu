@@ -37,6 +37,9 @@
 // shading frame across grid strides was measured too: 72.8 vs 74.7 — with two batches in flight the other batch's kernels already fill the stalls.)
 #define B2PT_LOGIC_MIN_BLOCKS 2
 #endif
+#ifndef B2PT_LOGIC_SPLIT_MIN_BLOCKS
+#define B2PT_LOGIC_SPLIT_MIN_BLOCKS 2
+#endif
 #ifndef B2PT_TRACE_MIN_BLOCKS
 #define B2PT_TRACE_MIN_BLOCKS 4  // traversal stages: 64 registers per thread
 #endif
@@ -298,8 +301,10 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 constexpr int kLogicStageWords = 12;  // words 0..10 of the record (vertex, pending sample, ray origin, hit) and the control word
 constexpr size_t kLogicStageBytes = size_t(2 * kLogicStageWords) * 256 * sizeof(float4);
 __host__ __device__ constexpr int logic_stage_index(int word) { return word == kRecCtl ? 11 : word; }
-template <bool kStaged>
-__global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
+// kEnd: 0 = both ends of the live queue (and the first iteration of a batch), 1 = the eye end only, 2 = the light end only — the two
+// halves of the stage as kernels of their own (B2PT_LOGIC_SPLIT): each holds one subpath's code and state.
+template <bool kStaged, int kEnd>
+__global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_LOGIC_SPLIT_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
                                                                                int first, int sort) {
   extern __shared__ float4 s_stage[];
   const DeviceScene& sc = cfg.scene;
@@ -318,8 +323,8 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
   const uint32_t max_subpath = cfg.params.max_subpath ? cfg.params.max_subpath : 1024u;
   // trip counts are rounded up to whole warps: every lane of a warp reaches the warp_* helpers below
   // the two ends of the live queue are walked one after the other, each rounded up to whole warps: a warp holds paths of one phase
-  const uint32_t n_eye = first ? 0u : cnt->trace_count[parity ^ 1];
-  const uint32_t n_light = first ? pool.size : cnt->light_count[parity ^ 1];
+  const uint32_t n_eye = first || kEnd == 2 ? 0u : cnt->trace_count[parity ^ 1];
+  const uint32_t n_light = first ? pool.size : kEnd == 1 ? 0u : cnt->light_count[parity ^ 1];
   const uint32_t n_eye_round = (n_eye + 31u) & ~31u;
   const uint32_t n_round = n_eye_round + ((n_light + 31u) & ~31u);
   const uint32_t* live_q = pool.trace_q[parity ^ 1];
@@ -369,7 +374,8 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
 #define B2PT_REC(k) (kStaged ? staged_rec[logic_stage_index(k) * 256] : rec[k])
     // iteration 0 of a batch never reads the records: every slot is born kNew.  Afterwards a live path waits for the hit of its
     // extension ray, and which end of the queue it sits at says for which subpath: the state is not stored.
-    const uint32_t st0 = lane_on ? (first ? uint32_t(kNew) : eye_end ? uint32_t(kEyeWait) : uint32_t(kLightWait)) : uint32_t(kDone);
+    const uint32_t st0 = !lane_on ? uint32_t(kDone) : kEnd == 1 ? uint32_t(kEyeWait) : kEnd == 2 ? uint32_t(kLightWait)
+                         : first ? uint32_t(kNew) : eye_end ? uint32_t(kEyeWait) : uint32_t(kLightWait);
     uint32_t st = st0;
     bool want_trace = false, finished = false;
     uint32_t emit_n = 0, emit_flags = 0;  // pair descriptors to write after the branches
@@ -387,9 +393,9 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
     bool cur_dirty = false;
 
     if (st != kDone) {
-      if (st == kNew && slot >= pool.valid) {
+      if (kEnd == 0 && st == kNew && slot >= pool.valid) {
         finished = true;  // padding slot
-      } else if (st == kNew) {
+      } else if (kEnd == 0 && st == kNew) {
         // Technique::_for_each_ray (Technique.cpp:321-331): jitter, primary direction
         const uint32_t pixel = slot % cfg.pixels;
         const uint32_t pass = batch_pass0 + slot / cfg.pixels;
@@ -439,7 +445,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
       }
 #undef B2PT_REC
 
-      if (st == kLightWait) {
+      if (kEnd != 1 && st == kLightWait) {
         // ---- _traceLight loop body after intersectMesh (BPT.cpp:139-176)
         const uint32_t tri = __float_as_uint(hv.w);
         if (tri == kInvalid) {
@@ -485,13 +491,13 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
         }
       }
 
-      if (st == kLightLoop) {
+      if (kEnd != 1 && st == kLightLoop) {
         if (roulette < rng.sample()) st = kLightFinal;  // while (!_russian_roulette(generator))
         else sample_kind = 1;
       }
-      if (st == kLightFinal) sample_kind = 2;  // BPT.cpp:184-191: one more BSDF sample at the last vertex
+      if (kEnd != 1 && st == kLightFinal) sample_kind = 2;  // BPT.cpp:184-191: one more BSDF sample at the last vertex
 
-      if (st0 == kEyeWait) {
+      if (kEnd != 2 && st0 == kEyeWait) {
         // ---- BPT.cpp:45-97: consume the closest hit of the extension ray
         const uint32_t tri = __float_as_uint(hv.w);
         if (tri == kInvalid) {
@@ -575,7 +581,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
       // paths that go on (kind 1) and paths at their last vertex (kind 2), and two call sites ran the whole function twice per warp.
       if (sample_kind) {
         const BsdfSample smp = bsdf_sample(sc, rng, cur.s, cur.omega);
-        if (sample_kind == 2) {
+        if (kEnd != 1 && sample_kind == 2) {
           if (smp.finite == 0) {  // a delta vertex cannot be connected
             head = pool.lv_link[head];
             --count;
@@ -590,7 +596,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_logic_kernel(R
         }
       }
 
-      if (st == kEyeStart) {
+      if (kEnd != 1 && st == kEyeStart) {
         // ---- BPT.cpp:26-34: the camera vertex
         Rng first; first.key = rng.key; first.ctr = 0;  // the two jitter draws open the stream (Technique.cpp:322)
         const float3 dir = shoot_primary(cfg, first, slot % cfg.pixels);
@@ -1119,13 +1125,16 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   bool staged_logic = false, staged_connect = false;
   { const char* e = getenv("B2PT_STAGED"); if (e && shade_block == block) { staged_logic = e[0] == '1' || e[0] == '3'; staged_connect = e[0] == '1' || e[0] == '2'; } }
   const bool staged = staged_logic || staged_connect;
+  // B2PT_LOGIC_SPLIT=1: the logic stage as two kernels, one per end of the live queue (light subpaths, then eye subpaths)
+  bool logic_split = false;
+  { const char* e = getenv("B2PT_LOGIC_SPLIT"); if (e) logic_split = e[0] == '1'; }
   int staged_grid = std::min(grid, kNumSMs * B2PT_LOGIC_MIN_BLOCKS);
   { const char* e = getenv("B2PT_STAGED_GRID"); if (e) { const int v = atoi(e); if (v >= 1 && v <= 8) staged_grid = std::min(grid, kNumSMs * v); } }
   if (staged) {
     static bool configured = false;  // per process; the attribute is per function and device-independent in effect
     if (!configured) {
-      B2_CUDA(cudaFuncSetAttribute(bpt_logic_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kLogicStageBytes)));
-      B2_CUDA(cudaFuncSetAttribute(bpt_logic_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, int(cudaSharedmemCarveoutMaxShared)));
+      B2_CUDA(cudaFuncSetAttribute(bpt_logic_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kLogicStageBytes)));
+      B2_CUDA(cudaFuncSetAttribute(bpt_logic_kernel<true, 0>, cudaFuncAttributePreferredSharedMemoryCarveout, int(cudaSharedmemCarveoutMaxShared)));
       B2_CUDA(cudaFuncSetAttribute(bpt_connect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kConnectStageBytes)));
       configured = true;
     }
@@ -1185,8 +1194,11 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       for (int j = 0; j < kBatchIters; ++j, ++g.it) {
         const int parity = g.it & 1;
         timer.begin(kStageShade);
-        if (staged_logic && g.it > 0) bpt_logic_kernel<true><<<staged_grid, block, kLogicStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
-        else bpt_logic_kernel<false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays);
+        if (staged_logic && g.it > 0) bpt_logic_kernel<true, 0><<<staged_grid, block, kLogicStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
+        else if (logic_split && g.it > 0) {
+          bpt_logic_kernel<false, 2><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
+          bpt_logic_kernel<false, 1><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
+        } else bpt_logic_kernel<false, 0><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays);
         timer.end();
         timer.begin(kStageShade);
         if (staged_connect) bpt_connect_kernel<true><<<staged_grid, block, kConnectStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity);

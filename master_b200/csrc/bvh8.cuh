@@ -29,9 +29,13 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t k) {
   return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u | k)) - 8388608.0f;
 }
 
-// 2^15 + byte, exactly: the byte lands in mantissa bits 8..15 of 2^15 (whose ulp is 2^-8)
-__device__ __forceinline__ float byte_to_float15(uint32_t word, uint32_t k) {
-  return __uint_as_float(__byte_perm(word, 0x47000000u, 0x7604u | (k << 4)));
+// 2^15 + byte, exactly: the byte lands in mantissa bits 8..15 of 2^15 (whose ulp is 2^-8).
+// `base` is 0x47000000 handed in as a RUN-TIME value (DeviceScene::prmt_base, a kernel parameter): with both the base and the selector
+// known at compile time ptxas keeps the base as the immediate of PRMT and moves the selector into a register before EVERY permute
+// (UMOV + IMAD.U32: 48 extra instructions per node, a sixth of the node test — cuobjdump, round 2); with the base in the constant
+// bank the selector is the immediate and the permute is one instruction.
+__device__ __forceinline__ float byte_to_float15(uint32_t word, uint32_t k, uint32_t base) {
+  return __uint_as_float(__byte_perm(word, base, 0x7604u | (k << 4)));
 }
 
 }  // namespace b2pt

@@ -61,6 +61,7 @@ struct DeviceScene {
   int dyn_tri_lanes = 8;
   int queue_fetch_lanes = 8;   // trace_queue8: idle lanes of a warp that trigger a refill (B2PT_QUEUE_FETCH)
   int queue_chunk = 128;       // trace_queue8: tickets a warp reserves per atomic (B2PT_QUEUE_CHUNK)
+  uint32_t prmt_base = 0x47000000u;  // bits of 2^15: the constant half of bvh8.cuh's byte -> float permute, kept out of the compiler's sight on purpose
   int queue_drain_lanes = 12;  // trace_queue8: a partial chunk of the triangle ring is tested when fewer lanes than this advanced a node (B2PT_QUEUE_DRAIN)
 };
 

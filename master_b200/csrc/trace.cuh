@@ -164,6 +164,15 @@ __device__ __forceinline__ Hit trace_ray_masked(const DeviceScene& sc, float3 O,
 // ---------------------------------------------------------------- compressed 8-wide BVH (layout: bvh8.cuh)
 // One node of the compressed 8-wide tree against one ray: five 128-bit loads, eight quantised slab tests, and the
 // hit children split into a node group G (inner children, priority-ordered hit bits | imask) and a triangle group T.
+#ifndef B2PT_FFMA2
+#define B2PT_FFMA2 1
+#endif
+// (d0, d1) = (a0, a1) * (b, b) + (c0, c1) as one packed instruction
+__device__ __forceinline__ void ffma2(float a0, float a1, float b, float c0, float c1, float& d0, float& d1) {
+  asm("{\n .reg .b64 ra, rb, rc, rd;\n mov.b64 ra, {%2, %3};\n mov.b64 rb, {%4, %4};\n mov.b64 rc, {%5, %6};\n"
+      " fma.rn.ftz.f32x2 rd, ra, rb, rc;\n mov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b), "f"(c0), "f"(c1));
+}
 struct Node8Data { float4 n0, n1, n2, n3, n4; };
 __device__ __forceinline__ Node8Data node8_load(const DeviceScene& sc, uint32_t child) {
   const float4* nd = sc.nodes8 + size_t(child) * kNode8Float4s;
@@ -171,7 +180,7 @@ __device__ __forceinline__ Node8Data node8_load(const DeviceScene& sc, uint32_t 
   d.n0 = __ldg(nd + 0); d.n1 = __ldg(nd + 1); d.n2 = __ldg(nd + 2); d.n3 = __ldg(nd + 3); d.n4 = __ldg(nd + 4);
   return d;
 }
-__device__ __forceinline__ void node8_test(const Node8Data& d, float3 O, float3 idir, uint32_t oct, float tnear, float tmax, uint2& G, uint2& T) {
+__device__ __forceinline__ void node8_test(const Node8Data& d, float3 O, float3 idir, uint32_t oct, float tnear, float tmax, uint2& G, uint2& T, uint32_t k47) {
   struct { float t; } hit = {tmax};
   const float4 n0 = d.n0, n1 = d.n1, n2 = d.n2, n3 = d.n3, n4 = d.n4;
   const uint32_t hdr = __float_as_uint(n0.w);
@@ -210,9 +219,17 @@ __device__ __forceinline__ void node8_test(const Node8Data& d, float3 O, float3 
   for (int h = 0; h < 2; ++h) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float x0 = __fmaf_rn(byte_to_float15(nx[h], k), adx, oxn), x1 = __fmaf_rn(byte_to_float15(fx[h], k), adx, oxf);
-      const float y0 = __fmaf_rn(byte_to_float15(ny[h], k), ady, oyn), y1 = __fmaf_rn(byte_to_float15(fy[h], k), ady, oyf);
-      const float z0 = __fmaf_rn(byte_to_float15(nz[h], k), adz, ozn), z1 = __fmaf_rn(byte_to_float15(fz[h], k), adz, ozf);
+#if B2PT_FFMA2
+      // entry and exit plane of an axis in ONE packed fp32x2 multiply-add (FFMA2, new with sm_100): 24 instead of 48 per node
+      float x0, x1, y0, y1, z0, z1;
+      ffma2(byte_to_float15(nx[h], k, k47), byte_to_float15(fx[h], k, k47), adx, oxn, oxf, x0, x1);
+      ffma2(byte_to_float15(ny[h], k, k47), byte_to_float15(fy[h], k, k47), ady, oyn, oyf, y0, y1);
+      ffma2(byte_to_float15(nz[h], k, k47), byte_to_float15(fz[h], k, k47), adz, ozn, ozf, z0, z1);
+#else
+      const float x0 = __fmaf_rn(byte_to_float15(nx[h], k, k47), adx, oxn), x1 = __fmaf_rn(byte_to_float15(fx[h], k, k47), adx, oxf);
+      const float y0 = __fmaf_rn(byte_to_float15(ny[h], k, k47), ady, oyn), y1 = __fmaf_rn(byte_to_float15(fy[h], k, k47), ady, oyf);
+      const float z0 = __fmaf_rn(byte_to_float15(nz[h], k, k47), adz, ozn), z1 = __fmaf_rn(byte_to_float15(fz[h], k, k47), adz, ozf);
+#endif
       const float t0 = fmaxf(fmaxf(x0, y0), fmaxf(z0, tnear));
       const float t1 = fminf(fminf(x1, y1), fminf(z1, hit.t)) * 1.0000003f;
       if (t0 <= t1) hits |= ((bits4[h] >> (8 * k)) & 0xFFu) << ((pos4[h] >> (8 * k)) & 0xFFu);
@@ -225,7 +242,7 @@ __device__ __forceinline__ void node8_test(const Node8Data& d, float3 O, float3 
 __device__ __forceinline__ void node8_step(const DeviceScene& sc, uint32_t child, float3 O, float3 idir, uint32_t oct, float tnear, float tmax,
                                            uint2& G, uint2& T) {
   const Node8Data d = node8_load(sc, child);
-  node8_test(d, O, idir, oct, tnear, tmax, G, T);
+  node8_test(d, O, idir, oct, tnear, tmax, G, T, sc.prmt_base);
 }
 
 // kCount (b2pt_debug_trace_counts): counts->x += node steps, counts->y += triangle tests of this ray
@@ -601,6 +618,8 @@ __device__ __forceinline__ void trace_queue8(const DeviceScene& sc, uint32_t n, 
           }
         }
         want = min(unsigned(__popc(T.y)), unsigned(kEnqueuePerRound));
+        // (asking for the lane's next node with prefetch.global.L1 at this point — CCTL.PF1, two per lane and round — was measured at
+        // 58.8 instead of 101.9 Msamples/s: the instruction itself is the cost.  profiles/r02_ab_runs.md, session s34.)
       }
     }
     unsigned incl = want;

@@ -12,6 +12,7 @@ for w in $what; do
   t0=$(date +%s)
   case $w in
     tests) timeout 1800 python -m pytest tests -m gpu -q -rA --durations=15 > gpurun_out/${tag}_tests.log 2>&1; echo "tests rc=$?"; tail -5 gpurun_out/${tag}_tests.log ;;
+    tests_variant) B2PT_LIB=$VARIANT_LIB timeout 900 python -m pytest tests/test_trace_gpu.py tests/test_large_scene_gpu.py tests/test_pt_gpu.py tests/test_bpt_gpu.py -m gpu -q -rA > gpurun_out/${tag}_tests_variant.log 2>&1; echo "tests_variant ($VARIANT_LIB) rc=$?"; tail -3 gpurun_out/${tag}_tests_variant.log ;;
     tests_nosplit) B2PT_SPLIT_BUDGET=0 timeout 900 python -m pytest tests/test_trace_gpu.py tests/test_pt_gpu.py tests/test_bpt_gpu.py -m gpu -q -rA > gpurun_out/${tag}_tests_nosplit.log 2>&1; echo "tests_nosplit rc=$?"; tail -3 gpurun_out/${tag}_tests_nosplit.log ;;
     large_nosplit) B2PT_SPLIT_BUDGET=0 timeout 900 python -m pytest tests/test_large_scene_gpu.py -m gpu -q -rA > gpurun_out/${tag}_large_nosplit.log 2>&1; echo "large_nosplit rc=$?"; grep "^{" gpurun_out/${tag}_large_nosplit.log ;;
     smoke) timeout 300 python __graft_entry__.py --smoke > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/${tag}_smoke.log ;;
