@@ -50,7 +50,8 @@ namespace {
 
 enum : uint32_t { kNew = 0, kLightWait = 1, kLightLoop = 2, kLightFinal = 3, kEyeStart = 4, kEyeWait = 5, kDone = 6 };
 constexpr uint32_t kPairCamera = 0x80000000u;  // descriptor.x bit 31: the eye vertex is the camera (light-image splat)
-constexpr uint32_t kNeeVertex = 0xFFFFFFFFu;   // descriptor.y: the freshly sampled emitter point instead of a stored vertex
+constexpr uint32_t kNeeVertex = 0xFF000000u;   // descriptor.y >= this: the freshly sampled emitter point instead of a stored vertex; low 24 bits = light id
+                                               // (so the connect stage asks for the light's record together with the vertices, not after the path record's word)
 constexpr uint32_t kShadowSplat = 1u;
 constexpr int kVertexFloat4s = 7;
 constexpr int kRecFloat4s = 16;
@@ -90,7 +91,8 @@ struct BptPool {
   // cost 2.5x their size in HBM traffic once most neighbours of a live slot are dead (ncu, profiles/).
   //   float4 0..6  current vertex (pack_vertex)            7  pending BSDF sample: throughput.xyz, density_rev
   //   8  pending BSDF sample: omega.xyz, density           9  extension ray origin, w = bits(bsdf.finite | ray mask selector << 1)
-  //   10 hit: t, u, v, bits(triangle)                      11 eye-path radiance (float atomics from the shadow stage)
+  //   10 hit: t, u, v, bits(triangle) — only with ray sorting; otherwise hits live in hit_q, in queue order
+  //   11 eye-path radiance (float atomics from the shadow and logic stages)
   //   12 bits(rng key, rng counter, light path head, light path count)
   //   14 next-event sample: position, bits(light id)       15 its emitter's lobe restriction (light_lobe_adjust), -, -, -
   // (14 and 15 share one 32-byte sector and are written together.)  The state of a live path is not stored: it waits for the hit of
@@ -100,6 +102,7 @@ struct BptPool {
   float4* lv;        // light vertex pool, AoS: 7 float4 per vertex
   uint32_t* lv_link; // previous vertex of the same path
   uint32_t* lp_idx;  // the first kLpTable vertices of every light path by position: lp_idx[slot * kLpTable + k], one 128-byte line per path
+  float4* hit_q;         // closest hits in QUEUE order: hit_q[position in trace_q] (t, u, v, bits(triangle)), written by the closest-hit stage
   uint32_t* trace_q[2];  // live slots = the slots with an extension ray in flight; written by the logic stage of iteration i into [i & 1]
   // ray sorting (B2PT_SORT_RAYS): the logic stage writes one key per entry of the live queue and counts the keys; a scan and a scatter
   // then lay the queue out in key order in sort_q, each end on its own, for the TRAVERSAL stage only — the next logic stage keeps
@@ -274,7 +277,7 @@ __global__ void __launch_bounds__(256) bpt_sort_scatter_kernel(BptPool pool, Bpt
   }
 }
 
-// ---------------------------------------------------------------- staging of gathered records through shared memory
+// ---------------------------------------------------------------- staging of gathered records through shared memory (A/B: B2PT_STAGED=2)
 // The shading stages reach their records through queues, i.e. as gathers: every item costs one or two dependent round trips to HBM
 // before any arithmetic can start (56 % / 47 % of the warp-state samples of the logic / connect stage were long-scoreboard stalls,
 // profiles/r02_bpt_logic_full_v4_summary.md), and asking for the next item's words early in registers spills (128 registers, measured
@@ -282,6 +285,9 @@ __global__ void __launch_bounds__(256) bpt_sort_scatter_kernel(BptPool pool, Bpt
 // NEXT item's words right after it has read the current item's out of its own staging column, and the copy lands while it computes.
 // Every thread owns one column [word][threadIdx.x] (conflict-free 128-bit accesses) and reads only what it copied itself, so the only
 // synchronisation is the thread's own cp.async.wait_all.
+// MEASURED NEGATIVE (profiles/r02_ab_runs.md, s31 / s32): 100.3 -> 96.3 Msamples/s for the connect stage, 93.0 for the logic stage
+// (double-buffered, 96 KB per CTA; that variant was removed again) — CTAs that hold this much shared memory cannot share an SM with
+// the other lane's traversal CTAs, and that overlap is worth more than the round trips.  The connect stage keeps the switch.
 __device__ __forceinline__ void cp_async16(float4* smem_dst, const float4* gmem_src) {
   const uint32_t d = uint32_t(__cvta_generic_to_shared(smem_dst));
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
@@ -293,20 +299,15 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // extension ray, so the trace queue the previous iteration wrote is exactly the list of live slots (`first` = iteration 0
 // of a batch walks every slot instead).  A pool-order loop would leave a warp with as many busy lanes as the pool has
 // live paths — 4 of 32 halfway through a batch (ncu, profiles/).
-// kStaged (never with `first`): the path record of a thread's NEXT item is copied to shared memory while the current one is worked
-// on (cp.async, above).  Two buffers: the words of the current item are read out of shared memory where they are used — the buffer
-// serves as an extension of the register file (holding a whole record in registers next to the prefetch state spilled 300 bytes) —
-// while the copy of the next item lands in the other one.  The launch is one wave of resident CTAs and needs kLogicStageBytes of
-// dynamic shared memory.
-constexpr int kLogicStageWords = 12;  // words 0..10 of the record (vertex, pending sample, ray origin, hit) and the control word
-constexpr size_t kLogicStageBytes = size_t(2 * kLogicStageWords) * 256 * sizeof(float4);
-__host__ __device__ constexpr int logic_stage_index(int word) { return word == kRecCtl ? 11 : word; }
 // kEnd: 0 = both ends of the live queue (and the first iteration of a batch), 1 = the eye end only, 2 = the light end only — the two
 // halves of the stage as kernels of their own (B2PT_LOGIC_SPLIT): each holds one subpath's code and state.
-template <bool kStaged, int kEnd>
+//
+// Dependent round trips per item: queue entry + hit (both by queue POSITION, coalesced: the closest-hit stage stores its hits in queue
+// order, BptPool::hit_q) -> path record + shading record of the hit triangle, asked for together -> arithmetic.  (With the hit inside
+// the path record the shading record was a third round trip: 13 % of the stage's warp-state samples.)
+template <int kEnd>
 __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_LOGIC_SPLIT_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
                                                                                int first, int sort) {
-  extern __shared__ float4 s_stage[];
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     // trace_count[parity ^ 1] is this launch's input; the closest-hit stage clears it afterwards
@@ -330,48 +331,34 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
   const uint32_t* live_q = pool.trace_q[parity ^ 1];
   uint32_t* next_q = pool.trace_q[parity];
   const uint32_t stride = gridDim.x * blockDim.x;
-  // which slot entry i of the two-ended queue names (eye end first, each end rounded up to whole warps)
-  auto item = [&](uint32_t i, bool& on, bool& eye) -> uint32_t {
-    eye = i < n_eye_round;
-    const uint32_t j = eye ? i : i - n_eye_round;
-    on = j < (eye ? n_eye : n_light);
-    return on ? (first ? j : live_q[eye ? j : pool.size - 1u - j]) : 0u;
-  };
-  float4* mine = s_stage + threadIdx.x;
-  auto stage = [&](uint32_t slot, uint32_t buf) {
-    const float4* src = pool.rec + size_t(slot) * kRecFloat4s;
-    float4* dst = mine + buf * (kLogicStageWords * 256);
-#pragma unroll
-    for (int k = 0; k <= kRecHit; ++k) cp_async16(dst + k * 256, src + k);
-    cp_async16(dst + logic_stage_index(kRecCtl) * 256, src + kRecCtl);
-  };
-  uint32_t pre_slot = 0, pre2_slot = 0, sbuf = 0;
-  bool pre_on = false, pre_eye = false, pre2_on = false, pre2_eye = false;
-  if (kStaged) {
-    const uint32_t i0 = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i0 < n_round) { pre_slot = item(i0, pre_on, pre_eye); if (pre_on) stage(pre_slot, 0u); }
-    cp_async_commit();
-    if (i0 + stride < n_round) pre2_slot = item(i0 + stride, pre2_on, pre2_eye);
-  }
+  const bool hit_by_position = sort == 0;  // with ray sorting the closest-hit stage walks another order and leaves its hits in the records
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
-    bool eye_end, lane_on;
-    uint32_t slot;
-    const float4* staged_rec = mine + sbuf * (kLogicStageWords * 256);
-    if (kStaged) {
-      eye_end = pre_eye; lane_on = pre_on; slot = pre_slot;
-      cp_async_wait_all();
-      // ask for the next item's record (into the other buffer), and for the queue entry after that
-      sbuf ^= 1u;
-      pre_slot = pre2_slot; pre_on = pre2_on; pre_eye = pre2_eye;
-      if (i + stride < n_round && pre_on) stage(pre_slot, sbuf);
-      cp_async_commit();
-      pre2_on = false;
-      if (i + stride < n_round && i + 2u * stride < n_round) pre2_slot = item(i + 2u * stride, pre2_on, pre2_eye);
-    } else {
-      slot = item(i, lane_on, eye_end);
+    // entry i of the two-ended queue: eye end first, each end rounded up to whole warps
+    const bool eye_end = i < n_eye_round;
+    const uint32_t j = eye_end ? i : i - n_eye_round;
+    const bool lane_on = j < (eye_end ? n_eye : n_light);
+    const uint32_t qpos = eye_end ? j : pool.size - 1u - j;
+    uint32_t slot = 0u;
+    float4 hv = make_float4(0.f, 0.f, 0.f, __uint_as_float(kInvalid));
+    if (lane_on) {
+      if (first) {
+        slot = j;
+      } else {
+        slot = live_q[qpos];
+        if (hit_by_position) hv = pool.hit_q[qpos];
+      }
     }
     float4* rec = pool.rec + size_t(slot) * kRecFloat4s;
-#define B2PT_REC(k) (kStaged ? staged_rec[logic_stage_index(k) * 256] : rec[k])
+    if (lane_on && !first && !hit_by_position) hv = rec[kRecHit];
+    // the shading record of the hit triangle, asked for here, next to the path record below
+    SurfaceRaw raw;
+    const bool has_tri = lane_on && !first && __float_as_uint(hv.w) != kInvalid;
+    if (has_tri) load_surface_early(sc, __float_as_uint(hv.w), raw);
+    // first entry of the path's vertex table, asked for now: the pair expansion at the end finds the table's line in L1
+    // (its loads used to start a round trip of their own after all the arithmetic: 5 % of the stage's warp-state samples)
+    uint32_t lp_first = 0u;
+    if (lane_on && !first) lp_first = pool.lp_idx[size_t(slot) * kLpTable];
+#define B2PT_REC(k) (rec[k])
     // iteration 0 of a batch never reads the records: every slot is born kNew.  Afterwards a live path waits for the hit of its
     // extension ray, and which end of the queue it sits at says for which subpath: the state is not stored.
     const uint32_t st0 = !lane_on ? uint32_t(kDone) : kEnd == 1 ? uint32_t(kEyeWait) : kEnd == 2 ? uint32_t(kLightWait)
@@ -380,12 +367,12 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
     bool want_trace = false, finished = false;
     uint32_t emit_n = 0, emit_flags = 0;  // pair descriptors to write after the branches
     bool emit_nee = false, emit_skip_first = false;
+    uint32_t nee_light = 0;
     uint32_t head = kInvalid, count = 0;
     uint32_t ray_mesh_only = 0;
     int sample_kind = 0;  // the BSDF sample this item needs, taken at ONE place below: 1 = light subpath goes on, 2 = its last vertex, 3 = eye subpath
     float3 O = f3(0.f), rad = f3(0.f);  // rad: what this iteration adds to the path's radiance (emission through a light, the sky)
     bool rad_add = false;
-    float4 hv = make_float4(0.f, 0.f, 0.f, 0.f);
     Rng rng; rng.key = 0; rng.ctr = 0;
     Vertex cur;
     BsdfSample bs;
@@ -421,6 +408,7 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
             store_pool_vertex(pool, idx, cur);
             pool.lv_link[idx] = kInvalid;
             pool.lp_idx[size_t(slot) * kLpTable] = idx;
+            lp_first = idx;
             head = idx; count = 1;
             cur_dirty = true;
             st = kLightLoop;
@@ -441,7 +429,6 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
         bs.throughput = f3(bt.x, bt.y, bt.z); bs.density_rev = bt.w;
         bs.finite = __float_as_uint(ro.w) & 1u;
         O = f3(ro.x, ro.y, ro.z);
-        hv = B2PT_REC(kRecHit);
       }
 #undef B2PT_REC
 
@@ -453,7 +440,8 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
         } else {
           Vertex nv;
           nv.ladj = -1.0f;
-          nv.s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, bs.omega);
+          load_surface_rest(sc, tri, raw);
+          nv.s = query_surface_raw(raw, hv.y, hv.z, hv.x, O, bs.omega);
           nv.omega = -bs.omega;
           const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
           nv.thr = cur.thr * bs.throughput * edge.b_cos * roulette_inv;
@@ -511,7 +499,8 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
         } else {
           Vertex nv;
           nv.ladj = -1.0f;
-          nv.s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, bs.omega);
+          load_surface_rest(sc, tri, raw);
+          nv.s = query_surface_raw(raw, hv.y, hv.z, hv.x, O, bs.omega);
           nv.omega = -bs.omega;
           const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
           nv.thr = cur.thr * bs.throughput * edge.b_cos;
@@ -543,6 +532,7 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
                   if (!ls.directional) {
                     emit_nee = true;
                     const uint32_t light_id = sc.materials[ls.surface.material_index()].light_id;
+                    nee_light = light_id & 0x00FFFFFFu;
                     rec[kRecNee] = make_float4(ls.surface.pos.x, ls.surface.pos.y, ls.surface.pos.z, __uint_as_float(light_id));
                     // the emitter's lobe restriction at this point: computed here, where every lane of the warp samples a light, instead of
                     // in the connect stage, where one pair in six needs it and the other lanes of its warp would wait for it
@@ -689,7 +679,7 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
       if (pq + emit_n > pool.q_capacity) {
         atomicAdd(&cnt->capacity_events, 1ull);
       } else {
-        if (emit_nee) pool.pair_q[pq++] = make_uint2(slot, kNeeVertex);
+        if (emit_nee) pool.pair_q[pq++] = make_uint2(slot, kNeeVertex | nee_light);
         // vertices kLpTable .. count-1 hang off the head of the chain; the rest come from the position table, four loads in flight
         uint32_t v = head;
         for (uint32_t k = count; k > kLpTable; --k) {
@@ -700,7 +690,7 @@ __global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_
         const uint4* table = reinterpret_cast<const uint4*>(pool.lp_idx + size_t(slot) * kLpTable);
         for (uint32_t k = 0; k < kt; k += 4u) {
           const uint4 a4 = table[k >> 2];
-          const uint32_t a[4] = {a4.x, a4.y, a4.z, a4.w};
+          const uint32_t a[4] = {k == 0u ? lp_first : a4.x, a4.y, a4.z, a4.w};
 #pragma unroll
           for (uint32_t j = 0; j < 4u; ++j)
             if (k + j < kt && !(emit_skip_first && k + j == 0u)) pool.pair_q[pq++] = make_uint2(slot | emit_flags, a[j]);
@@ -795,7 +785,7 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel
     const float4* rec = pool.rec + size_t(desc.x & ~kPairCamera) * kRecFloat4s;
 #pragma unroll
     for (int k = 0; k < kVertexFloat4s; ++k) cp_async16(mine + k * 256, rec + k);
-    if (desc.y == kNeeVertex) {
+    if (desc.y >= kNeeVertex) {
       cp_async16(mine + kVertexFloat4s * 256, rec + kRecNee);
       cp_async16(mine + (kVertexFloat4s + 1) * 256, rec + kRecLadj);
     } else {
@@ -833,9 +823,9 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel
         const uint32_t slot = dcur.x & ~kPairCamera;
         const Vertex eye = unpack_vertex(q);
         Vertex light;
-        if (dcur.y == kNeeVertex) {
+        if (dcur.y >= kNeeVertex) {
           const float4 nr = q[kVertexFloat4s];
-          light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), roulette_inv, beta, q[kVertexFloat4s + 1].x);
+          light = sample_to_vertex(light_sample_at(sc, dcur.y & 0x00FFFFFFu, f3(nr.x, nr.y, nr.z)), roulette_inv, beta, q[kVertexFloat4s + 1].x);
         } else {
           light = unpack_vertex(q + kVertexFloat4s);
         }
@@ -846,9 +836,9 @@ __global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel
       const uint32_t slot = d.x & ~kPairCamera;
       const Vertex eye = load_slot_vertex(pool, slot);
       Vertex light;
-      if (d.y == kNeeVertex) {
+      if (d.y >= kNeeVertex) {
         const float4 nr = pool.rec[size_t(slot) * kRecFloat4s + kRecNee];
-        light = sample_to_vertex(light_sample_at(sc, __float_as_uint(nr.w), f3(nr.x, nr.y, nr.z)), roulette_inv, beta,
+        light = sample_to_vertex(light_sample_at(sc, d.y & 0x00FFFFFFu, f3(nr.x, nr.y, nr.z)), roulette_inv, beta,
                                  pool.rec[size_t(slot) * kRecFloat4s + kRecLadj].x);
       } else {
         light = load_pool_vertex(pool, d.y);
@@ -865,24 +855,28 @@ struct BptTraceIo {
   const uint32_t* q;
   uint32_t n_eye;  // entries [0, n_eye) from the front of the queue, the rest from its back
   const unsigned* oct_count;  // non-null: q is the array of eight octant queues and ray i is found through the prefix of the counts
+  bool by_position;  // the hit goes to hit_q[queue position] (the logic stage reads it with the queue entry); else into the path record
   __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
-    uint32_t slot;
+    uint32_t slot, pos = 0u;
     if (oct_count) {
       uint32_t o = 0, j = i;
 #pragma unroll
       for (int k = 0; k < 7; ++k) { const uint32_t c = oct_count[k]; if (o == uint32_t(k) && j >= c) { j -= c; ++o; } }
       slot = q[size_t(o) * pool->size + j];
     } else {
-      slot = q[i < n_eye ? i : pool->size - 1u - (i - n_eye)];
+      pos = i < n_eye ? i : pool->size - 1u - (i - n_eye);
+      slot = q[pos];
     }
     const float4* rec = pool->rec + size_t(slot) * kRecFloat4s;
     const float4 o = rec[kRecRayO], d = rec[kRecOmega];
     O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY;
     mask = (__float_as_uint(o.w) & 2u) ? kMaskMesh : kMaskAll;  // Scene::intersectMesh (light subpaths) / Scene::intersect
-    return slot;
+    return by_position ? pos : slot;
   }
-  __device__ __forceinline__ void store(uint32_t slot, const Hit& h) const {
-    pool->rec[size_t(slot) * kRecFloat4s + kRecHit] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+  __device__ __forceinline__ void store(uint32_t tag, const Hit& h) const {
+    const float4 v = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+    if (by_position) pool->hit_q[tag] = v;
+    else pool->rec[size_t(tag) * kRecFloat4s + kRecHit] = v;
   }
 };
 struct BptShadowIo {
@@ -918,7 +912,7 @@ __global__ void __launch_bounds__(256, B2PT_TRACE_MIN_BLOCKS) bpt_trace_kernel(R
     cnt->trace_count[parity ^ 1] = 0;  // consumed by this iteration's logic stage; the next one appends to it
     cnt->light_count[parity ^ 1] = 0;
   }
-  BptTraceIo io{&pool, sorted == 2 ? pool.oct_q : sorted == 1 ? pool.sort_q : pool.trace_q[parity], n_eye, sorted == 2 ? cnt->oct_count[parity] : nullptr};
+  BptTraceIo io{&pool, sorted == 2 ? pool.oct_q : sorted == 1 ? pool.sort_q : pool.trace_q[parity], n_eye, sorted == 2 ? cnt->oct_count[parity] : nullptr, sorted == 0};
   if (kStream == 3) { trace_queue8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   if (kStream == 2) { trace_dyn8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
   if (kStream == 1) { trace_stream8<false>(cfg.scene, n, &cnt->ticket[0], io); return; }
@@ -1054,6 +1048,7 @@ int bpt_workspace(b2pt_scene_s* scene, uint32_t size, uint32_t per_path, int lan
     if ((rc = ws_alloc(w, &p.lv, size_t(p.lv_capacity) * kVertexFloat4s))) return rc;
     if ((rc = ws_alloc(w, &p.lv_link, p.lv_capacity))) return rc;
     if ((rc = ws_alloc(w, &p.lp_idx, size_t(size) * kLpTable))) return rc;
+    if ((rc = ws_alloc(w, &p.hit_q, size))) return rc;
     if ((rc = ws_alloc(w, &p.trace_q[0], size))) return rc;
     if ((rc = ws_alloc(w, &p.trace_q[1], size))) return rc;
     if (bpt_sort_mode() == 2) { if ((rc = ws_alloc(w, &p.oct_q, size_t(size) * 8))) return rc; }
@@ -1099,6 +1094,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   while (batch_paths > pixels && uint64_t(batch_paths) * per_path > (uint64_t(12) << 23)) batch_paths >>= 1;
   uint32_t passes_per_batch = batch_paths / pixels;
   if (passes_per_batch < 1) passes_per_batch = 1;
+  B2_CHECK(base.scene.num_lights < (1u << 24), B2PT_ERR_INVALID, "render_bpt: more than 2^24 lights (the pair descriptor carries the light id in 24 bits)");
   const int kLanes = bpt_lanes();
   if (passes_per_batch > (num_passes + kLanes - 1) / kLanes) passes_per_batch = (num_passes + kLanes - 1) / kLanes;
   const uint32_t num_batches = (num_passes + passes_per_batch - 1) / passes_per_batch;
@@ -1120,25 +1116,21 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       const size_t want = (size_t(size) + v - 1) / v, cap = size_t(kNumSMs) * 8 * (block / v);  // the same number of threads in flight
       shade_grid = int(std::min(want < 1 ? size_t(1) : want, cap));
   } } }
-  // Shading stages with their gathers staged through shared memory (cp.async, see bpt_logic_kernel): one wave of resident CTAs.
-  // B2PT_STAGED=0 keeps the plain loads for A/B runs (2: connect stage only, 3: logic stage only).
-  bool staged_logic = false, staged_connect = false;
-  { const char* e = getenv("B2PT_STAGED"); if (e && shade_block == block) { staged_logic = e[0] == '1' || e[0] == '3'; staged_connect = e[0] == '1' || e[0] == '2'; } }
-  const bool staged = staged_logic || staged_connect;
-  // B2PT_LOGIC_SPLIT=1: the logic stage as two kernels, one per end of the live queue (light subpaths, then eye subpaths)
-  bool logic_split = false;
-  { const char* e = getenv("B2PT_LOGIC_SPLIT"); if (e) logic_split = e[0] == '1'; }
+  // Connect stage with its gathers staged through shared memory (cp.async, see above; measured negative): B2PT_STAGED=2
+  bool staged_connect = false;
+  { const char* e = getenv("B2PT_STAGED"); if (e && shade_block == block) staged_connect = e[0] == '2'; }
   int staged_grid = std::min(grid, kNumSMs * B2PT_LOGIC_MIN_BLOCKS);
   { const char* e = getenv("B2PT_STAGED_GRID"); if (e) { const int v = atoi(e); if (v >= 1 && v <= 8) staged_grid = std::min(grid, kNumSMs * v); } }
-  if (staged) {
-    static bool configured = false;  // per process; the attribute is per function and device-independent in effect
+  if (staged_connect) {
+    static bool configured = false;  // per process; the attribute is per function
     if (!configured) {
-      B2_CUDA(cudaFuncSetAttribute(bpt_logic_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kLogicStageBytes)));
-      B2_CUDA(cudaFuncSetAttribute(bpt_logic_kernel<true, 0>, cudaFuncAttributePreferredSharedMemoryCarveout, int(cudaSharedmemCarveoutMaxShared)));
       B2_CUDA(cudaFuncSetAttribute(bpt_connect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kConnectStageBytes)));
       configured = true;
     }
   }
+  // B2PT_LOGIC_SPLIT=1: the logic stage as two kernels, one per end of the live queue (light subpaths, then eye subpaths)
+  bool logic_split = false;
+  { const char* e = getenv("B2PT_LOGIC_SPLIT"); if (e) logic_split = e[0] == '1'; }
   // traversal form per stage: 0 = one ray per thread, 1 = persistent warps with dynamic fetch, 2 = the same plus postponed triangle
   // groups (trace.cuh: trace_dyn8), 3 = warp-synchronous rounds with a shared triangle queue (trace_queue8, the default).
   // B2PT_TRACE_STREAM / B2PT_SHADOW_STREAM select them for A/B runs; measured on the LivingRoom stand-in with 2^23-path batches:
@@ -1194,11 +1186,10 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       for (int j = 0; j < kBatchIters; ++j, ++g.it) {
         const int parity = g.it & 1;
         timer.begin(kStageShade);
-        if (staged_logic && g.it > 0) bpt_logic_kernel<true, 0><<<staged_grid, block, kLogicStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
-        else if (logic_split && g.it > 0) {
-          bpt_logic_kernel<false, 2><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
-          bpt_logic_kernel<false, 1><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
-        } else bpt_logic_kernel<false, 0><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays);
+        if (logic_split && g.it > 0) {
+          bpt_logic_kernel<2><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
+          bpt_logic_kernel<1><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
+        } else bpt_logic_kernel<0><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays);
         timer.end();
         timer.begin(kStageShade);
         if (staged_connect) bpt_connect_kernel<true><<<staged_grid, block, kConnectStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity);

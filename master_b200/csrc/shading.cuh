@@ -64,11 +64,34 @@ __device__ __forceinline__ float pow_beta(float x, float beta) {  // std::pow(x,
 }
 
 // ---------------------------------------------------------------- Scene::querySurface (Scene.cpp:80-126)
-__device__ __forceinline__ Surface query_surface(const DeviceScene& sc, uint32_t tri, float u, float v, float t, float3 org,
-                                                 float3 dir) {
+// The words of triangle `tri` querySurface needs: its shading record (7 float4) and the two edge words of its intersection record.
+// Split from the arithmetic so that a stage can ask for them as soon as it knows the triangle, next to its other loads.
+struct SurfaceRaw { float4 a[7]; float4 q1, q2; };
+__device__ __forceinline__ SurfaceRaw load_surface_raw(const DeviceScene& sc, uint32_t tri) {
   const float4* fr = sc.tri_frames + size_t(tri) * kFrameFloat4s;
-  const float4 a0 = __ldg(fr + 0), a1 = __ldg(fr + 1), a2 = __ldg(fr + 2), a3 = __ldg(fr + 3), a4 = __ldg(fr + 4),
-               a5 = __ldg(fr + 5), a6 = __ldg(fr + 6);
+  SurfaceRaw r;
+#pragma unroll
+  for (int k = 0; k < 7; ++k) r.a[k] = __ldg(fr + k);
+  r.q1 = __ldg(sc.tris + size_t(tri) * kTriFloat4s + 1);
+  r.q2 = __ldg(sc.tris + size_t(tri) * kTriFloat4s + 2);
+  return r;
+}
+// The same in two steps for a stage short of registers: the first and the last word of the shading record and one edge word are asked
+// for early (they pull the record's one or two 128-byte lines and the triangle's sector into L1), the other six words where they are used.
+__device__ __forceinline__ void load_surface_early(const DeviceScene& sc, uint32_t tri, SurfaceRaw& r) {
+  const float4* fr = sc.tri_frames + size_t(tri) * kFrameFloat4s;
+  r.a[0] = __ldg(fr + 0);
+  r.a[6] = __ldg(fr + 6);
+  r.q1 = __ldg(sc.tris + size_t(tri) * kTriFloat4s + 1);
+}
+__device__ __forceinline__ void load_surface_rest(const DeviceScene& sc, uint32_t tri, SurfaceRaw& r) {
+  const float4* fr = sc.tri_frames + size_t(tri) * kFrameFloat4s;
+#pragma unroll
+  for (int k = 1; k < 6; ++k) r.a[k] = __ldg(fr + k);
+  r.q2 = __ldg(sc.tris + size_t(tri) * kTriFloat4s + 2);
+}
+__device__ __forceinline__ Surface query_surface_raw(const SurfaceRaw& raw, float u, float v, float t, float3 org, float3 dir) {
+  const float4 a0 = raw.a[0], a1 = raw.a[1], a2 = raw.a[2], a3 = raw.a[3], a4 = raw.a[4], a5 = raw.a[5], a6 = raw.a[6];
   const float m[28] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w, a2.x, a2.y, a2.z, a2.w, a3.x, a3.y,
                        a3.z, a3.w, a4.x, a4.y, a4.z, a4.w, a5.x, a5.y, a5.z, a5.w, a6.x, a6.y, a6.z, a6.w};
   const float w = 1.f - u - v;
@@ -85,7 +108,7 @@ __device__ __forceinline__ Surface query_surface(const DeviceScene& sc, uint32_t
   t2 = normalize(t2);
   p.tan.c0 = t0; p.tan.c1 = t1; p.tan.c2 = t2;
   // RayIsect::gnormal() = normalize(-Ng) with Embree's Ng = cross(e1, e2) (triangle.h:54)
-  const float4 q1 = __ldg(sc.tris + size_t(tri) * kTriFloat4s + 1), q2 = __ldg(sc.tris + size_t(tri) * kTriFloat4s + 2);
+  const float4 q1 = raw.q1, q2 = raw.q2;
   const float3 e1 = f3(q1.x, q1.y, q1.z), e2 = f3(q2.x, q2.y, q2.z);
   const float3 Ng = f3(e1.y * e2.z - e1.z * e2.y, e1.z * e2.x - e1.x * e2.z, e1.x * e2.y - e1.y * e2.x);
   float3 gn = normalize(-Ng);
@@ -94,6 +117,11 @@ __device__ __forceinline__ Surface query_surface(const DeviceScene& sc, uint32_t
   p.gnormal = gn;
   p.material_id = __float_as_uint(m[27]);
   return p;
+}
+__device__ __forceinline__ Surface query_surface(const DeviceScene& sc, uint32_t tri, float u, float v, float t, float3 org,
+                                                 float3 dir) {
+  const SurfaceRaw raw = load_surface_raw(sc, tri);
+  return query_surface_raw(raw, u, v, t, org, dir);
 }
 
 // Ray origin of Scene::intersect / intersectMesh (Scene.cpp:186-189): 1e-4 along +-gnormal
