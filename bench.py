@@ -461,16 +461,18 @@ def main():
         except Exception as e:  # pragma: no cover
             cpu = {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "failed: %s" % e}
 
+    l2w = scene.l2_window()
     line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": N, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": t_ms / a.steps, "higher_is_better": True, "scaling": a.scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": config, "mrays_per_s": mrays,
             "rays_per_sample": float(counts[0] + counts[1]) / samples,
             "gpu_launches": int(counts[2].item()), "e2e": e2e, "e2e_1pass": e2e_1pass, "roofline": roofline, "cpu_baseline": cpu,
             "clocks": sampler.summary(), "film_ok": film_ok, "film_check": film_check,
-            "l2_policy": "inputs larger than L2: scene %.0f MB (BVH %.0f MB + shading frames) + path pools > 126 MB; the BVH block is "
-                         "pinned in persisting L2 (cudaAccessPolicyWindow), pools stream through the rest" % (
-                             (info["bvh_bytes"] + info["triangles"] * 112) / 1e6, info["bvh_bytes"] / 1e6),
-            "scene_info": info, "l2_window": scene.l2_window(), "numeric_errors": tot["numeric_errors"], "capacity_events": tot["capacity_events"]}
+            "l2_policy": "inputs larger than L2: scene %.0f MB (BVH %.0f MB + shading frames) + path pools > 126 MB, no flush needed; %s" % (
+                (info["bvh_bytes"] + info["triangles"] * 112) / 1e6, info["bvh_bytes"] / 1e6,
+                "the BVH block is pinned in persisting L2 (cudaAccessPolicyWindow, B2PT_L2_PERSIST=1), pools stream through the rest"
+                if l2w.get("window_bytes") else "no persisting-L2 window (measured slower, profiles/r02_ab_runs.md): plain LRU"),
+            "scene_info": info, "l2_window": l2w, "numeric_errors": tot["numeric_errors"], "capacity_events": tot["capacity_events"]}
     emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -37,6 +37,18 @@
 // shading frame across grid strides was measured too: 72.8 vs 74.7 — with two batches in flight the other batch's kernels already fill the stalls.)
 #define B2PT_LOGIC_MIN_BLOCKS 2
 #endif
+#ifndef B2PT_LOGIC_THREADS
+#define B2PT_LOGIC_THREADS 256  // largest CTA the shading stages are compiled for; with B2PT_LOGIC_MIN_BLOCKS it sets the register cap
+#endif
+// The connect stage fits 96 registers with 36 bytes of spills: 128-thread CTAs, five per SM (20 warps instead of 16) measured
+// 102.15 / 102.12 against 101.75 / 101.71 Msamples/s (256 x 2) and 101.74 (128 x 4, the same registers); the logic stage spills
+// 418 bytes at that cap and stays at 256 x 2.
+#ifndef B2PT_CONNECT_THREADS
+#define B2PT_CONNECT_THREADS 128
+#endif
+#ifndef B2PT_CONNECT_MIN_BLOCKS
+#define B2PT_CONNECT_MIN_BLOCKS 5
+#endif
 #ifndef B2PT_LOGIC_SPLIT_MIN_BLOCKS
 #define B2PT_LOGIC_SPLIT_MIN_BLOCKS 2
 #endif
@@ -306,7 +318,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // order, BptPool::hit_q) -> path record + shading record of the hit triangle, asked for together -> arithmetic.  (With the hit inside
 // the path record the shading record was a third round trip: 13 % of the stage's warp-state samples.)
 template <int kEnd>
-__global__ void __launch_bounds__(256, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_LOGIC_SPLIT_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
+__global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_LOGIC_SPLIT_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
                                                                                int first, int sort) {
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -770,7 +782,7 @@ __device__ __forceinline__ void connect_emit(const BptPool& pool, BptCounters* c
 constexpr int kConnectStageWords = 2 * kVertexFloat4s;
 constexpr size_t kConnectStageBytes = size_t(kConnectStageWords) * 256 * sizeof(float4);
 template <bool kStaged>
-__global__ void __launch_bounds__(256, B2PT_LOGIC_MIN_BLOCKS) bpt_connect_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
+__global__ void __launch_bounds__(kStaged ? 256 : B2PT_CONNECT_THREADS, kStaged ? 2 : B2PT_CONNECT_MIN_BLOCKS) bpt_connect_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity) {
   extern __shared__ float4 s_stage[];
   const DeviceScene& sc = cfg.scene;
   const uint32_t n = min(cnt->pair_count[parity], pool.q_capacity);
@@ -1116,6 +1128,9 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       const size_t want = (size_t(size) + v - 1) / v, cap = size_t(kNumSMs) * 8 * (block / v);  // the same number of threads in flight
       shade_grid = int(std::min(want < 1 ? size_t(1) : want, cap));
   } } }
+  // the connect stage may be compiled for smaller CTAs and a lower register cap than the logic stage (-DB2PT_CONNECT_THREADS / _MIN_BLOCKS)
+  const int connect_block = std::min(shade_block, int(B2PT_CONNECT_THREADS));
+  const int connect_grid = int(std::min((size_t(size) + connect_block - 1) / connect_block, size_t(kNumSMs) * 8 * (block / connect_block)));
   // Connect stage with its gathers staged through shared memory (cp.async, see above; measured negative): B2PT_STAGED=2
   bool staged_connect = false;
   { const char* e = getenv("B2PT_STAGED"); if (e && shade_block == block) staged_connect = e[0] == '2'; }
@@ -1193,7 +1208,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
         timer.end();
         timer.begin(kStageShade);
         if (staged_connect) bpt_connect_kernel<true><<<staged_grid, block, kConnectStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity);
-        else bpt_connect_kernel<false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
+        else bpt_connect_kernel<false><<<connect_grid, connect_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity);
         timer.end();
         if (cfg.scene.has_directional) {
           timer.begin(kStageTrace);
