@@ -722,7 +722,10 @@ __device__ __forceinline__ void connect_pair(const RenderConfig& cfg, const BptP
                                              const Vertex& light, float beta, PairOut& o) {
   const DeviceScene& sc = cfg.scene;
   o.want = false; o.a = f3(0.f); o.d = f3(0.f); o.c = f3(0.f); o.target = 0; o.flags = 0;
+  // ONE evaluation of the connection for camera pairs and eye-vertex pairs alike (two call sites were two copies of both BSDF switches:
+  // the stage spent 10 % of its warp-state samples waiting for instructions)
   bool inside = true;
+  float cc = 1.0f;
   if (camera) {
     // Technique::_accumulate (Technique.cpp:276-305): which pixel the light vertex projects to
     const float3 omega = normalize(light.s.pos - eye.s.pos);
@@ -736,12 +739,14 @@ __device__ __forceinline__ void connect_pair(const RenderConfig& cfg, const BptP
       const uint32_t pixel = uint32_t(int(pp.y)) * cfg.params.width + uint32_t(int(pp.x));
       o.target = (slot / cfg.pixels) * cfg.pixels + pixel;  // same pass, other pixel
       o.flags = kShadowSplat;
-      const float cc = camera_coefficient(light.omega, light.s.gnormal, light.s.normal(), omega, eye.s.normal());
-      o.c = connect_vertices(sc, light, eye, beta) * cfg.focal_factor_y * cc;
+      cc = camera_coefficient(light.omega, light.s.gnormal, light.s.normal(), omega, eye.s.normal());
     }
   } else {
     o.target = slot;
+  }
+  if (inside) {
     o.c = connect_vertices(sc, light, eye, beta);
+    if (camera) o.c = o.c * cfg.focal_factor_y * cc;
   }
   if (inside) {
     const float l1 = l1norm(o.c);

@@ -137,7 +137,7 @@ __device__ B2PT_MATH_INLINE float cr_powf_slow(float x, float y) {
 // all BSDF queries of a connection): pow(+0, y > 0) = +0 and pow(1, y) = 1 exactly (C11 F.10.4.4), without the call — the general
 // double pow those arguments used to fall into was 6 % of the connect stage's warp instructions at 9 lanes.
 __device__ __forceinline__ float cr_powf(float x, float y) {
-  if (x == 1.0f) return 1.0f;
+  if (x == 1.0f || y == 0.0f) return 1.0f;  // pow(1, y) = pow(x, +-0) = 1 for every x and y, NaN included: a Phong exponent of 0 is a legal material
   if (x == 0.0f && y > 0.0f && __float_as_uint(x) == 0u) return 0.0f;
   return cr_powf_slow(x, y);
 }

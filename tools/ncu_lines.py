@@ -37,16 +37,21 @@ def main():
             lines.setdefault(cur, dict(src=r[1].strip()[:100], inst=0, thr=0, samp=0, lsb=0, ssb=0))
         if cur is None:
             continue
+        def num(key):
+            try:
+                return int(r[ix[key]])
+            except (ValueError, KeyError, IndexError):
+                return 0
         try:
             n = int(r[ix["Instructions Executed"]])
         except (ValueError, KeyError):
             continue
         d = lines[cur]
         d["inst"] += n
-        d["thr"] += int(r[ix["Thread Instructions Executed"]] or 0)
-        d["samp"] += int(r[ix["# Samples"]] or 0)
-        d["lsb"] += int(r[ix["stall_long_sb"]] or 0)
-        d["ssb"] += int(r[ix["stall_short_sb"]] or 0)
+        d["thr"] += num("Thread Instructions Executed")
+        d["samp"] += num("# Samples")
+        d["lsb"] += num("stall_long_sb")
+        d["ssb"] += num("stall_short_sb")
     tot = sum(d["inst"] for d in lines.values()) or 1
     tots = sum(d["samp"] for d in lines.values()) or 1
     print("total warp instructions %d, samples %d" % (tot, tots))
