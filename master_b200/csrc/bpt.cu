@@ -220,7 +220,7 @@ __device__ __forceinline__ float3 connect_vertices(const DeviceScene& sc, const 
 
 // BPTBase::_connect_light (BPT.cpp:225-243)
 __device__ __forceinline__ float3 connect_light(const DeviceScene& sc, const Vertex& eye, float beta) {
-  const BsdfQuery b = bsdf_query(sc, eye.s, f3(0.0f), eye.omega);
+  const BsdfQuery b = bsdf_query_emitter(sc, eye.s, f3(0.0f), eye.omega);  // the caller found eye.s.is_light()
   if (l1norm(b.throughput) < kFltMin) return f3(0.0f);
   float3 lr; float ld;
   query_lsdf(sc, eye.s, eye.omega, lr, ld);
@@ -317,9 +317,11 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // Dependent round trips per item: queue entry + hit (both by queue POSITION, coalesced: the closest-hit stage stores its hits in queue
 // order, BptPool::hit_q) -> path record + shading record of the hit triangle, asked for together -> arithmetic.  (With the hit inside
 // the path record the shading record was a third round trip: 13 % of the stage's warp-state samples.)
-template <int kEnd>
+// kFirst: iteration 0 of a batch (every slot is born here; kEnd = 0) — a kernel of its own so that the steady-state kernel does not carry its code.
+template <int kEnd, bool kFirst>
 __global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_LOGIC_SPLIT_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
-                                                                               int first, int sort) {
+                                                                               int sort) {
+  constexpr bool first = kFirst;
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     // trace_count[parity ^ 1] is this launch's input; the closest-hit stage clears it afterwards
@@ -392,9 +394,9 @@ __global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN
     bool cur_dirty = false;
 
     if (st != kDone) {
-      if (kEnd == 0 && st == kNew && slot >= pool.valid) {
+      if (kFirst && st == kNew && slot >= pool.valid) {
         finished = true;  // padding slot
-      } else if (kEnd == 0 && st == kNew) {
+      } else if (kFirst && st == kNew) {
         // Technique::_for_each_ray (Technique.cpp:321-331): jitter, primary direction
         const uint32_t pixel = slot % cfg.pixels;
         const uint32_t pass = batch_pass0 + slot / cfg.pixels;
@@ -444,27 +446,37 @@ __global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN
       }
 #undef B2PT_REC
 
+      // ---- the hit of the extension ray becomes the next vertex: the same arithmetic for both subpaths (BPT.cpp:139-157 and
+      // BPT.cpp:45-66), written once — the light subpath carries the roulette factor in its throughput
+      const uint32_t tri = __float_as_uint(hv.w);
+      Vertex nv;
+      nv.ladj = -1.0f;
+      bool nv_ok = false;  // the hit is a vertex with a throughput that counts
+      if (has_tri) {
+        load_surface_rest(sc, tri, raw);
+        nv.s = query_surface_raw(raw, hv.y, hv.z, hv.x, O, bs.omega);
+        nv.omega = -bs.omega;
+        const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
+        nv.thr = cur.thr * bs.throughput * edge.b_cos;
+        if (kEnd == 2 || (kEnd == 0 && st == kLightWait)) nv.thr = nv.thr * roulette_inv;
+        if (!(l1norm(nv.thr) < kFltEpsilon)) {
+          nv_ok = true;
+          nv.thr /= bs.density;
+          cur.finite = min(cur.finite, bs.finite);
+          nv.finite = bs.finite;
+          nv.w0 = 1.0f / beta_fn(edge.f_geometry * bs.density, beta);
+          nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + cur.w0 * float(cur.finite)) * beta_fn(edge.b_geometry, beta) * nv.w0;
+        }
+      }
+
       if (kEnd != 1 && st == kLightWait) {
         // ---- _traceLight loop body after intersectMesh (BPT.cpp:139-176)
-        const uint32_t tri = __float_as_uint(hv.w);
         if (tri == kInvalid) {
           st = kLightFinal;
         } else {
-          Vertex nv;
-          nv.ladj = -1.0f;
-          load_surface_rest(sc, tri, raw);
-          nv.s = query_surface_raw(raw, hv.y, hv.z, hv.x, O, bs.omega);
-          nv.omega = -bs.omega;
-          const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
-          nv.thr = cur.thr * bs.throughput * edge.b_cos * roulette_inv;
-          if (l1norm(nv.thr) < kFltEpsilon) {
+          if (!nv_ok) {
             st = kLightFinal;  // path.pop_back(); break;  — prv is untouched
           } else {
-            nv.thr /= bs.density;
-            cur.finite = min(cur.finite, bs.finite);
-            nv.finite = bs.finite;
-            nv.w0 = 1.0f / beta_fn(edge.f_geometry * bs.density, beta);
-            nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + cur.w0 * float(cur.finite)) * beta_fn(edge.b_geometry, beta) * nv.w0;
             if (bs.finite == 0) {
               store_pool_vertex(pool, head, nv);  // path[prv] = path[itr]; path.pop_back();
               cur = nv; cur_dirty = true;
@@ -509,21 +521,9 @@ __global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN
           }
           finished = true;
         } else {
-          Vertex nv;
-          nv.ladj = -1.0f;
-          load_surface_rest(sc, tri, raw);
-          nv.s = query_surface_raw(raw, hv.y, hv.z, hv.x, O, bs.omega);
-          nv.omega = -bs.omega;
-          const Edge edge(cur.s.pos, cur.s.normal(), nv.s.pos, nv.s.normal(), nv.omega);
-          nv.thr = cur.thr * bs.throughput * edge.b_cos;
-          if (l1norm(nv.thr) < kFltEpsilon) {
+          if (!nv_ok) {
             finished = true;
           } else {
-            nv.thr /= bs.density;
-            cur.finite = min(cur.finite, bs.finite);
-            nv.finite = bs.finite;
-            nv.w0 = 1.0f / beta_fn(edge.f_geometry * bs.density, beta);
-            nv.w1 = (cur.w1 * beta_fn(bs.density_rev, beta) + cur.w0 * float(cur.finite)) * beta_fn(edge.b_geometry, beta) * nv.w0;
             if (nv.s.is_light()) {
               rad = connect_light(sc, nv, beta);
               rad_add = true;
@@ -552,7 +552,7 @@ __global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN
                   } else {
                     // _connect_directional (BPT.cpp:245-269): queued for the directional stage
                     const float3 n = ls.surface.normal();
-                    const BsdfQuery eb = bsdf_query(sc, cur.s, -n, cur.omega);
+                    const BsdfQuery eb = bsdf_query_outofline(sc, cur.s, -n, cur.omega);
                     const float cosine = fabsf(dot(n, cur.s.normal()));
                     const float3 result = ls.radiance / ls.light_density * roulette_inv * cur.thr * eb.throughput * cosine;
                     const float KC = cur.w1 * beta_fn(eb.density, beta) + cur.w0 * float(cur.finite);
@@ -1206,10 +1206,11 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       for (int j = 0; j < kBatchIters; ++j, ++g.it) {
         const int parity = g.it & 1;
         timer.begin(kStageShade);
-        if (logic_split && g.it > 0) {
-          bpt_logic_kernel<2><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
-          bpt_logic_kernel<1><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0, sort_rays);
-        } else bpt_logic_kernel<0><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, g.it == 0 ? 1 : 0, sort_rays);
+        if (g.it == 0) bpt_logic_kernel<0, true><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
+        else if (logic_split) {
+          bpt_logic_kernel<2, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
+          bpt_logic_kernel<1, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
+        } else bpt_logic_kernel<0, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
         timer.end();
         timer.begin(kStageShade);
         if (staged_connect) bpt_connect_kernel<true><<<staged_grid, block, kConnectStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity);

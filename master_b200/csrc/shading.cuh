@@ -169,7 +169,9 @@ __device__ __forceinline__ float cos_of_bound(float x) {
   return cr_cosf(x);
 }
 
-__device__ __forceinline__ LambertRange lambert_range(float3 center, float radius) {
+// the general case out of line: three asin, one atan2 and two cos in double are ~850 instructions, and five inlined copies of them
+// (emitter sampling, next-event sampling, emission, the LightBSDF cases of query and sample) were 40 % of the logic stage's code
+__device__ B2PT_MATH_INLINE LambertRange lambert_range_general(float3 center, float radius) {
   const AngularBound bound = angular_bound(center, radius);
   LambertRange r;
   const float cos_sup = cos_of_bound(bound.theta_sup), cos_inf = cos_of_bound(bound.theta_inf);
@@ -177,6 +179,25 @@ __device__ __forceinline__ LambertRange lambert_range(float3 center, float radiu
   const float uniform_theta_sup = cos_inf * cos_inf;
   const float uniform_phi_inf = bound.phi_inf * kOneOverPi * 0.5f;
   const float uniform_phi_sup = bound.phi_sup * kOneOverPi * 0.5f;
+  r.theta_inf = uniform_theta_inf;
+  r.theta_range = uniform_theta_sup - uniform_theta_inf;
+  r.phi_inf = uniform_phi_inf;
+  r.phi_range = uniform_phi_sup - uniform_phi_inf;
+  return r;
+}
+__device__ __forceinline__ LambertRange lambert_range(float3 center, float radius) {
+  // angular_bound's own test (Sample.inl:13): a sphere that contains the point restricts nothing, and the same expressions on the
+  // bounds (0, pi/2, 0, 2 pi) are constants
+  const float lateral_distance_sq = center.x * center.x + center.z * center.z;
+  const float distance_sq = lateral_distance_sq + center.y * center.y;
+  const float radius_sq = radius * radius;
+  if (radius_sq < distance_sq) return lambert_range_general(center, radius);
+  LambertRange r;
+  const float cos_sup = cos_of_bound(kHalfPi), cos_inf = cos_of_bound(0.0f);
+  const float uniform_theta_inf = cos_sup * cos_sup;
+  const float uniform_theta_sup = cos_inf * cos_inf;
+  const float uniform_phi_inf = 0.0f * kOneOverPi * 0.5f;
+  const float uniform_phi_sup = kTwoPi * kOneOverPi * 0.5f;
   r.theta_inf = uniform_theta_inf;
   r.theta_range = uniform_theta_sup - uniform_theta_inf;
   r.phi_inf = uniform_phi_inf;
@@ -336,6 +357,32 @@ __device__ __forceinline__ BsdfQuery bsdf_query(const DeviceScene& sc, const Sur
       q.throughput = f3(0.0f); q.density = 0.0f; q.density_rev = 0.0f; q.finite = 0;
       return q;
   }
+}
+
+// bsdf_query for the places a stage reaches rarely (a sun light's next-event sample, a surface that is not what its entity type says):
+// one out-of-line copy instead of another inlined switch in the stage's hot code
+__device__ B2PT_MATH_INLINE BsdfQuery bsdf_query_outofline(const DeviceScene& sc, Surface s, float3 incident, float3 outgoing) {
+  return bsdf_query(sc, s, incident, outgoing);
+}
+// bsdf_query of a surface ON an emitter (entity type light: LightBSDF or sun_light_bsdf, AreaLights.cpp:25-33), the only materials a
+// path that hits a light can find there
+__device__ __forceinline__ BsdfQuery bsdf_query_emitter(const DeviceScene& sc, const Surface& s, float3 incident, float3 outgoing) {
+  const B2ptMaterial& m = sc.materials[s.material_index()];
+  BsdfQuery q;
+  if (m.type == B2PT_BSDF_LIGHT) {  // LightBSDF::query (BSDF.cpp:93-114), as in bsdf_query
+    const float3 local_outgoing = s.to_surface(outgoing);
+    const float adjust = lambert_adjust(s.to_surface(f3(m.sphere[0], m.sphere[1], m.sphere[2]) - s.pos), m.sphere[3]);
+    q.throughput = local_outgoing.y > 0.0f ? f3(1.0f) : f3(0.0f);
+    q.density = (local_outgoing.y > 0.0f ? 1.0f : 0.0f) * local_outgoing.y * kOneOverPi / adjust;
+    q.density_rev = 0.0f;
+    q.finite = 1;
+    return q;
+  }
+  if (m.type == B2PT_BSDF_SUN) {  // sun_light_bsdf::query (BSDF.cpp:179-189)
+    q.throughput = f3(0.0f); q.density = 1.0f; q.density_rev = 1.0f; q.finite = 1;
+    return q;
+  }
+  return bsdf_query_outofline(sc, s, incident, outgoing);
 }
 
 // CameraBSDF::sample (BSDF.cpp:197-208): no draws
