@@ -1123,6 +1123,7 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
   cfg.pool_size = size;
   const int grid = grid_for(size, block);
   int grid_t = persistent_grid(size, block);  // traversal stages: persistent warps fetch rays from a ticket counter
+  if (B2PT_TRACE_MIN_BLOCKS != 4) grid_t = int(std::min((size_t(size) + block - 1) / block, size_t(kNumSMs) * B2PT_TRACE_MIN_BLOCKS));  // A/B builds: one wave at another register cap
   // Co-residency experiment (A/B): B2PT_TRACE_CTAS=n caps the persistent traversal grids at n CTAs per SM (4 fill the register file),
   // B2PT_SHADE_BLOCK=128 launches the shading stages with 128-thread CTAs, so that a shading CTA of the OTHER lane fits beside the
   // traversal CTAs and the latency-bound shading overlaps the issue-bound traversal on the same SM.
