@@ -68,6 +68,11 @@ int b2pt_debug_trace_counts(b2pt_scene_t scene, const B2ptRay* rays, size_t n, u
    persistingL2CacheMaxSize, out[4] = its accessPolicyMaxWindowSize, out[5] = its l2CacheSize. */
 int b2pt_debug_l2_window(b2pt_scene_t scene, double* out6);
 
+/* The shading stages' powf (csrc/common.cuh: cr_powf — Phong lobes, PhongBSDF::_query BSDF.cpp:349-391, sample_phong Sample.inl:137-149)
+ * on n host (x, y) pairs: `table` = the table-driven evaluation that runs (csrc/pow_core.h), `lib` = float(exp2(y log2 x)) through the CUDA
+ * math library, which it replaced.  tests/test_pow_gpu.py sets both beside the host build of the same header and libquadmath. */
+int b2pt_debug_pow(const float* x, const float* y, size_t n, float* table, float* lib);
+
 #ifdef __cplusplus
 }
 #endif

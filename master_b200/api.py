@@ -113,7 +113,7 @@ EXPORTS = [
 # parity probes of include/b2pt_debug.h (not part of the drop-in boundary)
 DEBUG_EXPORTS = [
     "b2pt_debug_density", "b2pt_debug_primary", "b2pt_debug_camera", "b2pt_debug_light_samples", "b2pt_debug_draws",
-    "b2pt_debug_tree_stats", "b2pt_debug_trace_counts", "b2pt_debug_l2_window",
+    "b2pt_debug_tree_stats", "b2pt_debug_trace_counts", "b2pt_debug_l2_window", "b2pt_debug_pow",
 ]
 DENSITY_JOB_DTYPE = np.dtype([("org", "<f4", 3), ("dir", "<f4", 3), ("target", "<f4", 3), ("radius", "<f4"), ("key", "<u4")])
 DENSITY_RESULT_DTYPE = np.dtype([("trials", "<u4"), ("density", "<f4"), ("kind", "<u4"), ("t", "<f4")])
@@ -169,6 +169,7 @@ def load_library():
     lib.b2pt_debug_camera.argtypes = [C.POINTER(RenderParams), C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
     lib.b2pt_debug_light_samples.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.b2pt_debug_draws.argtypes = [C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.b2pt_debug_pow.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
     lib.b2pt_debug_tree_stats.argtypes = [C.c_void_p, C.c_void_p]
     lib.b2pt_debug_trace_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint, C.c_void_p]
     lib.b2pt_debug_l2_window.argtypes = [C.c_void_p, C.c_void_p]
@@ -353,6 +354,16 @@ def debug_draws(key, n):
     raw, fl, db = np.zeros(n, dtype=np.uint32), np.zeros(n, dtype=np.float32), np.zeros(n, dtype=np.float64)
     check(load_library().b2pt_debug_draws(C.c_uint32(key), n, _ptr(raw), _ptr(fl), _ptr(db)))
     return raw, fl, db
+
+
+def debug_pow(x, y):
+    """(table-driven cr_powf, math-library form) of the device on float arrays x, y (b2pt_debug_pow)."""
+    x = np.ascontiguousarray(x, dtype=np.float32).ravel()
+    y = np.ascontiguousarray(y, dtype=np.float32).ravel()
+    assert x.shape == y.shape
+    tab, lib = np.zeros_like(x), np.zeros_like(x)
+    check(load_library().b2pt_debug_pow(_ptr(x), _ptr(y), len(x), _ptr(tab), _ptr(lib)))
+    return tab, lib
 
 
 class Comm:

@@ -110,6 +110,13 @@ __global__ void __launch_bounds__(256) trace_counts_kernel(DeviceScene sc, const
   }
 }
 
+__global__ void debug_pow_kernel(const float* x, const float* y, uint32_t n, float* table, float* lib) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  table[i] = cr_powf(x[i], y[i]);
+  lib[i] = cr_powf_lib(x[i], y[i]);
+}
+
 int need_device(const char* who) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); set_error(std::string(who) + ": no CUDA device (there is no CPU fallback)"); return B2PT_ERR_NO_DEVICE; }
@@ -120,6 +127,22 @@ int need_device(const char* who) {
 }  // namespace b2pt
 
 extern "C" {
+
+int b2pt_debug_pow(const float* x, const float* y, size_t n, float* table, float* lib) {
+  using namespace b2pt;
+  B2_CHECK(x && y && table && lib, B2PT_ERR_INVALID, "b2pt_debug_pow: null argument");
+  if (int rc = need_device("b2pt_debug_pow")) return rc;
+  if (n == 0) return B2PT_OK;
+  DevBuf dx, dy, dt, dl;
+  B2_CUDA(dx.alloc(n * 4)); B2_CUDA(dy.alloc(n * 4)); B2_CUDA(dt.alloc(n * 4)); B2_CUDA(dl.alloc(n * 4));
+  B2_CUDA(cudaMemcpy(dx.p, x, n * 4, cudaMemcpyHostToDevice));
+  B2_CUDA(cudaMemcpy(dy.p, y, n * 4, cudaMemcpyHostToDevice));
+  debug_pow_kernel<<<unsigned((n + 255) / 256), 256>>>(dx.as<float>(), dy.as<float>(), uint32_t(n), dt.as<float>(), dl.as<float>());
+  B2_CUDA(cudaGetLastError());
+  B2_CUDA(cudaMemcpy(table, dt.p, n * 4, cudaMemcpyDeviceToHost));
+  B2_CUDA(cudaMemcpy(lib, dl.p, n * 4, cudaMemcpyDeviceToHost));
+  return B2PT_OK;
+}
 
 int b2pt_debug_primary(const B2ptRenderParams* params, const uint32_t* pixels, const uint32_t* samples, size_t n, float* directions) {
   using namespace b2pt;

@@ -30,7 +30,35 @@ static uint64_t rng_state = 0x9E3779B97F4A7C15ull;
 static uint64_t next64(void) { uint64_t z = (rng_state += 0x9E3779B97F4A7C15ull); z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; return z ^ (z >> 31); }
 static double u01(void) { return (double)(next64() >> 11) * (1.0 / 9007199254740992.0); }
 
+// --eval in out: `in` holds n (x, y) float pairs; `out` gets n (table result, correctly rounded result) float pairs — for tests/test_pow_gpu.py,
+// which sets the DEVICE's evaluation of the same header beside them
+static int eval_file(const char* in, const char* out) {
+  FILE* f = fopen(in, "rb");
+  if (!f) return 2;
+  fseek(f, 0, SEEK_END);
+  const long n = ftell(f) / 8;
+  fseek(f, 0, SEEK_SET);
+  float* xy = (float*)malloc((size_t)n * 8);
+  float* r = (float*)malloc((size_t)n * 8);
+  if (fread(xy, 8, (size_t)n, f) != (size_t)n) return 2;
+  fclose(f);
+  for (long i = 0; i < n; ++i) {
+    float tab = 0.0f;
+    if (!b2pt_pow_core(xy[2 * i], xy[2 * i + 1], &tab)) tab = __builtin_nanf("");
+    float cr = (float)powq((__float128)xy[2 * i], (__float128)xy[2 * i + 1]);
+    if (fabsf(cr) < 1.17549435e-38f) cr = 0.0f;   // the device flushes subnormal floats
+    if (fabsf(tab) < 1.17549435e-38f) tab = 0.0f;
+    r[2 * i] = tab; r[2 * i + 1] = cr;
+  }
+  f = fopen(out, "wb");
+  if (!f) return 2;
+  fwrite(r, 8, (size_t)n, f);
+  fclose(f);
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc == 4 && strcmp(argv[1], "--eval") == 0) return eval_file(argv[2], argv[3]);
   long n = argc > 1 ? atol(argv[1]) : 20000000;
   long bad_tab = 0, bad_lib = 0, differ = 0, outside = 0;
   double worst = 0.0;
