@@ -73,3 +73,27 @@ def test_exhausted_vertex_pool_is_an_error_not_a_biased_film(device_scenes, flat
     with pytest.raises(api.B2ptError) as e:
         gpu_render(device_scenes("CornellBoxDiffuse"), flat_scenes("CornellBoxDiffuse"), "BPT", 96, 96, 2, 3, per_path=False, beta=2.0)
     assert e.value.code == 4 and "B2PT_LV_PER_PATH" in str(e.value)
+
+
+# the forms kept behind switches for A/B runs must stay the same computation: the logic stage as two kernels, the connect
+# stage with its gathers staged through shared memory, the closest-hit queue sorted (hits then travel in the path records instead of
+# hit_q), and the older traversal form
+@pytest.mark.parametrize("switch", ["B2PT_LOGIC_SPLIT=1", "B2PT_STAGED=2", "B2PT_SORT_RAYS=1", "B2PT_SORT_RAYS=2", "B2PT_TRACE_STREAM=2"])
+def test_bpt_ab_switches_render_the_same_paths(switch, flat_scenes, monkeypatch):
+    from master_b200 import api
+    key, value = switch.split("=")
+    monkeypatch.setenv(key, value)
+    name = "CornellBoxSpecular"
+    flat = flat_scenes(name)
+    scene = api.DeviceSceneHandle(flat)  # its own workspace: the queues a switch needs are allocated with it
+    try:
+        g = np.load(golden_path("render_%s_BPT.npz" % name))
+        w, h, spp = int(g["width"]), int(g["height"]), g["paths"].shape[0]
+        accum, paths, stats = gpu_render(scene, flat, "BPT", w, h, spp, int(g["seed"]), beta=2.0)
+        frac, err = path_agreement(paths, g["paths"])
+        assert stats["capacity_events"] == 0
+        assert int((err > 1e-4).sum()) <= max(1, err.size // 5000)
+        assert np.all(accum[:, 3] + 0 == g["accum"][:, 3])
+        assert image_rel_rmse(accum, g["accum"]) <= 2e-2
+    finally:
+        scene.close()
