@@ -34,10 +34,9 @@ enum { kQueueTrace = 0, kQueueShadow = 1, kQueueFree = 2, kQueueTicket = 3 };  /
 enum { kShadowCommit = 1u };
 
 struct PtPool {
-  uint32_t* state;
   float4* ray_o;    // extension ray origin (already offset), w unused
   float4* ray_d;    // extension ray direction, w unused
-  float4* hit;      // t, u, v, bits(triangle)
+  float4* hit;      // t, u, v, bits(triangle) of the ray at POSITION i of the trace queue (not by slot)
   float4* prev;     // previous vertex position xyz, w = bsdf.density of the sampled direction
   float4* thr;      // throughput of the NEXT vertex (already * f * cos / pdf), w = bits(finite | path_size << 1)
   float4* rad;      // radiance gathered so far
@@ -79,8 +78,24 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
   const uint32_t n_free = (first || cnt->next_work >= cfg.total_work) ? 0u : cnt->queue_count[parity ^ 1][kQueueFree];
   const uint32_t n_live = first ? cfg.pool_size : n_trace + n_free;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_live; i += gridDim.x * blockDim.x) {
-    const uint32_t slot = first ? i : (i < n_trace ? pool.trace_q[parity ^ 1][i] : pool.free_q[parity ^ 1][i - n_trace]);
-    uint32_t st = first ? uint32_t(kFree) : pool.state[slot];
+    // A live slot's queue entry says which kind of vertex it waits for (bit 31: the primary hit), and its closest hit sits at the same
+    // POSITION of the hit array (the closest-hit stage stores hits in queue order): queue entry and hit are one coalesced round trip,
+    // the slot's streams and the shading record of the hit triangle the next — no state word, no hit gathered by slot in between.
+    uint32_t slot, st = kFree;
+    float4 hv = make_float4(0.f, 0.f, 0.f, __uint_as_float(kInvalid));
+    if (first) {
+      slot = i;
+    } else if (i < n_trace) {
+      const uint32_t e = pool.trace_q[parity ^ 1][i];
+      slot = e & 0x7FFFFFFFu;
+      st = (e & 0x80000000u) ? uint32_t(kPrimary) : uint32_t(kBounce);
+      hv = pool.hit[i];
+    } else {
+      slot = pool.free_q[parity ^ 1][i - n_trace];
+    }
+    SurfaceRaw raw;
+    const bool has_tri = st != kFree && __float_as_uint(hv.w) != kInvalid;
+    if (has_tri) load_surface_early(sc, __float_as_uint(hv.w), raw);
     bool want_trace = false, want_shadow = false;
     float3 sh_o = f3(0.f), sh_d = f3(0.f), sh_c = f3(0.f);
     uint32_t sh_flags = 0;
@@ -89,7 +104,7 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
     unsigned long long work = 0;
 
     if (st == kPrimary || st == kBounce) {
-      const float4 ro = pool.ray_o[slot], rd = pool.ray_d[slot], hv = pool.hit[slot], rv = pool.rad[slot];
+      const float4 ro = pool.ray_o[slot], rd = pool.ray_d[slot], rv = pool.rad[slot];
       const uint2 rs = pool.rng[slot];
       O = f3(ro.x, ro.y, ro.z); D = f3(rd.x, rd.y, rd.z); rad = f3(rv.x, rv.y, rv.z);
       rng.key = rs.x; rng.ctr = rs.y;
@@ -102,7 +117,8 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
       if (tri == kInvalid) {
         terminated = true;  // PT.cpp:49-51 / :28-30: the ray left the scene
       } else {
-        s = query_surface(sc, tri, hv.y, hv.z, hv.x, O, D);
+        load_surface_rest(sc, tri, raw);
+        s = query_surface_raw(raw, hv.y, hv.z, hv.x, O, D);
         const float3 omega = -D;
         if (st == kPrimary) {
           if (s.is_light() && max_path > 0) {  // PT.cpp:23-26: lights seen directly, then look through them
@@ -220,10 +236,8 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
         want_trace = true;
       }
     }
-    pool.state[slot] = st;
-
     const unsigned tq = warp_append(&cnt->queue_count[parity][kQueueTrace], want_trace);
-    if (want_trace) pool.trace_q[parity][tq] = slot;
+    if (want_trace) pool.trace_q[parity][tq] = slot | (st == kPrimary ? 0x80000000u : 0u);
     const unsigned sq = warp_append(&cnt->queue_count[parity][kQueueShadow], want_shadow);
     if (want_shadow) {
       float4* e = pool.shadow_q + size_t(sq) * 3;
@@ -238,13 +252,13 @@ struct PtTraceIo {
   const PtPool* pool;
   const uint32_t* q;
   __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
-    const uint32_t slot = q[i];
+    const uint32_t slot = q[i] & 0x7FFFFFFFu;
     const float4 o = pool->ray_o[slot], d = pool->ray_d[slot];
     O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY; mask = kMaskAll;
-    return slot;
+    return i;  // the hit goes to position i of the hit array: the logic stage reads it with the queue entry
   }
-  __device__ __forceinline__ void store(uint32_t slot, const Hit& h) const {
-    pool->hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+  __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
+    pool->hit[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
   }
 };
 
@@ -280,11 +294,11 @@ __global__ void __launch_bounds__(256) pt_trace_kernel(RenderConfig cfg, PtPool 
     cfg.counters->queue_count[parity ^ 1][kQueueFree] = 0;
   }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t slot = pool.trace_q[parity][i];
+    const uint32_t slot = pool.trace_q[parity][i] & 0x7FFFFFFFu;
     const float4 o = pool.ray_o[slot], d = pool.ray_d[slot];
     // Scene::intersect: tnear 0, tfar inf, mask 0xFFFFFFFF (Scene.cpp:190-197)
     const Hit h = trace_ray<false, false>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY);
-    pool.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+    pool.hit[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
   }
 }
 
@@ -304,7 +318,6 @@ __global__ void __launch_bounds__(256) pt_shadow_kernel(RenderConfig cfg, PtPool
     }
     if (flags & kShadowCommit) {
       commit_sample(cfg, pool.work[slot], f3(r.x, r.y, r.z));
-      pool.state[slot] = kFree;
       pool.free_q[parity][warp_append(&cfg.counters->queue_count[parity][kQueueFree], true)] = slot;
     }
   }
@@ -335,7 +348,6 @@ struct PtShadowIo {
     const bool commit = (flags & kShadowCommit) != 0u;
     if (commit) {
       commit_sample(*cfg, pool->work[slot], f3(r.x, r.y, r.z));
-      pool->state[slot] = kFree;
     }
     const unsigned fq = warp_append(&cfg->counters->queue_count[parity][kQueueFree], commit);
     if (commit) pool->free_q[parity][fq] = slot;
@@ -414,7 +426,6 @@ static int pt_workspace(b2pt_scene_s* scene, int k, uint32_t pool_size, PtWorksp
 static int pt_workspace_fill(PtWorkspace* w, uint32_t pool_size) {
   w->pool_size = pool_size; w->capacity = pool_size;
   int rc;
-  if ((rc = ws_alloc(w, &w->pool.state, pool_size))) return rc;
   if ((rc = ws_alloc(w, &w->pool.ray_o, pool_size))) return rc;
   if ((rc = ws_alloc(w, &w->pool.ray_d, pool_size))) return rc;
   if ((rc = ws_alloc(w, &w->pool.hit, pool_size))) return rc;
