@@ -33,19 +33,28 @@ enum { kFree = 0, kPrimary = 1, kBounce = 2, kAwaitShadow = 3 };
 enum { kQueueTrace = 0, kQueueShadow = 1, kQueueFree = 2, kQueueTicket = 3 };  // [3]: ray ticket of the persistent traversal stage
 enum { kShadowCommit = 1u };
 
+// One 96-byte record per slot = three 32-byte sectors, each read and written whole: the stages reach slots through queues, i.e. as
+// gathers, and the same words kept as seven SoA streams cost seven half-used sectors per slot and iteration (224 B of DRAM traffic
+// for 96 B of state; the BPT pool made the same move in round 1).
+//   0 extension ray origin (already offset)        1 extension ray direction                    <- all the closest-hit stage reads
+//   2 radiance gathered so far                     3 previous vertex position, w = bsdf.density of the sampled direction
+//   4 throughput of the NEXT vertex (already * f * cos / pdf), w = bits(finite | path_size << 1)
+//   5 bits(rng key, rng counter, work index low, high)
+enum { kPtRayO = 0, kPtRayD = 1, kPtRad = 2, kPtPrev = 3, kPtThr = 4, kPtCtl = 5, kPtRec = 6 };
 struct PtPool {
-  float4* ray_o;    // extension ray origin (already offset), w unused
-  float4* ray_d;    // extension ray direction, w unused
+  float4* rec;      // [slot * kPtRec + word]
   float4* hit;      // t, u, v, bits(triangle) of the ray at POSITION i of the trace queue (not by slot)
-  float4* prev;     // previous vertex position xyz, w = bsdf.density of the sampled direction
-  float4* thr;      // throughput of the NEXT vertex (already * f * cos / pdf), w = bits(finite | path_size << 1)
-  float4* rad;      // radiance gathered so far
-  uint2* rng;       // key, counter
-  unsigned long long* work;
-  uint32_t* trace_q[2];  // slots with an extension ray in flight = the live paths; iteration i writes [i & 1], iteration i + 1 walks it
+  uint32_t* trace_q[2];  // slots with an extension ray in flight = the live paths (bit 31: waits for its primary hit); iteration i writes [i & 1], iteration i + 1 walks it
   uint32_t* free_q[2];   // slots the shadow stage committed and freed: the next logic stage refills them
   float4* shadow_q; // 3 float4 per entry: (org, bits slot) (dir, bits flags) (contribution, 0)
 };
+#define PT_W(pool, slot, word) ((pool).rec[size_t(slot) * kPtRec + (word)])
+__device__ __forceinline__ float4 pt_ctl(uint32_t key, uint32_t ctr, unsigned long long work) {
+  return make_float4(__uint_as_float(key), __uint_as_float(ctr), __uint_as_float(uint32_t(work)), __uint_as_float(uint32_t(work >> 32)));
+}
+__device__ __forceinline__ unsigned long long pt_ctl_work(float4 c) {
+  return (unsigned long long)__float_as_uint(c.z) | ((unsigned long long)__float_as_uint(c.w) << 32);
+}
 
 __device__ __forceinline__ unsigned long long warp_grab_work(unsigned long long* counter, bool want) {
   const unsigned active = __activemask();
@@ -104,11 +113,12 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
     unsigned long long work = 0;
 
     if (st == kPrimary || st == kBounce) {
-      const float4 ro = pool.ray_o[slot], rd = pool.ray_d[slot], rv = pool.rad[slot];
-      const uint2 rs = pool.rng[slot];
+      const float4 ro = PT_W(pool, slot, kPtRayO), rd = PT_W(pool, slot, kPtRayD), rv = PT_W(pool, slot, kPtRad);
+      const float4 cw = PT_W(pool, slot, kPtCtl);
+      const uint2 rs = make_uint2(__float_as_uint(cw.x), __float_as_uint(cw.y));
       O = f3(ro.x, ro.y, ro.z); D = f3(rd.x, rd.y, rd.z); rad = f3(rv.x, rv.y, rv.z);
       rng.key = rs.x; rng.ctr = rs.y;
-      work = pool.work[slot];
+      work = pt_ctl_work(cw);
       const uint32_t tri = __float_as_uint(hv.w);
       bool terminated = false, proceed = false;
       float3 thr = f3(1.0f);
@@ -133,7 +143,7 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
             proceed = true;  // first surface vertex: throughput 1, path_size 2 (PT.cpp:32-38)
           }
         } else {
-          const float4 pv = pool.prev[slot], tv = pool.thr[slot];
+          const float4 pv = PT_W(pool, slot, kPtPrev), tv = PT_W(pool, slot, kPtThr);
           const float bsdf_density = pv.w;
           const uint32_t packed = __float_as_uint(tv.w);
           const uint32_t finite = packed & 1u;
@@ -192,9 +202,9 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
           thr_next /= bs.density;
           D = bs.omega;
           O = offset_origin(s.pos, s.gnormal, D);
-          pool.prev[slot] = make_float4(s.pos.x, s.pos.y, s.pos.z, bs.density);
-          pool.thr[slot] = make_float4(thr_next.x, thr_next.y, thr_next.z, __uint_as_float((bs.finite & 1u) | (path_size << 1)));
-          pool.ray_d[slot] = make_float4(D.x, D.y, D.z, 0.f);
+          PT_W(pool, slot, kPtPrev) = make_float4(s.pos.x, s.pos.y, s.pos.z, bs.density);
+          PT_W(pool, slot, kPtThr) = make_float4(thr_next.x, thr_next.y, thr_next.z, __uint_as_float((bs.finite & 1u) | (path_size << 1)));
+          PT_W(pool, slot, kPtRayD) = make_float4(D.x, D.y, D.z, 0.f);
           st = kBounce;
           want_trace = true;
         }
@@ -204,15 +214,15 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
         if (want_shadow) {
           sh_flags = kShadowCommit;  // the shadow stage adds the last contribution, then commits
           st = kAwaitShadow;
-          pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+          PT_W(pool, slot, kPtRad) = make_float4(rad.x, rad.y, rad.z, 0.f);
         } else {
           commit_sample(cfg, work, rad);
           st = kFree;
         }
       } else {
-        pool.ray_o[slot] = make_float4(O.x, O.y, O.z, 0.f);
-        pool.rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
-        pool.rng[slot] = make_uint2(rng.key, rng.ctr);
+        PT_W(pool, slot, kPtRayO) = make_float4(O.x, O.y, O.z, 0.f);
+        PT_W(pool, slot, kPtRad) = make_float4(rad.x, rad.y, rad.z, 0.f);
+        PT_W(pool, slot, kPtCtl) = pt_ctl(rng.key, rng.ctr, work);
       }
     }
 
@@ -227,11 +237,10 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
         Rng g; g.key = stream_key(cfg.params.seed, kDomainPixel, pixel, sample); g.ctr = 0;
         const float3 dir = shoot_primary(cfg, g, pixel);
         const float3 org = offset_origin(cfg.camera.pos, cfg.camera.gnormal, dir);
-        pool.ray_o[slot] = make_float4(org.x, org.y, org.z, 0.f);
-        pool.ray_d[slot] = make_float4(dir.x, dir.y, dir.z, 0.f);
-        pool.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
-        pool.rng[slot] = make_uint2(g.key, g.ctr);
-        pool.work[slot] = w;
+        PT_W(pool, slot, kPtRayO) = make_float4(org.x, org.y, org.z, 0.f);
+        PT_W(pool, slot, kPtRayD) = make_float4(dir.x, dir.y, dir.z, 0.f);
+        PT_W(pool, slot, kPtRad) = make_float4(0.f, 0.f, 0.f, 0.f);
+        PT_W(pool, slot, kPtCtl) = pt_ctl(g.key, g.ctr, w);
         st = kPrimary;
         want_trace = true;
       }
@@ -253,7 +262,7 @@ struct PtTraceIo {
   const uint32_t* q;
   __device__ __forceinline__ uint32_t load(uint32_t i, float3& O, float3& D, float& tnear, float& tfar, uint32_t& mask) const {
     const uint32_t slot = q[i] & 0x7FFFFFFFu;
-    const float4 o = pool->ray_o[slot], d = pool->ray_d[slot];
+    const float4 o = PT_W(*pool, slot, kPtRayO), d = PT_W(*pool, slot, kPtRayD);
     O = f3(o.x, o.y, o.z); D = f3(d.x, d.y, d.z); tnear = 0.0f; tfar = INFINITY; mask = kMaskAll;
     return i;  // the hit goes to position i of the hit array: the logic stage reads it with the queue entry
   }
@@ -295,7 +304,7 @@ __global__ void __launch_bounds__(256) pt_trace_kernel(RenderConfig cfg, PtPool 
   }
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint32_t slot = pool.trace_q[parity][i] & 0x7FFFFFFFu;
-    const float4 o = pool.ray_o[slot], d = pool.ray_d[slot];
+    const float4 o = PT_W(pool, slot, kPtRayO), d = PT_W(pool, slot, kPtRayD);
     // Scene::intersect: tnear 0, tfar inf, mask 0xFFFFFFFF (Scene.cpp:190-197)
     const Hit h = trace_ray<false, false>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, INFINITY);
     pool.hit[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
@@ -311,13 +320,13 @@ __global__ void __launch_bounds__(256) pt_shadow_kernel(RenderConfig cfg, PtPool
     const uint32_t slot = __float_as_uint(o.w), flags = __float_as_uint(d.w);
     // Scene::occluded: t in (0, 1) along the unnormalised segment, meshes only (Scene.cpp:162-176)
     const Hit h = trace_ray<true, true>(cfg.scene, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), 0.0f, 1.0f);
-    float4 r = pool.rad[slot];
+    float4 r = PT_W(pool, slot, kPtRad);
     if (h.tri == kInvalid) {
       r.x += c.x; r.y += c.y; r.z += c.z;
-      if (!(flags & kShadowCommit)) pool.rad[slot] = r;
+      if (!(flags & kShadowCommit)) PT_W(pool, slot, kPtRad) = r;
     }
     if (flags & kShadowCommit) {
-      commit_sample(cfg, pool.work[slot], f3(r.x, r.y, r.z));
+      commit_sample(cfg, pt_ctl_work(PT_W(pool, slot, kPtCtl)), f3(r.x, r.y, r.z));
       pool.free_q[parity][warp_append(&cfg.counters->queue_count[parity][kQueueFree], true)] = slot;
     }
   }
@@ -340,14 +349,14 @@ struct PtShadowIo {
     const float4* e = pool->shadow_q + size_t(i) * 3;
     const uint32_t slot = __float_as_uint(e[0].w), flags = __float_as_uint(e[1].w);
     const float4 c = e[2];
-    float4 r = pool->rad[slot];
+    float4 r = PT_W(*pool, slot, kPtRad);
     if (h.tri == kInvalid) {
       r.x += c.x; r.y += c.y; r.z += c.z;
-      if (!(flags & kShadowCommit)) pool->rad[slot] = r;
+      if (!(flags & kShadowCommit)) PT_W(*pool, slot, kPtRad) = r;
     }
     const bool commit = (flags & kShadowCommit) != 0u;
     if (commit) {
-      commit_sample(*cfg, pool->work[slot], f3(r.x, r.y, r.z));
+      commit_sample(*cfg, pt_ctl_work(PT_W(*pool, slot, kPtCtl)), f3(r.x, r.y, r.z));
     }
     const unsigned fq = warp_append(&cfg->counters->queue_count[parity][kQueueFree], commit);
     if (commit) pool->free_q[parity][fq] = slot;
@@ -426,14 +435,8 @@ static int pt_workspace(b2pt_scene_s* scene, int k, uint32_t pool_size, PtWorksp
 static int pt_workspace_fill(PtWorkspace* w, uint32_t pool_size) {
   w->pool_size = pool_size; w->capacity = pool_size;
   int rc;
-  if ((rc = ws_alloc(w, &w->pool.ray_o, pool_size))) return rc;
-  if ((rc = ws_alloc(w, &w->pool.ray_d, pool_size))) return rc;
+  if ((rc = ws_alloc(w, &w->pool.rec, size_t(pool_size) * kPtRec))) return rc;
   if ((rc = ws_alloc(w, &w->pool.hit, pool_size))) return rc;
-  if ((rc = ws_alloc(w, &w->pool.prev, pool_size))) return rc;
-  if ((rc = ws_alloc(w, &w->pool.thr, pool_size))) return rc;
-  if ((rc = ws_alloc(w, &w->pool.rad, pool_size))) return rc;
-  if ((rc = ws_alloc(w, &w->pool.rng, pool_size))) return rc;
-  if ((rc = ws_alloc(w, &w->pool.work, pool_size))) return rc;
   for (int k = 0; k < 2; ++k) {
     if ((rc = ws_alloc(w, &w->pool.trace_q[k], pool_size))) return rc;
     if ((rc = ws_alloc(w, &w->pool.free_q[k], pool_size))) return rc;
