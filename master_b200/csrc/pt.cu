@@ -71,7 +71,13 @@ __device__ __forceinline__ unsigned long long warp_grab_work(unsigned long long*
 // The stage walks the LIVE slots only — the trace queue of the previous iteration — plus the slots the shadow stage freed
 // (`first`: every slot, all free).  Walking the pool in slot order costs a full scan per iteration however few paths are
 // left, which is what the drain phase of a render call consists of.
-__global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool pool, int parity, int first) {
+#ifndef B2PT_PT_LOGIC_THREADS
+#define B2PT_PT_LOGIC_THREADS 256  // CTA size and resident CTAs per SM the logic stage is compiled for (-D... for A/B builds): 256 x 2 = 128 registers
+#endif
+#ifndef B2PT_PT_LOGIC_MIN_BLOCKS
+#define B2PT_PT_LOGIC_MIN_BLOCKS 2
+#endif
+__global__ void __launch_bounds__(B2PT_PT_LOGIC_THREADS, B2PT_PT_LOGIC_MIN_BLOCKS) pt_logic_kernel(RenderConfig cfg, PtPool pool, int parity, int first) {
   const DeviceScene& sc = cfg.scene;
   RenderCounters* cnt = cfg.counters;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -86,13 +92,17 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
   // freed slots only matter while there is work left to hand out
   const uint32_t n_free = (first || cnt->next_work >= cfg.total_work) ? 0u : cnt->queue_count[parity ^ 1][kQueueFree];
   const uint32_t n_live = first ? cfg.pool_size : n_trace + n_free;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_live; i += gridDim.x * blockDim.x) {
+  const uint32_t n_round = (n_live + 31u) & ~31u;  // whole warps: every lane of a warp reaches the ballots below (the padding lanes do nothing)
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+    const bool lane_on = i < n_live;
     // A live slot's queue entry says which kind of vertex it waits for (bit 31: the primary hit), and its closest hit sits at the same
     // POSITION of the hit array (the closest-hit stage stores hits in queue order): queue entry and hit are one coalesced round trip,
     // the slot's streams and the shading record of the hit triangle the next — no state word, no hit gathered by slot in between.
     uint32_t slot, st = kFree;
     float4 hv = make_float4(0.f, 0.f, 0.f, __uint_as_float(kInvalid));
-    if (first) {
+    if (!lane_on) {
+      slot = 0;
+    } else if (first) {
       slot = i;
     } else if (i < n_trace) {
       const uint32_t e = pool.trace_q[parity ^ 1][i];
@@ -179,7 +189,7 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
         // ---- PathTracing::_connect (PT.cpp:100-120): next-event estimation
         const LightSample light = sample_light(sc, rng);
         const float3 omega = normalize(s.pos - light.surface.pos);
-        const BsdfQuery lb = bsdf_query(sc, light.surface, light.surface.normal(), omega);
+        const BsdfQuery lb = bsdf_query_emitter(sc, light.surface, light.surface.normal(), omega);  // a sampled emitter point: LightBSDF or sun_light_bsdf
         if (!(l1norm(lb.throughput) < kFltEpsilon)) {
           const BsdfQuery eb = bsdf_query(sc, s, -omega, eye_omega);
           const Edge edge(light.surface.pos, light.surface.normal(), s.pos, s.normal(), omega);
@@ -228,7 +238,7 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
 
     // ---- regeneration: a free slot takes the next (sample, pixel) (Technique::_for_each_ray, Technique.cpp:307-352)
     {
-      const bool was_free = st == kFree;
+      const bool was_free = lane_on && st == kFree;
       const unsigned long long w = warp_grab_work(&cnt->next_work, was_free);
       if (was_free && w < cfg.total_work) {
         const uint32_t pixel = uint32_t(w % cfg.pixels);
@@ -245,9 +255,19 @@ __global__ void __launch_bounds__(256) pt_logic_kernel(RenderConfig cfg, PtPool 
         want_trace = true;
       }
     }
-    const unsigned tq = warp_append(&cnt->queue_count[parity][kQueueTrace], want_trace);
+    // both reservations by lane 0, back to back: one round trip to the L2 per warp instead of two in a row (every lane of the warp is
+    // here: the loop's trip count is rounded up to whole warps)
+    const unsigned lane_id = threadIdx.x & 31u;
+    const unsigned m_t = __ballot_sync(0xFFFFFFFFu, want_trace), m_s = __ballot_sync(0xFFFFFFFFu, want_shadow);
+    unsigned base_t = 0, base_s = 0;
+    if (lane_id == 0) {
+      if (m_t) base_t = atomicAdd(&cnt->queue_count[parity][kQueueTrace], unsigned(__popc(m_t)));
+      if (m_s) base_s = atomicAdd(&cnt->queue_count[parity][kQueueShadow], unsigned(__popc(m_s)));
+    }
+    base_t = __shfl_sync(0xFFFFFFFFu, base_t, 0);
+    base_s = __shfl_sync(0xFFFFFFFFu, base_s, 0);
+    const unsigned tq = base_t + __popc(m_t & ((1u << lane_id) - 1u)), sq = base_s + __popc(m_s & ((1u << lane_id) - 1u));
     if (want_trace) pool.trace_q[parity][tq] = slot | (st == kPrimary ? 0x80000000u : 0u);
-    const unsigned sq = warp_append(&cnt->queue_count[parity][kQueueShadow], want_shadow);
     if (want_shadow) {
       float4* e = pool.shadow_q + size_t(sq) * 3;
       e[0] = make_float4(sh_o.x, sh_o.y, sh_o.z, __uint_as_float(slot));
@@ -468,6 +488,8 @@ static int render_pt_lane(const RenderConfig& base, PtWorkspace* w, cudaStream_t
   cfg.counters = w->counters;
   B2_CUDA(cudaMemsetAsync(w->counters, 0, sizeof(RenderCounters), stream));
   const int grid = grid_for(pool_size, block);
+  const int logic_block = B2PT_PT_LOGIC_THREADS;  // the same number of threads in flight whatever the CTA size
+  const int logic_grid = int(std::min((size_t(pool_size) + logic_block - 1) / logic_block, size_t(kNumSMs) * 8 * (block / logic_block)));
   // closest-hit stage: persistent warps + dynamic fetch + postponed triangle groups (166.4 -> 170.9 Msamples/s on the LivingRoom
   // stand-in); B2PT_TRACE_STREAM=0 selects one ray per thread for A/B runs
   const char* tv = getenv("B2PT_TRACE_STREAM");
@@ -479,7 +501,7 @@ static int render_pt_lane(const RenderConfig& base, PtWorkspace* w, cudaStream_t
   for (int it = 0;; ) {
     for (int k = 0; k < kBatch; ++k, ++it) {
       const int parity = it & 1;
-      timer.begin(kStageShade); pt_logic_kernel<<<grid, block, 0, stream>>>(cfg, w->pool, parity, it == 0 ? 1 : 0); timer.end();
+      timer.begin(kStageShade); pt_logic_kernel<<<logic_grid, logic_block, 0, stream>>>(cfg, w->pool, parity, it == 0 ? 1 : 0); timer.end();
       timer.begin(kStageTrace);
       if (queue_trace) pt_trace_queue_kernel<<<persistent_grid(cfg.pool_size, block), block, 0, stream>>>(cfg, w->pool, parity);
       else if (dyn_trace) pt_trace_dyn_kernel<<<persistent_grid(cfg.pool_size, block), block, 0, stream>>>(cfg, w->pool, parity);
