@@ -810,6 +810,13 @@ struct DensityLoop {
   Surface s;
   float3 center, omega, target;
   float target_length, N, diffuse_probability, combined_adjust, power;
+  // The restricted lobes of the loop: sample_lambert(generator, sphere, omega) and sample_phong(generator, omega, power, sphere)
+  // (Sample.inl:58-82, 151-205) recompute these ranges in every call from arguments that do not change inside the loop — three asin,
+  // an atan2, two cos (and two pow for the Phong lobe), all correctly rounded, per TRIAL.  The same functions on the same arguments
+  // return the same bits, so they are evaluated once per loop here.  (angular_bound reads center.y only squared, so the sign flip of
+  // Sample.inl:61 does not enter.)
+  LambertRange lr;
+  PhongRange pr;
   uint32_t type;
   uint32_t key;  // trial t draws from its own stream (key, t): the outcome of a trial does not depend on who runs it, or when
 };
@@ -823,9 +830,11 @@ __device__ __forceinline__ void density_begin(DensityLoop& L, const DeviceScene&
   L.N = 1.0f;
   L.type = m.type; L.power = m.power;
   L.diffuse_probability = 1.0f; L.combined_adjust = 1.0f;
+  if (m.type == B2PT_BSDF_DIFFUSE || m.type == B2PT_BSDF_PHONG) L.lr = lambert_range(L.center, radius);
   if (m.type == B2PT_BSDF_PHONG) {
-    const float diffuse_adjust = lambert_adjust(L.center, radius);
-    const float specular_adjust = phong_adjust(L.omega, m.power, L.center, radius);
+    L.pr = phong_range(L.omega, m.power, L.center, radius);
+    const float diffuse_adjust = L.lr.theta_range * L.lr.phi_range;      // lambert_adjust (Sample.inl:119-131)
+    const float specular_adjust = L.pr.theta_range * L.pr.phi_range;     // phong_adjust (Sample.inl:197-205)
     L.combined_adjust = diffuse_adjust * m.diffuse_probability + specular_adjust * (1.0f - m.diffuse_probability);
     L.diffuse_probability =
         diffuse_adjust * m.diffuse_probability / (diffuse_adjust * m.diffuse_probability + specular_adjust * (1.0f - m.diffuse_probability));
@@ -838,13 +847,21 @@ __device__ __forceinline__ bool density_trial(const DensityLoop& L, const Device
   Rng r; r.key = mix32(L.key ^ mix32(uint32_t(t) * 0x9E3779B9u + 0x85EBCA6Bu)); r.ctr = 0;
   float3 d;
   float adjust = 1.0f;
-  if (L.type == B2PT_BSDF_DIFFUSE) {
-    d = sample_lambert_bounded(r, L.center, radius, L.omega, adjust);
+  // the two sampling functions with their ranges taken from the loop; ONE polar conversion after the branch (the draws, the operations and
+  // their order are those of sample_lambert_bounded / sample_phong_bounded in shading.cuh)
+  const bool lambert = L.type == B2PT_BSDF_DIFFUSE || r.sample() < L.diffuse_probability;
+  float y, phi;
+  if (lambert) {
+    y = sqrtf(r.sample() * L.lr.theta_range + L.lr.theta_inf) * sign_glm(L.omega.y);
+    phi = kTwoPi * (r.sample() * L.lr.phi_range + L.lr.phi_inf);
   } else {
-    if (r.sample() < L.diffuse_probability) { float unused; d = sample_lambert_bounded(r, L.center, radius, L.omega, unused); }
-    else d = sample_phong_bounded(r, L.omega, L.power, L.center, radius);
-    adjust = L.combined_adjust;
+    y = cr_powf(r.sample() * L.pr.theta_range + L.pr.theta_inf, 1.0f / (L.power + 1.0f));
+    phi = kTwoPi * (r.sample() * L.pr.phi_range + L.pr.phi_inf);
   }
+  const float rr = sqrtf(1 - y * y);
+  d = cr_polar(rr, y, phi);
+  if (!lambert) d = mul(L.pr.reflection, d);
+  adjust = L.type == B2PT_BSDF_DIFFUSE ? L.lr.theta_range * L.lr.phi_range : L.combined_adjust;
   density = t / adjust;
   return intersect_fast(sc, L.s, L.s.to_world(d), L.target_length, L.target, radius);
 }
@@ -1063,7 +1080,7 @@ constexpr int kWideChunk = 128;          // trials per ticket in the grid stage
 // them are idle, and a loop that has not ended after kLaneTrials trials moves to upg_density_long_kernel (measured on the LivingRoom
 // stand-in: 60 density rays per pixel-sample in total, but single loops of tens of thousands of trials, which used to set the duration
 // of the whole launch).
-__global__ void __launch_bounds__(256) upg_density_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
+__global__ void __launch_bounds__(256, 2) upg_density_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
   const DeviceScene& sc = cfg.scene;
   const uint32_t n = min(cnt->job_count, pool.m_capacity);
   const unsigned lane = threadIdx.x & 31u, lane_lt = (1u << lane) - 1u;
@@ -1115,7 +1132,7 @@ __global__ void __launch_bounds__(256) upg_density_kernel(RenderConfig cfg, VcmP
 
 // Long density loops, one WARP per loop: the trials are independent (trial t has its own stream), so 32 of them run per round and
 // the first one that lands is the answer — the same estimate in 1/32 of the rounds.  Only the trials up to that one count as rays.
-__global__ void __launch_bounds__(256) upg_density_long_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
+__global__ void __launch_bounds__(256, 2) upg_density_long_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
   const DeviceScene& sc = cfg.scene;
   const uint32_t n = min(cnt->long_count, pool.m_capacity);
   const unsigned lane = threadIdx.x & 31u;
@@ -1170,7 +1187,7 @@ __global__ void __launch_bounds__(256) upg_density_long_kernel(RenderConfig cfg,
 
 // The longest density loops, one GRID per loop: warps draw chunks of kWideChunk trials from the loop's ticket until a chunk starts past
 // the first trial known to have landed (atomicMin) or past the test limit.  The answer is the smallest landing trial, as in the serial loop.
-__global__ void __launch_bounds__(256) upg_density_wide_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
+__global__ void __launch_bounds__(256, 2) upg_density_wide_kernel(RenderConfig cfg, VcmParams P, VcmPool pool, VcmCounters* cnt) {
   const DeviceScene& sc = cfg.scene;
   const uint32_t n = min(cnt->wide_count, kWideCap);
   const unsigned lane = threadIdx.x & 31u;
