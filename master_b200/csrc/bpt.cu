@@ -372,7 +372,6 @@ __global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN
     // (its loads used to start a round trip of their own after all the arithmetic: 5 % of the stage's warp-state samples)
     uint32_t lp_first = 0u;
     if (lane_on && !first) lp_first = pool.lp_idx[size_t(slot) * kLpTable];
-#define B2PT_REC(k) (rec[k])
     // iteration 0 of a batch never reads the records: every slot is born kNew.  Afterwards a live path waits for the hit of its
     // extension ray, and which end of the queue it sits at says for which subpath: the state is not stored.
     const uint32_t st0 = !lane_on ? uint32_t(kDone) : kEnd == 1 ? uint32_t(kEyeWait) : kEnd == 2 ? uint32_t(kLightWait)
@@ -429,22 +428,21 @@ __global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN
           }
         }
       } else {
-        const float4 ctl = B2PT_REC(kRecCtl);
+        const float4 ctl = rec[kRecCtl];
         rng.key = __float_as_uint(ctl.x); rng.ctr = __float_as_uint(ctl.y);
         head = __float_as_uint(ctl.z); count = __float_as_uint(ctl.w);
         {
           float4 q[kVertexFloat4s];
 #pragma unroll
-          for (int k = 0; k < kVertexFloat4s; ++k) q[k] = B2PT_REC(k);
+          for (int k = 0; k < kVertexFloat4s; ++k) q[k] = rec[k];
           cur = unpack_vertex(q);
         }
-        const float4 bo = B2PT_REC(kRecOmega), bt = B2PT_REC(kRecThr), ro = B2PT_REC(kRecRayO);
+        const float4 bo = rec[kRecOmega], bt = rec[kRecThr], ro = rec[kRecRayO];
         bs.omega = f3(bo.x, bo.y, bo.z); bs.density = bo.w;
         bs.throughput = f3(bt.x, bt.y, bt.z); bs.density_rev = bt.w;
         bs.finite = __float_as_uint(ro.w) & 1u;
         O = f3(ro.x, ro.y, ro.z);
       }
-#undef B2PT_REC
 
       // ---- the hit of the extension ray becomes the next vertex: the same arithmetic for both subpaths (BPT.cpp:139-157 and
       // BPT.cpp:45-66), written once — the light subpath carries the roulette factor in its throughput
