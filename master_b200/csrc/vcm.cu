@@ -123,16 +123,19 @@ __device__ __forceinline__ Vertex unpack_vertex(const float4* q) {
   return v;
 }
 // slot vertices are SoA (stride = number of slots), pool vertices AoS
-__device__ __forceinline__ void store_slot_vertex(float4* base, uint32_t stride, uint32_t slot, const Vertex& v) {
+// A slot's vertex is ONE 128-byte-aligned record (seven words + one spare): the stages reach slots through queues, and the same words as
+// seven SoA streams were seven half-used sectors per vertex (the PT and BPT pools made the same move).  `stride` (the slot count) is unused.
+constexpr int kSlotVertexFloat4s = 8;
+__device__ __forceinline__ void store_slot_vertex(float4* base, uint32_t /*stride*/, uint32_t slot, const Vertex& v) {
   float4 q[kVertexFloat4s];
   pack_vertex(v, q);
 #pragma unroll
-  for (int k = 0; k < kVertexFloat4s; ++k) base[size_t(k) * stride + slot] = q[k];
+  for (int k = 0; k < kVertexFloat4s; ++k) base[size_t(slot) * kSlotVertexFloat4s + k] = q[k];
 }
-__device__ __forceinline__ Vertex load_slot_vertex(const float4* base, uint32_t stride, uint32_t slot) {
+__device__ __forceinline__ Vertex load_slot_vertex(const float4* base, uint32_t /*stride*/, uint32_t slot) {
   float4 q[kVertexFloat4s];
 #pragma unroll
-  for (int k = 0; k < kVertexFloat4s; ++k) q[k] = base[size_t(k) * stride + slot];
+  for (int k = 0; k < kVertexFloat4s; ++k) q[k] = base[size_t(slot) * kSlotVertexFloat4s + k];
   return unpack_vertex(q);
 }
 __device__ __forceinline__ void store_pool_vertex(const VcmPool& p, uint32_t idx, const Vertex& v) {
@@ -990,7 +993,7 @@ __global__ void __launch_bounds__(256) vcm_gather_kernel(RenderConfig cfg, VcmPa
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
     const bool on = i < n;
     const uint32_t slot = on ? pool.gather_q[i] : 0u;
-    const float4 p0 = pool.cv[slot];  // float4 0 of the tentative vertex: its position
+    const float4 p0 = pool.cv[size_t(slot) * kSlotVertexFloat4s];  // float4 0 of the tentative vertex: its position
     const float3 q = f3(p0.x, p0.y, p0.z);
     uint32_t count = 0;
     uint32_t found[kFoundMax];
@@ -1367,7 +1370,7 @@ int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons, uint3
   int rc;
   if ((rc = ws_alloc(w, &p.p_state, np))) return rc;
   if ((rc = ws_alloc(w, &p.p_rng, np))) return rc;
-  if ((rc = ws_alloc(w, &p.p_cv, np * kVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.p_cv, np * kSlotVertexFloat4s))) return rc;
   if ((rc = ws_alloc(w, &p.p_bs_omega, np))) return rc;
   if ((rc = ws_alloc(w, &p.p_bs_thr, np))) return rc;
   if ((rc = ws_alloc(w, &p.p_ray_o, np))) return rc;
@@ -1376,8 +1379,8 @@ int vcm_workspace_fill(VcmWorkspace* w, uint32_t pixels, uint32_t photons, uint3
   if ((rc = ws_alloc(w, &p.lp_count, nl))) return rc;
   if ((rc = ws_alloc(w, &p.state, ne))) return rc;
   if ((rc = ws_alloc(w, &p.rng, ne))) return rc;
-  if ((rc = ws_alloc(w, &p.cv, ne * kVertexFloat4s))) return rc;
-  if ((rc = ws_alloc(w, &p.pv, ne * kVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.cv, ne * kSlotVertexFloat4s))) return rc;
+  if ((rc = ws_alloc(w, &p.pv, ne * kSlotVertexFloat4s))) return rc;
   if ((rc = ws_alloc(w, &p.bs_omega, ne))) return rc;
   if ((rc = ws_alloc(w, &p.bs_thr, ne))) return rc;
   if ((rc = ws_alloc(w, &p.ray_o, ne))) return rc;
