@@ -318,10 +318,12 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // order, BptPool::hit_q) -> path record + shading record of the hit triangle, asked for together -> arithmetic.  (With the hit inside
 // the path record the shading record was a third round trip: 13 % of the stage's warp-state samples.)
 // kFirst: iteration 0 of a batch (every slot is born here; kEnd = 0) — a kernel of its own so that the steady-state kernel does not carry its code.
-template <int kEnd, bool kFirst>
+// kSorting: the launch may be asked to order the closest-hit queue (B2PT_SORT_RAYS); the default instantiation does not carry that code.
+template <int kEnd, bool kFirst, bool kSorting = false>
 __global__ void __launch_bounds__(B2PT_LOGIC_THREADS, kEnd == 0 ? B2PT_LOGIC_MIN_BLOCKS : B2PT_LOGIC_SPLIT_MIN_BLOCKS) bpt_logic_kernel(RenderConfig cfg, BptPool pool, BptCounters* cnt, int parity, uint32_t batch_pass0,
-                                                                               int sort) {
+                                                                               int sort_arg) {
   constexpr bool first = kFirst;
+  const int sort = kSorting ? sort_arg : 0;
   const DeviceScene& sc = cfg.scene;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     // trace_count[parity ^ 1] is this launch's input; the closest-hit stage clears it afterwards
@@ -1205,11 +1207,15 @@ int render_bpt(b2pt_scene_s* scene, const RenderConfig& base, cudaStream_t strea
       for (int j = 0; j < kBatchIters; ++j, ++g.it) {
         const int parity = g.it & 1;
         timer.begin(kStageShade);
-        if (g.it == 0) bpt_logic_kernel<0, true><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
-        else if (logic_split) {
-          bpt_logic_kernel<2, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
-          bpt_logic_kernel<1, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
-        } else bpt_logic_kernel<0, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
+        if (g.it == 0) {
+          if (sort_rays) bpt_logic_kernel<0, true, true><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
+          else bpt_logic_kernel<0, true><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0);
+        } else if (sort_rays) {
+          bpt_logic_kernel<0, false, true><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, sort_rays);
+        } else if (logic_split) {
+          bpt_logic_kernel<2, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0);
+          bpt_logic_kernel<1, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0);
+        } else bpt_logic_kernel<0, false><<<shade_grid, shade_block, 0, l.stream>>>(cfg, g.pool, l.counters, parity, g.pass0, 0);
         timer.end();
         timer.begin(kStageShade);
         if (staged_connect) bpt_connect_kernel<true><<<staged_grid, block, kConnectStageBytes, l.stream>>>(cfg, g.pool, l.counters, parity);
